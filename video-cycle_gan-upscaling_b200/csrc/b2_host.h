@@ -1,0 +1,36 @@
+// b2_host.h — host-side helpers shared by the launchers: error reporting for the C ABI, device queries,
+// and TMA tensor-map encoding through the driver entry point (no link-time dependency on libcuda).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "b2_conv_igemm.cuh"
+
+namespace b2 {
+
+// Records a printf-style message retrievable through b2_last_error() and returns -1.
+int set_error(const char* fmt, ...);
+const char* last_error();
+
+int device_sm_count();
+
+// rank-`rank` bf16 tensor, 128-byte swizzle, zero fill for out-of-bounds elements.
+int encode_tensor_map(CUtensorMap* map, const void* base, int rank, const cuuint64_t* dims,
+                      const cuuint64_t* strides_bytes /* rank-1 entries */, const cuuint32_t* box,
+                      const cuuint32_t* elem_strides);
+
+struct ConvIgemmArgs {
+    const __nv_bfloat16* x;  // input NHWC
+    int xB, xH, xW, xC;
+    const __nv_bfloat16* w;  // packed weights [w_rows][w_k], k = tap*Cin + cin contiguous
+    int w_rows, w_k;
+    IgemmParams p;  // grid, taps, output mapping and epilogue filled by the caller; tiling filled by the launcher
+};
+
+int launch_conv_igemm(const ConvIgemmArgs& a, cudaStream_t stream);
+// CUDA-core cross-check with identical semantics (tests only).
+int launch_conv_direct(const ConvIgemmArgs& a, cudaStream_t stream);
+
+}  // namespace b2
