@@ -20,6 +20,10 @@
 extern "C" {
 #endif
 
+/* Activations and packed weights are 16-bit: bf16 (training; gradient range) or IEEE fp16 (inference: 3 more
+ * mantissa bits are what it takes to meet the 2e-2 max-abs bar through 37 conv layers).  Both run the
+ * same tcgen05 kind::f16 instruction at the same rate; the `f16` flags below select the element type per call. */
+
 /* activation codes of the convolution epilogue */
 enum { B2_ACT_NONE = 0, B2_ACT_RELU = 1, B2_ACT_LEAKY = 2, B2_ACT_PRELU = 3, B2_ACT_TANH = 4 };
 
@@ -40,6 +44,7 @@ typedef struct {
     const void* residual; /* bf16, same geometry as out */
     void* out;            /* bf16, or float when out_fp32 != 0 */
     int out_fp32;
+    int f16; /* 16-bit element type of x / w / residual / out: 0 = bf16, 1 = IEEE fp16 */
 } b2_epilogue;
 
 /* Conv2D(padding='same') forward on tcgen05 tensor cores — replaces the TF conv2d behind keras.layers.Conv2D at
@@ -65,12 +70,12 @@ int b2_conv2d_direct(const void* x, int B, int H, int W, int Cin, const void* w,
  * 64-channel one:  out[b,y,x, t*Cin + c] = in[b, y*stride + dy[t], x*stride + dx[t], c]  (0 outside the image),
  * channels >= ntaps*Cin are zero.  `in` is float when in_fp32 != 0, else bf16.  out: [B,OH,OW,64]. */
 int b2_fold_taps(const void* in, int in_fp32, int B, int H, int W, int Cin, int OH, int OW, int stride, int ntaps,
-                 const int* dy, const int* dx, void* out, void* stream);
+                 const int* dy, const int* dx, void* out, int f16, void* stream);
 
-/* Weight (re)packing: out[i] = idx[i] >= 0 ? bf16(src[idx[i]]) : 0.  The index map is built once per layer on the
+/* Weight (re)packing: out[i] = idx[i] >= 0 ? half_or_bf16(src[idx[i]]) : 0.  The index map is built once per layer on the
  * host (Keras kernel layout (kh,kw,Cin,Cout) / (kh,kw,Cout,Cin) -> packed [Cout][tap*Cin_pad + c], its dgrad
  * transpose, or the tap-folded layouts); this call refreshes the bf16 shadow copy from the fp32 master weights. */
-int b2_gather_cast_bf16(const float* src, const int32_t* idx, int64_t n, void* out, void* stream);
+int b2_gather_cast(const float* src, const int32_t* idx, int64_t n, void* out, int f16, void* stream);
 
 #ifdef __cplusplus
 }

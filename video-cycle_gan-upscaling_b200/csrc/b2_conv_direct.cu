@@ -32,7 +32,13 @@ __global__ void conv_direct_kernel(const __nv_bfloat16* __restrict__ x, int xB, 
             if (ix < 0 || iy < 0 || ix >= xW || iy >= xH) continue;
             const __nv_bfloat16* xp = x + ((size_t(gb) * xH + iy) * xW + ix) * xC;
             const __nv_bfloat16* wp = w + size_t(n) * w_k + size_t(p.wtap[tap]) * p.cin;
-            for (int c = 0; c < p.cin; ++c) acc = fmaf(__bfloat162float(xp[c]), __bfloat162float(wp[c]), acc);
+            if (p.f16) {
+                const __half* xh = reinterpret_cast<const __half*>(xp);
+                const __half* wh = reinterpret_cast<const __half*>(wp);
+                for (int c = 0; c < p.cin; ++c) acc = fmaf(__half2float(xh[c]), __half2float(wh[c]), acc);
+            } else {
+                for (int c = 0; c < p.cin; ++c) acc = fmaf(__bfloat162float(xp[c]), __bfloat162float(wp[c]), acc);
+            }
         }
         const float sc = p.scale ? p.scale[n] : 1.f;
         const float sh = p.shift ? p.shift[n] : 0.f;
@@ -40,8 +46,10 @@ __global__ void conv_direct_kernel(const __nv_bfloat16* __restrict__ x, int xB, 
         float v = direct_act(fmaf(acc, sc, sh), p.act, p.leaky, al);
         const size_t pix = (size_t(gb) * p.OH + size_t(gy * p.out_sy + p.out_oy)) * p.OW + size_t(gx * p.out_sx + p.out_ox);
         const size_t o = pix * size_t(p.out_ld) + n;
-        if (p.residual) v += __bfloat162float(p.residual[o]);
+        if (p.residual)
+            v += p.f16 ? __half2float(reinterpret_cast<const __half*>(p.residual)[o]) : __bfloat162float(p.residual[o]);
         if (p.out_fp32) reinterpret_cast<float*>(p.out)[o] = v;
+        else if (p.f16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(v);
         else reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(v);
     }
 }

@@ -33,6 +33,31 @@ struct IgemmCfg {
     static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/ + 3 * kMaxChan * 4;
 };
 
+// 16-bit element helpers: the storage type is bf16 or IEEE fp16, chosen per launch (IgemmParams::f16).
+__device__ __forceinline__ uint32_t pack2(float a, float b, int f16) {
+    if (f16) {
+        // clamp to the finite half range so a stray large activation saturates instead of becoming inf
+        a = fminf(fmaxf(a, -65504.f), 65504.f);
+        b = fminf(fmaxf(b, -65504.f), 65504.f);
+        const __half2 h = __floats2half2_rn(a, b);
+        return *reinterpret_cast<const uint32_t*>(&h);
+    }
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+__device__ __forceinline__ float2 unpack2(uint32_t u, int f16) {
+    if (f16) return __half22float2(*reinterpret_cast<const __half2*>(&u));
+    return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u));
+}
+__device__ __forceinline__ float load1(const void* base, size_t i, int f16) {
+    if (f16) return __half2float(reinterpret_cast<const __half*>(base)[i]);
+    return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(base)[i]);
+}
+__device__ __forceinline__ void store1(void* base, size_t i, float v, int f16) {
+    if (f16) reinterpret_cast<__half*>(base)[i] = __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));
+    else reinterpret_cast<__nv_bfloat16*>(base)[i] = __float2bfloat16_rn(v);
+}
+
 template <int ACT>
 __device__ __forceinline__ float apply_act_t(float v, float leaky, float alpha) {
     if constexpr (ACT == ACT_RELU) return fmaxf(v, 0.f);
@@ -84,10 +109,9 @@ __device__ __forceinline__ void epilogue_tile(const IgemmParams& p, uint32_t tad
                 for (int g = 0; g < CH / 8; ++g) rv[g] = __ldg(rp + g);
 #pragma unroll
                 for (int g = 0; g < CH / 8; ++g) {
-                    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rv[g]);
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
-                        const float2 f = __bfloat1622float2(h[e]);
+                        const float2 f = unpack2(reinterpret_cast<const uint32_t*>(&rv[g])[e], p.f16);
                         v[g * 8 + 2 * e] += f.x;
                         v[g * 8 + 2 * e + 1] += f.y;
                     }
@@ -97,9 +121,9 @@ __device__ __forceinline__ void epilogue_tile(const IgemmParams& p, uint32_t tad
 #pragma unroll
             for (int g = 0; g < CH / 8; ++g) {
                 uint4 o;
-                __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
+                uint32_t* h = reinterpret_cast<uint32_t*>(&o);
 #pragma unroll
-                for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(v[g * 8 + 2 * e], v[g * 8 + 2 * e + 1]);
+                for (int e = 0; e < 4; ++e) h[e] = pack2(v[g * 8 + 2 * e], v[g * 8 + 2 * e + 1], p.f16);
                 op[g] = o;
             }
         } else {
@@ -108,9 +132,9 @@ __device__ __forceinline__ void epilogue_tile(const IgemmParams& p, uint32_t tad
                 const int c = n0 + c0 + j;
                 if (c < p.n_valid) {
                     float o = v[j];
-                    if (p.residual) o += __bfloat162float(p.residual[obase + c0 + j]);
+                    if (p.residual) o += load1(p.residual, obase + c0 + j, p.f16);
                     if (p.out_fp32) reinterpret_cast<float*>(p.out)[obase + c0 + j] = o;
-                    else reinterpret_cast<__nv_bfloat16*>(p.out)[obase + c0 + j] = __float2bfloat16_rn(o);
+                    else store1(p.out, obase + c0 + j, o, p.f16);
                 }
             }
         }
@@ -199,7 +223,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------ MMA issuer
-        constexpr uint32_t idesc = make_idesc_bf16(128, BN);
+        const uint32_t idesc = p.f16 ? make_idesc_f16(128, BN) : make_idesc_bf16(128, BN);
         int stage = 0;
         uint32_t phase = 0;
         int as = 0;

@@ -4,6 +4,7 @@
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 
 namespace b2 {
@@ -35,7 +36,8 @@ struct IgemmParams {
     const float* alpha;  // PReLU slope per channel (act == ACT_PRELU)
     const __nv_bfloat16* residual;  // added after the activation; same geometry as out; may be null
     void* out;
-    int out_fp32;  // 1: out is float, 0: out is bf16
+    int out_fp32;  // 1: out is float, 0: out is the 16-bit element type
+    int f16;       // 16-bit element type of x / w / residual / out: 0 = bf16, 1 = fp16 (IEEE half)
 };
 
 }  // namespace b2

@@ -1,0 +1,108 @@
+// b2_elementwise.cu — memory-bound helper kernels of the path: tap folding for 3-channel inputs, weight repacking.
+// All are vectorised (16-byte stores) grid-stride kernels sized to a multiple of the SM count.
+#include "../../include/b2srgan.h"
+#include <cuda_fp16.h>
+
+#include "b2_host.h"
+
+using namespace b2;
+
+namespace {
+
+constexpr int kFoldMaxTaps = 21;  // 21 taps x 3 channels = 63 <= 64
+
+struct FoldParams {
+    int B, H, W, Cin, OH, OW, stride, ntaps, f16;
+    int dy[kFoldMaxTaps], dx[kFoldMaxTaps];
+};
+
+template <typename TIn>
+__global__ void fold_taps_kernel(const TIn* __restrict__ in, void* __restrict__ out, FoldParams p) {
+    const long total = long(p.B) * p.OH * p.OW * 8;  // 8 groups of 8 channels per output pixel
+    const int used = p.ntaps * p.Cin;
+    for (long idx = blockIdx.x * long(blockDim.x) + threadIdx.x; idx < total; idx += long(gridDim.x) * blockDim.x) {
+        const int g = int(idx & 7);
+        long t = idx >> 3;
+        const int ox = int(t % p.OW); t /= p.OW;
+        const int oy = int(t % p.OH); t /= p.OH;
+        const int b = int(t);
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int ch = g * 8 + e;
+            float f = 0.f;
+            if (ch < used) {
+                const int tap = ch / p.Cin, c = ch - tap * p.Cin;
+                const int iy = oy * p.stride + p.dy[tap], ix = ox * p.stride + p.dx[tap];
+                if (iy >= 0 && iy < p.H && ix >= 0 && ix < p.W)
+                    f = float(in[((size_t(b) * p.H + iy) * p.W + ix) * p.Cin + c]);
+            }
+            v[e] = f;
+        }
+        uint4 o;
+        if (p.f16) {
+            __half2* h = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) h[e] = __floats2half2_rn(v[2 * e], v[2 * e + 1]);
+        } else {
+            __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+        }
+        reinterpret_cast<uint4*>(out)[idx] = o;
+    }
+}
+
+__global__ void gather_cast_kernel(const float* __restrict__ src, const int32_t* __restrict__ idx, long n,
+                                   void* __restrict__ out, int f16) {
+    for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < n; i += long(gridDim.x) * blockDim.x) {
+        const int32_t j = idx[i];
+        const float v = j >= 0 ? src[j] : 0.f;
+        if (f16) reinterpret_cast<__half*>(out)[i] = __float2half_rn(v);
+        else reinterpret_cast<__nv_bfloat16*>(out)[i] = __float2bfloat16_rn(v);
+    }
+}
+
+inline int grid_for(long work, int threads) {
+    long blocks = (work + threads - 1) / threads;
+    const long cap = long(device_sm_count()) * 16;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return int(blocks);
+}
+
+}  // namespace
+
+extern "C" {
+
+int b2_fold_taps(const void* in, int in_fp32, int B, int H, int W, int Cin, int OH, int OW, int stride, int ntaps,
+                 const int* dy, const int* dx, void* out, int f16, void* stream) {
+    if (!in || !out || !dy || !dx) return set_error("b2_fold_taps: null pointer");
+    if (ntaps < 1 || ntaps > kFoldMaxTaps || ntaps * Cin > 64) return set_error("b2_fold_taps: %d taps x %d channels do not fit 64", ntaps, Cin);
+    FoldParams p;
+    p.B = B; p.H = H; p.W = W; p.Cin = Cin; p.OH = OH; p.OW = OW; p.stride = stride; p.ntaps = ntaps; p.f16 = f16;
+    for (int t = 0; t < ntaps; ++t) { p.dy[t] = dy[t]; p.dx[t] = dx[t]; }
+    const long total = long(B) * OH * OW * 8;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (in_fp32)
+        fold_taps_kernel<float><<<grid_for(total, 256), 256, 0, s>>>(reinterpret_cast<const float*>(in), out, p);
+    else if (f16)
+        fold_taps_kernel<__half><<<grid_for(total, 256), 256, 0, s>>>(reinterpret_cast<const __half*>(in), out, p);
+    else
+        fold_taps_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>(
+            reinterpret_cast<const __nv_bfloat16*>(in), out, p);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error("b2_fold_taps launch: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+int b2_gather_cast(const float* src, const int32_t* idx, int64_t n, void* out, int f16, void* stream) {
+    if (!src || !idx || !out) return set_error("b2_gather_cast: null pointer");
+    gather_cast_kernel<<<grid_for(n, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        src, idx, long(n), out, f16);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error("b2_gather_cast launch: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+}  // extern "C"

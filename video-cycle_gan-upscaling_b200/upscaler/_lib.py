@@ -1,0 +1,105 @@
+"""ctypes binding of libb2srgan.so (the C ABI declared in include/b2srgan.h).
+
+There is no fallback: if the CUDA extension is missing or a call fails, this raises.
+"""
+import ctypes
+import os
+
+from . import _build
+
+_lib = None
+
+ACT_NONE, ACT_RELU, ACT_LEAKY, ACT_PRELU, ACT_TANH = 0, 1, 2, 3, 4
+
+
+class B2Error(RuntimeError):
+    pass
+
+
+class Epilogue(ctypes.Structure):
+    _fields_ = [
+        ("scale", ctypes.c_void_p),
+        ("shift", ctypes.c_void_p),
+        ("alpha", ctypes.c_void_p),
+        ("act", ctypes.c_int),
+        ("leaky", ctypes.c_float),
+        ("residual", ctypes.c_void_p),
+        ("out", ctypes.c_void_p),
+        ("out_fp32", ctypes.c_int),
+        ("f16", ctypes.c_int),
+    ]
+
+
+_SIGNATURES = {
+    "b2_last_error": (ctypes.c_char_p, []),
+    "b2_version": (ctypes.c_int, []),
+    "b2_conv2d_fprop": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p] + [ctypes.c_int] * 4 +
+                        [ctypes.POINTER(Epilogue), ctypes.c_void_p]),
+    "b2_conv2d_transpose_s2_fprop": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p] +
+                                     [ctypes.c_int] * 3 + [ctypes.POINTER(Epilogue), ctypes.c_void_p]),
+    "b2_conv2d_direct": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p] + [ctypes.c_int] * 5 +
+                         [ctypes.POINTER(Epilogue), ctypes.c_void_p]),
+    "b2_fold_taps": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 9 + [ctypes.POINTER(ctypes.c_int)] * 2 +
+                     [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]),
+    "b2_gather_cast": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int,
+                                      ctypes.c_void_p]),
+}
+
+
+def exported_symbols():
+    """Names include/b2srgan.h declares; tests check the loaded library exports each of them."""
+    return sorted(_SIGNATURES)
+
+
+def lib_path():
+    return _build.LIB_PATH
+
+
+def load():
+    """Loads libb2srgan.so (building it first if nvcc is available and it is missing). Raises if it cannot."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB_PATH
+    if not os.path.exists(path):
+        try:
+            _build.build()
+        except Exception as e:  # noqa: BLE001
+            raise B2Error("libb2srgan.so is missing and could not be built: %s" % e)
+    lib = ctypes.CDLL(path)
+    for name, (res, args) in _SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = load().b2_last_error()
+        raise B2Error("%s failed: %s" % (what, msg.decode(errors="replace") if msg else rc))
+
+
+def ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def stream_ptr():
+    import torch
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def make_epilogue(out, scale=None, shift=None, alpha=None, act=ACT_NONE, leaky=0.0, residual=None, f16=0):
+    import torch
+    ep = Epilogue()
+    ep.scale = scale.data_ptr() if scale is not None else None
+    ep.shift = shift.data_ptr() if shift is not None else None
+    ep.alpha = alpha.data_ptr() if alpha is not None else None
+    ep.act = act
+    ep.leaky = leaky
+    ep.residual = residual.data_ptr() if residual is not None else None
+    ep.out = out.data_ptr()
+    ep.out_fp32 = 1 if out.dtype == torch.float32 else 0
+    ep.f16 = int(f16)
+    return ep

@@ -1,0 +1,170 @@
+"""Tensor-level wrappers over the C ABI: validate geometry, allocate outputs, call libb2srgan.so.
+
+Tensors are torch CUDA tensors used purely as device-memory handles (NHWC, contiguous).  Every function here ends in
+a hand-written sm_100a kernel; nothing falls back to torch ops.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import ACT_LEAKY, ACT_NONE, ACT_PRELU, ACT_RELU, ACT_TANH  # noqa: F401
+
+
+def _require_cuda(*ts):
+    for t in ts:
+        if t is not None and (not t.is_cuda or not t.is_contiguous()):
+            raise ValueError("expected contiguous CUDA tensors")
+
+
+def _elem_flag(x, w):
+    """16-bit element type of a conv's operands: 0 = bf16, 1 = fp16; activations and weights must agree."""
+    if x.dtype != w.dtype or x.dtype not in (torch.bfloat16, torch.float16):
+        raise ValueError("expected matching bf16 or fp16 activations and packed weights, got %s / %s" % (x.dtype, w.dtype))
+    return 1 if x.dtype == torch.float16 else 0
+
+
+def tf_same_out(size, stride):
+    return -(-size // stride)
+
+
+def conv2d(x, w_packed, cout, kh, kw, stride=1, out=None, out_dtype=None, scale=None, shift=None, alpha=None,
+           act=ACT_NONE, leaky=0.0, residual=None, direct=False):
+    """Conv2D(padding='same') forward (reference: keras Conv2D at model.py:19, 22, 275, 283, 290, 839-871)."""
+    B, H, W, Cin = x.shape
+    OH, OW = tf_same_out(H, stride), tf_same_out(W, stride)
+    f16 = _elem_flag(x, w_packed)
+    if Cin % 64 != 0:
+        raise ValueError("conv2d: Cin=%d must be a multiple of 64 (fold narrow inputs first)" % Cin)
+    if w_packed.numel() != cout * kh * kw * Cin:
+        raise ValueError("conv2d: packed weight has %d elements, expected %d" % (w_packed.numel(), cout * kh * kw * Cin))
+    if out is None:
+        out = torch.empty((B, OH, OW, cout), dtype=out_dtype or x.dtype, device=x.device)
+    elif tuple(out.shape) != (B, OH, OW, cout):
+        raise ValueError("conv2d: bad output shape %s" % (tuple(out.shape),))
+    if out.dtype not in (x.dtype, torch.float32):
+        raise ValueError("conv2d: output must be float32 or the activation dtype")
+    if residual is not None and (tuple(residual.shape) != tuple(out.shape) or residual.dtype != x.dtype):
+        raise ValueError("conv2d: residual must have the activation dtype and the output's shape")
+    _require_cuda(x, w_packed, out, scale, shift, alpha, residual)
+    ep = _lib.make_epilogue(out, scale, shift, alpha, act, leaky, residual, f16)
+    lib = _lib.load()
+    if direct:
+        rc = lib.b2_conv2d_direct(_lib.ptr(x), B, H, W, Cin, _lib.ptr(w_packed), cout, kh, kw, stride, 0,
+                                  ctypes.byref(ep), _lib.stream_ptr())
+    else:
+        rc = lib.b2_conv2d_fprop(_lib.ptr(x), B, H, W, Cin, _lib.ptr(w_packed), cout, kh, kw, stride, ctypes.byref(ep),
+                                 _lib.stream_ptr())
+    _lib.check(rc, "b2_conv2d_fprop")
+    return out
+
+
+def conv2d_transpose_s2(x, w_packed, cout, kh, kw, out=None, scale=None, shift=None, alpha=None, act=ACT_NONE,
+                        leaky=0.0, direct=False):
+    """Conv2DTranspose(strides=2, padding='same') forward (reference: model.py:72)."""
+    B, H, W, Cin = x.shape
+    f16 = _elem_flag(x, w_packed)
+    if Cin % 64 != 0:
+        raise ValueError("conv2d_transpose_s2: Cin=%d must be a multiple of 64" % Cin)
+    if w_packed.numel() != cout * kh * kw * Cin:
+        raise ValueError("conv2d_transpose_s2: packed weight size mismatch")
+    if out is None:
+        out = torch.empty((B, 2 * H, 2 * W, cout), dtype=x.dtype, device=x.device)
+    elif tuple(out.shape) != (B, 2 * H, 2 * W, cout) or out.dtype != x.dtype:
+        raise ValueError("conv2d_transpose_s2: bad output shape / dtype")
+    _require_cuda(x, w_packed, out, scale, shift, alpha)
+    ep = _lib.make_epilogue(out, scale, shift, alpha, act, leaky, None, f16)
+    lib = _lib.load()
+    if direct:
+        rc = lib.b2_conv2d_direct(_lib.ptr(x), B, H, W, Cin, _lib.ptr(w_packed), cout, kh, kw, 1, 1, ctypes.byref(ep),
+                                  _lib.stream_ptr())
+    else:
+        rc = lib.b2_conv2d_transpose_s2_fprop(_lib.ptr(x), B, H, W, Cin, _lib.ptr(w_packed), cout, kh, kw,
+                                              ctypes.byref(ep), _lib.stream_ptr())
+    _lib.check(rc, "b2_conv2d_transpose_s2_fprop")
+    return out
+
+
+def fold_taps(x, taps, stride=1, out_hw=None, out=None, dtype=torch.bfloat16):
+    """out[b,y,x, t*Cin + c] = x[b, y*stride + dy_t, x*stride + dx_t, c]; 64 output channels, zero padded."""
+    B, H, W, Cin = x.shape
+    if x.dtype not in (torch.float32, torch.bfloat16, torch.float16):
+        raise ValueError("fold_taps expects float32, bf16 or fp16 input")
+    OH, OW = out_hw if out_hw is not None else (tf_same_out(H, stride), tf_same_out(W, stride))
+    if out is None:
+        out = torch.empty((B, OH, OW, 64), dtype=dtype, device=x.device)
+    if x.dtype != torch.float32 and x.dtype != out.dtype:
+        raise ValueError("fold_taps: 16-bit input and output types must match")
+    _require_cuda(x, out)
+    n = len(taps)
+    dy = (ctypes.c_int * n)(*[int(t[0]) for t in taps])
+    dx = (ctypes.c_int * n)(*[int(t[1]) for t in taps])
+    rc = _lib.load().b2_fold_taps(_lib.ptr(x), 1 if x.dtype == torch.float32 else 0, B, H, W, Cin, OH, OW, stride, n,
+                                  dy, dx, _lib.ptr(out), 1 if out.dtype == torch.float16 else 0, _lib.stream_ptr())
+    _lib.check(rc, "b2_fold_taps")
+    return out
+
+
+def gather_cast(src, idx, out=None, dtype=torch.bfloat16):
+    """out[i] = idx[i] >= 0 ? cast(src.flat[idx[i]]) : 0 — refreshes a packed 16-bit weight copy from fp32 masters."""
+    if src.dtype != torch.float32 or idx.dtype != torch.int32:
+        raise ValueError("gather_cast expects float32 source and int32 index map")
+    if out is None:
+        out = torch.empty(idx.shape, dtype=dtype, device=src.device)
+    if out.dtype not in (torch.bfloat16, torch.float16) or out.numel() != idx.numel():
+        raise ValueError("gather_cast: bad output")
+    _require_cuda(src, idx, out)
+    rc = _lib.load().b2_gather_cast(_lib.ptr(src), _lib.ptr(idx), idx.numel(), _lib.ptr(out),
+                                    1 if out.dtype == torch.float16 else 0, _lib.stream_ptr())
+    _lib.check(rc, "b2_gather_cast")
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ packing index maps
+def conv_pack_index(kh, kw, cin, cout, cin_pad=None):
+    """Keras Conv2D kernel (kh,kw,Cin,Cout) -> packed [Cout][kh*kw][cin_pad] index map (int32, -1 = zero)."""
+    cp = cin_pad or cin
+    T = kh * kw
+    idx = -np.ones((cout, T, cp), np.int64)
+    t = np.arange(T)[None, :, None]
+    c = np.arange(cin)[None, None, :]
+    co = np.arange(cout)[:, None, None]
+    idx[:, :, :cin] = (t * cin + c) * cout + co
+    return idx.astype(np.int32)
+
+
+def convT_pack_index(kh, kw, cin, cout):
+    """Keras Conv2DTranspose kernel (kh,kw,Cout,Cin) -> packed [Cout][kh*kw][Cin]."""
+    T = kh * kw
+    t = np.arange(T)[None, :, None]
+    c = np.arange(cin)[None, None, :]
+    co = np.arange(cout)[:, None, None]
+    return ((t * cout + co) * cin + c).astype(np.int32)
+
+
+def conv_rowfold_pack_index(kh, kw, cin, cout):
+    """Narrow-Cin conv whose kw taps of each filter row are folded into channels (fold_taps with dx taps):
+    packed [Cout][kh][64], channel = kx*Cin + c."""
+    if kw * cin > 64:
+        raise ValueError("row fold needs kw*Cin <= 64")
+    idx = -np.ones((cout, kh, 64), np.int64)
+    ky = np.arange(kh)[None, :, None, None]
+    kx = np.arange(kw)[None, None, :, None]
+    c = np.arange(cin)[None, None, None, :]
+    co = np.arange(cout)[:, None, None, None]
+    src = ((ky * kw + kx) * cin + c) * cout + co
+    idx[:, :, :kw * cin] = src.reshape(cout, kh, kw * cin)
+    return idx.astype(np.int32)
+
+
+def conv_fullfold_pack_index(kh, kw, cin, cout):
+    """Narrow-Cin conv with ALL taps folded into channels: packed [Cout][1][64], channel = (ky*kw+kx)*Cin + c."""
+    if kh * kw * cin > 64:
+        raise ValueError("full fold needs kh*kw*Cin <= 64")
+    idx = -np.ones((cout, 1, 64), np.int64)
+    t = np.arange(kh * kw)[None, :, None]
+    c = np.arange(cin)[None, None, :]
+    co = np.arange(cout)[:, None, None]
+    idx[:, 0, :kh * kw * cin] = ((t * cin + c) * cout + co).reshape(cout, kh * kw * cin)
+    return idx.astype(np.int32)
