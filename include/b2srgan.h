@@ -60,6 +60,14 @@ int b2_conv2d_fprop(const void* x, int B, int H, int W, int Cin, const void* w, 
 int b2_conv2d_transpose_s2_fprop(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh,
                                  int kw, const b2_epilogue* ep, void* stream);
 
+/* Conv2D(Cout=3, 9 x KW, 'same', stride 1) + bias + optional tanh, fp32 NHWC output — the generator's final/conv +
+ * final/tanh (model.py:290-291).  Row-streaming kernel: filter rows folded into the GEMM N dimension, filter columns
+ * into K through descriptor shifts, every input element fetched once.
+ *   x: [B,H,W,Cin] 16-bit, Cin in {64,128,192,256};  w: packed [32][KW*Cin] with row n = dy*3 + co (rows 27..31 zero),
+ *   column k = dx*Cin + c;  bias: [3] fp32 or null;  out: [B,H,W,3] fp32. */
+int b2_conv2d_rows_fprop(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw,
+                         const float* bias, int act, int f16, float* out, void* stream);
+
 /* Same semantics as b2_conv2d_fprop / b2_conv2d_transpose_s2_fprop on CUDA cores, one thread per output element.
  * Cross-check for the tests; not used by the model path. transposed != 0 selects the Conv2DTranspose form. */
 int b2_conv2d_direct(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw, int stride,

@@ -91,6 +91,7 @@ class UpscalerOrigNet:
         self._packed = {}
         self._infer = {}
         self._buffers = {}
+        self._final_rows = False
         self._build_index_maps()
         self.refresh()
 
@@ -98,7 +99,10 @@ class UpscalerOrigNet:
     def _build_index_maps(self):
         for name, kind, c in self.specs:
             if kind == "conv":
-                if c["cin"] < 64:
+                if name == "final/conv" and c["kh"] == 9 and c["cout"] == 3 and c["cin"] % 64 == 0 and c["cin"] <= 256:
+                    idx = ops.conv_rows_pack_index(c["kh"], c["kw"], c["cin"], c["cout"])
+                    self._final_rows = True
+                elif c["cin"] < 64:
                     idx = ops.conv_rowfold_pack_index(c["kh"], c["kw"], c["cin"], c["cout"])
                 else:
                     idx = ops.conv_pack_index(c["kh"], c["kw"], c["cin"], c["cout"])
@@ -135,6 +139,14 @@ class UpscalerOrigNet:
             inf[n] = (None, w[n][1], None)
         inf["final/conv"] = (None, w["final/conv"][1], None)
         self._infer = inf
+
+    input_name = "initial/input"
+    extra_layers = [("prefinal/tanh", "add"), ("final/tanh", "activation")]
+
+    def output_shape_for(self, input_shape):
+        h, w, c = input_shape
+        f = 2 ** self.upscale_times
+        return (None if h is None else h * f, None if w is None else w * f, 3)
 
     def host_weights(self):
         return OrderedDict((k, [t.detach().cpu().numpy() for t in ts]) for k, ts in self.weights.items())
@@ -186,4 +198,6 @@ class UpscalerOrigNet:
         _, b, _ = inf["final/conv"]
         if out is None:
             out = torch.empty((B, h, w_, 3), dtype=torch.float32, device=self.device)
+        if self._final_rows:
+            return ops.conv2d_rows(m, pk["final/conv"], 3, 9, 9, bias=b, act=ops.ACT_TANH, out=out)
         return ops.conv2d(m, pk["final/conv"], 3, 9, 9, out=out, shift=b, act=ops.ACT_TANH)

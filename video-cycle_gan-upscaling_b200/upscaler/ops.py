@@ -60,6 +60,24 @@ def conv2d(x, w_packed, cout, kh, kw, stride=1, out=None, out_dtype=None, scale=
     return out
 
 
+def conv2d_rows(x, w_rows, cout, kh, kw, bias=None, act=ACT_TANH, out=None):
+    """Final Conv2D(3, 9xKW, 'same') + bias + tanh with fp32 output (reference: model.py:290-291), row-streaming
+    kernel.  `w_rows` is packed by conv_rows_pack_index."""
+    B, H, W, Cin = x.shape
+    f16 = _elem_flag(x, w_rows)
+    if w_rows.numel() != 32 * kw * Cin:
+        raise ValueError("conv2d_rows: packed weight size mismatch")
+    if out is None:
+        out = torch.empty((B, H, W, cout), dtype=torch.float32, device=x.device)
+    elif tuple(out.shape) != (B, H, W, cout) or out.dtype != torch.float32:
+        raise ValueError("conv2d_rows: output must be float32 (B,H,W,%d)" % cout)
+    _require_cuda(x, w_rows, out, bias)
+    rc = _lib.load().b2_conv2d_rows_fprop(_lib.ptr(x), B, H, W, Cin, _lib.ptr(w_rows), cout, kh, kw, _lib.ptr(bias), act,
+                                          f16, _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(rc, "b2_conv2d_rows_fprop")
+    return out
+
+
 def conv2d_transpose_s2(x, w_packed, cout, kh, kw, out=None, scale=None, shift=None, alpha=None, act=ACT_NONE,
                         leaky=0.0, direct=False):
     """Conv2DTranspose(strides=2, padding='same') forward (reference: model.py:72)."""
@@ -167,4 +185,19 @@ def conv_fullfold_pack_index(kh, kw, cin, cout):
     c = np.arange(cin)[None, None, :]
     co = np.arange(cout)[:, None, None]
     idx[:, 0, :kh * kw * cin] = ((t * cin + c) * cout + co).reshape(cout, kh * kw * cin)
+    return idx.astype(np.int32)
+
+
+def conv_rows_pack_index(kh, kw, cin, cout):
+    """Keras Conv2D kernel (kh,kw,Cin,Cout) -> packed [32][kw*Cin] for conv2d_rows: row n = dy*Cout + co,
+    column k = dx*Cin + c."""
+    if kh * cout > 32:
+        raise ValueError("conv_rows needs kh*Cout <= 32")
+    idx = -np.ones((32, kw, cin), np.int64)
+    dy = np.arange(kh)[:, None, None, None]
+    co = np.arange(cout)[None, :, None, None]
+    dx = np.arange(kw)[None, None, :, None]
+    c = np.arange(cin)[None, None, None, :]
+    src = ((dy * kw + dx) * cin + c) * cout + co
+    idx[:kh * cout] = src.reshape(kh * cout, kw, cin)
     return idx.astype(np.int32)
