@@ -1,0 +1,260 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark: x4 frame upscaling 270p -> 1080p through the SRGAN generator (BASELINE.json
+configs[1], k=3 = the shipped-weights architecture), one process per GPU, frames sharded with no collective.
+
+  python bench.py --gpus N --steps K --warmup W            # our CUDA path
+  python bench.py --impl reference --gpus N ...            # the reference's CPU path (oracle restatement; the
+                                                           #  reference's TensorFlow is unavailable on this box)
+
+A step = one batch of `--batch` synthetic 270x480 frames per GPU pushed through the generator.
+  value : frames/s with inputs resident in HBM (device-timed, CUDA events, max over ranks)
+  e2e   : frames/s through the public API Model.predict(host ndarray) -> host ndarray (H2D + D2H inside)
+  roofline : the dominant kernel (second Conv2DTranspose, 256->256, 50 % of the FLOPs), timed with CUDA events on the
+             launching stream inside the timed region, against MEASURED_PEAKS.json
+  cpu_baseline : the CPU oracle on the host cores, 1 frame (bounded sample)
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "video-cycle_gan-upscaling_b200"))
+
+GEN_FLOPS = {3: 1227.09e9, 5: 2942.77e9}      # per 270x480 frame, SURVEY.md 8(d)
+CONVT2_FLOPS = {3: 611.5e9, 5: 1698.7e9}      # second Conv2DTranspose 256->256 at 540x960 -> 1080x1920
+H_LR, W_LR = 270, 480
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return {"bf16_tflops": p.get("bf16_tflops", 1590.0), "bf16_tflops_sustained": p.get("bf16_tflops_sustained", 1400.0),
+                "hbm_gbs": p.get("hbm_gbs", 6650.0), "source": "measured"}
+    return {"bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "hbm_gbs": 6650.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:  # noqa: BLE001
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx = float(r[2])
+                for name, col in (("hw_slowdown", 4), ("hw_thermal_slowdown", 5), ("sw_thermal_slowdown", 6),
+                                  ("sw_power_cap", 7)):
+                    if r[col].lower().startswith("active"):
+                        reasons.add(name)
+            except (ValueError, IndexError):
+                pass
+        sm.sort()
+        # median over the samples taken under load (upper half: the region includes idle samples at both ends)
+        load = sm[len(sm) // 2:] if sm else []
+        med = load[len(load) // 2] if load else None
+        return {"sm_mhz": med, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_oracle_frames_per_s(ks, frames=1, hw=(H_LR, W_LR)):
+    """The CPU restatement of the reference's generator (oracle/) on all host cores; bounded sample."""
+    import numpy as np
+    import torch
+    from oracle import srgan_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    w = O.to_torch(O.init_upscaler_orig_weights(seed=1234, kernel_size=ks))
+    rng = np.random.default_rng(0)
+    with torch.no_grad():
+        O.upscaler_orig_forward(w, rng.uniform(-1, 1, (1, 32, 32, 3)).astype(np.float32))  # warm oneDNN
+        x = rng.uniform(-1, 1, (frames, hw[0], hw[1], 3)).astype(np.float32)
+        t0 = time.perf_counter()
+        O.upscaler_orig_forward(w, x)
+        dt = time.perf_counter() - t0
+    return frames / dt, cores, dt
+
+
+def run_reference(args, rank, world):
+    """Reference arm: the reference's own (CPU) implementation of the path on the host cores. TensorFlow/Keras are
+    not installable here, so this times the oracle restatement (kind = 'port')."""
+    if rank != 0:
+        return
+    vals = []
+    cores = os.cpu_count() or 1
+    for i in range(args.warmup + args.steps):
+        fps, cores, dt = cpu_oracle_frames_per_s(args.kernel_size, 1)
+        if i >= args.warmup:
+            vals.append(dt)
+        if sum(vals) > 240:  # keep the whole run within a few minutes
+            break
+    steps = len(vals)
+    ms = 1000.0 * sum(vals) / max(steps, 1)
+    v = 1000.0 / ms
+    line = {"impl": "reference", "metric": "x4 frames/sec 270p->1080p", "value": v, "unit": "frames/s", "n_gpus": args.gpus,
+            "steps": steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "generator x4 inference 270x480->1080x1920, k=%d, CPU oracle, 1 frame/step" % args.kernel_size},
+            "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": "port",
+                             "sample": "1 frame of 270x480 per step (PyTorch-CPU fp32 restatement; reference TensorFlow unavailable on this box)"},
+            "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=8, help="frames per step per GPU")
+    ap.add_argument("--kernel-size", type=int, default=3, dest="kernel_size")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback for the product path)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    from upscaler import ops
+    from upscaler.model import make_upscaler_orig
+
+    B, ks = args.batch, args.kernel_size
+    model = make_upscaler_orig((4 * H_LR, 4 * W_LR, 3), kernel_size=ks)
+    net = model.net
+    gen = torch.Generator(device="cpu").manual_seed(1000 + rank)   # each rank upscales its own shard of frames
+    x_host = (torch.rand((B, H_LR, W_LR, 3), generator=gen) * 2 - 1).numpy()
+    x_dev = torch.from_numpy(x_host).to(dev)
+    out_dev = torch.empty((B, 4 * H_LR, 4 * W_LR, 3), dtype=torch.float32, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ------------------------------------------------------------------ device-resident throughput
+    for _ in range(args.warmup):
+        net.forward_infer(x_dev, out_dev)
+    barrier()
+    ops.reset_launch_count()
+    net.layer_events = {}            # per-layer CUDA events on the launching stream (roofline)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        net.forward_infer(x_dev, out_dev)
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = ops.launch_count()
+    layer_ms = {k: sum(a.elapsed_time(b) for a, b in v) / len(v) for k, v in net.layer_events.items()}
+    net.layer_events = None
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+    value = world * B * 1000.0 / ms_step
+
+    # ------------------------------------------------------------------ end to end through Model.predict (host buffers)
+    for _ in range(2):
+        model.predict(x_host, batch_size=B)
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps = max(3, min(args.steps, 10))
+    for _ in range(e2e_steps):
+        y = model.predict(x_host, batch_size=B)
+    barrier()
+    t_e2e = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
+    e2e_value = world * B * e2e_steps / float(t_e2e.item())
+    assert y.shape == (B, 4 * H_LR, 4 * W_LR, 3)
+
+    if rank == 0:
+        peaks = load_peaks()
+        dom = "upscaling/1/block/conv_transp"
+        dom_ms = layer_ms.get(dom)
+        achieved = CONVT2_FLOPS[ks] * B / (dom_ms * 1e-3) / 1e12 if dom_ms else None
+        roof = {"bound": "tensor", "kernel": "conv_igemm_kernel<256> (4 sub-pixel phases of " + dom + ")",
+                "achieved": achieved, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                "frac": (achieved / peaks["bf16_tflops_sustained"]) if achieved else None,
+                "peak_kind": "bf16 dense sustained, %s" % peaks["source"], "traffic": None,
+                "share_of_step": (dom_ms / ms_step) if dom_ms else None}
+        whole = GEN_FLOPS[ks] * world * B / (ms_step * 1e-3) / 1e12
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            fps, cores, dt = cpu_oracle_frames_per_s(ks, 1)
+            cpu = {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
+                   "sample": "1 frame of 270x480 (%.1f s) through the PyTorch-CPU fp32 oracle; reference TensorFlow unavailable on this box" % dt}
+        line = {"metric": "x4 frames/sec 270p->1080p", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "fp16 storage / fp32 accumulate (tcgen05 kind::f16)", "data": "synthetic",
+                "config": {"workload": "SRGAN generator x4 inference, %d frames/step/GPU of 270x480 -> 1080x1920, k=%d, frames sharded, no collective" % (B, ks),
+                           "l2": "working set per step (%.1f GB of activations) >> 126 MB L2" % (B * 1.4),
+                           "whole_step_tflops": whole, "frac_of_bf16_sustained_peak": whole / world / peaks["bf16_tflops_sustained"]},
+                "clocks": clocks,
+                "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": int(x_host.nbytes),
+                        "d2h_bytes_per_step": int(y.nbytes), "api": "upscaler Model.predict(ndarray)->ndarray"},
+                "gpu_launches": launches,
+                "roofline": roof, "cpu_baseline": cpu,
+                "layers_ms": {k: round(v, 4) for k, v in sorted(layer_ms.items(), key=lambda kv: -kv[1])[:8]}}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

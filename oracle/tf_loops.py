@@ -1,0 +1,51 @@
+"""Pure-Python/NumPy loop restatement of TensorFlow's documented conv rules — TEST INFRASTRUCTURE ONLY.
+
+Independent of the vectorised oracle (srgan_oracle.py): used by tests/test_oracle.py to pin the oracle's padding and
+tap alignment on small cases.
+  * tf.nn.conv2d, padding='SAME': out = ceil(in/stride); pad_total = max((out-1)*stride + k - in, 0);
+    pad_before = pad_total // 2 (the extra pixel goes after).
+  * keras Conv2DTranspose(strides=2, padding='same') = tf.nn.conv2d_transpose with output 2*in, i.e. the gradient
+    w.r.t. the input of the SAME stride-2 conv above: every input pixel i scatters x[i] * W[k] into
+    y = 2*i + k - pad_before, where pad_before is the forward conv's (input size 2*in).
+"""
+import numpy as np
+
+
+def same_pad(size, k, s):
+    out = -(-size // s)
+    total = max((out - 1) * s + k - size, 0)
+    return total // 2, out
+
+
+def conv2d_same_loops(x, kernel, stride=1):
+    """x (H,W,Cin), kernel (kh,kw,Cin,Cout) -> (OH,OW,Cout)."""
+    H, W, _ = x.shape
+    kh, kw, _, cout = kernel.shape
+    pt, OH = same_pad(H, kh, stride)
+    pl, OW = same_pad(W, kw, stride)
+    out = np.zeros((OH, OW, cout), np.float64)
+    for oy in range(OH):
+        for ox in range(OW):
+            for ky in range(kh):
+                for kx in range(kw):
+                    iy, ix = oy * stride + ky - pt, ox * stride + kx - pl
+                    if 0 <= iy < H and 0 <= ix < W:
+                        out[oy, ox] += x[iy, ix].astype(np.float64) @ kernel[ky, kx].astype(np.float64)
+    return out
+
+
+def conv2d_transpose_same_s2_loops(x, kernel):
+    """x (H,W,Cin), Keras Conv2DTranspose kernel (kh,kw,Cout,Cin) -> (2H,2W,Cout)."""
+    H, W, _ = x.shape
+    kh, kw, cout, _ = kernel.shape
+    pt, _ = same_pad(2 * H, kh, 2)
+    pl, _ = same_pad(2 * W, kw, 2)
+    out = np.zeros((2 * H, 2 * W, cout), np.float64)
+    for iy in range(H):
+        for ix in range(W):
+            for ky in range(kh):
+                for kx in range(kw):
+                    y, xx = 2 * iy + ky - pt, 2 * ix + kx - pl
+                    if 0 <= y < 2 * H and 0 <= xx < 2 * W:
+                        out[y, xx] += kernel[ky, kx].astype(np.float64) @ x[iy, ix].astype(np.float64)
+    return out

@@ -372,6 +372,78 @@ static int run_mma() {
     return 0;
 }
 
+
+// ============================================================== experiment 4b: MMA rate vs operand view alignment
+// A is a [512 rows x 128 B] region; each MMA group reads a view at `shift` rows with group stride `sbo`; `rotate`
+// cycles the view start over 9 different row offsets (like the taps of a 3x3 conv).
+template <int N>
+__global__ void __launch_bounds__(128, 1) probe_mma2_kernel(int iters, int shift, int sbo, int rotate, int bshift, long long* cycles) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sA = smem;               // 64 KB
+    uint8_t* sB = smem + 65536;       // up to 9 x N x 128 B
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(smem + 65536 + 9 * 256 * 128);
+    uint32_t* slot = reinterpret_cast<uint32_t*>(mbar + 1);
+    for (int i = threadIdx.x; i < (65536 + 9 * N * 128) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u + i;
+    fence_proxy_async();
+    const int warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { mbar_init(mbar, 1); fence_mbar_init(); }
+    if (warp == 0) tmem_alloc<256>(slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *slot;
+    if (threadIdx.x == 0) {
+        const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
+        const long long t0 = clock64();
+        for (int i = 0; i < iters; ++i) {
+            const int tap = rotate ? (i % 9) : 0;
+            const uint32_t a = a0 + uint32_t(shift + (rotate ? (tap / 3) * (sbo / 128) + (tap % 3) : 0)) * 128u;
+            const uint32_t b = b0 + (bshift ? uint32_t(tap) * N * 128 : 0);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                umma_bf16(tmem, make_sdesc_k_sw128(a + k * 32, sbo), make_sdesc_k_sw128(b + k * 32, 1024),
+                          make_idesc_bf16(128, N), 1);
+        }
+        umma_commit(mbar);
+        mbar_wait(mbar, 0);
+        const long long t1 = clock64();
+        if (blockIdx.x == 0) *cycles = t1 - t0;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<256>(tmem);
+}
+
+template <int N>
+static void run_mma2_n() {
+    long long* dC;
+    CK(cudaMalloc(&dC, 8));
+    const int smem = 65536 + 9 * 256 * 128 + 2048;
+    CK(cudaFuncSetAttribute(probe_mma2_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const int iters = 2048;
+    struct V { int shift, sbo, rotate, bshift; } vs[] = {{0, 1024, 0, 0}, {1, 1024, 0, 0}, {8, 1024, 0, 0}, {0, 1280, 0, 0},
+                                                          {1, 1280, 0, 0}, {0, 2048, 0, 0}, {0, 1280, 1, 0}, {0, 1280, 1, 1},
+                                                          {0, 1024, 1, 1}, {0, 2048, 1, 1}};
+    for (auto v : vs) {
+        for (int rep = 0; rep < 2; ++rep) {
+            probe_mma2_kernel<N><<<148, 128, smem>>>(iters, v.shift, v.sbo, v.rotate, v.bshift, dC);
+            CK(cudaDeviceSynchronize());
+        }
+        long long cyc;
+        CK(cudaMemcpy(&cyc, dC, 8, cudaMemcpyDeviceToHost));
+        printf("MMA2 N=%d shift=%d sbo=%d rotate=%d bshift=%d: %.1f cycles/MMA\n", N, v.shift, v.sbo, v.rotate, v.bshift,
+               double(cyc) / (iters * 4));
+    }
+}
+static int run_mma2() {
+    run_mma2_n<32>();
+    run_mma2_n<64>();
+    run_mma2_n<128>();
+    run_mma2_n<256>();
+    return 0;
+}
+
 // ============================================================== igemm vs direct
 struct ConvCase {
     const char* name;
@@ -554,6 +626,7 @@ int main(int argc, char** argv) {
     if (!strcmp(what, "mn")) return run_mn();
     if (!strcmp(what, "tma")) return run_tma();
     if (!strcmp(what, "mma")) return run_mma();
+    if (!strcmp(what, "mma2")) return run_mma2();
     if (!strcmp(what, "conv")) return run_conv();
     if (!strcmp(what, "time")) return run_time();
     printf("unknown experiment %s\n", what);

@@ -13,6 +13,9 @@
 // Epilogue: 4 warps read TMEM (tcgen05.ld 32x32b), apply scale/shift (bias or folded BatchNorm), activation
 //   (ReLU / LeakyReLU / PReLU / tanh), residual add, and store bf16 or fp32 NHWC.
 // Warp roles: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2..5 = epilogue.
+#include <stdlib.h>
+
+#include "b2_conv_epilogue.cuh"
 #include "b2_conv_igemm.cuh"
 #include "b2_host.h"
 #include "b2_ptx.cuh"
@@ -21,7 +24,6 @@ namespace b2 {
 
 constexpr int kThreads = 192;
 constexpr int kATileBytes = 128 * 128;  // 128 pixel rows x 64 bf16
-constexpr int kMaxChan = 512;            // widest layer on the path (VGG19 block4/5, discriminator)
 
 template <int BN>
 struct IgemmCfg {
@@ -32,114 +34,6 @@ struct IgemmCfg {
     static constexpr int kTmemCols = (2 * BN) < 32 ? 32 : 2 * BN;
     static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/ + 3 * kMaxChan * 4;
 };
-
-// 16-bit element helpers: the storage type is bf16 or IEEE fp16, chosen per launch (IgemmParams::f16).
-__device__ __forceinline__ uint32_t pack2(float a, float b, int f16) {
-    if (f16) {
-        // clamp to the finite half range so a stray large activation saturates instead of becoming inf
-        a = fminf(fmaxf(a, -65504.f), 65504.f);
-        b = fminf(fmaxf(b, -65504.f), 65504.f);
-        const __half2 h = __floats2half2_rn(a, b);
-        return *reinterpret_cast<const uint32_t*>(&h);
-    }
-    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<const uint32_t*>(&h);
-}
-__device__ __forceinline__ float2 unpack2(uint32_t u, int f16) {
-    if (f16) return __half22float2(*reinterpret_cast<const __half2*>(&u));
-    return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u));
-}
-__device__ __forceinline__ float load1(const void* base, size_t i, int f16) {
-    if (f16) return __half2float(reinterpret_cast<const __half*>(base)[i]);
-    return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(base)[i]);
-}
-__device__ __forceinline__ void store1(void* base, size_t i, float v, int f16) {
-    if (f16) reinterpret_cast<__half*>(base)[i] = __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));
-    else reinterpret_cast<__nv_bfloat16*>(base)[i] = __float2bfloat16_rn(v);
-}
-
-template <int ACT>
-__device__ __forceinline__ float apply_act_t(float v, float leaky, float alpha) {
-    if constexpr (ACT == ACT_RELU) return fmaxf(v, 0.f);
-    else if constexpr (ACT == ACT_LEAKY) return v > 0.f ? v : v * leaky;
-    else if constexpr (ACT == ACT_PRELU) return v > 0.f ? v : v * alpha;
-    else if constexpr (ACT == ACT_TANH) return tanhf(v);
-    else return v;
-}
-
-// Epilogue for one 128 x BN accumulator tile: this thread owns one pixel row (TMEM lane) and walks the columns in
-// chunks.  Per-channel scale / shift / alpha come from shared memory (staged once per CTA, padded to the N tiling).
-template <int BN, int ACT>
-__device__ __forceinline__ void epilogue_tile(const IgemmParams& p, uint32_t taddr, bool valid, int n0, size_t obase,
-                                              const float* s_scale, const float* s_shift, const float* s_alpha) {
-    constexpr int CH = BN < 32 ? 16 : 32;
-#pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += CH) {
-        uint32_t r[32];
-        if constexpr (CH == 32) {
-            tmem_ld32(taddr + c0, r);
-        } else {
-            uint32_t r16[16];
-            tmem_ld16(taddr + c0, r16);
-#pragma unroll
-            for (int j = 0; j < 16; ++j) r[j] = r16[j];
-        }
-        tmem_ld_wait();
-        if (!valid || n0 + c0 >= p.n_valid) continue;
-        float v[CH];
-        const float4* sc4 = reinterpret_cast<const float4*>(s_scale + n0 + c0);
-        const float4* sh4 = reinterpret_cast<const float4*>(s_shift + n0 + c0);
-        const float4* al4 = reinterpret_cast<const float4*>(s_alpha + n0 + c0);
-#pragma unroll
-        for (int g = 0; g < CH / 4; ++g) {
-            const float4 sc = sc4[g], sh = sh4[g];
-            float4 al = make_float4(0.f, 0.f, 0.f, 0.f);
-            if constexpr (ACT == ACT_PRELU) al = al4[g];
-            v[4 * g + 0] = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g + 0]), sc.x, sh.x), p.leaky, al.x);
-            v[4 * g + 1] = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g + 1]), sc.y, sh.y), p.leaky, al.y);
-            v[4 * g + 2] = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g + 2]), sc.z, sh.z), p.leaky, al.z);
-            v[4 * g + 3] = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g + 3]), sc.w, sh.w), p.leaky, al.w);
-        }
-        const bool vec = (!p.out_fp32) && ((p.out_ld & 7) == 0) && (n0 + c0 + CH <= p.n_valid);
-        if (vec) {
-            if (p.residual) {
-                const uint4* rp = reinterpret_cast<const uint4*>(p.residual + obase + c0);
-                uint4 rv[CH / 8];
-#pragma unroll
-                for (int g = 0; g < CH / 8; ++g) rv[g] = __ldg(rp + g);
-#pragma unroll
-                for (int g = 0; g < CH / 8; ++g) {
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const float2 f = unpack2(reinterpret_cast<const uint32_t*>(&rv[g])[e], p.f16);
-                        v[g * 8 + 2 * e] += f.x;
-                        v[g * 8 + 2 * e + 1] += f.y;
-                    }
-                }
-            }
-            uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + obase + c0);
-#pragma unroll
-            for (int g = 0; g < CH / 8; ++g) {
-                uint4 o;
-                uint32_t* h = reinterpret_cast<uint32_t*>(&o);
-#pragma unroll
-                for (int e = 0; e < 4; ++e) h[e] = pack2(v[g * 8 + 2 * e], v[g * 8 + 2 * e + 1], p.f16);
-                op[g] = o;
-            }
-        } else {
-#pragma unroll
-            for (int j = 0; j < CH; ++j) {
-                const int c = n0 + c0 + j;
-                if (c < p.n_valid) {
-                    float o = v[j];
-                    if (p.residual) o += load1(p.residual, obase + c0 + j, p.f16);
-                    if (p.out_fp32) reinterpret_cast<float*>(p.out)[obase + c0 + j] = o;
-                    else store1(p.out, obase + c0 + j, o, p.f16);
-                }
-            }
-        }
-    }
-}
 
 template <int BN>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -193,6 +87,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     const int cin_blocks = p.cin >> 6;
     const int num_kb = p.num_taps * cin_blocks;
     const int rows = p.TB * p.TH * p.TW;
+    const int kb_rot = int(blockIdx.x % uint32_t(num_kb));
     const uint32_t tx_bytes = uint32_t(rows) * 128u + uint32_t(Cfg::kBTileBytes);
 
     if (warp == 0) {
@@ -206,19 +101,22 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
             const int yt = t % p.tiles_y; t /= p.tiles_y;
             const int bt = t;
             const int x0 = xt * p.TW * p.in_mul, y0 = yt * p.TH * p.in_mul, b0 = bt * p.TB, n0 = nt * BN;
-            for (int tap = 0; tap < p.num_taps; ++tap) {
+            // Every CTA walks the same K blocks; starting each CTA at a different block (the accumulation order is
+            // free) keeps the 148 SMs from hammering the same few L2 lines of the weight matrix at the same time.
+            for (int i = 0; i < num_kb; ++i) {
+                int kb = i + kb_rot;
+                if (kb >= num_kb) kb -= num_kb;
+                const int tap = kb / cin_blocks, cb = kb - tap * cin_blocks;
                 const int cx = x0 + p.dx[tap], cy = y0 + p.dy[tap];
                 const int kbase = int(p.wtap[tap]) * p.cin;
-                for (int cb = 0; cb < cin_blocks; ++cb) {
-                    mbar_wait(&empty[stage], phase ^ 1);
-                    if (lane == 0) {
-                        mbar_expect_tx(&full[stage], tx_bytes);
-                        tma_load_4d(smemA + stage * kATileBytes, &mapA, &full[stage], cb * 64, cx, cy, b0);
-                        tma_load_2d(smemB + stage * Cfg::kBTileBytes, &mapB, &full[stage], kbase + cb * 64, n0);
-                    }
-                    __syncwarp();
-                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                mbar_wait(&empty[stage], phase ^ 1);
+                if (lane == 0) {
+                    mbar_expect_tx(&full[stage], tx_bytes);
+                    tma_load_4d(smemA + stage * kATileBytes, &mapA, &full[stage], cb * 64, cx, cy, b0);
+                    tma_load_2d(smemB + stage * Cfg::kBTileBytes, &mapB, &full[stage], kbase + cb * 64, n0);
                 }
+                __syncwarp();
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
@@ -340,6 +238,8 @@ static int launch_bn(const CUtensorMap& mapA, const CUtensorMap& mapB, const Ige
 }
 
 int launch_conv_igemm(const ConvIgemmArgs& a, cudaStream_t stream) {
+    static const bool no_halo = getenv("B2_NO_HALO") != nullptr;   // A/B switch for profiling the two main loops
+    if (!no_halo && conv_halo_applicable(a)) return launch_conv_halo(a, stream);
     IgemmParams p = a.p;
     if (a.xC % 64 != 0 || p.cin != a.xC) return set_error("igemm: Cin=%d must be a multiple of 64", a.xC);
     if (p.num_taps < 1 || p.num_taps > kMaxTaps) return set_error("igemm: bad tap count %d", p.num_taps);

@@ -98,6 +98,8 @@ conv_tail_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     const long t_end = p.total_tiles * (blockIdx.x + 1) / gridDim.x;
     const int cbs = p.cin >> 6;
     const int kblocks = p.KW * cbs;
+    // each CTA starts its K walk at a different weight block so the SMs do not all hit the same L2 lines at once
+    const int kb_rot = int(blockIdx.x % uint32_t(kblocks));
     const int halo_lo = p.ph, halo_hi = KH - 1 - p.ph;   // input rows needed above / below an output row
 
     Seg sg;
@@ -126,7 +128,9 @@ conv_tail_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             const int y0 = sg.y0, y1 = sg.y1, img = sg.img, x0 = sg.x0;
             const int nrows = (y1 + halo_hi) - (y0 - halo_lo);
             for (int r = 0; r < nrows; ++r)
-                for (int kb = 0; kb < kblocks; ++kb) {
+                for (int i = 0; i < kblocks; ++i) {
+                    int kb = i + kb_rot;
+                    if (kb >= kblocks) kb -= kblocks;
                     mbar_wait(&bempty[st], ph ^ 1);
                     if (lane == 0) {
                         mbar_expect_tx(&bfull[st], kTailBBlock);
@@ -152,9 +156,10 @@ conv_tail_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + uint32_t(as * 32);
                 const uint32_t a_base = smem_u32(smemA + sa * kTailAStage);
-                int kb = 0;
-                for (int dx = 0; dx < p.KW; ++dx)
-                    for (int cb = 0; cb < cbs; ++cb, ++kb) {
+                for (int i = 0; i < kblocks; ++i) {
+                        int kb = i + kb_rot;
+                        if (kb >= kblocks) kb -= kblocks;
+                        const int dx = kb / cbs, cb = kb - dx * cbs;
                         mbar_wait(&bfull[sb], pb);
                         tc_fence_after();
                         if (lane == 0) {
@@ -163,9 +168,9 @@ conv_tail_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 #pragma unroll
                             for (int k = 0; k < 4; ++k)
                                 umma_bf16(tmem_d, make_sdesc_k_sw128(a_addr + k * 32, 1024),
-                                          make_sdesc_k_sw128(b_addr + k * 32, 1024), idesc, (kb | k) != 0);
+                                          make_sdesc_k_sw128(b_addr + k * 32, 1024), idesc, (i | k) != 0);
                             umma_commit(&bempty[sb]);
-                            if (kb == kblocks - 1) {
+                            if (i == kblocks - 1) {
                                 umma_commit(&aempty[sa]);
                                 umma_commit(&tfull[as]);
                             }

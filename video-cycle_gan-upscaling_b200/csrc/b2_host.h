@@ -33,6 +33,10 @@ int launch_conv_igemm(const ConvIgemmArgs& a, cudaStream_t stream);
 // CUDA-core cross-check with identical semantics (tests only).
 int launch_conv_direct(const ConvIgemmArgs& a, cudaStream_t stream);
 
+// Halo-tile variant (b2_conv_halo.cu): input tile staged once in shared memory, taps as shifted descriptor views.
+bool conv_halo_applicable(const ConvIgemmArgs& a);
+int launch_conv_halo(const ConvIgemmArgs& a, cudaStream_t stream);
+
 // Final 9xKW conv with Cout=3 as a row-streaming kernel (b2_conv_tail.cu).
 int launch_conv_tail(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int KH, int KW,
                      const float* bias, int act, int f16, float* out, cudaStream_t stream);

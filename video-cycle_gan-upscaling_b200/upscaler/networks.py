@@ -75,7 +75,10 @@ class UpscalerOrigNet:
         self.kernel_size, self.filters = kernel_size, filters
         self.upscale_factor, self.res_block_num = upscale_factor, res_block_num
         self.upscale_times = int(math.log(upscale_factor, 2))
-        self.device = torch.device(device)
+        # Without a CUDA device the object still carries structure and weights (shapes, parameter counts, .h5 I/O);
+        # anything that computes raises, there is no CPU execution path.
+        self.on_gpu = torch.cuda.is_available()
+        self.device = torch.device(device) if self.on_gpu else torch.device("cpu")
         # 16-bit storage type of the inference path (activations + packed weights): fp16 keeps 11 significand bits,
         # which is what holds max-abs error under 2e-2 across 37 layers; bf16 is accepted and ~8x noisier.
         self.infer_dtype = infer_dtype
@@ -92,8 +95,10 @@ class UpscalerOrigNet:
         self._infer = {}
         self._buffers = {}
         self._final_rows = False
+        self.layer_events = None  # dict name -> [(start, end) CUDA events] when bench.py enables per-layer timing
         self._build_index_maps()
-        self.refresh()
+        if self.on_gpu:
+            self.refresh()
 
     # ---------------------------------------------------------------- weights
     def _build_index_maps(self):
@@ -162,42 +167,59 @@ class UpscalerOrigNet:
             self._buffers[key] = b
         return b
 
+    def _timed(self, name, fn):
+        if self.layer_events is None:
+            return fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        r = fn()
+        e1.record()
+        self.layer_events.setdefault(name, []).append((e0, e1))
+        return r
+
     def forward_infer(self, x, out=None):
         """x: (B,H,W,3) float32 CUDA in [-1,1] -> (B, H*f, W*f, 3) float32.  BatchNorm uses moving statistics folded
         into the conv epilogues (Keras learning_phase=0, i.e. Model.predict)."""
+        if not self.on_gpu:
+            raise RuntimeError("the generator runs on hand-written sm_100a kernels only; no CUDA device is available")
         B, H, W, C = x.shape
         if C != 3 or x.dtype != torch.float32:
             raise ValueError("expected (B,H,W,3) float32 input, got %s %s" % (tuple(x.shape), x.dtype))
         k, f, dt = self.kernel_size, self.filters, self.infer_dtype
         inf, pk = self._infer, self._packed
         # head: fold the 9 horizontal taps of the 3-channel input into 27 (of 64) channels, then a 9x1 conv
-        xp = ops.fold_taps(x, [(0, dx - 4) for dx in range(9)], out=self._buf("fold", (B, H, W, 64), dt), dtype=dt)
+        T = self._timed
+        xp = T("initial/fold", lambda: ops.fold_taps(x, [(0, dx - 4) for dx in range(9)],
+                                                     out=self._buf("fold", (B, H, W, 64), dt), dtype=dt))
         s, b, a = inf["initial/conv"]
-        skip = ops.conv2d(xp, pk["initial/conv"], f, 9, 1, out=self._buf("skip", (B, H, W, f), dt),
-                          scale=s, shift=b, alpha=a, act=ops.ACT_PRELU)
+        skip = T("initial/conv", lambda: ops.conv2d(xp, pk["initial/conv"], f, 9, 1,
+                                                    out=self._buf("skip", (B, H, W, f), dt), scale=s, shift=b, alpha=a,
+                                                    act=ops.ACT_PRELU))
         m = skip
         ping = [self._buf("t%d" % i, (B, H, W, f), dt) for i in range(3)]
         for i in range(self.res_block_num):
             n = "res_block/%d" % i
             free = [t for t in ping if t is not m]
             s, b, a = inf[n + "/conv_pre"]
-            h = ops.conv2d(m, pk[n + "/conv_pre"], f, k, k, out=free[0], scale=s, shift=b, alpha=a, act=ops.ACT_PRELU)
+            h = T("res_block/*/conv_pre", lambda: ops.conv2d(m, pk[n + "/conv_pre"], f, k, k, out=free[0], scale=s, shift=b,
+                                                             alpha=a, act=ops.ACT_PRELU))
             s, b, _ = inf[n + "/conv_post"]
-            m = ops.conv2d(h, pk[n + "/conv_post"], f, k, k, out=free[1], scale=s, shift=b, residual=m)
+            m = T("res_block/*/conv_post", lambda: ops.conv2d(h, pk[n + "/conv_post"], f, k, k, out=free[1], scale=s,
+                                                              shift=b, residual=m))
         free = [t for t in ping if t is not m]
         s, b, _ = inf["prefinal/conv2d"]
-        m = ops.conv2d(m, pk["prefinal/conv2d"], 64, k, k, out=free[0], scale=s, shift=b, residual=skip)
+        m = T("prefinal/conv2d", lambda: ops.conv2d(m, pk["prefinal/conv2d"], 64, k, k, out=free[0], scale=s, shift=b,
+                                                    residual=skip))
         h, w_ = H, W
         for i in range(self.upscale_times):
             n = "upscaling/%d/block/conv_transp" % i
             _, b, _ = inf[n]
-            m = ops.conv2d_transpose_s2(m, pk[n], 256, k, k, out=self._buf("up%d" % i, (B, 2 * h, 2 * w_, 256),
-                                                                           dt),
-                                        shift=b, act=ops.ACT_LEAKY, leaky=0.2)
+            ob = self._buf("up%d" % i, (B, 2 * h, 2 * w_, 256), dt)
+            m = T(n, lambda: ops.conv2d_transpose_s2(m, pk[n], 256, k, k, out=ob, shift=b, act=ops.ACT_LEAKY, leaky=0.2))
             h, w_ = 2 * h, 2 * w_
         _, b, _ = inf["final/conv"]
         if out is None:
             out = torch.empty((B, h, w_, 3), dtype=torch.float32, device=self.device)
         if self._final_rows:
-            return ops.conv2d_rows(m, pk["final/conv"], 3, 9, 9, bias=b, act=ops.ACT_TANH, out=out)
-        return ops.conv2d(m, pk["final/conv"], 3, 9, 9, out=out, shift=b, act=ops.ACT_TANH)
+            return T("final/conv", lambda: ops.conv2d_rows(m, pk["final/conv"], 3, 9, 9, bias=b, act=ops.ACT_TANH, out=out))
+        return T("final/conv", lambda: ops.conv2d(m, pk["final/conv"], 3, 9, 9, out=out, shift=b, act=ops.ACT_TANH))

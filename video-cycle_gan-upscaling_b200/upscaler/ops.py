@@ -12,6 +12,23 @@ from . import _lib
 from ._lib import ACT_LEAKY, ACT_NONE, ACT_PRELU, ACT_RELU, ACT_TANH  # noqa: F401
 
 
+_launches = 0  # kernels launched through this module (bench.py reports it as gpu_launches)
+
+
+def reset_launch_count():
+    global _launches
+    _launches = 0
+
+
+def launch_count():
+    return _launches
+
+
+def _count(n):
+    global _launches
+    _launches += n
+
+
 def _require_cuda(*ts):
     for t in ts:
         if t is not None and (not t.is_cuda or not t.is_contiguous()):
@@ -57,6 +74,7 @@ def conv2d(x, w_packed, cout, kh, kw, stride=1, out=None, out_dtype=None, scale=
         rc = lib.b2_conv2d_fprop(_lib.ptr(x), B, H, W, Cin, _lib.ptr(w_packed), cout, kh, kw, stride, ctypes.byref(ep),
                                  _lib.stream_ptr())
     _lib.check(rc, "b2_conv2d_fprop")
+    _count(1)
     return out
 
 
@@ -75,6 +93,7 @@ def conv2d_rows(x, w_rows, cout, kh, kw, bias=None, act=ACT_TANH, out=None):
     rc = _lib.load().b2_conv2d_rows_fprop(_lib.ptr(x), B, H, W, Cin, _lib.ptr(w_rows), cout, kh, kw, _lib.ptr(bias), act,
                                           f16, _lib.ptr(out), _lib.stream_ptr())
     _lib.check(rc, "b2_conv2d_rows_fprop")
+    _count(1)
     return out
 
 
@@ -101,6 +120,7 @@ def conv2d_transpose_s2(x, w_packed, cout, kh, kw, out=None, scale=None, shift=N
         rc = lib.b2_conv2d_transpose_s2_fprop(_lib.ptr(x), B, H, W, Cin, _lib.ptr(w_packed), cout, kh, kw,
                                               ctypes.byref(ep), _lib.stream_ptr())
     _lib.check(rc, "b2_conv2d_transpose_s2_fprop")
+    _count(4)
     return out
 
 
@@ -121,6 +141,7 @@ def fold_taps(x, taps, stride=1, out_hw=None, out=None, dtype=torch.bfloat16):
     rc = _lib.load().b2_fold_taps(_lib.ptr(x), 1 if x.dtype == torch.float32 else 0, B, H, W, Cin, OH, OW, stride, n,
                                   dy, dx, _lib.ptr(out), 1 if out.dtype == torch.float16 else 0, _lib.stream_ptr())
     _lib.check(rc, "b2_fold_taps")
+    _count(1)
     return out
 
 
@@ -136,6 +157,7 @@ def gather_cast(src, idx, out=None, dtype=torch.bfloat16):
     rc = _lib.load().b2_gather_cast(_lib.ptr(src), _lib.ptr(idx), idx.numel(), _lib.ptr(out),
                                     1 if out.dtype == torch.float16 else 0, _lib.stream_ptr())
     _lib.check(rc, "b2_gather_cast")
+    _count(1)
     return out
 
 
