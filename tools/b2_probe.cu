@@ -382,9 +382,10 @@ __global__ void __launch_bounds__(128, 1) probe_mma2_kernel(int iters, int shift
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sA = smem;               // 64 KB
     uint8_t* sB = smem + 65536;       // up to 9 x N x 128 B
-    uint64_t* mbar = reinterpret_cast<uint64_t*>(smem + 65536 + 9 * 256 * 128);
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(smem + 65536 + 98304);
     uint32_t* slot = reinterpret_cast<uint32_t*>(mbar + 1);
-    for (int i = threadIdx.x; i < (65536 + 9 * N * 128) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u + i;
+    constexpr int NB = 98304 / (N * 128) > 9 ? 9 : 98304 / (N * 128);
+    for (int i = threadIdx.x; i < (65536 + 98304) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u + i;
     fence_proxy_async();
     const int warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) { mbar_init(mbar, 1); fence_mbar_init(); }
@@ -399,7 +400,7 @@ __global__ void __launch_bounds__(128, 1) probe_mma2_kernel(int iters, int shift
         for (int i = 0; i < iters; ++i) {
             const int tap = rotate ? (i % 9) : 0;
             const uint32_t a = a0 + uint32_t(shift + (rotate ? (tap / 3) * (sbo / 128) + (tap % 3) : 0)) * 128u;
-            const uint32_t b = b0 + (bshift ? uint32_t(tap) * N * 128 : 0);
+            const uint32_t b = b0 + (bshift ? uint32_t(tap % NB) * N * 128 : 0);
 #pragma unroll
             for (int k = 0; k < 4; ++k)
                 umma_bf16(tmem, make_sdesc_k_sw128(a + k * 32, sbo), make_sdesc_k_sw128(b + k * 32, 1024),
@@ -419,7 +420,7 @@ template <int N>
 static void run_mma2_n() {
     long long* dC;
     CK(cudaMalloc(&dC, 8));
-    const int smem = 65536 + 9 * 256 * 128 + 2048;
+    const int smem = 65536 + 98304 + 2048;
     CK(cudaFuncSetAttribute(probe_mma2_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     const int iters = 2048;
     struct V { int shift, sbo, rotate, bshift; } vs[] = {{0, 1024, 0, 0}, {1, 1024, 0, 0}, {8, 1024, 0, 0}, {0, 1280, 0, 0},
@@ -600,7 +601,7 @@ static int run_conv() {
     return fails;
 }
 
-static int run_time() {
+static int run_time(int only = -1) {
     const ConvCase cases[] = {
         {"res3x3 270x480", 1, 270, 480, 64, 64, 3, 1, -1, ACT_PRELU, 0, 0},
         {"res3x3 270x480 B8", 8, 270, 480, 64, 64, 3, 1, -1, ACT_PRELU, 0, 0},
@@ -613,7 +614,11 @@ static int run_time() {
         {"vgg 48 512->512", 16, 48, 48, 512, 512, 3, 1, -1, ACT_RELU, 0, 0},
         {"tail9x9 540x960", 1, 540, 960, 256, 3, 9, 1, -1, ACT_TANH, 0, 1},
     };
-    for (const auto& c : cases) run_conv_case(c, false, 5);
+    int i = 0;
+    for (const auto& c : cases) {
+        if (only < 0 || only == i) run_conv_case(c, false, only < 0 ? 5 : 2);
+        ++i;
+    }
     return 0;
 }
 
@@ -628,7 +633,7 @@ int main(int argc, char** argv) {
     if (!strcmp(what, "mma")) return run_mma();
     if (!strcmp(what, "mma2")) return run_mma2();
     if (!strcmp(what, "conv")) return run_conv();
-    if (!strcmp(what, "time")) return run_time();
+    if (!strcmp(what, "time")) return run_time(argc > 2 ? atoi(argv[2]) : -1);
     printf("unknown experiment %s\n", what);
     return 1;
 }

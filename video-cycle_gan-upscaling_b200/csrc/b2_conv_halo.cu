@@ -55,7 +55,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     uint64_t* tfull = bars + 48;       // [2]
     uint64_t* tempty = bars + 50;      // [2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 52);
-    float* s_scale = reinterpret_cast<float*>(tail + 512);
+    uint32_t* s_tapoff = reinterpret_cast<uint32_t*>(tail + 512);   // [kMaxTaps] descriptor-lo offset of each tap's view
+    float* s_scale = reinterpret_cast<float*>(tail + 1024);
     float* s_shift = s_scale + kMaxChan;
     float* s_alpha = s_shift + kMaxChan;
 
@@ -70,6 +71,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc<kTmemCols>(tmem_slot);
+    for (int t = threadIdx.x; t < p.num_taps; t += kHaloThreads)
+        s_tapoff[t] = uint32_t((int(p.dy[t]) - g.dy_min) * g.HW + (int(p.dx[t]) - g.dx_min)) * 8u;   // 128 B per pixel = 8 x 16 B
     for (int c = threadIdx.x; c < p.tiles_n * BN; c += kHaloThreads) {
         const bool cv = c < p.n_valid;
         s_scale[c] = (p.scale && cv) ? p.scale[c] : 1.f;
@@ -79,7 +82,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);   // warp-uniform for the MMA issue path
 
     const int cbs = p.cin >> 6;
     const int taps = p.num_taps;
@@ -134,7 +137,9 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     } else if (warp == 1) {
         // ------------------------------------------------------------ MMA issuer
         const uint32_t idesc = p.f16 ? make_idesc_f16(128, BN) : make_idesc_bf16(128, BN);
-        const uint32_t sbo = uint32_t(g.HW) * 128u;
+        const uint32_t a_hi = sdesc_hi_k_sw128(uint32_t(g.HW) * 128u);
+        constexpr uint32_t b_hi = sdesc_hi_k_sw128(1024);
+        const uint32_t a_lo0 = sdesc_lo(smem_u32(smemA)), b_lo0 = sdesc_lo(smem_u32(smemB));
         int sa = 0; uint32_t pa = 0;
         int sb = 0; uint32_t pb = 0;
         int as = 0; uint32_t aph = 0;
@@ -146,24 +151,25 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             for (int cb = 0; cb < cbs; ++cb) {
                 mbar_wait(&afull[sa], pa);
                 tc_fence_after();
-                const uint32_t a_base = smem_u32(smemA + sa * g.a_block);
+                const uint32_t a_lo_blk = a_lo0 + uint32_t(sa) * uint32_t(g.a_block >> 4);
                 for (int i = 0; i < taps; ++i) {
                     int t = i + tap_rot;
                     if (t >= taps) t -= taps;
-                    uint32_t b_addr;
+                    uint32_t b_lo;
                     if (g.resident) {
-                        b_addr = smem_u32(smemB + (t * cbs + cb) * kBBlock);
+                        b_lo = b_lo0 + uint32_t(t * cbs + cb) * (kBBlock >> 4);
                     } else {
                         mbar_wait(&bfull[sb], pb);
                         tc_fence_after();
-                        b_addr = smem_u32(smemB + sb * kBBlock);
+                        b_lo = b_lo0 + uint32_t(sb) * (kBBlock >> 4);
                     }
-                    if (lane == 0) {
-                        const uint32_t a_addr = a_base + uint32_t((int(p.dy[t]) - g.dy_min) * g.HW + (int(p.dx[t]) - g.dx_min)) * 128u;
-#pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            umma_bf16(tmem_d, make_sdesc_k_sw128(a_addr + k * 32, sbo), make_sdesc_k_sw128(b_addr + k * 32, 1024),
-                                      idesc, (cb | i | k) != 0);
+                    // tap offset straight from the kernel parameters (constant bank) so it stays warp-uniform
+                    const uint32_t a_lo = a_lo_blk + uint32_t((int(p.dy[t]) - g.dy_min) * g.HW + (int(p.dx[t]) - g.dx_min)) * 8u;
+                    if (elect_one()) {
+                        umma_f16_lohi(tmem_d, a_lo, a_hi, b_lo, b_hi, idesc, (cb | i) != 0);
+                        umma_f16_lohi(tmem_d, a_lo + 2, a_hi, b_lo + 2, b_hi, idesc, 1);
+                        umma_f16_lohi(tmem_d, a_lo + 4, a_hi, b_lo + 4, b_hi, idesc, 1);
+                        umma_f16_lohi(tmem_d, a_lo + 6, a_hi, b_lo + 6, b_hi, idesc, 1);
                         if (!g.resident) umma_commit(&bempty[sb]);
                         if (i == taps - 1) {
                             umma_commit(&aempty[sa]);
@@ -285,7 +291,7 @@ int launch_conv_halo(const ConvIgemmArgs& a, cudaStream_t stream) {
     g.a_stages = (kHaloSmemBudget - g.b_bytes) / g.a_block;
     if (g.a_stages > 8) g.a_stages = 8;
     if (g.a_stages < 2) return set_error("conv_halo: halo block of %d bytes leaves no room for double buffering", g.a_block);
-    const int smem_bytes = g.b_bytes + g.a_stages * g.a_block + 512 + 3 * kMaxChan * 4 + 1024;
+    const int smem_bytes = g.b_bytes + g.a_stages * g.a_block + 1024 + 3 * kMaxChan * 4 + 1024;
 
     CUtensorMap mapA, mapB;
     {

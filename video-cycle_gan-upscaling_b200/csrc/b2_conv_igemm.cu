@@ -82,7 +82,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
     const int cin_blocks = p.cin >> 6;
     const int num_kb = p.num_taps * cin_blocks;
@@ -122,6 +122,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     } else if (warp == 1) {
         // ------------------------------------------------------------ MMA issuer
         const uint32_t idesc = p.f16 ? make_idesc_f16(128, BN) : make_idesc_bf16(128, BN);
+        constexpr uint32_t desc_hi = sdesc_hi_k_sw128(1024);
+        const uint32_t a_lo0 = sdesc_lo(smem_u32(smemA)), b_lo0 = sdesc_lo(smem_u32(smemB));
         int stage = 0;
         uint32_t phase = 0;
         int as = 0;
@@ -133,15 +135,15 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
             for (int kb = 0; kb < num_kb; ++kb) {
                 mbar_wait(&full[stage], phase);
                 tc_fence_after();
-                if (lane == 0) {
-                    const uint32_t a_addr = smem_u32(smemA + stage * kATileBytes);
-                    const uint32_t b_addr = smem_u32(smemB + stage * Cfg::kBTileBytes);
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const uint64_t adesc = make_sdesc_k_sw128(a_addr + k * 32, 1024);
-                        const uint64_t bdesc = make_sdesc_k_sw128(b_addr + k * 32, 1024);
-                        umma_bf16(tmem_d, adesc, bdesc, idesc, (kb | k) != 0);
-                    }
+                // elect.sync (not `lane == 0`): ptxas then knows a single thread runs the block and keeps the descriptors
+                // in uniform registers, so the four UTCHMMA issue back to back
+                if (elect_one()) {
+                    const uint32_t a_lo = a_lo0 + uint32_t(stage) * (kATileBytes >> 4);
+                    const uint32_t b_lo = b_lo0 + uint32_t(stage) * (Cfg::kBTileBytes >> 4);
+                    umma_f16_lohi(tmem_d, a_lo, desc_hi, b_lo, desc_hi, idesc, kb != 0);
+                    umma_f16_lohi(tmem_d, a_lo + 2, desc_hi, b_lo + 2, desc_hi, idesc, 1);
+                    umma_f16_lohi(tmem_d, a_lo + 4, desc_hi, b_lo + 4, desc_hi, idesc, 1);
+                    umma_f16_lohi(tmem_d, a_lo + 6, desc_hi, b_lo + 6, desc_hi, idesc, 1);
                     umma_commit(&empty[stage]);
                     if (kb == num_kb - 1) umma_commit(&tfull[as]);
                 }

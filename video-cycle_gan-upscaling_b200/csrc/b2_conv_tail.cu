@@ -91,7 +91,7 @@ conv_tail_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
     // This CTA's contiguous range of output-row tiles in the flattened (image, strip, row) order.
     const long t_begin = p.total_tiles * blockIdx.x / gridDim.x;
@@ -144,6 +144,8 @@ conv_tail_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     } else if (warp == 1) {
         // ---------------------------------------------------------------- MMA issuer
         const uint32_t idesc = p.f16 ? make_idesc_f16(128, 32) : make_idesc_bf16(128, 32);
+        constexpr uint32_t desc_hi = sdesc_hi_k_sw128(1024);
+        const uint32_t a_lo0 = sdesc_lo(smem_u32(smemA)), b_lo0 = sdesc_lo(smem_u32(smemB));
         int sa = 0; uint32_t pa = 0;
         int sb = 0; uint32_t pb = 0;
         int as = 0; uint32_t aph = 0;
@@ -155,20 +157,20 @@ conv_tail_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 mbar_wait(&afull[sa], pa);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + uint32_t(as * 32);
-                const uint32_t a_base = smem_u32(smemA + sa * kTailAStage);
+                const uint32_t a_lo_stage = a_lo0 + uint32_t(sa) * (kTailAStage >> 4);
                 for (int i = 0; i < kblocks; ++i) {
                         int kb = i + kb_rot;
                         if (kb >= kblocks) kb -= kblocks;
                         const int dx = kb / cbs, cb = kb - dx * cbs;
                         mbar_wait(&bfull[sb], pb);
                         tc_fence_after();
-                        if (lane == 0) {
-                            const uint32_t a_addr = a_base + cb * kTailABlock + dx * 128;
-                            const uint32_t b_addr = smem_u32(smemB + sb * kTailBBlock);
-#pragma unroll
-                            for (int k = 0; k < 4; ++k)
-                                umma_bf16(tmem_d, make_sdesc_k_sw128(a_addr + k * 32, 1024),
-                                          make_sdesc_k_sw128(b_addr + k * 32, 1024), idesc, (i | k) != 0);
+                        if (elect_one()) {
+                            const uint32_t a_lo = a_lo_stage + uint32_t(cb) * (kTailABlock >> 4) + uint32_t(dx) * 8u;
+                            const uint32_t b_lo = b_lo0 + uint32_t(sb) * (kTailBBlock >> 4);
+                            umma_f16_lohi(tmem_d, a_lo, desc_hi, b_lo, desc_hi, idesc, i != 0);
+                            umma_f16_lohi(tmem_d, a_lo + 2, desc_hi, b_lo + 2, desc_hi, idesc, 1);
+                            umma_f16_lohi(tmem_d, a_lo + 4, desc_hi, b_lo + 4, desc_hi, idesc, 1);
+                            umma_f16_lohi(tmem_d, a_lo + 6, desc_hi, b_lo + 6, desc_hi, idesc, 1);
                             umma_commit(&bempty[sb]);
                             if (i == kblocks - 1) {
                                 umma_commit(&aempty[sa]);

@@ -136,6 +136,59 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
         ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// Same instruction with the two 64-bit shared-memory descriptors passed as (lo, hi) halves.  Only the start-address
+// field (lo) changes between the MMAs of a main loop, so the issuing thread spends one add per operand per MMA
+// instead of rebuilding 64-bit descriptors: with a single thread issuing, every scalar instruction between two
+// tcgen05.mma is on the critical path (measured: ~20 SASS instructions per MMA capped the kernels at ~2x the MMA time).
+__device__ __forceinline__ void umma_f16_lohi(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                              uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %6, 0;\n\t"
+        "mov.b64 da, {%1, %2};\n\t"
+        "mov.b64 db, {%3, %4};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t"
+        "}\n"
+        ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// Warp-convergent form: EVERY lane executes this with identical (warp-uniform) operands and `issue` is non-zero in
+// exactly one lane.  Keeping the call outside divergent control flow lets ptxas hold the descriptors in uniform
+// registers; under `if (lane == 0)` it emits an ELECT / R2UR.BROADCAST / BRA.U.ANY loop (~15 instructions) per MMA.
+__device__ __forceinline__ void umma_f16_lohi_pred(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                                   uint32_t idesc, uint32_t accumulate, uint32_t issue) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p, q;\n\t"
+        ".reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %6, 0;\n\t"
+        "setp.ne.b32 q, %7, 0;\n\t"
+        "mov.b64 da, {%1, %2};\n\t"
+        "mov.b64 db, {%3, %4};\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t"
+        "}\n"
+        ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate), "r"(issue)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_pred(uint64_t* bar, uint32_t issue) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred q;\n\t"
+        "setp.ne.b32 q, %1, 0;\n\t"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t"
+        "}\n"
+        ::"r"(smem_u32(bar)), "r"(issue)
+        : "memory");
+}
+// hi word of a K-major SWIZZLE_128B descriptor: SBO>>4 in [0,14), version=1 at bit 14, layout=2 at bits [29,32)
+__host__ __device__ constexpr uint32_t sdesc_hi_k_sw128(uint32_t sbo_bytes) {
+    return ((sbo_bytes >> 4) & 0x3FFF) | (1u << 14) | (2u << 29);
+}
+// lo word: start address >> 4 in [0,14), LBO field = 1 at bit 16; advancing the operand by n bytes adds n >> 4
+__device__ __forceinline__ uint32_t sdesc_lo(uint32_t saddr) { return ((saddr & 0x3FFFF) >> 4) | (1u << 16); }
+
 // Arrive on an mbarrier once every previously issued tcgen05.mma of this thread has retired.
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
