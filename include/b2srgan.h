@@ -45,6 +45,11 @@ typedef struct {
     void* out;            /* bf16, or float when out_fp32 != 0 */
     int out_fp32;
     int f16; /* 16-bit element type of x / w / residual / out: 0 = bf16, 1 = IEEE fp16 */
+    /* Backward of ReLU / LeakyReLU fused into a data-gradient convolution: after the activation step the value is
+     * multiplied by (gate > 0 ? 1 : gate_slope), gate being the forward OUTPUT of the layer whose input gradient this
+     * is (same geometry as out, 16-bit).  Null = no gating. */
+    const void* gate;
+    float gate_slope;
 } b2_epilogue;
 
 /* Conv2D(padding='same') forward on tcgen05 tensor cores — replaces the TF conv2d behind keras.layers.Conv2D at
@@ -84,6 +89,92 @@ int b2_fold_taps(const void* in, int in_fp32, int B, int H, int W, int Cin, int 
  * host (Keras kernel layout (kh,kw,Cin,Cout) / (kh,kw,Cout,Cin) -> packed [Cout][tap*Cin_pad + c], its dgrad
  * transpose, or the tap-folded layouts); this call refreshes the bf16 shadow copy from the fp32 master weights. */
 int b2_gather_cast(const float* src, const int32_t* idx, int64_t n, void* out, int f16, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Training step (Model.train_on_batch of the models compile_training_model / make_and_compile_gan build,
+ * model.py:1017-1137; call sites train.py:220, train_mini.py:232, train_gan.py:316-317, train_gan3.py:353-354).
+ * Data gradients of stride-1 convolutions are b2_conv2d_fprop calls on weights packed flipped/transposed
+ * (upscaler/ops.py conv_dgrad_pack_index); the data gradient of Conv2DTranspose is b2_conv2d_fprop with stride 2.
+ * ------------------------------------------------------------------------------------------------------------- */
+
+/* Data gradient of Conv2D(strides=2, padding='same') — TF conv2d_backprop_input behind the discriminator convs
+ * (model.py:843-871).  dz: [B,OH,OW,Cout] 16-bit; w: packed [Cin][kh*kw*Cout] (un-flipped taps, transposed channels);
+ * ep->out: [B,H,W,Cin] where (OH,OW) = ceil((H,W)/2).  Runs as up to four sub-pixel phases. */
+int b2_conv2d_s2_dgrad(const void* dz, int B, int OH, int OW, int Cout, const void* w, int Cin, int kh, int kw, int H, int W,
+                       const b2_epilogue* ep, void* stream);
+
+/* Weight gradient — TF conv2d_backprop_filter:  dw[ky][kx][cx][cz] += sum_p x[p*stride + (ky,kx) - pad, cx] * dz[p, cz],
+ * fp32, ACCUMULATED into dw (zero it first), tcgen05 with the pixel dimension as GEMM K and split-K over pixels.
+ *   Conv2D:           x = layer input [B,H,W,Cin],  dz = gradient of the layer output [B,ceil(H/s),ceil(W/s),Cout]
+ *                     -> dw in Keras layout (kh,kw,Cin,Cout).
+ *   Conv2DTranspose:  x = gradient of the layer output [B,2H,2W,Cout], dz = layer input [B,H,W,Cin], stride 2
+ *                     -> dw in Keras layout (kh,kw,Cout,Cin).
+ * Cx and Cz must be multiples of 64. */
+int b2_conv2d_wgrad(const void* x, int B, int H, int W, int Cx, const void* dz, int Cz, int kh, int kw, int stride, float* dw,
+                    int f16, void* stream);
+
+/* Per-channel sums over the rows of a [rows][C] 16-bit tensor: sum[c] += x, sumsq[c] += x^2 (sumsq may be null).
+ * Batch statistics of BatchNormalization in the training phase (model.py:20, 23, 284, 840-884) and bias gradients. */
+int b2_colstats(const void* x, int64_t rows, int C, int f16, float* sum, float* sumsq, void* stream);
+
+/* mean = sum/count, var = sumsq/count - mean^2 (biased) -> scale = gamma/sqrt(var+eps), shift = beta - mean*scale;
+ * optional Keras moving-statistics update (momentum 0.99; variance corrected by n/(n-(1+eps))); optional mean/invstd
+ * outputs for the backward pass. */
+int b2_bn_finalize(const float* sum, const float* sumsq, float count, const float* gamma, const float* beta, float eps,
+                   float momentum, float* moving_mean, float* moving_var, float* scale, float* shift, float* mean_out,
+                   float* invstd_out, int C, void* stream);
+
+/* Inference fold of BatchNormalization after a biased conv: scale = gamma/sqrt(var+eps), shift = beta+(bias-mean)*scale. */
+int b2_bn_fold(const float* gamma, const float* beta, const float* mean, const float* var, const float* bias, float eps,
+               float* scale, float* shift, int C, void* stream);
+
+/* out = act(z*scale + shift) + residual over [rows][C] 16-bit: BatchNorm apply fused with PReLU / LeakyReLU and the
+ * residual Add (model.py:20-25, 284-285, 840-841). */
+int b2_affine_act(const void* z, int64_t rows, int C, int f16, const float* scale, const float* shift, const float* alpha,
+                  int act, float leaky, const void* residual, void* out, void* stream);
+
+/* Backward reductions through act(BN(z)): with u = z*scale+shift, dy = g*act'(u), xhat = (z-mean)*invstd:
+ *   s1[c] += dy (= dbeta), s2[c] += dy*xhat (= dgamma), dalpha[c] += g*min(u,0) (PReLU slope gradient; may be null). */
+int b2_bn_bwd_reduce(const void* z, const void* g, int64_t rows, int C, int f16, const float* scale, const float* shift,
+                     const float* alpha, int act, float leaky, const float* mean, const float* invstd, float* s1, float* s2,
+                     float* dalpha, void* stream);
+
+/* dz = scale*(dy - s1/count - xhat*s2/count): gradient w.r.t. the conv output under train-mode BatchNormalization.
+ * With s1 == s2 == null (count 0) it is the plain activation backward dz = scale*dy. */
+int b2_bn_bwd_apply(const void* z, const void* g, int64_t rows, int C, int f16, const float* scale, const float* shift,
+                    const float* alpha, int act, float leaky, const float* mean, const float* invstd, const float* s1,
+                    const float* s2, float count, void* dz, void* stream);
+
+/* MaxPooling2D(2,2) 'valid' of VGG19 (keras.applications behind model.py:108) and its gradient (first maximum of each
+ * window takes the gradient; relu_gate != 0 additionally zeroes it where x <= 0, i.e. the ReLU of the conv below). */
+int b2_maxpool2x2(const void* x, int B, int H, int W, int C, int f16, void* y, void* stream);
+int b2_maxpool2x2_bwd(const void* x, const void* y, const void* dy, int B, int H, int W, int C, int f16, int relu_gate,
+                      void* dx, void* stream);
+
+/* Content-loss reductions (model.py:117, 137, 157): *loss += weight * mean(f(a-b)), f = square (mae=0) or abs (mae=1);
+ * grad (nullable, same type as a) = gscale * f'(a-b) / n.  dtype: 0 bf16, 1 fp16, 2 fp32. */
+int b2_loss_pair(const void* a, const void* b, int64_t n, int dtype, int mae, float weight, float gscale, float* loss,
+                 void* grad, void* stream);
+
+/* Wasserstein-type reductions (model.py:159-160, 215-261): *loss += weight * mean(x*y) with y an array or the constant
+ * yconst; grad[i] = gscale * y[i] / n.  fp32, n = batch size. */
+int b2_mean_prod(const float* x, const float* y, float yconst, int64_t n, float weight, float gscale, float* loss, float* grad,
+                 void* stream);
+
+/* Backward of the generator's final tanh (model.py:291): dz = (g1 + g2 + g3) * (1 - y*y); g2, g3 may be null. fp32. */
+int b2_tanh_bwd(const float* y, const float* g1, const float* g2, const float* g3, int64_t n, float* dz, void* stream);
+
+/* out[i] (+)= idx[i] >= 0 ? src[idx[i]] : 0 in fp32 (weight gradients of tap-folded layers back to the Keras layout). */
+int b2_gather_f32(const float* src, const int32_t* idx, int64_t n, float* out, int accumulate, void* stream);
+
+/* out = cast(in * scale); dtype codes as in b2_loss_pair. */
+int b2_cast_scale(const void* in, int in_dtype, int64_t n, float scale, void* out, int out_dtype, void* stream);
+
+/* keras.optimizers.Adam update over a flat fp32 parameter buffer (model.py:1026, 1066, 1130):
+ *   g *= gscale; m = b1*m + (1-b1)*g; v = b2*v + (1-b2)*g*g; p -= lr_t * m / (sqrt(v) + eps),
+ * lr_t = lr*sqrt(1-b2^t)/(1-b1^t) computed by the caller. */
+int b2_adam(float* params, const float* grads, float* m, float* v, int64_t n, float lr_t, float beta1, float beta2, float eps,
+            float gscale, void* stream);
 
 #ifdef __cplusplus
 }

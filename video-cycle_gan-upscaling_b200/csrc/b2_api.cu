@@ -14,6 +14,8 @@ static void fill_epilogue(IgemmParams& p, const b2_epilogue* ep, int Cout) {
     p.act = ep->act;
     p.leaky = ep->leaky;
     p.residual = reinterpret_cast<const __nv_bfloat16*>(ep->residual);
+    p.gate = ep->gate;
+    p.gate_slope = ep->gate_slope;
     p.out = ep->out;
     p.out_fp32 = ep->out_fp32;
     p.f16 = ep->f16;
@@ -51,10 +53,12 @@ static int conv_taps(IgemmParams& p, int B, int H, int W, int Cin, int kh, int k
 }
 
 // Conv2DTranspose(stride 2, same) is the input-gradient of a SAME stride-2 conv: out[y] = sum_i x[i] * W[y - 2i + pb],
-// pb = (k-2)/2.  For output parity py: y = 2j + py, i = j + d  =>  ky = py + pb - 2d.
-static void convT_phase_taps(IgemmParams& p, int B, int H, int W, int Cin, int kh, int kw, int py, int px) {
-    const int pbh = (kh - 2) / 2, pbw = (kw - 2) / 2;
-    p.B = B; p.H = H; p.W = W;
+// pb = the forward conv's pad_before ((k-2)/2 when out = 2*in).  For output parity py: y = 2j + py, i = j + d
+// =>  ky = py + pb - 2d.  The same tap lists give the data gradient of a stride-2 Conv2D (discriminator, model.py:843-871)
+// with (Hout, Wout) = the forward conv's input size, which need not be even.
+static void convT_phase_taps(IgemmParams& p, int B, int Hout, int Wout, int Cin, int kh, int kw, int pbh, int pbw, int py,
+                             int px) {
+    p.B = B; p.H = (Hout - py + 1) / 2; p.W = (Wout - px + 1) / 2;
     p.cin = Cin;
     p.in_mul = 1;
     int nt = 0;
@@ -69,8 +73,30 @@ static void convT_phase_taps(IgemmParams& p, int B, int H, int W, int Cin, int k
         }
     }
     p.num_taps = nt;
-    p.OH = 2 * H; p.OW = 2 * W;
+    p.OH = Hout; p.OW = Wout;
     p.out_sy = 2; p.out_sx = 2; p.out_oy = py; p.out_ox = px;
+}
+
+// Launches the (up to) four sub-pixel phases of a stride-2 transposed convolution; phases without taps or pixels write
+// nothing (their outputs are zero only through the bias-free epilogue, so callers needing them pre-zero `out`).
+static int run_transposed(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw, int Hout,
+                          int Wout, int pbh, int pbw, const b2_epilogue* ep, void* stream, bool direct) {
+    for (int ph = 0; ph < 4; ++ph) {
+        ConvIgemmArgs a;
+        memset(&a, 0, sizeof(a));
+        convT_phase_taps(a.p, B, Hout, Wout, Cin, kh, kw, pbh, pbw, ph >> 1, ph & 1);
+        if (a.p.H <= 0 || a.p.W <= 0) continue;
+        fill_epilogue(a.p, ep, Cout);
+        a.x = reinterpret_cast<const __nv_bfloat16*>(x);
+        a.xB = B; a.xH = H; a.xW = W; a.xC = Cin;
+        a.w = reinterpret_cast<const __nv_bfloat16*>(w);
+        a.w_rows = Cout; a.w_k = kh * kw * Cin;
+        if (a.p.num_taps == 0) return set_error("transposed conv: phase %d has no taps (filter %dx%d)", ph, kh, kw);
+        int rc = direct ? launch_conv_direct(a, reinterpret_cast<cudaStream_t>(stream))
+                        : launch_conv_igemm(a, reinterpret_cast<cudaStream_t>(stream));
+        if (rc) return rc;
+    }
+    return 0;
 }
 
 extern "C" {
@@ -97,20 +123,43 @@ int b2_conv2d_transpose_s2_fprop(const void* x, int B, int H, int W, int Cin, co
                                  int kw, const b2_epilogue* ep, void* stream) {
     if (!x || !w || !ep || !ep->out) return set_error("b2_conv2d_transpose_s2_fprop: null pointer");
     if (kh < 2 || kw < 2 || kh * kw > kMaxTaps) return set_error("b2_conv2d_transpose_s2_fprop: bad filter %dx%d", kh, kw);
-    for (int ph = 0; ph < 4; ++ph) {
-        ConvIgemmArgs a;
-        memset(&a, 0, sizeof(a));
-        convT_phase_taps(a.p, B, H, W, Cin, kh, kw, ph >> 1, ph & 1);
-        fill_epilogue(a.p, ep, Cout);
-        a.x = reinterpret_cast<const __nv_bfloat16*>(x);
-        a.xB = B; a.xH = H; a.xW = W; a.xC = Cin;
-        a.w = reinterpret_cast<const __nv_bfloat16*>(w);
-        a.w_rows = Cout; a.w_k = kh * kw * Cin;
-        if (a.p.num_taps == 0) return set_error("b2_conv2d_transpose_s2_fprop: phase %d has no taps", ph);
-        int rc = launch_conv_igemm(a, reinterpret_cast<cudaStream_t>(stream));
-        if (rc) return rc;
-    }
-    return 0;
+    return run_transposed(x, B, H, W, Cin, w, Cout, kh, kw, 2 * H, 2 * W, (kh - 2) / 2, (kw - 2) / 2, ep, stream, false);
+}
+
+int b2_conv2d_s2_dgrad(const void* dz, int B, int OH, int OW, int Cout, const void* w, int Cin, int kh, int kw, int H, int W,
+                       const b2_epilogue* ep, void* stream) {
+    if (!dz || !w || !ep || !ep->out) return set_error("b2_conv2d_s2_dgrad: null pointer");
+    int oh, ow, pbh, pbw;
+    tf_same(H, kh, 2, oh, pbh);
+    tf_same(W, kw, 2, ow, pbw);
+    if (oh != OH || ow != OW) return set_error("b2_conv2d_s2_dgrad: %dx%d is not the stride-2 SAME output of %dx%d", OH, OW, H, W);
+    if (kh < 2 || kw < 2 || kh * kw > kMaxTaps) return set_error("b2_conv2d_s2_dgrad: bad filter %dx%d", kh, kw);
+    return run_transposed(dz, B, OH, OW, Cout, w, Cin, kh, kw, H, W, pbh, pbw, ep, stream, false);
+}
+
+int b2_conv2d_wgrad(const void* x, int B, int H, int W, int Cx, const void* dz, int Cz, int kh, int kw, int stride, float* dw,
+                    int f16, void* stream) {
+    if (!x || !dz || !dw) return set_error("b2_conv2d_wgrad: null pointer");
+    if (stride != 1 && stride != 2) return set_error("b2_conv2d_wgrad: stride %d unsupported", stride);
+    if (kh * kw > kMaxTaps) return set_error("b2_conv2d_wgrad: %dx%d filter exceeds %d taps", kh, kw, kMaxTaps);
+    WgradArgs a;
+    memset(&a, 0, sizeof(a));
+    int OH, OW, pbh, pbw;
+    tf_same(H, kh, stride, OH, pbh);
+    tf_same(W, kw, stride, OW, pbw);
+    a.x = x; a.xB = B; a.xH = H; a.xW = W; a.cx = Cx;
+    a.dz = dz; a.zB = B; a.zH = OH; a.zW = OW; a.cz = Cz;
+    a.num_taps = kh * kw; a.in_mul = stride;
+    for (int ky = 0; ky < kh; ++ky)
+        for (int kx = 0; kx < kw; ++kx) {
+            const int t = ky * kw + kx;
+            a.dy[t] = int8_t(ky - pbh);
+            a.dx[t] = int8_t(kx - pbw);
+            a.wtap[t] = int16_t(t);
+        }
+    a.dw = dw;
+    a.f16 = f16;
+    return launch_conv_wgrad(a, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int b2_conv2d_rows_fprop(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw,
@@ -122,20 +171,17 @@ int b2_conv2d_rows_fprop(const void* x, int B, int H, int W, int Cin, const void
 int b2_conv2d_direct(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw, int stride,
                      int transposed, const b2_epilogue* ep, void* stream) {
     if (!x || !w || !ep || !ep->out) return set_error("b2_conv2d_direct: null pointer");
-    for (int ph = 0; ph < (transposed ? 4 : 1); ++ph) {
-        ConvIgemmArgs a;
-        memset(&a, 0, sizeof(a));
-        if (transposed) convT_phase_taps(a.p, B, H, W, Cin, kh, kw, ph >> 1, ph & 1);
-        else if (conv_taps(a.p, B, H, W, Cin, kh, kw, stride)) return -1;
-        fill_epilogue(a.p, ep, Cout);
-        a.x = reinterpret_cast<const __nv_bfloat16*>(x);
-        a.xB = B; a.xH = H; a.xW = W; a.xC = Cin;
-        a.w = reinterpret_cast<const __nv_bfloat16*>(w);
-        a.w_rows = Cout; a.w_k = kh * kw * Cin;
-        int rc = launch_conv_direct(a, reinterpret_cast<cudaStream_t>(stream));
-        if (rc) return rc;
-    }
-    return 0;
+    if (transposed)
+        return run_transposed(x, B, H, W, Cin, w, Cout, kh, kw, 2 * H, 2 * W, (kh - 2) / 2, (kw - 2) / 2, ep, stream, true);
+    ConvIgemmArgs a;
+    memset(&a, 0, sizeof(a));
+    if (conv_taps(a.p, B, H, W, Cin, kh, kw, stride)) return -1;
+    fill_epilogue(a.p, ep, Cout);
+    a.x = reinterpret_cast<const __nv_bfloat16*>(x);
+    a.xB = B; a.xH = H; a.xW = W; a.xC = Cin;
+    a.w = reinterpret_cast<const __nv_bfloat16*>(w);
+    a.w_rows = Cout; a.w_k = kh * kw * Cin;
+    return launch_conv_direct(a, reinterpret_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -46,6 +46,11 @@ __global__ void conv_direct_kernel(const __nv_bfloat16* __restrict__ x, int xB, 
         float v = direct_act(fmaf(acc, sc, sh), p.act, p.leaky, al);
         const size_t pix = (size_t(gb) * p.OH + size_t(gy * p.out_sy + p.out_oy)) * p.OW + size_t(gx * p.out_sx + p.out_ox);
         const size_t o = pix * size_t(p.out_ld) + n;
+        if (p.gate) {
+            const float gv = p.f16 ? __half2float(reinterpret_cast<const __half*>(p.gate)[o])
+                                   : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.gate)[o]);
+            if (!(gv > 0.f)) v *= p.gate_slope;
+        }
         if (p.residual)
             v += p.f16 ? __half2float(reinterpret_cast<const __half*>(p.residual)[o]) : __bfloat162float(p.residual[o]);
         if (p.out_fp32) reinterpret_cast<float*>(p.out)[o] = v;

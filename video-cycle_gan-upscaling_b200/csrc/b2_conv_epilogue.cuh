@@ -6,7 +6,7 @@
 
 namespace b2 {
 
-constexpr int kMaxChan = 512;  // widest layer on the path (VGG19 block4/5, discriminator)
+constexpr int kMaxChan = 1024;  // widest layer on the path (discriminator Dense_1, model.py:876)
 
 // 16-bit element helpers: the storage type is bf16 or IEEE fp16, chosen per launch (IgemmParams::f16).
 __device__ __forceinline__ uint32_t pack2(float a, float b, int f16) {
@@ -77,6 +77,21 @@ __device__ __forceinline__ void epilogue_tile(const IgemmParams& p, uint32_t tad
         }
         const bool vec = (!p.out_fp32) && ((p.out_ld & 7) == 0) && (n0 + c0 + CH <= p.n_valid);
         if (vec) {
+            if (p.gate) {
+                const uint4* gp = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.gate) + obase + c0);
+                uint4 gv[CH / 8];
+#pragma unroll
+                for (int g = 0; g < CH / 8; ++g) gv[g] = __ldg(gp + g);
+#pragma unroll
+                for (int g = 0; g < CH / 8; ++g) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float2 f = unpack2(reinterpret_cast<const uint32_t*>(&gv[g])[e], p.f16);
+                        if (!(f.x > 0.f)) v[g * 8 + 2 * e] *= p.gate_slope;
+                        if (!(f.y > 0.f)) v[g * 8 + 2 * e + 1] *= p.gate_slope;
+                    }
+                }
+            }
             if (p.residual) {
                 const uint4* rp = reinterpret_cast<const uint4*>(p.residual + obase + c0);
                 uint4 rv[CH / 8];
@@ -107,6 +122,7 @@ __device__ __forceinline__ void epilogue_tile(const IgemmParams& p, uint32_t tad
                 const int c = n0 + c0 + j;
                 if (c < p.n_valid) {
                     float o = v[j];
+                    if (p.gate && !(load1(p.gate, obase + c0 + j, p.f16) > 0.f)) o *= p.gate_slope;
                     if (p.residual) o += load1(p.residual, obase + c0 + j, p.f16);
                     if (p.out_fp32) reinterpret_cast<float*>(p.out)[obase + c0 + j] = o;
                     else store1(p.out, obase + c0 + j, o, p.f16);

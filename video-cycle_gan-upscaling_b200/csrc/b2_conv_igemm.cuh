@@ -35,6 +35,8 @@ struct IgemmParams {
     const float* shift;  // per output channel, may be null (=0)
     const float* alpha;  // PReLU slope per channel (act == ACT_PRELU)
     const __nv_bfloat16* residual;  // added after the activation; same geometry as out; may be null
+    const void* gate;     // backward of ReLU / LeakyReLU fused into a dgrad: value *= (gate > 0 ? 1 : gate_slope); same
+    float gate_slope;     //   geometry and element type as out's 16-bit form; may be null
     void* out;
     int out_fp32;  // 1: out is float, 0: out is the 16-bit element type
     int f16;       // 16-bit element type of x / w / residual / out: 0 = bf16, 1 = fp16 (IEEE half)

@@ -37,6 +37,20 @@ int launch_conv_direct(const ConvIgemmArgs& a, cudaStream_t stream);
 bool conv_halo_applicable(const ConvIgemmArgs& a);
 int launch_conv_halo(const ConvIgemmArgs& a, cudaStream_t stream);
 
+// Weight gradient (b2_conv_wgrad.cu): dw[wtap[t]][cx][cz] += sum_p x[p*in_mul + d(t), cx] * dz[p, cz], fp32 accumulate.
+struct WgradArgs {
+    const void* x;   // [xB, xH, xW, cx] 16-bit
+    int xB, xH, xW, cx;
+    const void* dz;  // [zB, zH, zW, cz] 16-bit
+    int zB, zH, zW, cz;
+    int num_taps, in_mul;
+    int8_t dy[kMaxTaps], dx[kMaxTaps];
+    int16_t wtap[kMaxTaps];
+    float* dw;
+    int f16;
+};
+int launch_conv_wgrad(const WgradArgs& a, cudaStream_t stream);
+
 // Final 9xKW conv with Cout=3 as a row-streaming kernel (b2_conv_tail.cu).
 int launch_conv_tail(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int KH, int KW,
                      const float* bias, int act, int f16, float* out, cudaStream_t stream);

@@ -27,8 +27,12 @@ class Epilogue(ctypes.Structure):
         ("out", ctypes.c_void_p),
         ("out_fp32", ctypes.c_int),
         ("f16", ctypes.c_int),
+        ("gate", ctypes.c_void_p),
+        ("gate_slope", ctypes.c_float),
     ]
 
+
+_P, _I, _L, _F = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float
 
 _SIGNATURES = {
     "b2_last_error": (ctypes.c_char_p, []),
@@ -45,6 +49,23 @@ _SIGNATURES = {
                      [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]),
     "b2_gather_cast": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int,
                                       ctypes.c_void_p]),
+    # ---- training step
+    "b2_conv2d_s2_dgrad": (ctypes.c_int, [_P] + [_I] * 4 + [_P] + [_I] * 5 + [ctypes.POINTER(Epilogue), _P]),
+    "b2_conv2d_wgrad": (ctypes.c_int, [_P] + [_I] * 4 + [_P] + [_I] * 4 + [_P, _I, _P]),
+    "b2_colstats": (ctypes.c_int, [_P, _L, _I, _I, _P, _P, _P]),
+    "b2_bn_finalize": (ctypes.c_int, [_P, _P, _F, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _I, _P]),
+    "b2_bn_fold": (ctypes.c_int, [_P, _P, _P, _P, _P, _F, _P, _P, _I, _P]),
+    "b2_affine_act": (ctypes.c_int, [_P, _L, _I, _I, _P, _P, _P, _I, _F, _P, _P, _P]),
+    "b2_bn_bwd_reduce": (ctypes.c_int, [_P, _P, _L, _I, _I, _P, _P, _P, _I, _F, _P, _P, _P, _P, _P, _P]),
+    "b2_bn_bwd_apply": (ctypes.c_int, [_P, _P, _L, _I, _I, _P, _P, _P, _I, _F, _P, _P, _P, _P, _F, _P, _P]),
+    "b2_maxpool2x2": (ctypes.c_int, [_P, _I, _I, _I, _I, _I, _P, _P]),
+    "b2_maxpool2x2_bwd": (ctypes.c_int, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
+    "b2_loss_pair": (ctypes.c_int, [_P, _P, _L, _I, _I, _F, _F, _P, _P, _P]),
+    "b2_mean_prod": (ctypes.c_int, [_P, _P, _F, _L, _F, _F, _P, _P, _P]),
+    "b2_tanh_bwd": (ctypes.c_int, [_P, _P, _P, _P, _L, _P, _P]),
+    "b2_gather_f32": (ctypes.c_int, [_P, _P, _L, _P, _I, _P]),
+    "b2_cast_scale": (ctypes.c_int, [_P, _I, _L, _F, _P, _I, _P]),
+    "b2_adam": (ctypes.c_int, [_P, _P, _P, _P, _L, _F, _F, _F, _F, _F, _P]),
 }
 
 
@@ -92,7 +113,8 @@ def stream_ptr():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
-def make_epilogue(out, scale=None, shift=None, alpha=None, act=ACT_NONE, leaky=0.0, residual=None, f16=0):
+def make_epilogue(out, scale=None, shift=None, alpha=None, act=ACT_NONE, leaky=0.0, residual=None, f16=0, gate=None,
+                  gate_slope=0.0):
     import torch
     ep = Epilogue()
     ep.scale = scale.data_ptr() if scale is not None else None
@@ -104,4 +126,6 @@ def make_epilogue(out, scale=None, shift=None, alpha=None, act=ACT_NONE, leaky=0
     ep.out = out.data_ptr()
     ep.out_fp32 = 1 if out.dtype == torch.float32 else 0
     ep.f16 = int(f16)
+    ep.gate = gate.data_ptr() if gate is not None else None
+    ep.gate_slope = gate_slope
     return ep

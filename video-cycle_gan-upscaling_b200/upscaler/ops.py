@@ -47,7 +47,7 @@ def tf_same_out(size, stride):
 
 
 def conv2d(x, w_packed, cout, kh, kw, stride=1, out=None, out_dtype=None, scale=None, shift=None, alpha=None,
-           act=ACT_NONE, leaky=0.0, residual=None, direct=False):
+           act=ACT_NONE, leaky=0.0, residual=None, direct=False, gate=None, gate_slope=0.0):
     """Conv2D(padding='same') forward (reference: keras Conv2D at model.py:19, 22, 275, 283, 290, 839-871)."""
     B, H, W, Cin = x.shape
     OH, OW = tf_same_out(H, stride), tf_same_out(W, stride)
@@ -64,8 +64,10 @@ def conv2d(x, w_packed, cout, kh, kw, stride=1, out=None, out_dtype=None, scale=
         raise ValueError("conv2d: output must be float32 or the activation dtype")
     if residual is not None and (tuple(residual.shape) != tuple(out.shape) or residual.dtype != x.dtype):
         raise ValueError("conv2d: residual must have the activation dtype and the output's shape")
-    _require_cuda(x, w_packed, out, scale, shift, alpha, residual)
-    ep = _lib.make_epilogue(out, scale, shift, alpha, act, leaky, residual, f16)
+    if gate is not None and (tuple(gate.shape) != tuple(out.shape) or gate.dtype != x.dtype):
+        raise ValueError("conv2d: gate must have the activation dtype and the output's shape")
+    _require_cuda(x, w_packed, out, scale, shift, alpha, residual, gate)
+    ep = _lib.make_epilogue(out, scale, shift, alpha, act, leaky, residual, f16, gate, gate_slope)
     lib = _lib.load()
     if direct:
         rc = lib.b2_conv2d_direct(_lib.ptr(x), B, H, W, Cin, _lib.ptr(w_packed), cout, kh, kw, stride, 0,
@@ -161,7 +163,206 @@ def gather_cast(src, idx, out=None, dtype=torch.bfloat16):
     return out
 
 
+# ------------------------------------------------------------------------------------------------ training step
+def _dt(t):
+    return {torch.bfloat16: 0, torch.float16: 1, torch.float32: 2}[t.dtype]
+
+
+def _rows_c(t):
+    return t.numel() // t.shape[-1], t.shape[-1]
+
+
+def conv2d_s2_dgrad(dz, w_packed_t, cin, kh, kw, in_hw, out=None, gate=None, gate_slope=0.0, residual=None):
+    """Data gradient of Conv2D(strides=2, 'same') (discriminator blocks, model.py:843-871): dz (B,OH,OW,Cout) ->
+    (B,H,W,Cin); `w_packed_t` from conv_s2_dgrad_pack_index."""
+    B, OH, OW, Cout = dz.shape
+    H, W = in_hw
+    f16 = _elem_flag(dz, w_packed_t)
+    if out is None:
+        out = torch.empty((B, H, W, cin), dtype=dz.dtype, device=dz.device)
+    _require_cuda(dz, w_packed_t, out, gate, residual)
+    ep = _lib.make_epilogue(out, None, None, None, ACT_NONE, 0.0, residual, f16, gate, gate_slope)
+    rc = _lib.load().b2_conv2d_s2_dgrad(_lib.ptr(dz), B, OH, OW, Cout, _lib.ptr(w_packed_t), cin, kh, kw, H, W,
+                                        ctypes.byref(ep), _lib.stream_ptr())
+    _lib.check(rc, "b2_conv2d_s2_dgrad")
+    _count(4)
+    return out
+
+
+def conv2d_wgrad(x, dz, kh, kw, stride, dw):
+    """dw (kh,kw,Cx,Cz) fp32 += sum_p x[p*stride + tap - pad] (x) dz[p]  (Conv2D: x = input, dz = output gradient;
+    Conv2DTranspose: x = output gradient, dz = input, stride 2)."""
+    B, H, W, Cx = x.shape
+    Cz = dz.shape[-1]
+    if x.dtype != dz.dtype or x.dtype not in (torch.bfloat16, torch.float16):
+        raise ValueError("conv2d_wgrad: x and dz must share a 16-bit dtype")
+    if tuple(dz.shape[:3]) != (B, tf_same_out(H, stride), tf_same_out(W, stride)):
+        raise ValueError("conv2d_wgrad: dz %s is not the stride-%d SAME output grid of x %s" % (tuple(dz.shape), stride, tuple(x.shape)))
+    if dw.dtype != torch.float32 or dw.numel() != kh * kw * Cx * Cz:
+        raise ValueError("conv2d_wgrad: dw must be float32 with %d elements" % (kh * kw * Cx * Cz))
+    _require_cuda(x, dz, dw)
+    rc = _lib.load().b2_conv2d_wgrad(_lib.ptr(x), B, H, W, Cx, _lib.ptr(dz), Cz, kh, kw, stride, _lib.ptr(dw),
+                                     1 if x.dtype == torch.float16 else 0, _lib.stream_ptr())
+    _lib.check(rc, "b2_conv2d_wgrad")
+    _count(1)
+    return dw
+
+
+def colstats(x, ssum, ssq=None):
+    rows, C = _rows_c(x)
+    _require_cuda(x, ssum, ssq)
+    rc = _lib.load().b2_colstats(_lib.ptr(x), rows, C, _dt(x), _lib.ptr(ssum), _lib.ptr(ssq), _lib.stream_ptr())
+    _lib.check(rc, "b2_colstats")
+    _count(1)
+
+
+def bn_finalize(ssum, ssq, count, gamma, beta, scale, shift, mean=None, invstd=None, moving_mean=None, moving_var=None,
+                eps=1e-3, momentum=0.99):
+    rc = _lib.load().b2_bn_finalize(_lib.ptr(ssum), _lib.ptr(ssq), float(count), _lib.ptr(gamma), _lib.ptr(beta), eps, momentum,
+                                    _lib.ptr(moving_mean), _lib.ptr(moving_var), _lib.ptr(scale), _lib.ptr(shift),
+                                    _lib.ptr(mean), _lib.ptr(invstd), gamma.numel(), _lib.stream_ptr())
+    _lib.check(rc, "b2_bn_finalize")
+    _count(1)
+
+
+def bn_fold(gamma, beta, mean, var, bias, scale, shift, eps=1e-3):
+    rc = _lib.load().b2_bn_fold(_lib.ptr(gamma), _lib.ptr(beta), _lib.ptr(mean), _lib.ptr(var), _lib.ptr(bias), eps,
+                                _lib.ptr(scale), _lib.ptr(shift), gamma.numel(), _lib.stream_ptr())
+    _lib.check(rc, "b2_bn_fold")
+    _count(1)
+
+
+def affine_act(z, out, scale=None, shift=None, alpha=None, act=ACT_NONE, leaky=0.0, residual=None):
+    rows, C = _rows_c(z)
+    _require_cuda(z, out, residual)
+    rc = _lib.load().b2_affine_act(_lib.ptr(z), rows, C, _dt(z), _lib.ptr(scale), _lib.ptr(shift), _lib.ptr(alpha), act, leaky,
+                                   _lib.ptr(residual), _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(rc, "b2_affine_act")
+    _count(1)
+    return out
+
+
+def bn_bwd_reduce(z, g, scale, shift, alpha, act, leaky, mean, invstd, s1, s2, dalpha=None):
+    rows, C = _rows_c(z)
+    _require_cuda(z, g)
+    rc = _lib.load().b2_bn_bwd_reduce(_lib.ptr(z), _lib.ptr(g), rows, C, _dt(z), _lib.ptr(scale), _lib.ptr(shift),
+                                      _lib.ptr(alpha), act, leaky, _lib.ptr(mean), _lib.ptr(invstd), _lib.ptr(s1), _lib.ptr(s2),
+                                      _lib.ptr(dalpha), _lib.stream_ptr())
+    _lib.check(rc, "b2_bn_bwd_reduce")
+    _count(1)
+
+
+def bn_bwd_apply(z, g, scale, shift, alpha, act, leaky, mean, invstd, s1, s2, count, dz):
+    rows, C = _rows_c(z)
+    _require_cuda(z, g, dz)
+    rc = _lib.load().b2_bn_bwd_apply(_lib.ptr(z), _lib.ptr(g), rows, C, _dt(z), _lib.ptr(scale), _lib.ptr(shift), _lib.ptr(alpha),
+                                     act, leaky, _lib.ptr(mean), _lib.ptr(invstd), _lib.ptr(s1), _lib.ptr(s2), float(count),
+                                     _lib.ptr(dz), _lib.stream_ptr())
+    _lib.check(rc, "b2_bn_bwd_apply")
+    _count(1)
+    return dz
+
+
+def maxpool2x2(x, out=None):
+    B, H, W, C = x.shape
+    if out is None:
+        out = torch.empty((B, H // 2, W // 2, C), dtype=x.dtype, device=x.device)
+    _require_cuda(x, out)
+    rc = _lib.load().b2_maxpool2x2(_lib.ptr(x), B, H, W, C, _dt(x), _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(rc, "b2_maxpool2x2")
+    _count(1)
+    return out
+
+
+def maxpool2x2_bwd(x, y, dy, relu_gate=False, out=None):
+    B, H, W, C = x.shape
+    if out is None:
+        out = torch.empty_like(x)
+    _require_cuda(x, y, dy, out)
+    rc = _lib.load().b2_maxpool2x2_bwd(_lib.ptr(x), _lib.ptr(y), _lib.ptr(dy), B, H, W, C, _dt(x), 1 if relu_gate else 0,
+                                       _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(rc, "b2_maxpool2x2_bwd")
+    _count(1)
+    return out
+
+
+def loss_pair(a, b, loss, mae=False, weight=1.0, gscale=1.0, grad=None):
+    """loss (1-element fp32 tensor) += weight * mean(f(a-b)); grad = gscale * f'(a-b)/n (same dtype as a)."""
+    if a.dtype != b.dtype or a.numel() != b.numel():
+        raise ValueError("loss_pair: operands must match")
+    _require_cuda(a, b, loss, grad)
+    rc = _lib.load().b2_loss_pair(_lib.ptr(a), _lib.ptr(b), a.numel(), _dt(a), 1 if mae else 0, weight, gscale, _lib.ptr(loss),
+                                  _lib.ptr(grad), _lib.stream_ptr())
+    _lib.check(rc, "b2_loss_pair")
+    _count(1)
+
+
+def mean_prod(x, y, loss, weight=1.0, gscale=1.0, grad=None, yconst=1.0):
+    rc = _lib.load().b2_mean_prod(_lib.ptr(x), _lib.ptr(y), yconst, x.numel(), weight, gscale, _lib.ptr(loss), _lib.ptr(grad),
+                                  _lib.stream_ptr())
+    _lib.check(rc, "b2_mean_prod")
+    _count(1)
+
+
+def tanh_bwd(y, g1, dz, g2=None, g3=None):
+    rc = _lib.load().b2_tanh_bwd(_lib.ptr(y), _lib.ptr(g1), _lib.ptr(g2), _lib.ptr(g3), y.numel(), _lib.ptr(dz), _lib.stream_ptr())
+    _lib.check(rc, "b2_tanh_bwd")
+    _count(1)
+    return dz
+
+
+def gather_f32(src, idx, out, accumulate=False):
+    rc = _lib.load().b2_gather_f32(_lib.ptr(src), _lib.ptr(idx), idx.numel(), _lib.ptr(out), 1 if accumulate else 0,
+                                   _lib.stream_ptr())
+    _lib.check(rc, "b2_gather_f32")
+    _count(1)
+    return out
+
+
+def cast_scale(x, out, scale=1.0):
+    rc = _lib.load().b2_cast_scale(_lib.ptr(x), _dt(x), x.numel(), scale, _lib.ptr(out), _dt(out), _lib.stream_ptr())
+    _lib.check(rc, "b2_cast_scale")
+    _count(1)
+    return out
+
+
+def adam(params, grads, m, v, lr_t, beta1, beta2, eps, gscale=1.0):
+    rc = _lib.load().b2_adam(_lib.ptr(params), _lib.ptr(grads), _lib.ptr(m), _lib.ptr(v), params.numel(), lr_t, beta1, beta2, eps,
+                             gscale, _lib.stream_ptr())
+    _lib.check(rc, "b2_adam")
+    _count(1)
+
+
 # ------------------------------------------------------------------------------------------------ packing index maps
+def conv_dgrad_pack_index(kh, kw, cin, cout):
+    """Keras Conv2D kernel (kh,kw,Cin,Cout) -> packed [Cin][kh*kw (flipped)][Cout]: the stride-1 data gradient
+    dX = conv(dZ, flip(W)^T) runs through conv2d with this weight."""
+    T = kh * kw
+    t = np.arange(T)
+    tf = (kh - 1 - t // kw) * kw + (kw - 1 - t % kw)
+    ci = np.arange(cin)[:, None, None]
+    co = np.arange(cout)[None, None, :]
+    return ((tf[None, :, None] * cin + ci) * cout + co).astype(np.int32)
+
+
+def conv_s2_dgrad_pack_index(kh, kw, cin, cout):
+    """Keras Conv2D kernel (kh,kw,Cin,Cout) -> packed [Cin][kh*kw][Cout] (taps NOT flipped) for conv2d_s2_dgrad."""
+    t = np.arange(kh * kw)[None, :, None]
+    ci = np.arange(cin)[:, None, None]
+    co = np.arange(cout)[None, None, :]
+    return ((t * cin + ci) * cout + co).astype(np.int32)
+
+
+def convT_dgrad_pack_index(kh, kw, cin, cout):
+    """Keras Conv2DTranspose kernel (kh,kw,Cout,Cin) -> packed [Cin][kh*kw][Cout]: the data gradient of
+    Conv2DTranspose(stride 2) is a stride-2 'same' conv2d of the output gradient with this weight."""
+    t = np.arange(kh * kw)[None, :, None]
+    ci = np.arange(cin)[:, None, None]
+    co = np.arange(cout)[None, None, :]
+    return ((t * cout + co) * cin + ci).astype(np.int32)
+
+
+
 def conv_pack_index(kh, kw, cin, cout, cin_pad=None):
     """Keras Conv2D kernel (kh,kw,Cin,Cout) -> packed [Cout][kh*kw][cin_pad] index map (int32, -1 = zero)."""
     cp = cin_pad or cin
