@@ -81,9 +81,11 @@ int b2_conv2d_direct(const void* x, int B, int H, int W, int Cin, const void* w,
 /* Gathers `ntaps` shifted copies of a narrow NHWC tensor into the channels of a 64-channel bf16 tensor so that a
  * small-Cin convolution (Cin=3 head conv model.py:275, VGG19 block1_conv1, discriminator block_1) becomes a
  * 64-channel one:  out[b,y,x, t*Cin + c] = in[b, y*stride + dy[t], x*stride + dx[t], c]  (0 outside the image),
- * channels >= ntaps*Cin are zero.  `in` is float when in_fp32 != 0, else bf16.  out: [B,OH,OW,64]. */
+ * channels >= ntaps*Cin are zero.  `in` is float when in_fp32 != 0, else bf16.  out: [B,OH,OW,out_ld] with the 64 folded
+ * channels written at channel offset out_c0 (out_ld = 64, out_c0 = 0 for a dense result; the backward of the final
+ * 9x9 conv, model.py:290, gathers its 81 taps into four 64-channel groups of one 256-channel tensor). */
 int b2_fold_taps(const void* in, int in_fp32, int B, int H, int W, int Cin, int OH, int OW, int stride, int ntaps,
-                 const int* dy, const int* dx, void* out, int f16, void* stream);
+                 const int* dy, const int* dx, void* out, int f16, int out_ld, int out_c0, void* stream);
 
 /* Weight (re)packing: out[i] = idx[i] >= 0 ? half_or_bf16(src[idx[i]]) : 0.  The index map is built once per layer on the
  * host (Keras kernel layout (kh,kw,Cin,Cout) / (kh,kw,Cout,Cin) -> packed [Cout][tap*Cin_pad + c], its dgrad
@@ -163,6 +165,21 @@ int b2_mean_prod(const float* x, const float* y, float yconst, int64_t n, float 
 
 /* Backward of the generator's final tanh (model.py:291): dz = (g1 + g2 + g3) * (1 - y*y); g2, g3 may be null. fp32. */
 int b2_tanh_bwd(const float* y, const float* g1, const float* g2, const float* g3, int64_t n, float* dz, void* stream);
+
+/* sum[c] += sum over rows of x[rows][C], fp32, C <= 8 (bias gradient of the 3-channel final conv, model.py:290). */
+int b2_colsum_f32(const float* x, int64_t rows, int C, float* sum, void* stream);
+
+/* Dense layers of the discriminator head (model.py:876-884; batch-sized M, negligible FLOPs) on CUDA cores, reading
+ * the fp32 master weights in Keras layout W[K][N] directly.  x / dy / dx / out are 16-bit unless the dtype code
+ * (0 bf16, 1 fp16, 2 fp32) says otherwise.
+ *   fwd:        out[n][o] = sum_i x[n][i] W[i][o] + b[o]
+ *   bwd_data:   dx[n][i]  = sum_o dy[n][o] W[i][o]
+ *   bwd_weight: dW[i][o] += sum_n x[n][i] dy[n][o];  db[o] += sum_n dy[n][o] */
+int b2_dense_fwd(const void* x, int x_dtype, int n, int K, int N, const float* W, const float* b, void* out, int out_dtype,
+                 void* stream);
+int b2_dense_bwd_data(const void* dy, int dy_dtype, int n, int K, int N, const float* W, void* dx, int dx_dtype, void* stream);
+int b2_dense_bwd_weight(const void* x, int x_dtype, const void* dy, int dy_dtype, int n, int K, int N, float* dW, float* db,
+                        void* stream);
 
 /* out[i] (+)= idx[i] >= 0 ? src[idx[i]] : 0 in fp32 (weight gradients of tap-folded layers back to the Keras layout). */
 int b2_gather_f32(const float* src, const int32_t* idx, int64_t n, float* out, int accumulate, void* stream);

@@ -237,15 +237,32 @@ def upscaler_bn_names(res_block_num=16):
 
 
 # ------------------------------------------------------------------------------------------------ VGG19 + losses
-def vgg19_block5_conv4(vw, x_nhwc):
-    """keras.applications VGG19(include_top=False) up to block5_conv4 (post-ReLU); raw [-1,1] input (model.py:117)."""
+def bf16_ste(x):
+    """Round to bf16 in the forward pass, identity in the backward pass (storage emulation for gradient tests)."""
+    return x + (x.to(torch.bfloat16).to(torch.float32) - x).detach()
+
+
+def f16_ste(x):
+    """Round to IEEE fp16 in the forward pass, identity in the backward pass."""
+    return x + (x.to(torch.float16).to(torch.float32) - x).detach()
+
+
+def vgg19_block5_conv4(vw, x_nhwc, q=None):
+    """keras.applications VGG19(include_top=False) up to block5_conv4 (post-ReLU); raw [-1,1] input (model.py:117).
+    `q` (tests only) is applied to every stored activation, e.g. bf16_ste to emulate 16-bit activation storage so that
+    ReLU gates are decided on the same rounded values as in the CUDA path."""
     x = _t(x_nhwc).permute(0, 3, 1, 2)
+    if q is not None:
+        x = q(x)
     i = 0
     for c in VGG19_CFG:
         if c == "M":
             x = F.max_pool2d(x, 2, 2)
         else:
-            x = F.relu(conv2d_same(x, *vw[VGG19_NAMES[i]]))
+            k, b = vw[VGG19_NAMES[i]]
+            x = F.relu(conv2d_same(x, q(k) if q is not None else k, b))
+            if q is not None:
+                x = q(x)
             i += 1
     return x.permute(0, 2, 3, 1)
 

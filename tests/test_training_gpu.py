@@ -1,0 +1,208 @@
+"""-m gpu parity of the training step (BASELINE.json configs 3-4) against the fp32 CPU oracle's GeneratorTrainer /
+GanTrainer (oracle/srgan_oracle.py, PyTorch autograd over TensorFlow-semantics layers).
+
+The CUDA path stores activations, gradients and packed weights as bf16 (fp32 accumulation, fp32 master weights, fp32
+BatchNorm statistics and Adam).  Tolerances, and why:
+  * forward quantities (feature maps, generated images, losses): relative L2 error <= 3e-2, losses within 1 %
+    (north_star: "loss curves within 1 %") — checked at every one of 200 steps with both sides stepping from the same
+    weights (teacher forcing);
+  * gradients: ReLU / PReLU / LeakyReLU gates are decided on bf16-rounded activations, so ~0.3-0.6 % of the gates
+    differ from the fp32 oracle's and each flipped gate changes its element's gradient by O(1): relative L2 error of a
+    gradient tensor is ~sqrt(flipped fraction) = 5-15 % while its norm agrees to ~1 % and its direction to cos > 0.98.
+    That is intrinsic to 16-bit activation storage, not to this implementation (tools/debug_vgg_grad.py shows the error
+    entering exactly at the gated layers); the bars below are norm ratio within 5 %, cosine >= 0.98;
+  * free-running 200-step trajectories: Adam's first updates have magnitude lr for every weight regardless of the
+    gradient's size, so the trajectory is chaotic — the fp32 oracle itself, re-run with 10 % relative gradient noise or
+    merely on a different CPU (summation order), moves its 20-step loss windows by up to 25-45 % at the reference's
+    lr = 1e-3 (measured).  The free-running check therefore only asserts the same training behaviour
+    (monotone decrease to a comparable level); the 1 % bar is enforced by the teacher-forced test.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import srgan_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(got, ref):
+    got, ref = np.asarray(got, np.float64), np.asarray(ref, np.float64)
+    return float(np.linalg.norm(got - ref) / max(np.linalg.norm(ref), 1e-30))
+
+
+def _data(B, lr, seed=0):
+    rng = np.random.default_rng(seed)
+    hr = rng.uniform(-1, 1, (B, 4 * lr, 4 * lr, 3)).astype(np.float32)
+    # smooth the HR image a little so the content loss is not pure noise; LR = 4x4 box mean
+    hr = (hr + np.roll(hr, 1, 1) + np.roll(hr, 1, 2) + np.roll(hr, (1, 1), (1, 2))) / 4
+    x = hr.reshape(B, lr, 4, lr, 4, 3).mean(axis=(2, 4)).astype(np.float32)
+    return x, hr.astype(np.float32)
+
+
+def test_vgg19_forward_and_image_gradient():
+    from upscaler.networks import Vgg19Net
+    from upscaler import ops
+    vw = O.init_vgg19_weights()
+    rng = np.random.default_rng(1)
+    x = rng.uniform(-1, 1, (2, 64, 48, 3)).astype(np.float32)
+    target = rng.uniform(0, 1, (2, 4, 3, 512)).astype(np.float32)
+    # The gradient of a ReLU network is discontinuous in the gate decisions: with bf16 activation storage ~0.3 % of the
+    # gates per layer flip relative to fp32, which alone moves the image gradient by ~25 % in L2 (measured) although the
+    # function value moves by < 1 %.  So the gradient is checked against the oracle with bf16 storage emulated
+    # (same gates), and the features against the plain fp32 oracle.
+    xt = torch.from_numpy(x).requires_grad_(True)
+    fq = O.vgg19_block5_conv4(O.to_torch(vw), xt, q=O.f16_ste)
+    loss = torch.mean((fq - torch.from_numpy(target).to(torch.float16).float()) ** 2)
+    loss.backward()
+    with torch.no_grad():
+        f = O.vgg19_block5_conv4(O.to_torch(vw), torch.from_numpy(x))
+    net = Vgg19Net(weights=vw)
+    fp, acts = net.forward(torch.from_numpy(x).cuda(), save=True)
+    ft = torch.from_numpy(target).cuda().to(torch.float16)
+    buf = torch.zeros(1, device="cuda")
+    dfeat = torch.empty_like(fp)
+    S = float(fp.numel())
+    ops.loss_pair(fp, ft, buf, gscale=S, grad=dfeat)
+    dimg = net.backward(acts, dfeat, S)
+    torch.cuda.synchronize()
+    assert fp.shape == (2, 4, 3, 512)
+    r = _rel(fp.float().cpu().numpy(), f.detach().numpy())
+    rg = _rel(dimg.cpu().numpy(), xt.grad.numpy())
+    print("vgg features rel err %.4f, image gradient rel err %.4f, loss %.5f vs %.5f" % (r, rg, float(buf), float(loss)))
+    assert r < 5e-3 and rg < 1e-1      # fp16 storage: features 0.1 %, gradient = residual gate flips (module docstring)
+    assert abs(float(buf) - float(loss)) <= 1e-2 * abs(float(loss))
+
+
+@pytest.mark.parametrize("ks", [3, 5])
+def test_generator_train_forward_backward(ks):
+    """forward_train output and every weight gradient of the generator vs autograd, pixel-MSE-like upstream gradient."""
+    from upscaler.networks import UpscalerOrigNet
+    from upscaler import ops
+    rbn = 2
+    gw = O.init_upscaler_orig_weights(seed=5, kernel_size=ks, res_block_num=rbn)
+    x, hr = _data(2, 12, seed=ks)
+    w = O.to_torch(gw, requires_grad=True)
+    y = O.upscaler_orig_forward(w, x, True, [], 4, rbn)
+    up = torch.from_numpy(hr)
+    loss = torch.mean((y - up) ** 2)
+    loss.backward()
+    net = UpscalerOrigNet(kernel_size=ks, res_block_num=rbn, weights=gw)
+    net.refresh(("train",))
+    yd, tape = net.forward_train(torch.from_numpy(x).cuda())
+    buf = torch.zeros(1, device="cuda")
+    gpix = torch.empty_like(yd)
+    ops.loss_pair(yd, torch.from_numpy(hr).cuda(), buf, grad=gpix)
+    dz = ops.tanh_bwd(yd, gpix, torch.empty_like(yd))
+    net.ensure_grads().zero_()
+    net.backward(tape, dz)
+    torch.cuda.synchronize()
+    r = _rel(yd.cpu().numpy(), y.detach().numpy())
+    print("k=%d forward_train rel err %.4f loss %.5f vs %.5f" % (ks, r, float(buf), float(loss)))
+    assert r < 3e-2
+    assert abs(float(buf) - float(loss)) <= 1e-2 * float(loss)
+    worst, bad = 0.0, []
+    for name, kind, cfg in net.specs:
+        for j, gt in enumerate(net.grads[name]):
+            ref = w[name][j].grad
+            if ref is None:
+                continue
+            ref = ref.numpy()
+            got = gt.cpu().numpy().reshape(ref.shape)
+            if kind == "conv" and j == 1 and name not in ("initial/conv", "final/conv"):
+                # bias in front of a train-mode BatchNorm: analytically zero gradient (autograd leaves round-off)
+                assert np.abs(got).max() <= 1e-6 + 1e-3 * np.abs(ref).max() + 1e-7
+                continue
+            e = _rel(got, ref)
+            worst = max(worst, e)
+            nr = np.linalg.norm(got) / np.linalg.norm(ref)
+            cos = float(np.vdot(got, ref) / (np.linalg.norm(got) * np.linalg.norm(ref)))
+            print("   grad %-40s[%d] rel err %.4f norm ratio %.4f cos %.4f" % (name, j, e, nr, cos))
+            if abs(nr - 1) > 5e-2 or cos < 0.98:
+                bad.append((name, j, e, nr, cos))
+    print("k=%d worst weight-gradient rel err %.4f" % (ks, worst))
+    assert not bad, bad
+
+
+def _gen_setup(ks, rbn, kind, rate):
+    from upscaler.model import (VGG_LOSS, VGG_MAE_LOSS, VGG_MSE_LOSS, compile_training_model, make_upscaler_orig)
+    from upscaler.keras_compat import Adam
+    gw = O.init_upscaler_orig_weights(seed=11, kernel_size=ks, res_block_num=rbn)
+    vw = O.init_vgg19_weights()
+    up = make_upscaler_orig((64, 64, 3), kernel_size=ks, res_block_num=rbn)
+    up.net.set_weights(gw)
+    loss = {"vgg": lambda: VGG_LOSS((64, 64, 3), vgg19=vw), "vgg-mse": lambda: VGG_MSE_LOSS((64, 64, 3), rate, vgg19=vw),
+            "vgg-mae": lambda: VGG_MAE_LOSS((64, 64, 3), rate, vgg19=vw)}[kind]()
+    tm = compile_training_model(up, loss.loss, optimizer=Adam())
+    ref = O.GeneratorTrainer(gw, vw, kind, rate, res_block_num=rbn)
+    _W0[kind] = {k: np.array(v[0]) for k, v in gw.items()}
+    return up, tm, ref
+
+
+_W0 = {}
+
+
+def _sync_weights(up, ref):
+    up.net.set_weights({k: [t.detach().numpy() for t in ts] for k, ts in ref.w.items()})
+
+
+@pytest.mark.parametrize("kind,rate", [("vgg-mse", 1e-3), ("vgg-mae", 1e-3), ("vgg", 0.0)])
+def test_generator_train_on_batch_first_steps(kind, rate):
+    """compile_training_model + train_on_batch (train_mini.py:232): first step's loss, the update it produces, the
+    BatchNorm moving statistics and inference through the updated weights vs the oracle trainer."""
+    up, tm, ref = _gen_setup(3, 2, kind, rate)
+    x, hr = _data(4, 16, seed=100)
+    got = tm.train_on_batch(x, hr)
+    want = ref.train_on_batch(x, hr)
+    print("%s step 0: loss %.6f vs oracle %.6f" % (kind, got, want))
+    assert abs(got - want) <= 1e-2 * abs(want)
+    # first Adam step: every weight moves by lr * sign(gradient); compare the big, well-conditioned tensors
+    for name in ("final/conv", "upscaling/1/block/conv_transp", "res_block/0/conv_post"):
+        ours = up.net.weights[name][0].cpu().numpy()
+        theirs = ref.w[name][0].detach().numpy()
+        agree = np.mean(np.sign(ours - _W0[kind][name]) == np.sign(theirs - _W0[kind][name]))
+        print("   %s: update signs agree on %.1f %% of the weights" % (name, 100 * agree))
+        assert agree > 0.9
+    mm = up.net.weights["res_block/0/batch_norm_pre"][2].cpu().numpy()
+    assert _rel(mm, ref.w["res_block/0/batch_norm_pre"][2].numpy()) < 2e-2
+    mv = up.net.weights["prefinal/batch_norm"][3].cpu().numpy()
+    assert _rel(mv, ref.w["prefinal/batch_norm"][3].numpy()) < 2e-2
+    # inference through updated weights: same weights on both sides
+    _sync_weights(up, ref)
+    x, _ = _data(1, 16, seed=7)
+    assert np.abs(up.predict(x) - ref.predict(x)).max() < 2e-2
+
+
+def test_generator_loss_curve_200_steps_teacher_forced():
+    """north_star: loss curves within 1 % over 200 synthetic steps.  Every step both sides start from the oracle's
+    current weights (and moving statistics), so the comparison is of the training-step arithmetic, not of two chaotic
+    trajectories; the oracle's own Adam trajectory supplies 200 different weight states."""
+    up, tm, ref = _gen_setup(3, 1, "vgg-mse", 1e-3)
+    got, want = [], []
+    for step in range(200):
+        x, hr = _data(2, 16, seed=1000 + step % 8)
+        _sync_weights(up, ref)
+        got.append(tm.train_on_batch(x, hr))
+        want.append(ref.train_on_batch(x, hr))
+    got, want = np.array(got), np.array(want)
+    rel = np.abs(got - want) / want
+    print("teacher-forced: max per-step rel diff %.4f, mean %.4f; loss %.4f -> %.4f" % (rel.max(), rel.mean(), want[0], want[-1]))
+    assert rel.max() <= 1e-2
+
+
+def test_generator_loss_curve_200_steps_free_running():
+    """Same 200 steps with each side following its own trajectory (see the module docstring for why this cannot be a
+    1 % comparison): both must train, to a comparable level."""
+    up, tm, ref = _gen_setup(3, 1, "vgg-mse", 1e-3)
+    got, want = [], []
+    for step in range(200):
+        x, hr = _data(2, 16, seed=1000 + step % 8)
+        got.append(tm.train_on_batch(x, hr))
+        want.append(ref.train_on_batch(x, hr))
+    got, want = np.array(got), np.array(want)
+    win_g, win_w = got.reshape(10, 20).mean(1), want.reshape(10, 20).mean(1)
+    print("loss windows ours  :", np.round(win_g, 5))
+    print("loss windows oracle:", np.round(win_w, 5))
+    assert abs(got[0] - want[0]) <= 1e-2 * want[0]
+    assert win_g[-1] < 0.5 * win_g[0] and win_w[-1] < 0.5 * win_w[0]      # both train
+    assert np.all(win_g < 1.6 * win_w) and np.all(win_g > win_w / 1.6)     # to a comparable level, all along

@@ -12,7 +12,7 @@ namespace {
 constexpr int kFoldMaxTaps = 21;  // 21 taps x 3 channels = 63 <= 64
 
 struct FoldParams {
-    int B, H, W, Cin, OH, OW, stride, ntaps, f16;
+    int B, H, W, Cin, OH, OW, stride, ntaps, f16, out_ld, out_c0;
     int dy[kFoldMaxTaps], dx[kFoldMaxTaps];
 };
 
@@ -49,7 +49,7 @@ __global__ void fold_taps_kernel(const TIn* __restrict__ in, void* __restrict__ 
 #pragma unroll
             for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
         }
-        reinterpret_cast<uint4*>(out)[idx] = o;
+        *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(out) + (size_t(idx >> 3) * p.out_ld + p.out_c0 + g * 8)) = o;
     }
 }
 
@@ -76,11 +76,13 @@ inline int grid_for(long work, int threads) {
 extern "C" {
 
 int b2_fold_taps(const void* in, int in_fp32, int B, int H, int W, int Cin, int OH, int OW, int stride, int ntaps,
-                 const int* dy, const int* dx, void* out, int f16, void* stream) {
+                 const int* dy, const int* dx, void* out, int f16, int out_ld, int out_c0, void* stream) {
     if (!in || !out || !dy || !dx) return set_error("b2_fold_taps: null pointer");
     if (ntaps < 1 || ntaps > kFoldMaxTaps || ntaps * Cin > 64) return set_error("b2_fold_taps: %d taps x %d channels do not fit 64", ntaps, Cin);
     FoldParams p;
+    if (out_ld < 64 || (out_ld & 7) || (out_c0 & 7) || out_c0 + 64 > out_ld) return set_error("b2_fold_taps: bad output pitch %d / offset %d", out_ld, out_c0);
     p.B = B; p.H = H; p.W = W; p.Cin = Cin; p.OH = OH; p.OW = OW; p.stride = stride; p.ntaps = ntaps; p.f16 = f16;
+    p.out_ld = out_ld; p.out_c0 = out_c0;
     for (int t = 0; t < ntaps; ++t) { p.dy[t] = dy[t]; p.dx[t] = dx[t]; }
     const long total = long(B) * OH * OW * 8;
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);

@@ -389,6 +389,71 @@ __global__ void tanh_bwd_kernel(const float* __restrict__ y, const float* __rest
     }
 }
 
+__global__ void __launch_bounds__(kEwThreads)
+colsum_f32_kernel(const float* __restrict__ x, long rows, int C, float* __restrict__ sum) {
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (long r = blockIdx.x * long(blockDim.x) + threadIdx.x; r < rows; r += long(gridDim.x) * blockDim.x)
+        for (int c = 0; c < C; ++c) acc[c] += x[r * C + c];
+    __shared__ float sh[8][kEwThreads / 32];
+    for (int c = 0; c < C; ++c) {
+        float v = acc[c];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) sh[c][threadIdx.x >> 5] = v;
+    }
+    __syncthreads();
+    if (int(threadIdx.x) < C) {
+        float v = 0.f;
+        for (int w = 0; w < kEwThreads / 32; ++w) v += sh[threadIdx.x][w];
+        atomicAdd(sum + threadIdx.x, v);
+    }
+}
+
+__device__ __forceinline__ float ld_any(const void* p, size_t i, int dtype) {
+    if (dtype == 2) return reinterpret_cast<const float*>(p)[i];
+    if (dtype == 1) return __half2float(reinterpret_cast<const __half*>(p)[i]);
+    return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[i]);
+}
+__device__ __forceinline__ void st_any(void* p, size_t i, int dtype, float v) {
+    if (dtype == 2) reinterpret_cast<float*>(p)[i] = v;
+    else if (dtype == 1) reinterpret_cast<__half*>(p)[i] = __float2half_rn(v);
+    else reinterpret_cast<__nv_bfloat16*>(p)[i] = __float2bfloat16_rn(v);
+}
+
+// Dense head of the discriminator: batch-sized M, so plain CUDA-core loops over the fp32 master weights.
+__global__ void dense_fwd_kernel(const void* x, int xd, int n, int K, int N, const float* __restrict__ W, const float* b,
+                                 void* out, int od) {
+    const long total = long(n) * N;
+    for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
+        const int o = int(i % N), r = int(i / N);
+        float acc = b ? b[o] : 0.f;
+        for (int k = 0; k < K; ++k) acc = fmaf(ld_any(x, size_t(r) * K + k, xd), W[size_t(k) * N + o], acc);
+        st_any(out, i, od, acc);
+    }
+}
+__global__ void dense_bwd_data_kernel(const void* dy, int yd, int n, int K, int N, const float* __restrict__ W, void* dx, int xd) {
+    const long total = long(n) * K;
+    for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
+        const int k = int(i % K), r = int(i / K);
+        float acc = 0.f;
+        for (int o = 0; o < N; ++o) acc = fmaf(ld_any(dy, size_t(r) * N + o, yd), W[size_t(k) * N + o], acc);
+        st_any(dx, i, xd, acc);
+    }
+}
+__global__ void dense_bwd_weight_kernel(const void* x, int xd, const void* dy, int yd, int n, int K, int N, float* dW, float* db) {
+    const long total = long(K) * N;
+    for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
+        const int o = int(i % N), k = int(i / N);
+        float acc = 0.f;
+        for (int r = 0; r < n; ++r) acc = fmaf(ld_any(x, size_t(r) * K + k, xd), ld_any(dy, size_t(r) * N + o, yd), acc);
+        dW[i] += acc;
+        if (k == 0 && db) {
+            float s = 0.f;
+            for (int r = 0; r < n; ++r) s += ld_any(dy, size_t(r) * N + o, yd);
+            db[o] += s;
+        }
+    }
+}
+
 // out[i] (+)= idx[i] >= 0 ? src[idx[i]] : 0   (fp32; folded-layer weight gradients back to the Keras layout)
 __global__ void gather_f32_kernel(const float* __restrict__ src, const int32_t* __restrict__ idx, long n, float* __restrict__ out,
                                   int accumulate) {
@@ -549,6 +614,31 @@ int b2_tanh_bwd(const float* y, const float* g1, const float* g2, const float* g
     if (!y || !g1 || !dz) return set_error("b2_tanh_bwd: null pointer");
     tanh_bwd_kernel<<<flat_grid(n), kEwThreads, 0, B2_STREAM>>>(y, g1, g2, g3, n, dz);
     return launch_ok("b2_tanh_bwd");
+}
+
+int b2_colsum_f32(const float* x, int64_t rows, int C, float* sum, void* stream) {
+    if (!x || !sum) return set_error("b2_colsum_f32: null pointer");
+    if (C < 1 || C > 8) return set_error("b2_colsum_f32: C=%d unsupported", C);
+    colsum_f32_kernel<<<flat_grid(rows, 2), kEwThreads, 0, B2_STREAM>>>(x, rows, C, sum);
+    return launch_ok("b2_colsum_f32");
+}
+
+int b2_dense_fwd(const void* x, int x_dtype, int n, int K, int N, const float* W, const float* b, void* out, int out_dtype,
+                 void* stream) {
+    if (!x || !W || !out) return set_error("b2_dense_fwd: null pointer");
+    dense_fwd_kernel<<<flat_grid(long(n) * N), kEwThreads, 0, B2_STREAM>>>(x, x_dtype, n, K, N, W, b, out, out_dtype);
+    return launch_ok("b2_dense_fwd");
+}
+int b2_dense_bwd_data(const void* dy, int dy_dtype, int n, int K, int N, const float* W, void* dx, int dx_dtype, void* stream) {
+    if (!dy || !W || !dx) return set_error("b2_dense_bwd_data: null pointer");
+    dense_bwd_data_kernel<<<flat_grid(long(n) * K), kEwThreads, 0, B2_STREAM>>>(dy, dy_dtype, n, K, N, W, dx, dx_dtype);
+    return launch_ok("b2_dense_bwd_data");
+}
+int b2_dense_bwd_weight(const void* x, int x_dtype, const void* dy, int dy_dtype, int n, int K, int N, float* dW, float* db,
+                        void* stream) {
+    if (!x || !dy || !dW) return set_error("b2_dense_bwd_weight: null pointer");
+    dense_bwd_weight_kernel<<<flat_grid(long(K) * N), kEwThreads, 0, B2_STREAM>>>(x, x_dtype, dy, dy_dtype, n, K, N, dW, db);
+    return launch_ok("b2_dense_bwd_weight");
 }
 
 int b2_gather_f32(const float* src, const int32_t* idx, int64_t n, float* out, int accumulate, void* stream) {

@@ -46,7 +46,7 @@ _SIGNATURES = {
     "b2_conv2d_direct": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p] + [ctypes.c_int] * 5 +
                          [ctypes.POINTER(Epilogue), ctypes.c_void_p]),
     "b2_fold_taps": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 9 + [ctypes.POINTER(ctypes.c_int)] * 2 +
-                     [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]),
+                     [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
     "b2_gather_cast": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int,
                                       ctypes.c_void_p]),
     # ---- training step
@@ -64,6 +64,10 @@ _SIGNATURES = {
     "b2_mean_prod": (ctypes.c_int, [_P, _P, _F, _L, _F, _F, _P, _P, _P]),
     "b2_tanh_bwd": (ctypes.c_int, [_P, _P, _P, _P, _L, _P, _P]),
     "b2_gather_f32": (ctypes.c_int, [_P, _P, _L, _P, _I, _P]),
+    "b2_colsum_f32": (ctypes.c_int, [_P, _L, _I, _P, _P]),
+    "b2_dense_fwd": (ctypes.c_int, [_P, _I, _I, _I, _I, _P, _P, _P, _I, _P]),
+    "b2_dense_bwd_data": (ctypes.c_int, [_P, _I, _I, _I, _I, _P, _P, _I, _P]),
+    "b2_dense_bwd_weight": (ctypes.c_int, [_P, _I, _P, _I, _I, _I, _I, _P, _P, _P]),
     "b2_cast_scale": (ctypes.c_int, [_P, _I, _L, _F, _P, _I, _P]),
     "b2_adam": (ctypes.c_int, [_P, _P, _P, _P, _L, _F, _F, _F, _F, _F, _P]),
 }

@@ -122,6 +122,15 @@ class Model:
             nets += m.leaf_nets()
         return nets
 
+    def leaf_models(self):
+        """The leaf Models (the ones that own a network) in application order."""
+        if self._is_leaf:
+            return [self]
+        out = []
+        for m in self._chain:
+            out += m.leaf_models()
+        return out
+
     @property
     def input_shape(self):
         shapes = [(None,) + tuple(i.shape) for i in self._inputs]

@@ -1,8 +1,15 @@
 """Device-side networks of the hot path, executed layer by layer through the C ABI.
 
 UpscalerOrigNet is the graph make_upscaler_orig declares (reference: upscaling/upscaler/model.py:267-295, with
-residual_block :15-27 and upsampling_block :70-75).  Weights are kept as fp32 master tensors in Keras layout under
-the reference's layer names (so .h5 files map one-to-one) plus packed bf16 copies in the kernels' layout.
+residual_block :15-27 and upsampling_block :70-75); Vgg19Net the frozen feature extractor behind the VGG losses
+(model.py:101-157); DiscriminatorSimple512Net the graph of make_discriminator_simple_512 (model.py:836-896).
+
+Memory layout: all parameters of a network live in ONE flat fp32 buffer (trainable tensors first, BatchNorm moving
+statistics last) with per-layer views in Keras layout under the reference's layer names, so that .h5 groups map
+one-to-one, the Adam update is a single launch over the flat buffer, and the data-parallel gradient all-reduce runs
+over contiguous slices of the matching flat gradient buffer.  The 16-bit packed copies the tensor-core kernels read
+(forward layouts, and flipped / transposed layouts for the data gradients) are refreshed from the masters by one
+gather launch per element type.
 """
 import math
 from collections import OrderedDict
@@ -12,7 +19,9 @@ import torch
 
 from . import ops
 
-BN_EPS = 1e-3  # keras BatchNormalization default, model.py:20
+BN_EPS = 1e-3       # keras BatchNormalization defaults, model.py:20
+BN_MOMENTUM = 0.99
+ALIGN = 64          # floats; keeps every tensor (and its gradient) 256-byte aligned inside the flat buffers
 
 
 def glorot_uniform(rng, shape, fan_in, fan_out):
@@ -42,6 +51,42 @@ def upscaler_orig_layer_specs(kernel_size=5, filters=64, upscale_factor=4, res_b
     return specs
 
 
+VGG19_CFG = [64, 64, "M", 128, 128, "M", 256, 256, 256, 256, "M", 512, 512, 512, 512, "M", 512, 512, 512, 512]
+VGG19_NAMES = ["block1_conv1", "block1_conv2", "block2_conv1", "block2_conv2", "block3_conv1", "block3_conv2",
+               "block3_conv3", "block3_conv4", "block4_conv1", "block4_conv2", "block4_conv3", "block4_conv4",
+               "block5_conv1", "block5_conv2", "block5_conv3", "block5_conv4"]
+
+
+def vgg19_layer_specs():
+    specs, cin, i = [], 3, 0
+    for c in VGG19_CFG:
+        if c == "M":
+            continue
+        specs.append((VGG19_NAMES[i], "conv", dict(kh=3, kw=3, cin=cin, cout=c)))
+        cin, i = c, i + 1
+    return specs
+
+
+DISC_FILTERS = [64, 128, 256, 512, 512, 512, 512, 512, 512]
+
+
+def discriminator_simple_512_layer_specs(input_shape):
+    h, w, cin = input_shape
+    specs = []
+    for i, c in enumerate(DISC_FILTERS):
+        specs.append(("discriminator/block_%d/Conv2d" % (i + 1), "conv", dict(kh=3, kw=3, cin=cin, cout=c, stride=1 if i == 0 else 2)))
+        specs.append(("discriminator/block_%d/BatchNorm" % (i + 1), "bn", dict(c=c)))
+        if i > 0:
+            h, w = -(-h // 2), -(-w // 2)
+        cin = c
+    flat = h * w * cin
+    for j, (fi, fo) in enumerate([(flat, 1024), (1024, 32), (32, 1)]):
+        specs.append(("discriminator/final/Dense_%d" % (j + 1), "dense", dict(cin=fi, cout=fo)))
+        if j < 2:
+            specs.append(("discriminator/final/BatchNorm_%d" % (j + 1), "bn", dict(c=fo)))
+    return specs
+
+
 def init_keras_weights(specs, seed=None):
     """Keras initialisers: glorot_uniform kernels, zero biases, BN (1,0,0,1), PReLU alpha 0 (model.py:21; Keras
     default for :276)."""
@@ -64,9 +109,216 @@ def init_keras_weights(specs, seed=None):
     return w
 
 
-class UpscalerOrigNet:
+def init_vgg19_weights(seed=4321):
+    """He-normal stand-in for the ImageNet weights keras.applications would download (model.py:108); same seeding as
+    the CPU oracle so parity runs share weights."""
+    rng = np.random.default_rng(seed)
+    w, cin, i = OrderedDict(), 3, 0
+    for c in VGG19_CFG:
+        if c == "M":
+            continue
+        k = (rng.standard_normal((3, 3, cin, c)) * math.sqrt(2.0 / (9 * cin))).astype(np.float32)
+        w[VGG19_NAMES[i]] = [k, (rng.standard_normal(c) * 0.01).astype(np.float32)]
+        cin, i = c, i + 1
+    return w
+
+
+def _shapes(kind, c):
+    if kind == "conv":
+        return [(c["kh"], c["kw"], c["cin"], c["cout"]), (c["cout"],)]
+    if kind == "convT":
+        return [(c["kh"], c["kw"], c["cout"], c["cin"]), (c["cout"],)]
+    if kind == "bn":
+        return [(c["c"],)] * 4
+    if kind == "prelu":
+        return [(1, 1, c["c"])]
+    if kind == "dense":
+        return [(c["cin"], c["cout"]), (c["cout"],)]
+    raise ValueError(kind)
+
+
+class Net:
+    """Flat parameter store + packed 16-bit weight copies shared by the three networks."""
+
+    train_dtype = torch.bfloat16   # gradients need bf16's range; every kernel takes the element type per call
+
+    def __init__(self, specs, weights, seed, device):
+        self.on_gpu = torch.cuda.is_available()
+        # Without a CUDA device the object still carries structure and weights (shapes, parameter counts, .h5 I/O);
+        # anything that computes raises, there is no CPU execution path.
+        self.device = torch.device(device) if self.on_gpu else torch.device("cpu")
+        self.specs = specs
+        host = weights if weights is not None else init_keras_weights(specs, seed)
+        # ---- flat layout: trainable tensors first, BatchNorm moving statistics after them
+        entries, off = [], 0
+        for trainable_pass in (True, False):
+            for name, kind, cfg in specs:
+                for j, shp in enumerate(_shapes(kind, cfg)):
+                    is_moving = kind == "bn" and j >= 2
+                    if is_moving == trainable_pass:
+                        continue
+                    n = int(np.prod(shp))
+                    entries.append((name, j, shp, off, n))
+                    off += -(-n // ALIGN) * ALIGN
+            if trainable_pass:
+                self.n_trainable = off
+        self.n_flat = off
+        flat = np.zeros(self.n_flat, np.float32)
+        self.offsets = {}
+        for name, j, shp, o, n in entries:
+            if name not in host:
+                raise KeyError("missing weights for layer %s" % name)
+            a = np.asarray(host[name][j], np.float32)
+            if tuple(a.shape) != tuple(shp):
+                raise ValueError("layer %s weight %d has shape %s, expected %s" % (name, j, a.shape, shp))
+            flat[o:o + n] = a.reshape(-1)
+            self.offsets[(name, j)] = (o, n, shp)
+        self.flat = torch.from_numpy(flat).to(self.device)
+        self.weights = OrderedDict()
+        for name, kind, cfg in specs:
+            self.weights[name] = [self._view(self.flat, name, j) for j in range(len(_shapes(kind, cfg)))]
+        self.grad_flat = None
+        self.grads = None
+        self._pack_sets = {}      # set name -> dict(dtype, idx tensor, views {key: (offset, shape)})
+        self._packed = {}         # set name -> {key: tensor view}
+        self._pack_src = {}       # set name -> [(key, layer, idx ndarray)]
+        self._buffers = {}
+        self.layer_events = None  # dict name -> [(start, end) CUDA events] when bench.py enables per-layer timing
+
+    def _view(self, flat, name, j):
+        o, n, shp = self.offsets[(name, j)]
+        return flat[o:o + n].view(shp)
+
+    # ---------------------------------------------------------------- gradients
+    def ensure_grads(self):
+        if self.grad_flat is None:
+            self.grad_flat = torch.zeros(self.n_trainable, dtype=torch.float32, device=self.device)
+            self.grads = OrderedDict()
+            for name, kind, cfg in self.specs:
+                nt = 2 if kind == "bn" else len(_shapes(kind, cfg))
+                self.grads[name] = [self._view(self.grad_flat, name, j) for j in range(nt)]
+        return self.grad_flat
+
+    # ---------------------------------------------------------------- packed weights
+    def add_pack(self, set_name, key, layer, idx):
+        """Registers packed[key] = cast(weights[layer][0].flat[idx]) (idx < 0 -> 0) in pack set `set_name`."""
+        self._pack_src.setdefault(set_name, []).append((key, layer, np.asarray(idx)))
+
+    def build_packs(self, dtypes):
+        for set_name, items in self._pack_src.items():
+            views, chunks, off = {}, [], 0
+            for key, layer, idx in items:
+                base = self.offsets[(layer, 0)][0]
+                g = np.where(idx >= 0, idx.astype(np.int64) + base, -1).astype(np.int32).reshape(-1)
+                views[key] = (off, idx.shape)
+                chunks.append(g)
+                pad = (-g.size) % 64     # keep every packed matrix 128-byte aligned (TMA global address)
+                if pad:
+                    chunks.append(-np.ones(pad, np.int32))
+                off += g.size + pad
+            self._pack_sets[set_name] = dict(dtype=dtypes[set_name], views=views, n=off,
+                                             idx=torch.from_numpy(np.concatenate(chunks)).to(self.device), buf=None)
+
+    def refresh_packs(self, set_name):
+        """Re-derives one set of packed 16-bit weights from the fp32 masters (one launch)."""
+        ps = self._pack_sets[set_name]
+        ps["buf"] = ops.gather_cast(self.flat, ps["idx"], ps["buf"], ps["dtype"])
+        self._packed[set_name] = {k: ps["buf"][o:o + int(np.prod(shp))].view(shp) for k, (o, shp) in ps["views"].items()}
+        return self._packed[set_name]
+
+    # ---------------------------------------------------------------- misc
+    def host_weights(self):
+        return OrderedDict((k, [t.detach().cpu().numpy() for t in ts]) for k, ts in self.weights.items())
+
+    def set_weights(self, host):
+        for name, ts in self.weights.items():
+            for t, a in zip(ts, host[name]):
+                t.copy_(torch.as_tensor(np.asarray(a, np.float32)).to(self.device).view(t.shape))
+        self._train_dirty = self._infer_dirty = True
+        if self.on_gpu:
+            self.refresh()
+
+    def count_params(self):
+        return int(sum(t.numel() for ts in self.weights.values() for t in ts))
+
+    def trainable_count(self):
+        return int(sum(t.numel() for (name, kind, cfg) in self.specs
+                       for j, t in enumerate(self.weights[name]) if not (kind == "bn" and j >= 2)))
+
+    def _buf(self, key, shape, dtype):
+        b = self._buffers.get(key)
+        if b is None or tuple(b.shape) != tuple(shape) or b.dtype != dtype:
+            b = torch.empty(shape, dtype=dtype, device=self.device)
+            self._buffers[key] = b
+        return b
+
+    def _vec(self, key, n, zero=False):
+        b = self._buffers.get(key)
+        if b is None or b.numel() != n:
+            b = torch.zeros(n, dtype=torch.float32, device=self.device)
+            self._buffers[key] = b
+        elif zero:
+            b.zero_()
+        return b
+
+    def _timed(self, name, fn):
+        if self.layer_events is None:
+            return fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        r = fn()
+        e1.record()
+        self.layer_events.setdefault(name, []).append((e0, e1))
+        return r
+
+    def _need_gpu(self):
+        if not self.on_gpu:
+            raise RuntimeError("this network runs on hand-written sm_100a kernels only; no CUDA device is available")
+
+    # ---------------------------------------------------------------- train-mode BatchNormalization helpers
+    def _bn_forward(self, tape, key, bn_name, z, out, act, alpha=None, leaky=0.0, residual=None, sync=None):
+        """Batch statistics of z (+ optional cross-replica sum), moving-stat update, out = act(BN(z)) + residual."""
+        C = z.shape[-1]
+        st = self._vec("st/" + key, 2 * C, zero=True)
+        ops.colstats(z, st[:C], st[C:])
+        rows = z.numel() // C
+        if sync is not None:
+            rows = sync(st, rows)
+        aff = self._vec("aff/" + key, 4 * C)
+        scale, shift, mean, invstd = aff[:C], aff[C:2 * C], aff[2 * C:3 * C], aff[3 * C:]
+        gamma, beta, mm, mv = self.weights[bn_name]
+        ops.bn_finalize(st[:C], st[C:], rows, gamma, beta, scale, shift, mean, invstd, mm, mv, BN_EPS, BN_MOMENTUM)
+        ops.affine_act(z, out, scale, shift, alpha, act, leaky, residual)
+        tape[key] = (z, scale, shift, mean, invstd, rows)
+        return out
+
+    def _bn_backward(self, tape, key, bn_name, g, dz, act, alpha=None, leaky=0.0, dalpha=None, sync=None, want_param_grads=True):
+        """g = gradient w.r.t. act(BN(z)); writes dgamma / dbeta (and dalpha) into the gradient views, returns dz."""
+        z, scale, shift, mean, invstd, rows = tape[key]
+        C = z.shape[-1]
+        if want_param_grads and sync is None:
+            s2, s1 = self.grads[bn_name][0], self.grads[bn_name][1]     # dgamma = sum dy*xhat, dbeta = sum dy
+            da = dalpha
+        else:
+            tmp = self._vec("bwd/" + key, 2 * C, zero=True)
+            s1, s2, da = tmp[:C], tmp[C:], (dalpha if want_param_grads else None)
+        ops.bn_bwd_reduce(z, g, scale, shift, alpha, act, leaky, mean, invstd, s1, s2, da)
+        if sync is not None:
+            world = sync(tmp, None)
+            if want_param_grads:
+                # the final gradient all-reduce sums over replicas: hand it 1/world of the global sums
+                ops.cast_scale(s2, self.grads[bn_name][0], 1.0 / world)
+                ops.cast_scale(s1, self.grads[bn_name][1], 1.0 / world)
+        ops.bn_bwd_apply(z, g, scale, shift, alpha, act, leaky, mean, invstd, s1, s2, rows, dz)
+        return dz
+
+
+class UpscalerOrigNet(Net):
     """SRGAN generator: 9x9 conv + PReLU -> N x (conv-BN-PReLU-conv-BN-add) -> conv-BN-add(skip) ->
     log2(factor) x (ConvT s2 + LeakyReLU 0.2) -> 9x9 conv -> tanh."""
+
+    input_name = "initial/input"
+    extra_layers = [("prefinal/tanh", "add"), ("final/tanh", "activation")]
 
     def __init__(self, kernel_size=5, filters=64, upscale_factor=4, res_block_num=16, weights=None, device="cuda",
                  seed=None, infer_dtype=torch.float16):
@@ -75,33 +327,19 @@ class UpscalerOrigNet:
         self.kernel_size, self.filters = kernel_size, filters
         self.upscale_factor, self.res_block_num = upscale_factor, res_block_num
         self.upscale_times = int(math.log(upscale_factor, 2))
-        # Without a CUDA device the object still carries structure and weights (shapes, parameter counts, .h5 I/O);
-        # anything that computes raises, there is no CPU execution path.
-        self.on_gpu = torch.cuda.is_available()
-        self.device = torch.device(device) if self.on_gpu else torch.device("cpu")
         # 16-bit storage type of the inference path (activations + packed weights): fp16 keeps 11 significand bits,
         # which is what holds max-abs error under 2e-2 across 37 layers; bf16 is accepted and ~8x noisier.
         self.infer_dtype = infer_dtype
-        self.specs = upscaler_orig_layer_specs(kernel_size, filters, upscale_factor, res_block_num)
-        host = weights if weights is not None else init_keras_weights(self.specs, seed)
-        self.weights = OrderedDict()
-        for name, kind, cfg in self.specs:
-            if name not in host:
-                raise KeyError("missing weights for layer %s" % name)
-            self.weights[name] = [torch.as_tensor(np.asarray(a), dtype=torch.float32).to(self.device).contiguous()
-                                  for a in host[name]]
-        self._pack_idx = {}
-        self._packed = {}
+        super().__init__(upscaler_orig_layer_specs(kernel_size, filters, upscale_factor, res_block_num), weights, seed, device)
         self._infer = {}
-        self._buffers = {}
         self._final_rows = False
-        self.layer_events = None  # dict name -> [(start, end) CUDA events] when bench.py enables per-layer timing
         self._build_index_maps()
         if self.on_gpu:
             self.refresh()
 
     # ---------------------------------------------------------------- weights
     def _build_index_maps(self):
+        k = self.kernel_size
         for name, kind, c in self.specs:
             if kind == "conv":
                 if name == "final/conv" and c["kh"] == 9 and c["cout"] == 3 and c["cin"] % 64 == 0 and c["cin"] <= 256:
@@ -115,26 +353,46 @@ class UpscalerOrigNet:
                 idx = ops.convT_pack_index(c["kh"], c["kw"], c["cin"], c["cout"])
             else:
                 continue
-            self._pack_idx[name] = torch.from_numpy(idx).to(self.device)
+            self.add_pack("infer", name, name, idx)
+            self.add_pack("train", name, name, idx)
+            # data-gradient layouts (training only)
+            if kind == "conv" and c["cin"] >= 64 and name != "final/conv":
+                self.add_pack("train", name + "#dgrad", name, ops.conv_dgrad_pack_index(c["kh"], c["kw"], c["cin"], c["cout"]))
+            elif kind == "convT":
+                self.add_pack("train", name + "#dgrad", name, ops.convT_dgrad_pack_index(c["kh"], c["kw"], c["cin"], c["cout"]))
+            elif name == "final/conv":
+                self.add_pack("train", name + "#dgrad", name, ops.final_dgrad_pack_index(c["kh"], c["kw"], c["cin"], c["cout"]))
+        self.build_packs({"infer": self.infer_dtype, "train": self.train_dtype})
+        c0 = self.specs[0][2]
+        self._head_wgrad_idx = torch.from_numpy(ops.rowfold_wgrad_gather_index(c0["kh"], c0["kw"], c0["cin"], c0["cout"])).to(self.device)
+        cf = self.specs[-1][2]
+        self._final_wgrad_idx = torch.from_numpy(ops.final_wgrad_gather_index(cf["kh"], cf["kw"], cf["cin"], cf["cout"])).to(self.device)
 
-    def refresh(self):
-        """Re-derive the packed bf16 weights and the folded inference epilogues from the fp32 masters."""
-        for name, idx in self._pack_idx.items():
-            self._packed[name] = ops.gather_cast(self.weights[name][0], idx, self._packed.get(name), self.infer_dtype)
+    def refresh(self, sets=("infer",)):
+        """Re-derive packed 16-bit weights (and, for inference, the folded BatchNorm epilogues) from the fp32 masters."""
+        for s in sets:
+            self.refresh_packs(s)
+            setattr(self, "_%s_dirty" % s, False)
+        if "infer" not in sets:
+            return
         w = self.weights
-        inf = {}
+        nfold = 2 * self.res_block_num + 1
+        fold = self._vec("fold", 2 * 64 * nfold)
+        inf, slot = {}, [0]
 
         def fold_bn(conv, bn):
+            i = slot[0]
+            slot[0] += 1
+            scale, shift = fold[2 * 64 * i:2 * 64 * i + 64], fold[2 * 64 * i + 64:2 * 64 * (i + 1)]
             gamma, beta, mean, var = w[bn]
-            scale = gamma / torch.sqrt(var + BN_EPS)
-            shift = beta + (w[conv][1] - mean) * scale
-            return scale.contiguous(), shift.contiguous()
+            ops.bn_fold(gamma, beta, mean, var, w[conv][1], scale, shift, BN_EPS)
+            return scale, shift
 
-        inf["initial/conv"] = (None, w["initial/conv"][1], w["initial/prelu"][0].reshape(-1).contiguous())
+        inf["initial/conv"] = (None, w["initial/conv"][1], w["initial/prelu"][0].reshape(-1))
         for i in range(self.res_block_num):
             n = "res_block/%d" % i
             s, b = fold_bn(n + "/conv_pre", n + "/batch_norm_pre")
-            inf[n + "/conv_pre"] = (s, b, w[n + "/prelu"][0].reshape(-1).contiguous())
+            inf[n + "/conv_pre"] = (s, b, w[n + "/prelu"][0].reshape(-1))
             s, b = fold_bn(n + "/conv_post", n + "/batch_norm_post")
             inf[n + "/conv_post"] = (s, b, None)
         s, b = fold_bn("prefinal/conv2d", "prefinal/batch_norm")
@@ -145,48 +403,23 @@ class UpscalerOrigNet:
         inf["final/conv"] = (None, w["final/conv"][1], None)
         self._infer = inf
 
-    input_name = "initial/input"
-    extra_layers = [("prefinal/tanh", "add"), ("final/tanh", "activation")]
-
     def output_shape_for(self, input_shape):
         h, w, c = input_shape
         f = 2 ** self.upscale_times
         return (None if h is None else h * f, None if w is None else w * f, 3)
 
-    def host_weights(self):
-        return OrderedDict((k, [t.detach().cpu().numpy() for t in ts]) for k, ts in self.weights.items())
-
-    def count_params(self):
-        return int(sum(t.numel() for ts in self.weights.values() for t in ts))
-
     # ---------------------------------------------------------------- inference
-    def _buf(self, key, shape, dtype):
-        b = self._buffers.get(key)
-        if b is None or tuple(b.shape) != tuple(shape) or b.dtype != dtype:
-            b = torch.empty(shape, dtype=dtype, device=self.device)
-            self._buffers[key] = b
-        return b
-
-    def _timed(self, name, fn):
-        if self.layer_events is None:
-            return fn()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        r = fn()
-        e1.record()
-        self.layer_events.setdefault(name, []).append((e0, e1))
-        return r
-
     def forward_infer(self, x, out=None):
         """x: (B,H,W,3) float32 CUDA in [-1,1] -> (B, H*f, W*f, 3) float32.  BatchNorm uses moving statistics folded
         into the conv epilogues (Keras learning_phase=0, i.e. Model.predict)."""
-        if not self.on_gpu:
-            raise RuntimeError("the generator runs on hand-written sm_100a kernels only; no CUDA device is available")
+        self._need_gpu()
+        if getattr(self, "_infer_dirty", False):     # fp32 masters changed (training step / set_weights)
+            self.refresh(("infer",))
         B, H, W, C = x.shape
         if C != 3 or x.dtype != torch.float32:
             raise ValueError("expected (B,H,W,3) float32 input, got %s %s" % (tuple(x.shape), x.dtype))
         k, f, dt = self.kernel_size, self.filters, self.infer_dtype
-        inf, pk = self._infer, self._packed
+        inf, pk = self._infer, self._packed["infer"]
         # head: fold the 9 horizontal taps of the 3-channel input into 27 (of 64) channels, then a 9x1 conv
         T = self._timed
         xp = T("initial/fold", lambda: ops.fold_taps(x, [(0, dx - 4) for dx in range(9)],
@@ -223,3 +456,326 @@ class UpscalerOrigNet:
         if self._final_rows:
             return T("final/conv", lambda: ops.conv2d_rows(m, pk["final/conv"], 3, 9, 9, bias=b, act=ops.ACT_TANH, out=out))
         return T("final/conv", lambda: ops.conv2d(m, pk["final/conv"], 3, 9, 9, out=out, shift=b, act=ops.ACT_TANH))
+
+    # ---------------------------------------------------------------- training
+    def forward_train(self, x, sync=None):
+        """Training-phase forward (BatchNorm on batch statistics, moving statistics updated).  Returns
+        (y fp32 (B,4H,4W,3), tape).  Packed 'train' weights must be current (refresh(('train',)))."""
+        self._need_gpu()
+        if not self._final_rows:
+            raise RuntimeError("training needs the row-streaming final conv (Cin <= 256)")
+        B, H, W, _ = x.shape
+        k, f, dt = self.kernel_size, self.filters, self.train_dtype
+        pk, w = self._packed["train"], self.weights
+        tape = {}
+        new = lambda shape: torch.empty(shape, dtype=dt, device=self.device)
+        xp = ops.fold_taps(x, [(0, dx - 4) for dx in range(9)], out=new((B, H, W, 64)), dtype=dt)
+        u0 = ops.conv2d(xp, pk["initial/conv"], f, 9, 1, out=new((B, H, W, f)), shift=w["initial/conv"][1])
+        a0 = w["initial/prelu"][0].reshape(-1)
+        skip = ops.affine_act(u0, new((B, H, W, f)), alpha=a0, act=ops.ACT_PRELU)
+        tape["head"] = (xp, u0)
+        m = skip
+        for i in range(self.res_block_num):
+            n = "res_block/%d" % i
+            z1 = ops.conv2d(m, pk[n + "/conv_pre"], f, k, k, out=new((B, H, W, f)), shift=w[n + "/conv_pre"][1])
+            h = self._bn_forward(tape, n + "/pre", n + "/batch_norm_pre", z1, new((B, H, W, f)), ops.ACT_PRELU,
+                                 alpha=w[n + "/prelu"][0].reshape(-1), sync=sync)
+            z2 = ops.conv2d(h, pk[n + "/conv_post"], f, k, k, out=new((B, H, W, f)), shift=w[n + "/conv_post"][1])
+            mo = self._bn_forward(tape, n + "/post", n + "/batch_norm_post", z2, new((B, H, W, f)), ops.ACT_NONE, residual=m,
+                                  sync=sync)
+            tape[n] = (m, h)
+            m = mo
+        zp = ops.conv2d(m, pk["prefinal/conv2d"], 64, k, k, out=new((B, H, W, 64)), shift=w["prefinal/conv2d"][1])
+        t = self._bn_forward(tape, "prefinal", "prefinal/batch_norm", zp, new((B, H, W, 64)), ops.ACT_NONE, residual=skip, sync=sync)
+        tape["prefinal/in"] = m
+        ups, h_, w_ = [t], H, W
+        for i in range(self.upscale_times):
+            n = "upscaling/%d/block/conv_transp" % i
+            u = ops.conv2d_transpose_s2(ups[-1], pk[n], 256, k, k, out=new((B, 2 * h_, 2 * w_, 256)), shift=w[n][1],
+                                        act=ops.ACT_LEAKY, leaky=0.2)
+            ups.append(u)
+            h_, w_ = 2 * h_, 2 * w_
+        tape["ups"] = ups
+        y = ops.conv2d_rows(ups[-1], pk["final/conv"], 3, 9, 9, bias=w["final/conv"][1], act=ops.ACT_TANH)
+        tape["y"] = y
+        return y, tape
+
+    def backward(self, tape, dz_final, sync=None):
+        """dz_final: fp32 (B,4H,4W,3) gradient w.r.t. the final conv's pre-tanh output (ops.tanh_bwd of the loss
+        gradients).  Accumulates every weight gradient into the flat gradient buffer."""
+        self.ensure_grads()
+        k, f, dt = self.kernel_size, self.filters, self.train_dtype
+        pk, w, g = self._packed["train"], self.weights, self.grads
+        new = lambda shape: torch.empty(shape, dtype=dt, device=self.device)
+        ups = tape["ups"]
+        B, HH, WW, _ = dz_final.shape
+        # ---- final 9x9 conv: fold the 81 shifted copies of the 3-channel gradient into 243 (of 256) channels; then the
+        #      data gradient is a 1x1 conv 256->256 and the weight gradient a plain GEMM over pixels
+        ops.colsum_f32(dz_final, g["final/conv"][1])
+        F = new((B, HH, WW, 256))
+        for q in range(4):
+            taps = [(4 - t // 9, 4 - t % 9) for t in range(21 * q, min(21 * q + 21, 81))]
+            ops.fold_taps(dz_final, taps, out=F, dtype=dt, out_c0=64 * q)
+        raw = self._buf("final_raw", (256 * 256,), torch.float32)
+        raw.zero_()
+        ops.conv2d_wgrad(ups[-1], F, 1, 1, 1, raw)
+        ops.gather_f32(raw, self._final_wgrad_idx, g["final/conv"][0], accumulate=True)
+        d = ops.conv2d(F, pk["final/conv#dgrad"], 256, 1, 1, out=new((B, HH, WW, 256)), gate=ups[-1], gate_slope=0.2)
+        del F
+        # ---- upsampling blocks (Conv2DTranspose stride 2 + LeakyReLU 0.2), last to first
+        for i in reversed(range(self.upscale_times)):
+            n = "upscaling/%d/block/conv_transp" % i
+            xin = ups[i]
+            ops.colstats(d, g[n][1])
+            ops.conv2d_wgrad(d, xin, k, k, 2, g[n][0])
+            cin = xin.shape[-1]
+            if i > 0:
+                d = ops.conv2d(d, pk[n + "#dgrad"], cin, k, k, stride=2, out=new(tuple(xin.shape)), gate=xin, gate_slope=0.2)
+            else:
+                d = ops.conv2d(d, pk[n + "#dgrad"], cin, k, k, stride=2, out=new(tuple(xin.shape)))
+        dt_ = d      # gradient w.r.t. t = skip + BN(prefinal conv): flows into both the trunk and the head skip
+        # ---- prefinal conv + BN
+        dzp = self._bn_backward(tape, "prefinal", "prefinal/batch_norm", dt_, new(tuple(dt_.shape)), ops.ACT_NONE, sync=sync)
+        m_in = tape["prefinal/in"]
+        ops.conv2d_wgrad(m_in, dzp, k, k, 1, g["prefinal/conv2d"][0])
+        gm = ops.conv2d(dzp, pk["prefinal/conv2d#dgrad"], f, k, k, out=new(tuple(m_in.shape)))
+        # ---- residual blocks, last to first; gm is the gradient w.r.t. each block's output (the residual stream)
+        for i in reversed(range(self.res_block_num)):
+            n = "res_block/%d" % i
+            m_in, h = tape[n]
+            dz2 = self._bn_backward(tape, n + "/post", n + "/batch_norm_post", gm, new(tuple(gm.shape)), ops.ACT_NONE, sync=sync)
+            ops.conv2d_wgrad(h, dz2, k, k, 1, g[n + "/conv_post"][0])
+            dh = ops.conv2d(dz2, pk[n + "/conv_post#dgrad"], f, k, k, out=dz2.new_empty(dz2.shape))
+            dz1 = self._bn_backward(tape, n + "/pre", n + "/batch_norm_pre", dh, dz2, ops.ACT_PRELU,
+                                    alpha=w[n + "/prelu"][0].reshape(-1), dalpha=g[n + "/prelu"][0].reshape(-1), sync=sync)
+            ops.conv2d_wgrad(m_in, dz1, k, k, 1, g[n + "/conv_pre"][0])
+            gm = ops.conv2d(dz1, pk[n + "/conv_pre#dgrad"], f, k, k, out=dh, residual=gm)
+        # ---- head: PReLU backward (dbias = sum dy, dalpha), then the weight gradient of the row-folded 9x1 conv
+        xp, u0 = tape["head"]
+        a0 = w["initial/prelu"][0].reshape(-1)
+        gm = ops.affine_act(gm, new(tuple(gm.shape)), residual=dt_)     # the skip connection joins here: trunk + upsampling path
+        ops.bn_bwd_reduce(u0, gm, None, None, a0, ops.ACT_PRELU, 0.0, None, None, g["initial/conv"][1], None,
+                          g["initial/prelu"][0].reshape(-1))
+        dz0 = ops.bn_bwd_apply(u0, gm, None, None, a0, ops.ACT_PRELU, 0.0, None, None, None, None, 0, new(tuple(u0.shape)))
+        raw = self._buf("head_raw", (9 * 64 * 64,), torch.float32)
+        raw.zero_()
+        ops.conv2d_wgrad(xp, dz0, 9, 1, 1, raw)
+        ops.gather_f32(raw, self._head_wgrad_idx, g["initial/conv"][0], accumulate=True)
+
+
+class Vgg19Net(Net):
+    """keras.applications VGG19(include_top=False) up to block5_conv4 (post-ReLU), frozen, fed the raw [-1,1] RGB
+    tensor (model.py:108-117).  Forward on either element type; dgrad back to the image for the y_pred branch."""
+
+    input_name = "input_1"
+    extra_layers = []
+    # The loss compares two feature maps that converge towards each other, so feature rounding noise biases it upwards
+    # (measured: bf16 features move a converged loss by up to 2 %, fp16 by < 0.1 %).  The frozen VGG therefore stores
+    # activations and packed weights as IEEE fp16; its data gradients are carried multiplied by `grad_scale` (the loss
+    # gradient is formed without the 1/n of the mean) so they sit in fp16's normal range, and the scale is divided out in
+    # the fp32 epilogue of the last data-gradient convolution.
+    train_dtype = torch.float16
+
+    def __init__(self, weights=None, device="cuda", seed=None):
+        super().__init__(vgg19_layer_specs(), weights, seed, device)
+        for name, kind, c in self.specs:
+            if c["cin"] < 64:
+                self.add_pack("train", name, name, ops.conv_fullfold_pack_index(3, 3, c["cin"], c["cout"]))
+                self.add_pack("train", name + "#dgrad", name, ops.conv_dgrad_pack_index(3, 3, c["cin"], c["cout"]))
+            else:
+                self.add_pack("train", name, name, ops.conv_pack_index(3, 3, c["cin"], c["cout"]))
+                self.add_pack("train", name + "#dgrad", name, ops.conv_dgrad_pack_index(3, 3, c["cin"], c["cout"]))
+        self.build_packs({"train": self.train_dtype})
+        if self.on_gpu:
+            self.refresh()
+
+    def refresh(self, sets=("train",)):
+        for s in sets:
+            self.refresh_packs(s)
+
+    def output_shape_for(self, input_shape):
+        h, w, _ = input_shape
+        for _ in range(4):
+            h, w = (None if h is None else h // 2), (None if w is None else w // 2)
+        return (h, w, 512)
+
+    def forward(self, x, save=False):
+        """x: (B,H,W,3) fp32 -> block5_conv4 features (B,H/16,W/16,512) 16-bit; `save` keeps the activations for
+        backward()."""
+        self._need_gpu()
+        dt, pk, w = self.train_dtype, self._packed["train"], self.weights
+        B, H, W, _ = x.shape
+        taps = [(ky - 1, kx - 1) for ky in range(3) for kx in range(3)]
+        a = ops.fold_taps(x, taps, dtype=dt)
+        acts, i, first = [], 0, True
+        for c in VGG19_CFG:
+            if c == "M":
+                p = ops.maxpool2x2(a)
+                acts.append(("pool", a, p))
+                a = p
+                continue
+            name = VGG19_NAMES[i]
+            kk = 1 if first else 3
+            a = ops.conv2d(a, pk[name], c, kk, kk, shift=w[name][1], act=ops.ACT_RELU)
+            acts.append(("conv", name, a))
+            first, i = False, i + 1
+        return (a, acts) if save else a
+
+    def forward_infer(self, x, out=None):
+        return self.forward(x)
+
+    def backward(self, acts, dfeat, grad_scale=1.0):
+        """dfeat: grad_scale x the gradient w.r.t. the (post-ReLU) block5_conv4 features, 16-bit.  Returns the gradient
+        w.r.t. the input image, fp32 (B,H,W,3), with the scale divided out.  Weights are frozen: data gradients only."""
+        pk = self._packed["train"]
+        top = acts[-1][2]
+        # ReLU backward of the top layer
+        d = ops.bn_bwd_apply(top, dfeat, None, None, None, ops.ACT_RELU, 0.0, None, None, None, None, 0, torch.empty_like(top))
+        for j in range(len(acts) - 1, 0, -1):
+            kind, name, _ = acts[j]
+            below = acts[j - 1]
+            if kind == "pool":
+                continue        # handled together with the conv above it
+            cin = pk[name + "#dgrad"].shape[0]
+            if below[0] == "conv":
+                d = ops.conv2d(d, pk[name + "#dgrad"], cin, 3, 3, gate=below[2], gate_slope=0.0)
+            else:
+                _, a_in, p_out = below
+                dp = ops.conv2d(d, pk[name + "#dgrad"], cin, 3, 3)
+                d = ops.maxpool2x2_bwd(a_in, p_out, dp, relu_gate=True)
+        name = acts[0][1]
+        B, H, W, _ = d.shape
+        inv = self._vec("inv_scale", 3)
+        inv.fill_(1.0 / grad_scale)
+        return ops.conv2d(d, pk[name + "#dgrad"], 3, 3, 3, scale=inv,
+                          out=torch.empty((B, H, W, 3), dtype=torch.float32, device=self.device))
+
+
+class DiscriminatorSimple512Net(Net):
+    """make_discriminator_simple_512 (model.py:836-896): 9 x (3x3 conv [s1 then 8 x s2] + BN + LeakyReLU 0.1) ->
+    Flatten -> Dense 1024 - BN - LReLU -> Dense 32 - BN - LReLU -> Dense 1 -> optional activation."""
+
+    input_name = "discriminator/input"
+
+    def __init__(self, input_shape, activation="none", weights=None, device="cuda", seed=None):
+        self.input_shape = tuple(input_shape)
+        self.activation = activation
+        specs = discriminator_simple_512_layer_specs(self.input_shape)
+        super().__init__(specs, weights, seed, device)
+        self.extra_layers = [("discriminator/final/Flatten", "flatten")]
+        h, w = self.input_shape[:2]
+        self._conv_geom = []
+        for name, kind, c in specs:
+            if kind != "conv":
+                continue
+            s = c["stride"]
+            oh, ow = -(-h // s), -(-w // s)
+            self._conv_geom.append((name, c, (h, w), (oh, ow)))
+            h, w = oh, ow
+            if c["cin"] < 64:
+                self.add_pack("train", name, name, ops.conv_fullfold_pack_index(3, 3, c["cin"], c["cout"]))
+                self.add_pack("train", name + "#dgrad", name, ops.conv_dgrad_pack_index(3, 3, c["cin"], c["cout"]))
+            else:
+                self.add_pack("train", name, name, ops.conv_pack_index(3, 3, c["cin"], c["cout"]))
+                self.add_pack("train", name + "#dgrad", name, ops.conv_s2_dgrad_pack_index(3, 3, c["cin"], c["cout"]))
+        self._flat_hw = (h, w)
+        self._dense = [(n, c) for n, kind, c in specs if kind == "dense"]
+        self.build_packs({"train": self.train_dtype})
+        c1 = specs[0][2]
+        self._first_wgrad_idx = torch.from_numpy(ops.fullfold_wgrad_gather_index(3, 3, c1["cin"], c1["cout"])).to(self.device)
+        if self.on_gpu:
+            self.refresh()
+
+    def refresh(self, sets=("train",)):
+        for s in sets:
+            self.refresh_packs(s)
+
+    def output_shape_for(self, input_shape):
+        return (1,)
+
+    def _bn_act(self, tape, bn_name, z, training, sync):
+        """BatchNormalization + LeakyReLU(0.1): batch statistics when training, moving statistics otherwise."""
+        out = torch.empty_like(z)
+        if training:
+            return self._bn_forward(tape, bn_name, bn_name, z, out, ops.ACT_LEAKY, leaky=0.1, sync=sync)
+        C = z.shape[-1]
+        aff = self._vec("aff/" + bn_name, 4 * C)
+        g, b, mm, mv = self.weights[bn_name]
+        ops.bn_fold(g, b, mm, mv, None, aff[:C], aff[C:2 * C], BN_EPS)
+        return ops.affine_act(z, out, aff[:C], aff[C:2 * C], None, ops.ACT_LEAKY, 0.1)
+
+    def forward(self, x, training, sync=None):
+        """x: (n,H,W,3) fp32 -> ((n,1) fp32 scores, tape).  training=True normalises with batch statistics (and updates
+        the moving ones, as Keras does even for a frozen discriminator inside the GAN model); False = Model.predict."""
+        self._need_gpu()
+        if self.activation not in ("none", "log", "linear", None):
+            raise NotImplementedError("discriminator output activation %r (model.py:885-892) is not built yet" % self.activation)
+        dt, pk, w = self.train_dtype, self._packed["train"], self.weights
+        n = x.shape[0]
+        if tuple(x.shape[1:]) != self.input_shape:
+            raise ValueError("discriminator expects input %s, got %s" % (self.input_shape, tuple(x.shape[1:])))
+        tape = {}
+        taps = [(ky - 1, kx - 1) for ky in range(3) for kx in range(3)]
+        a = ops.fold_taps(x, taps, dtype=dt)
+        ins = []
+        for bi, (name, c, _, _) in enumerate(self._conv_geom):
+            kk = 1 if bi == 0 else 3
+            ins.append(a)
+            z = ops.conv2d(a, pk[name], c["cout"], kk, kk, stride=c["stride"], shift=w[name][1])
+            a = self._bn_act(tape, name.replace("Conv2d", "BatchNorm"), z, training, sync)
+        tape["ins"] = ins
+        a = a.reshape(n, -1)                                   # Keras Flatten of an NHWC tensor
+        dins = []
+        for j, (name, c) in enumerate(self._dense):
+            dins.append(a)
+            last = j == len(self._dense) - 1
+            z = ops.dense_fwd(a, w[name][0], w[name][1],
+                              torch.empty((n, c["cout"]), dtype=torch.float32 if last else dt, device=self.device))
+            a = z if last else self._bn_act(tape, "discriminator/final/BatchNorm_%d" % (j + 1), z, training, sync)
+        tape["dins"] = dins
+        return a, tape
+
+    def forward_infer(self, x, out=None):
+        return self.forward(x, False)[0]
+
+    def backward(self, tape, dscore, want_wgrad=True, want_input_grad=False, sync=None):
+        """dscore: (n,1) fp32 gradient w.r.t. the scores.  Accumulates weight gradients unless the discriminator is
+        frozen (gan_train, model.py:1040); returns the gradient w.r.t. the input image (fp32) when asked."""
+        dt, pk, w = self.train_dtype, self._packed["train"], self.weights
+        if want_wgrad:
+            self.ensure_grads()
+        g = self.grads
+        n = dscore.shape[0]
+        dins = tape["dins"]
+        d = dscore
+        for j in reversed(range(len(self._dense))):
+            name, c = self._dense[j]
+            if j < len(self._dense) - 1:
+                bn = "discriminator/final/BatchNorm_%d" % (j + 1)
+                d = self._bn_backward(tape, bn, bn, d, torch.empty_like(d), ops.ACT_LEAKY, leaky=0.1, sync=sync,
+                                      want_param_grads=want_wgrad)
+            if want_wgrad:
+                ops.dense_bwd_weight(dins[j], d, g[name][0], g[name][1])
+            d = ops.dense_bwd_data(d, w[name][0], torch.empty((n, c["cin"]), dtype=dt, device=self.device))
+        ins = tape["ins"]
+        last = self._conv_geom[-1]
+        d = d.view(n, last[3][0], last[3][1], last[1]["cout"])
+        for bi in reversed(range(len(self._conv_geom))):
+            name, c, (h, w_), _ = self._conv_geom[bi]
+            bn = name.replace("Conv2d", "BatchNorm")
+            dz = self._bn_backward(tape, bn, bn, d, torch.empty_like(d), ops.ACT_LEAKY, leaky=0.1, sync=sync,
+                                   want_param_grads=want_wgrad)
+            if bi > 0:
+                if want_wgrad:
+                    ops.conv2d_wgrad(ins[bi], dz, 3, 3, c["stride"], g[name][0])
+                d = ops.conv2d_s2_dgrad(dz, pk[name + "#dgrad"], c["cin"], 3, 3, (h, w_))
+            else:
+                if want_wgrad:
+                    raw = self._buf("first_raw", (64 * c["cout"],), torch.float32)
+                    raw.zero_()
+                    ops.conv2d_wgrad(ins[0], dz, 1, 1, 1, raw)
+                    ops.gather_f32(raw, self._first_wgrad_idx, g[name][0], accumulate=True)
+                if want_input_grad:
+                    return ops.conv2d(dz, pk[name + "#dgrad"], c["cin"], 3, 3,
+                                      out=torch.empty((n, h, w_, c["cin"]), dtype=torch.float32, device=self.device))
+        return None

@@ -126,8 +126,9 @@ def conv2d_transpose_s2(x, w_packed, cout, kh, kw, out=None, scale=None, shift=N
     return out
 
 
-def fold_taps(x, taps, stride=1, out_hw=None, out=None, dtype=torch.bfloat16):
-    """out[b,y,x, t*Cin + c] = x[b, y*stride + dy_t, x*stride + dx_t, c]; 64 output channels, zero padded."""
+def fold_taps(x, taps, stride=1, out_hw=None, out=None, dtype=torch.bfloat16, out_c0=0):
+    """out[b,y,x, out_c0 + t*Cin + c] = x[b, y*stride + dy_t, x*stride + dx_t, c]; 64 channels written (zero padded) at
+    channel offset out_c0 of `out` (which may be wider than 64 channels)."""
     B, H, W, Cin = x.shape
     if x.dtype not in (torch.float32, torch.bfloat16, torch.float16):
         raise ValueError("fold_taps expects float32, bf16 or fp16 input")
@@ -141,7 +142,8 @@ def fold_taps(x, taps, stride=1, out_hw=None, out=None, dtype=torch.bfloat16):
     dy = (ctypes.c_int * n)(*[int(t[0]) for t in taps])
     dx = (ctypes.c_int * n)(*[int(t[1]) for t in taps])
     rc = _lib.load().b2_fold_taps(_lib.ptr(x), 1 if x.dtype == torch.float32 else 0, B, H, W, Cin, OH, OW, stride, n,
-                                  dy, dx, _lib.ptr(out), 1 if out.dtype == torch.float16 else 0, _lib.stream_ptr())
+                                  dy, dx, _lib.ptr(out), 1 if out.dtype == torch.float16 else 0, out.shape[-1], out_c0,
+                                  _lib.stream_ptr())
     _lib.check(rc, "b2_fold_taps")
     _count(1)
     return out
@@ -319,6 +321,40 @@ def gather_f32(src, idx, out, accumulate=False):
     return out
 
 
+def colsum_f32(x, out):
+    """out[c] += sum over rows of the fp32 tensor x (..., C), C <= 8."""
+    rows, C = _rows_c(x)
+    rc = _lib.load().b2_colsum_f32(_lib.ptr(x), rows, C, _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(rc, "b2_colsum_f32")
+    _count(1)
+
+
+def dense_fwd(x, W, b, out):
+    n, K = x.shape[0], x.numel() // x.shape[0]
+    N = W.shape[1]
+    rc = _lib.load().b2_dense_fwd(_lib.ptr(x), _dt(x), n, K, N, _lib.ptr(W), _lib.ptr(b), _lib.ptr(out), _dt(out), _lib.stream_ptr())
+    _lib.check(rc, "b2_dense_fwd")
+    _count(1)
+    return out
+
+
+def dense_bwd_data(dy, W, dx):
+    n, N = dy.shape[0], W.shape[1]
+    K = W.shape[0]
+    rc = _lib.load().b2_dense_bwd_data(_lib.ptr(dy), _dt(dy), n, K, N, _lib.ptr(W), _lib.ptr(dx), _dt(dx), _lib.stream_ptr())
+    _lib.check(rc, "b2_dense_bwd_data")
+    _count(1)
+    return dx
+
+
+def dense_bwd_weight(x, dy, dW, db):
+    n, K, N = x.shape[0], dW.shape[0], dW.shape[1]
+    rc = _lib.load().b2_dense_bwd_weight(_lib.ptr(x), _dt(x), _lib.ptr(dy), _dt(dy), n, K, N, _lib.ptr(dW), _lib.ptr(db),
+                                         _lib.stream_ptr())
+    _lib.check(rc, "b2_dense_bwd_weight")
+    _count(1)
+
+
 def cast_scale(x, out, scale=1.0):
     rc = _lib.load().b2_cast_scale(_lib.ptr(x), _dt(x), x.numel(), scale, _lib.ptr(out), _dt(out), _lib.stream_ptr())
     _lib.check(rc, "b2_cast_scale")
@@ -334,6 +370,52 @@ def adam(params, grads, m, v, lr_t, beta1, beta2, eps, gscale=1.0):
 
 
 # ------------------------------------------------------------------------------------------------ packing index maps
+FINAL_TAPS_PER_GROUP = 21      # 21 taps x 3 channels = 63 of the 64 channels of one fold group
+
+
+def _final_fold_channel(t, co, cout):
+    return 64 * (t // FINAL_TAPS_PER_GROUP) + (t % FINAL_TAPS_PER_GROUP) * cout + co
+
+
+def final_dgrad_pack_index(kh, kw, cin, cout):
+    """Data gradient of the final Conv2D(3, 9x9) (model.py:290) as a 1x1 conv over the tap-folded output gradient F
+    (F[q, f(t,co)] = dz[q - d(t), co]): packed [Cin rows][256 folded channels], entry = W[t, c, co]."""
+    T = kh * kw
+    idx = -np.ones((cin, 64 * (-(-T // FINAL_TAPS_PER_GROUP))), np.int64)
+    c = np.arange(cin)
+    for t in range(T):
+        for co in range(cout):
+            idx[:, _final_fold_channel(t, co, cout)] = (t * cin + c) * cout + co
+    return idx.astype(np.int32)
+
+
+def final_wgrad_gather_index(kh, kw, cin, cout):
+    """Keras (kh,kw,Cin,Cout) gradient of the final conv <- raw[c][f] = sum_p X[p,c] * F[p,f] (raw row pitch 256)."""
+    T = kh * kw
+    nf = 64 * (-(-T // FINAL_TAPS_PER_GROUP))
+    idx = np.zeros((T, cin, cout), np.int64)
+    c = np.arange(cin)[:, None]
+    for t in range(T):
+        f = np.array([_final_fold_channel(t, co, cout) for co in range(cout)])[None, :]
+        idx[t] = c * nf + f
+    return idx.astype(np.int32)
+
+
+def rowfold_wgrad_gather_index(kh, kw, cin, cout):
+    """Keras (kh,kw,Cin,Cout) gradient of a row-folded narrow conv <- raw (kh,1,64,Cout) from conv2d_wgrad(kh x 1) on
+    the folded input (channel = kx*Cin + c)."""
+    ky = np.arange(kh)[:, None, None, None]
+    kx = np.arange(kw)[None, :, None, None]
+    c = np.arange(cin)[None, None, :, None]
+    co = np.arange(cout)[None, None, None, :]
+    return ((ky * 64 + kx * cin + c) * cout + co).astype(np.int32)
+
+
+def fullfold_wgrad_gather_index(kh, kw, cin, cout):
+    """Keras (kh,kw,Cin,Cout) gradient of a fully folded narrow conv <- raw (1,1,64,Cout): the first kh*kw*Cin rows."""
+    return np.arange(kh * kw * cin * cout, dtype=np.int32).reshape(kh, kw, cin, cout)
+
+
 def conv_dgrad_pack_index(kh, kw, cin, cout):
     """Keras Conv2D kernel (kh,kw,Cin,Cout) -> packed [Cin][kh*kw (flipped)][Cout]: the stride-1 data gradient
     dX = conv(dZ, flip(W)^T) runs through conv2d with this weight."""

@@ -1,0 +1,437 @@
+"""Model.compile / Model.train_on_batch for the models the reference's compile helpers build
+(upscaling/upscaler/model.py:1017-1137), executed as hand-written sm_100a kernels through the C ABI.
+
+Recognised structures (everything else raises at compile time):
+  'gen'    outputs G(x),               loss = content loss                        compile_training_model, gen_train
+  'disc'   outputs D(x),               loss = wasserstein_loss                    make_and_compile_gan  disc_train
+  'gan'    outputs [G(x), D(G(x))],    loss = [content, wasserstein_loss]         make_and_compile_gan  gan_train
+  'disc2'  inputs [real, fake], out D(fake), loss = GanLosses.discriminator_loss  make_and_compile_gan2 disc_train
+  'gan2'   inputs [x, real], outputs [G(x), D(G(x))], loss = [content, GanLosses.generator_loss]   ...  gan_train
+
+Keras semantics kept: losses are returned as computed in the forward pass (before the update); a model's `trainable`
+flag is snapshotted at compile time (model.py:1034, 1040); BatchNormalization of a frozen discriminator still runs on
+batch statistics inside a training step and still updates its moving statistics; one Adam instance shared between
+compiled models shares `iterations` while each compiled model owns its moment slots.
+
+Data parallelism: when torch.distributed is initialised, every rank runs the same step on its shard of the batch;
+BatchNorm statistics (forward sums and backward sums) are all-reduced so that N replicas normalise like one big batch,
+loss gradients are scaled by 1/world at the source and the flat gradient buffer is sum-all-reduced over NCCL in
+buckets, launched on a side stream as soon as backward has finished the slice (the flat layout follows the graph
+order, so the tail of the network — whose gradients are ready first — is the last slice).
+"""
+import math
+
+import numpy as np
+import torch
+
+from . import ops
+from .keras_compat import as_batch
+
+
+# ------------------------------------------------------------------------------------------------ loss descriptors
+class ContentLoss:
+    """What VGG_LOSS / VGG_MSE_LOSS / VGG_MAE_LOSS(...).loss hands to compile (model.py:101-157)."""
+
+    def __init__(self, kind, rate, vgg_net):
+        self.kind, self.rate, self.vgg = kind, float(rate), vgg_net
+
+    @property
+    def mae(self):
+        return self.kind == "vgg-mae"
+
+
+class GanLossFn:
+    """The closures GanLosses.discriminator_loss / generator_loss return (model.py:215-261): they ignore
+    (y_true, y_pred) and read the symbolic discriminator outputs stored on the GanLosses object."""
+
+    def __init__(self, owner, role):
+        self.owner, self.role = owner, role
+
+    def __call__(self, y_true, y_pred):
+        raise TypeError("GAN loss closures are evaluated inside train_on_batch")
+
+
+def loss_activation(name, x):
+    """(value, derivative) of GanLosses' loss activations at the scalar x (model.py:170-181)."""
+    if name == "sigmoid":
+        s = 1.0 / (1.0 + math.exp(-x))
+        return s, s * (1 - s)
+    if name == "log-sigm":
+        s = 1.0 / (1.0 + math.exp(-x))
+        return math.log(s), 1 - s
+    if name == "tanh":
+        t = math.tanh(x)
+        return t, 1 - t * t
+    if name == "bi-log":
+        a = abs(x)
+        f = x / (1 + a)
+        return f * math.log(a + 2), math.log(a + 2) / (1 + a) ** 2 + f * (1.0 if x >= 0 else -1.0) / (a + 2)
+    return x, 1.0
+
+
+# ------------------------------------------------------------------------------------------------ distributed helpers
+def _dist():
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        return dist
+    return None
+
+
+def _make_sync():
+    """Cross-replica sum for BatchNorm statistics: sync(buffer, rows) -> global rows (or the world size)."""
+    dist = _dist()
+    if dist is None:
+        return None
+    world = dist.get_world_size()
+
+    def sync(buf, rows):
+        dist.all_reduce(buf)
+        return rows * world if rows is not None else world
+    return sync
+
+
+class GradReducer:
+    """Bucketed sum-all-reduce of a flat gradient buffer, overlapped with the rest of backward on a side stream."""
+
+    def __init__(self, n_buckets=3):
+        self.n_buckets = n_buckets
+        self.stream = None
+        self.pending = []
+
+    def reduce_slice(self, flat, lo, hi):
+        dist = _dist()
+        if dist is None or hi <= lo:
+            return
+        if self.stream is None:
+            self.stream = torch.cuda.Stream()
+        ev = torch.cuda.Event()
+        ev.record()
+        self.stream.wait_event(ev)
+        with torch.cuda.stream(self.stream):
+            dist.all_reduce(flat[lo:hi])
+            done = torch.cuda.Event()
+            done.record()
+        self.pending.append(done)
+
+    def wait(self):
+        for ev in self.pending:
+            torch.cuda.current_stream().wait_event(ev)
+        self.pending = []
+
+
+# ------------------------------------------------------------------------------------------------ compiled models
+def _to_dev(a, dev):
+    t = torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32))
+    return t.pin_memory().to(dev, non_blocking=True)
+
+
+class Compiled:
+    def __init__(self, kind, model, optimizer):
+        self.kind, self.model, self.opt = kind, model, optimizer
+        self.G = self.D = None
+        self.content = None
+        self.g_frozen = self.d_frozen = False
+        self.weights = (1.0, 1.0)
+        self.slots = {}
+        self.gan_losses = None
+        self.reducer = GradReducer()
+
+    # -------------------------------------------------------------- Adam
+    def _adam(self, net):
+        opt = self.opt
+        opt.iterations += 1
+        t = opt.iterations
+        lr = opt.lr * (1.0 / (1.0 + opt.decay * (t - 1))) if opt.decay else opt.lr
+        lr_t = lr * math.sqrt(1.0 - opt.beta_2 ** t) / (1.0 - opt.beta_1 ** t)
+        key = id(net)
+        if key not in self.slots:
+            self.slots[key] = (torch.zeros_like(net.grad_flat), torch.zeros_like(net.grad_flat))
+        m, v = self.slots[key]
+        self.reducer.wait()
+        ops.adam(net.flat[:net.n_trainable], net.grad_flat, m, v, lr_t, opt.beta_1, opt.beta_2, opt.epsilon)
+        net._train_dirty = True
+        net._infer_dirty = True
+
+    @staticmethod
+    def _fresh(net, sets=("train",)):
+        """Packed 16-bit weights are re-derived lazily after an update of the fp32 masters."""
+        for s in sets:
+            flag = "_%s_dirty" % s
+            if getattr(net, flag, True) or s not in net._packed:
+                net.refresh((s,))
+                setattr(net, flag, False)
+
+    # -------------------------------------------------------------- content loss (+ gradient w.r.t. the generated image)
+    def _content(self, y, y_true, loss_buf, weight):
+        """loss_buf += content loss (unweighted); returns the gradient tensors (fp32 images) scaled by `weight`/world."""
+        cl = self.content
+        dist = _dist()
+        gs = weight / (dist.get_world_size() if dist else 1)
+        vgg = cl.vgg
+        self._fresh(vgg)
+        ft = vgg.forward(y_true)
+        fp, acts = vgg.forward(y, save=True)
+        dfeat = torch.empty_like(fp)
+        S = float(fp.numel())       # carry the feature gradient without the 1/n of the mean (fp16 range), see Vgg19Net
+        ops.loss_pair(fp, ft, loss_buf, mae=cl.mae, weight=1.0, gscale=gs * S, grad=dfeat)
+        grads = [vgg.backward(acts, dfeat, S)]
+        if cl.kind in ("vgg-mse", "vgg-mae"):
+            gpix = torch.empty_like(y)
+            ops.loss_pair(y, y_true, loss_buf, mae=cl.mae, weight=cl.rate, gscale=gs * cl.rate, grad=gpix)
+            grads.append(gpix)
+        return grads
+
+    def _reduce_all(self, net):
+        """Sum-all-reduce of the flat gradients in graph-ordered buckets (no-op on one GPU)."""
+        if _dist() is None:
+            return
+        n, nb = net.n_trainable, self.reducer.n_buckets
+        for b in reversed(range(nb)):
+            self.reducer.reduce_slice(net.grad_flat, n * b // nb, n * (b + 1) // nb)
+
+    # -------------------------------------------------------------- steps
+    def step_gen(self, x, y_true):
+        G = self.G
+        dev = G.device
+        self._fresh(G)
+        xd, yt = _to_dev(x, dev), _to_dev(y_true, dev)
+        sync = _make_sync()
+        y, tape = G.forward_train(xd, sync)
+        loss = torch.zeros(1, device=dev)
+        grads = self._content(y, yt, loss, 1.0)
+        dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1] if len(grads) > 1 else None)
+        G.ensure_grads().zero_()
+        G.backward(tape, dz, sync)
+        self._reduce_all(G)
+        self._adam(G)
+        return self._mean_over_ranks(loss)[0]
+
+    def step_disc(self, x, y):
+        D = self.D
+        dev = D.device
+        self._fresh(D)
+        xd = _to_dev(x, dev)
+        yd = _to_dev(np.asarray(y, np.float32).reshape(-1), dev)
+        sync = _make_sync()
+        scores, tape = D.forward(xd, True, sync)
+        loss = torch.zeros(1, device=dev)
+        ds = torch.empty_like(scores)
+        dist = _dist()
+        ops.mean_prod(scores, yd, loss, 1.0, 1.0 / (dist.get_world_size() if dist else 1), ds)
+        D.ensure_grads().zero_()
+        D.backward(tape, ds, True, False, sync)
+        self._reduce_all(D)
+        self._adam(D)
+        return self._mean_over_ranks(loss)[0]
+
+    def step_gan(self, x, y_true, adv_y):
+        G, D = self.G, self.D
+        dev = G.device
+        self._fresh(G)
+        self._fresh(D)
+        cw, dw = self.weights
+        xd, yt = _to_dev(x, dev), _to_dev(y_true, dev)
+        ad = _to_dev(np.asarray(adv_y, np.float32).reshape(-1), dev)
+        sync = _make_sync()
+        dist = _dist()
+        world = dist.get_world_size() if dist else 1
+        y, gtape = G.forward_train(xd, sync)
+        scores, dtape = D.forward(y, True, sync)
+        losses = torch.zeros(2, device=dev)
+        grads = self._content(y, yt, losses[0:1], cw)
+        ds = torch.empty_like(scores)
+        ops.mean_prod(scores, ad, losses[1:2], 1.0, dw / world, ds)
+        grads.append(D.backward(dtape, ds, not self.d_frozen, True, sync))
+        dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1], g3=grads[2] if len(grads) > 2 else None)
+        G.ensure_grads().zero_()
+        G.backward(gtape, dz, sync)
+        self._reduce_all(G)
+        self._adam(G)
+        lc, la = self._mean_over_ranks(losses)
+        return [cw * lc + dw * la, lc, la]
+
+    def _relativistic(self, mean_real, mean_fake, role):
+        gl = self.gan_losses
+        if gl.family == "wasserstein":
+            if role == "disc":
+                return mean_real - mean_fake, 1.0, -1.0
+            return mean_fake, 0.0, 1.0
+        delta = (mean_real - mean_fake) if role == "disc" else (mean_fake - mean_real)
+        val, der = loss_activation(gl.loss_activation_name, delta)
+        return (val, der, -der) if role == "disc" else (val, -der, der)
+
+    def step_disc2(self, real, fake):
+        """train_gan3.py:353 — loss = act(mean(D(real)) - mean(D(fake))); real and fake are separate BatchNorm batches."""
+        D = self.D
+        dev = D.device
+        self._fresh(D)
+        rd, fd = _to_dev(real, dev), _to_dev(fake, dev)
+        sync = _make_sync()
+        dist = _dist()
+        world = dist.get_world_size() if dist else 1
+        sr, tr = D.forward(rd, True, sync)
+        sf, tf = D.forward(fd, True, sync)
+        means = torch.zeros(2, device=dev)
+        ops.mean_prod(sr, None, means[0:1], 1.0, 0.0, None, 1.0)
+        ops.mean_prod(sf, None, means[1:2], 1.0, 0.0, None, 1.0)
+        mr, mf = self._mean_over_ranks(means)
+        val, d_real, d_fake = self._relativistic(mr, mf, "disc")
+        D.ensure_grads().zero_()
+        for scores, tape, coef in ((sr, tr, d_real), (sf, tf, d_fake)):
+            ds = torch.empty_like(scores)
+            ops.mean_prod(scores, None, None, 0.0, coef / world, ds, 1.0)
+            D.backward(tape, ds, True, False, sync)
+        self._reduce_all(D)
+        self._adam(D)
+        return val
+
+    def step_gan2(self, x, real, y_true):
+        """train_gan3.py:354 — outputs [G(x), D(G(x))]; generator loss from D(fake) and D(real), D frozen."""
+        G, D = self.G, self.D
+        dev = G.device
+        self._fresh(G)
+        self._fresh(D)
+        cw, dw = self.weights
+        xd, rd, yt = _to_dev(x, dev), _to_dev(real, dev), _to_dev(y_true, dev)
+        sync = _make_sync()
+        dist = _dist()
+        world = dist.get_world_size() if dist else 1
+        sr, _ = D.forward(rd, True, sync)
+        y, gtape = G.forward_train(xd, sync)
+        sf, dtape = D.forward(y, True, sync)
+        buf = torch.zeros(3, device=dev)
+        ops.mean_prod(sr, None, buf[0:1], 1.0, 0.0, None, 1.0)
+        ops.mean_prod(sf, None, buf[1:2], 1.0, 0.0, None, 1.0)
+        grads = self._content(y, yt, buf[2:3], cw)
+        mr, mf, lc = self._mean_over_ranks(buf)
+        la, _, d_fake = self._relativistic(mr, mf, "gen")
+        ds = torch.empty_like(sf)
+        ops.mean_prod(sf, None, None, 0.0, dw * d_fake / world, ds, 1.0)
+        grads.append(D.backward(dtape, ds, not self.d_frozen, True, sync))
+        dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1], g3=grads[2] if len(grads) > 2 else None)
+        G.ensure_grads().zero_()
+        G.backward(gtape, dz, sync)
+        self._reduce_all(G)
+        self._adam(G)
+        return [cw * lc + dw * la, lc, la]
+
+    def _mean_over_ranks(self, buf):
+        """Device scalars -> host floats (the step's single D2H read); averaged over replicas so every rank reports
+        the global-batch loss."""
+        dist = _dist()
+        if dist is not None:
+            dist.all_reduce(buf)
+            buf = buf / dist.get_world_size()
+        return [float(v) for v in buf.cpu().numpy()]
+
+
+def evaluate_content_loss(loss_obj, y_true, y_pred):
+    """Content loss of two host batches (float): the eager form of VGG_*_LOSS.loss."""
+    c = Compiled("eval", None, None)
+    c.content = ContentLoss(loss_obj.kind, loss_obj.rate, loss_obj.net)
+    dev = loss_obj.net.device
+    buf = torch.zeros(1, device=dev)
+    vgg = loss_obj.net
+    yt, yp = _to_dev(as_batch(y_true), dev), _to_dev(as_batch(y_pred), dev)
+    c._fresh(vgg)
+    ft, fp = vgg.forward(yt), vgg.forward(yp)
+    ops.loss_pair(fp, ft, buf, mae=c.content.mae, weight=1.0, gscale=0.0, grad=None)
+    if loss_obj.kind in ("vgg-mse", "vgg-mae"):
+        ops.loss_pair(yp, yt, buf, mae=c.content.mae, weight=c.content.rate, gscale=0.0, grad=None)
+    return float(buf.item())
+
+
+# ------------------------------------------------------------------------------------------------ compile
+def _leafs(applied):
+    src, chain = applied.chain()
+    nets, models = [], []
+    for m in chain:
+        for leaf in m.leaf_models():
+            nets.append(leaf.net)
+            models.append(leaf)
+    return src, nets, models
+
+
+def compile_model(model, loss, optimizer, loss_weights):
+    from .networks import DiscriminatorSimple512Net, UpscalerOrigNet
+    from . import model as M
+    if model._is_leaf:
+        outs = None
+        nets_per_out = [[model.net]]
+        models_per_out = [[model]]
+        srcs = [model._inputs[0]]
+    else:
+        outs = model._outputs
+        info = [_leafs(o) for o in outs]
+        srcs = [i[0] for i in info]
+        nets_per_out = [i[1] for i in info]
+        models_per_out = [i[2] for i in info]
+    losses = list(loss) if isinstance(loss, (list, tuple)) else [loss]
+    if len(losses) != len(nets_per_out):
+        raise ValueError("When passing a list as loss, it should have one entry per model output")
+
+    def content_of(l):
+        owner = getattr(l, "__self__", None)
+        if isinstance(owner, M._VggLossBase):
+            return ContentLoss(owner.kind, owner.rate, owner.net)
+        raise ValueError("unsupported content loss %r: the B200 path implements VGG_LOSS / VGG_MSE_LOSS / VGG_MAE_LOSS" % (l,))
+
+    isG = lambda n: isinstance(n, UpscalerOrigNet)
+    isD = lambda n: isinstance(n, DiscriminatorSimple512Net)
+    n_in = len(model._inputs)
+    c = None
+    if len(nets_per_out) == 1 and len(nets_per_out[0]) == 1 and isG(nets_per_out[0][0]) and n_in == 1:
+        c = Compiled("gen", model, optimizer)
+        c.G, c.content = nets_per_out[0][0], content_of(losses[0])
+        c.g_frozen = not models_per_out[0][0].trainable
+    elif len(nets_per_out) == 1 and len(nets_per_out[0]) == 1 and isD(nets_per_out[0][0]):
+        D = nets_per_out[0][0]
+        if n_in == 1 and losses[0] is M.wasserstein_loss:
+            c = Compiled("disc", model, optimizer)
+        elif n_in == 2 and isinstance(losses[0], GanLossFn) and losses[0].role == "disc":
+            c = Compiled("disc2", model, optimizer)
+            c.gan_losses = losses[0].owner
+            c.fake_input_index = model._inputs.index(srcs[0])
+        else:
+            raise ValueError("unsupported discriminator loss %r" % (losses[0],))
+        c.D = D
+        c.d_frozen = not models_per_out[0][0].trainable
+    elif len(nets_per_out) == 2 and len(nets_per_out[0]) == 1 and isG(nets_per_out[0][0]) and \
+            len(nets_per_out[1]) == 2 and nets_per_out[1][0] is nets_per_out[0][0] and isD(nets_per_out[1][1]):
+        if n_in == 1 and losses[1] is M.wasserstein_loss:
+            c = Compiled("gan", model, optimizer)
+        elif n_in == 2 and isinstance(losses[1], GanLossFn) and losses[1].role == "gen":
+            c = Compiled("gan2", model, optimizer)
+            c.gan_losses = losses[1].owner
+            c.lr_input_index = model._inputs.index(srcs[0])
+        else:
+            raise ValueError("unsupported adversarial loss %r" % (losses[1],))
+        c.G, c.D = nets_per_out[0][0], nets_per_out[1][1]
+        c.content = content_of(losses[0])
+        c.d_frozen = not models_per_out[1][1].trainable
+        lw = list(loss_weights) if loss_weights is not None else [1.0, 1.0]
+        c.weights = (float(lw[0]), float(lw[1]))
+    if c is None:
+        raise ValueError("compile: this model structure is not one the reference's compile helpers build "
+                         "(model.py:1017-1137); see upscaler/training.py")
+    return c
+
+
+def train_on_batch(model, x, y):
+    c = model._compiled
+    xs = list(x) if isinstance(x, (list, tuple)) else [x]
+    ys = list(y) if isinstance(y, (list, tuple)) else [y]
+    xs = [as_batch(a) for a in xs]
+    if c.kind == "gen":
+        return c.step_gen(xs[0], as_batch(ys[0]))
+    if c.kind == "disc":
+        return c.step_disc(xs[0], ys[0])
+    if c.kind == "gan":
+        return c.step_gan(xs[0], as_batch(ys[0]), ys[1])
+    if c.kind == "disc2":
+        fi = c.fake_input_index
+        return c.step_disc2(xs[1 - fi], xs[fi])
+    if c.kind == "gan2":
+        li = c.lr_input_index
+        return c.step_gan2(xs[li], xs[1 - li], as_batch(ys[0]))
+    raise RuntimeError(c.kind)
