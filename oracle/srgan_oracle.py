@@ -461,6 +461,46 @@ class GanTrainer:
         return ld, lg
 
 
+class Gan2Trainer(GanTrainer):
+    """make_and_compile_gan2 + the train_gan3.py loop body (model.py:1057-1125; train_gan3.py:339-354): the
+    discriminator model takes [real, fake] as two inputs (two separate BatchNorm batches) and its loss is
+    GanLosses.discriminator_loss of the two symbolic outputs; the GAN model takes [x_lr, real] and adds
+    GanLosses.generator_loss, the discriminator being frozen."""
+
+    def __init__(self, *args, family="relativistic", loss_act="log-sigm", **kw):
+        super().__init__(*args, **kw)
+        self.family, self.loss_act = family, loss_act
+
+    def disc_train_on_batch2(self, real, fake):
+        s1, s2 = [], []
+        r = discriminator_simple_512_forward(self.d, real, self.dact, True, s1)
+        f = discriminator_simple_512_forward(self.d, fake, self.dact, True, s2)
+        loss, _ = gan_losses(self.family, self.loss_act, r, f)
+        loss.backward()
+        self.opt_d.apply(_trainable(self.d, "d"))
+        _apply_moving(self.d, discriminator_bn_names(), s1)
+        _apply_moving(self.d, discriminator_bn_names(), s2)
+        return float(loss.detach())
+
+    def gan_train_on_batch2(self, x_lr, real, y_hr):
+        gstats, s1, s2 = [], [], []
+        r = discriminator_simple_512_forward(self.d, real, self.dact, True, s1)
+        y = upscaler_orig_forward(self.g, x_lr, True, gstats, self.uf, self.rbn)
+        f = discriminator_simple_512_forward(self.d, y, self.dact, True, s2)
+        lc = content_loss(self.kind, self.vw, _t(y_hr), y, self.rate)
+        _, la = gan_losses(self.family, self.loss_act, r, f)
+        total = self.cw * lc + self.dw * la
+        total.backward()
+        for ts in self.d.values():
+            for t in ts:
+                t.grad = None
+        self.opt_g.apply(_trainable(self.g, "g"))
+        _apply_moving(self.g, upscaler_bn_names(self.rbn), gstats)
+        _apply_moving(self.d, discriminator_bn_names(), s1)
+        _apply_moving(self.d, discriminator_bn_names(), s2)
+        return [float(total.detach()), float(lc.detach()), float(la.detach())]
+
+
 # ------------------------------------------------------------------------------------------------ tensor I/O contract
 def convert_image_to_array(img_u8):
     """data.py:259-263."""

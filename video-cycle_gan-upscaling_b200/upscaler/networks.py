@@ -657,9 +657,11 @@ class DiscriminatorSimple512Net(Net):
 
     input_name = "discriminator/input"
 
-    def __init__(self, input_shape, activation="none", weights=None, device="cuda", seed=None):
+    def __init__(self, input_shape, activation="none", weights=None, device="cuda", seed=None, dtype=None):
         self.input_shape = tuple(input_shape)
         self.activation = activation
+        if dtype is not None:       # fp16 storage is offered for numerics checks; bf16 (default) has the range a
+            self.train_dtype = dtype  # diverging Wasserstein critic needs (gan_test.ipynb cell 17: |D| up to 2e11)
         specs = discriminator_simple_512_layer_specs(self.input_shape)
         super().__init__(specs, weights, seed, device)
         self.extra_layers = [("discriminator/final/Flatten", "flatten")]
