@@ -73,6 +73,15 @@ int b2_conv2d_transpose_s2_fprop(const void* x, int B, int H, int W, int Cin, co
 int b2_conv2d_rows_fprop(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw,
                          const float* bias, int act, int f16, float* out, void* stream);
 
+/* The same layer (Conv2D(3, 9x9, 'same') + bias + optional tanh, fp32 NHWC output; model.py:290-291) in scatter form:
+ * all 81 taps folded into the GEMM N dimension (P[x,(dy,dx,co)] = sum_c X[x,c] W[dy,dx,c,co], N = 243 -> 256, K = Cin),
+ * then out[y+4-dy, x+4-dx, co] += P summed in the epilogue through warp shuffles and a register ring of 9 partial
+ * rows.  16 full-rate MMAs per 128-pixel row instead of 144 narrow ones; bound by reading x from HBM.
+ *   x: [B,H,W,Cin] 16-bit, Cin in {64,128,192,256};  w: packed [256][Cin], row n = (dy*9+dx)*3+co (rows 243..255 zero);
+ *   bias: [3] fp32 or null;  out: [B,H,W,3] fp32. */
+int b2_conv2d_scatter_fprop(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw,
+                            const float* bias, int act, int f16, float* out, void* stream);
+
 /* Same semantics as b2_conv2d_fprop / b2_conv2d_transpose_s2_fprop on CUDA cores, one thread per output element.
  * Cross-check for the tests; not used by the model path. transposed != 0 selects the Conv2DTranspose form. */
 int b2_conv2d_direct(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw, int stride,

@@ -147,3 +147,25 @@ def test_errors_are_loud():
         ops.conv2d(x, w, 64, 3, 3)  # Cin not a multiple of 64
     with pytest.raises(ValueError):
         ops.conv2d(torch.zeros((1, 8, 8, 64), dtype=torch.float16, device="cuda"), w, 64, 3, 3)  # dtype mismatch
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(1, 24, 40, 256), (2, 9, 150, 256), (1, 3, 5, 256), (1, 20, 96, 128), (1, 31, 257, 64),
+                                   (3, 12, 193, 256)])
+def test_final_conv_scatter(shape, dtype):
+    """final/conv 9x9 Cin->3 + tanh, scatter-form kernel (all 81 taps in the GEMM N dimension, shuffle + register-ring
+    epilogue): ragged widths around the 96-pixel strip, heights below the filter size, several images (segments of
+    the flattened row space crossing image boundaries)."""
+    from upscaler import ops
+    B, H, W, C = shape
+    rng = np.random.default_rng(H * 1000 + W)
+    x = _rnd((B, H, W, C), rng)
+    kern = _rnd((9, 9, C, 3), rng, 1.0 / np.sqrt(81 * C))
+    bias = _rnd((3,), rng, 0.1)
+    ref = torch.tanh(O.conv2d_same(_q(x, dtype).permute(0, 3, 1, 2), _q(kern, dtype), torch.from_numpy(bias)))
+    ref = ref.permute(0, 2, 3, 1).numpy()
+    idx = torch.from_numpy(ops.conv_scatter_pack_index(9, 9, C, 3)).cuda()
+    wp = ops.gather_cast(torch.from_numpy(kern).cuda(), idx, dtype=dtype)
+    y = ops.conv2d_scatter(torch.from_numpy(x).cuda().to(dtype), wp, 3, 9, 9, bias=torch.from_numpy(bias).cuda())
+    torch.cuda.synchronize()
+    _close(y.cpu().numpy(), ref, 1e-3, 1e-3)

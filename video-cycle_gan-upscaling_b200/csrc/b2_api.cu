@@ -168,6 +168,12 @@ int b2_conv2d_rows_fprop(const void* x, int B, int H, int W, int Cin, const void
     return launch_conv_tail(x, B, H, W, Cin, w, Cout, kh, kw, bias, act, f16, out, reinterpret_cast<cudaStream_t>(stream));
 }
 
+int b2_conv2d_scatter_fprop(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw,
+                            const float* bias, int act, int f16, float* out, void* stream) {
+    if (!x || !w || !out) return set_error("b2_conv2d_scatter_fprop: null pointer");
+    return launch_conv_scatter(x, B, H, W, Cin, w, Cout, kh, kw, bias, act, f16, out, reinterpret_cast<cudaStream_t>(stream));
+}
+
 int b2_conv2d_direct(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw, int stride,
                      int transposed, const b2_epilogue* ep, void* stream) {
     if (!x || !w || !ep || !ep->out) return set_error("b2_conv2d_direct: null pointer");

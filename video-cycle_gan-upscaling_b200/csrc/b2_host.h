@@ -55,4 +55,8 @@ int launch_conv_wgrad(const WgradArgs& a, cudaStream_t stream);
 int launch_conv_tail(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int KH, int KW,
                      const float* bias, int act, int f16, float* out, cudaStream_t stream);
 
+// Final 9x9 conv with Cout=3 as one N=256 GEMM per pixel row + register scatter epilogue (b2_conv_scatter.cu).
+int launch_conv_scatter(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int KH, int KW,
+                        const float* bias, int act, int f16, float* out, cudaStream_t stream);
+
 }  // namespace b2

@@ -43,6 +43,8 @@ _SIGNATURES = {
                                      [ctypes.c_int] * 3 + [ctypes.POINTER(Epilogue), ctypes.c_void_p]),
     "b2_conv2d_rows_fprop": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p] + [ctypes.c_int] * 3 +
                              [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]),
+    "b2_conv2d_scatter_fprop": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p] + [ctypes.c_int] * 3 +
+                                [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]),
     "b2_conv2d_direct": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p] + [ctypes.c_int] * 5 +
                          [ctypes.POINTER(Epilogue), ctypes.c_void_p]),
     "b2_fold_taps": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 9 + [ctypes.POINTER(ctypes.c_int)] * 2 +

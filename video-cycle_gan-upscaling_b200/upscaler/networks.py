@@ -342,8 +342,8 @@ class UpscalerOrigNet(Net):
         k = self.kernel_size
         for name, kind, c in self.specs:
             if kind == "conv":
-                if name == "final/conv" and c["kh"] == 9 and c["cout"] == 3 and c["cin"] % 64 == 0 and c["cin"] <= 256:
-                    idx = ops.conv_rows_pack_index(c["kh"], c["kw"], c["cin"], c["cout"])
+                if name == "final/conv" and c["kh"] == 9 and c["kw"] == 9 and c["cout"] == 3 and c["cin"] % 64 == 0 and c["cin"] <= 256:
+                    idx = ops.conv_scatter_pack_index(c["kh"], c["kw"], c["cin"], c["cout"])
                     self._final_rows = True
                 elif c["cin"] < 64:
                     idx = ops.conv_rowfold_pack_index(c["kh"], c["kw"], c["cin"], c["cout"])
@@ -454,7 +454,7 @@ class UpscalerOrigNet(Net):
         if out is None:
             out = torch.empty((B, h, w_, 3), dtype=torch.float32, device=self.device)
         if self._final_rows:
-            return T("final/conv", lambda: ops.conv2d_rows(m, pk["final/conv"], 3, 9, 9, bias=b, act=ops.ACT_TANH, out=out))
+            return T("final/conv", lambda: ops.conv2d_scatter(m, pk["final/conv"], 3, 9, 9, bias=b, act=ops.ACT_TANH, out=out))
         return T("final/conv", lambda: ops.conv2d(m, pk["final/conv"], 3, 9, 9, out=out, shift=b, act=ops.ACT_TANH))
 
     # ---------------------------------------------------------------- training
@@ -496,7 +496,7 @@ class UpscalerOrigNet(Net):
             ups.append(u)
             h_, w_ = 2 * h_, 2 * w_
         tape["ups"] = ups
-        y = ops.conv2d_rows(ups[-1], pk["final/conv"], 3, 9, 9, bias=w["final/conv"][1], act=ops.ACT_TANH)
+        y = ops.conv2d_scatter(ups[-1], pk["final/conv"], 3, 9, 9, bias=w["final/conv"][1], act=ops.ACT_TANH)
         tape["y"] = y
         return y, tape
 

@@ -99,6 +99,25 @@ def conv2d_rows(x, w_rows, cout, kh, kw, bias=None, act=ACT_TANH, out=None):
     return out
 
 
+def conv2d_scatter(x, w_taps, cout, kh, kw, bias=None, act=ACT_TANH, out=None):
+    """Final Conv2D(3, 9x9, 'same') + bias + tanh with fp32 output (reference: model.py:290-291), scatter-form kernel
+    (all taps in the GEMM N dimension).  `w_taps` is packed by conv_scatter_pack_index."""
+    B, H, W, Cin = x.shape
+    f16 = _elem_flag(x, w_taps)
+    if w_taps.numel() != 256 * Cin:
+        raise ValueError("conv2d_scatter: packed weight size mismatch")
+    if out is None:
+        out = torch.empty((B, H, W, cout), dtype=torch.float32, device=x.device)
+    elif tuple(out.shape) != (B, H, W, cout) or out.dtype != torch.float32:
+        raise ValueError("conv2d_scatter: output must be float32 (B,H,W,%d)" % cout)
+    _require_cuda(x, w_taps, out, bias)
+    rc = _lib.load().b2_conv2d_scatter_fprop(_lib.ptr(x), B, H, W, Cin, _lib.ptr(w_taps), cout, kh, kw, _lib.ptr(bias), act,
+                                             f16, _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(rc, "b2_conv2d_scatter_fprop")
+    _count(1)
+    return out
+
+
 def conv2d_transpose_s2(x, w_packed, cout, kh, kw, out=None, scale=None, shift=None, alpha=None, act=ACT_NONE,
                         leaky=0.0, direct=False):
     """Conv2DTranspose(strides=2, padding='same') forward (reference: model.py:72)."""
@@ -490,6 +509,18 @@ def conv_fullfold_pack_index(kh, kw, cin, cout):
     c = np.arange(cin)[None, None, :]
     co = np.arange(cout)[:, None, None]
     idx[:, 0, :kh * kw * cin] = ((t * cin + c) * cout + co).reshape(cout, kh * kw * cin)
+    return idx.astype(np.int32)
+
+
+def conv_scatter_pack_index(kh, kw, cin, cout):
+    """Keras Conv2D kernel (kh,kw,Cin,Cout) -> packed [256][Cin] for conv2d_scatter: row n = (dy*kw + dx)*Cout + co."""
+    if kh * kw * cout > 256:
+        raise ValueError("conv_scatter needs kh*kw*Cout <= 256")
+    idx = -np.ones((256, cin), np.int64)
+    t = np.arange(kh * kw)[:, None, None]
+    co = np.arange(cout)[None, :, None]
+    c = np.arange(cin)[None, None, :]
+    idx[:kh * kw * cout] = ((t * cin + c) * cout + co).reshape(kh * kw * cout, cin)
     return idx.astype(np.int32)
 
 
