@@ -169,3 +169,59 @@ def test_final_conv_scatter(shape, dtype):
     y = ops.conv2d_scatter(torch.from_numpy(x).cuda().to(dtype), wp, 3, 9, 9, bias=torch.from_numpy(bias).cuda())
     torch.cuda.synchronize()
     _close(y.cpu().numpy(), ref, 1e-3, 1e-3)
+
+
+STACK_CASES = [
+    # B, H, W, kh, kw, epilogue  -- all Cin = Cout = 64, stride 1: shapes the row-stacked kernel (b2_conv_stack.cu) takes
+    (1, 96, 24, 3, 3, "prelu"),        # R = 3, whole tiles
+    (2, 92, 21, 3, 3, "residual"),     # R = 3, ragged bottom rows and right columns
+    (1, 60, 30, 3, 3, "residual"),     # R = 2 (48-row tiles would waste too much)
+    (2, 47, 16, 9, 1, "prelu"),        # the folded 9x1 head conv
+    (1, 48, 40, 3, 3, "gate"),         # dgrad form: ReLU gate + residual, bf16
+    (1, 144, 8, 1, 3, "fp32"),         # 1x3 filter, fp32 output, several tiles per column strip
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("case", STACK_CASES)
+def test_conv2d_row_stacked(case, dtype):
+    """Cout = 64 stride-1 convs run with R output rows stacked in the GEMM N dimension; same oracle, same tolerance,
+    and bit-for-bit the same taps as the plain implicit GEMM (cross-checked against the CUDA-core direct kernel)."""
+    from upscaler import ops
+    B, H, W, kh, kw, mode = case
+    C = 64
+    rng = np.random.default_rng(abs(hash(case)) % 2 ** 31)
+    x = _rnd((B, H, W, C), rng)
+    kern = _rnd((kh, kw, C, C), rng, 1.0 / np.sqrt(kh * kw * C))
+    scale = rng.uniform(0.5, 1.5, C).astype(np.float32)
+    shift = _rnd((C,), rng, 0.1)
+    alpha = rng.uniform(0, 0.3, C).astype(np.float32)
+    res = _rnd((B, H, W, C), rng)
+    gate = _rnd((B, H, W, C), rng)
+    xq, kq = _q(x, dtype), _q(kern, dtype)
+    ref = O.conv2d_same(xq.permute(0, 3, 1, 2), kq, None, stride=1)
+    ref = ref * torch.from_numpy(scale).view(1, -1, 1, 1) + torch.from_numpy(shift).view(1, -1, 1, 1)
+    kwargs = dict(scale=torch.from_numpy(scale).cuda(), shift=torch.from_numpy(shift).cuda())
+    if mode == "prelu":
+        ref = O.prelu(ref, torch.from_numpy(alpha))
+        kwargs.update(alpha=torch.from_numpy(alpha).cuda(), act=ops.ACT_PRELU)
+    if mode == "gate":
+        gq = _q(gate, dtype).permute(0, 3, 1, 2)
+        ref = torch.where(gq > 0, ref, ref * 0.2)
+        kwargs.update(gate=torch.from_numpy(gate).cuda().to(dtype), gate_slope=0.2)
+    if mode in ("residual", "gate"):
+        ref = ref + _q(res, dtype).permute(0, 3, 1, 2)
+        kwargs.update(residual=torch.from_numpy(res).cuda().to(dtype))
+    if mode == "fp32":
+        kwargs.update(out_dtype=torch.float32)
+    ref = ref.permute(0, 2, 3, 1).numpy()
+    idx = torch.from_numpy(ops.conv_pack_index(kh, kw, C, C)).cuda()
+    wp = ops.gather_cast(torch.from_numpy(kern).cuda(), idx, dtype=dtype)
+    xd = torch.from_numpy(x).cuda().to(dtype)
+    y = ops.conv2d(xd, wp, C, kh, kw, **kwargs)
+    yd = ops.conv2d(xd, wp, C, kh, kw, direct=True, **kwargs)
+    torch.cuda.synchronize()
+    assert tuple(y.shape) == ref.shape
+    tol = 1e-3 if mode == "fp32" else (4e-3 if dtype == torch.float16 else 2e-2)
+    _close(y.float().cpu().numpy(), ref, tol, 1e-2)
+    _close(y.float().cpu().numpy(), yd.float().cpu().numpy(), tol, 1e-2)

@@ -437,6 +437,79 @@ static void run_mma2_n() {
                double(cyc) / (iters * 4));
     }
 }
+// ============================================================== experiment 4c: MMA rate vs number of accumulators
+// Same as 4b, but consecutive MMA groups rotate over `nacc` different TMEM accumulators: tells whether the ~80-cycle
+// floor for N <= 128 is a dependency on the accumulator (then interleaving two tiles hides it) or an operand-fetch limit.
+// mode 0: rotate the accumulator per group of 4 K-steps; mode 1: rotate per single MMA.
+template <int N>
+__global__ void __launch_bounds__(128, 1) probe_mma3_kernel(int iters, int nacc, int mode, long long* cycles) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sA = smem;
+    uint8_t* sB = smem + 65536;
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(smem + 65536 + 98304);
+    uint32_t* slot = reinterpret_cast<uint32_t*>(mbar + 1);
+    for (int i = threadIdx.x; i < (65536 + 98304) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u + i;
+    fence_proxy_async();
+    const int warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { mbar_init(mbar, 1); fence_mbar_init(); }
+    if (warp == 0) tmem_alloc<512>(slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *slot;
+    if (threadIdx.x == 0) {
+        const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
+        const long long t0 = clock64();
+        int acc = 0;
+        for (int i = 0; i < iters; ++i) {
+            const int tap = i % 9;
+            const uint32_t a = a0 + uint32_t((tap / 3) * 10 + (tap % 3)) * 128u;
+            const uint32_t b = b0 + uint32_t(tap % 6) * N * 128;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                umma_bf16(tmem + uint32_t(acc) * N, make_sdesc_k_sw128(a + k * 32, 1280), make_sdesc_k_sw128(b + k * 32, 1024),
+                          make_idesc_bf16(128, N), 1);
+                if (mode == 1) { if (++acc == nacc) acc = 0; }
+            }
+            if (mode == 0) { if (++acc == nacc) acc = 0; }
+        }
+        umma_commit(mbar);
+        mbar_wait(mbar, 0);
+        const long long t1 = clock64();
+        if (blockIdx.x == 0) *cycles = t1 - t0;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<512>(tmem);
+}
+
+template <int N>
+static void run_mma3_n() {
+    long long* dC;
+    CK(cudaMalloc(&dC, 8));
+    const int smem = 65536 + 98304 + 2048;
+    CK(cudaFuncSetAttribute(probe_mma3_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const int iters = 2048;
+    for (int mode = 0; mode < 2; ++mode)
+        for (int nacc = 1; nacc <= 4 && nacc * N <= 512; nacc *= 2) {
+            for (int rep = 0; rep < 2; ++rep) {
+                probe_mma3_kernel<N><<<148, 128, smem>>>(iters, nacc, mode, dC);
+                CK(cudaDeviceSynchronize());
+            }
+            long long cyc;
+            CK(cudaMemcpy(&cyc, dC, 8, cudaMemcpyDeviceToHost));
+            printf("MMA3 N=%d nacc=%d mode=%d: %.1f cycles/MMA\n", N, nacc, mode, double(cyc) / (iters * 4));
+        }
+}
+static int run_mma3() {
+    run_mma3_n<64>();
+    run_mma3_n<128>();
+    run_mma3_n<192>();
+    run_mma3_n<256>();
+    return 0;
+}
+
 static int run_mma2() {
     run_mma2_n<32>();
     run_mma2_n<64>();
@@ -632,6 +705,7 @@ int main(int argc, char** argv) {
     if (!strcmp(what, "tma")) return run_tma();
     if (!strcmp(what, "mma")) return run_mma();
     if (!strcmp(what, "mma2")) return run_mma2();
+    if (!strcmp(what, "mma3")) return run_mma3();
     if (!strcmp(what, "conv")) return run_conv();
     if (!strcmp(what, "time")) return run_time(argc > 2 ? atoi(argv[2]) : -1);
     printf("unknown experiment %s\n", what);

@@ -241,6 +241,8 @@ static int launch_bn(const CUtensorMap& mapA, const CUtensorMap& mapB, const Ige
 
 int launch_conv_igemm(const ConvIgemmArgs& a, cudaStream_t stream) {
     static const bool no_halo = getenv("B2_NO_HALO") != nullptr;   // A/B switch for profiling the two main loops
+    static const bool no_stack = getenv("B2_NO_STACK") != nullptr;
+    if (!no_halo && !no_stack && conv_stack_applicable(a)) return launch_conv_stack(a, stream);
     if (!no_halo && conv_halo_applicable(a)) return launch_conv_halo(a, stream);
     IgemmParams p = a.p;
     if (a.xC % 64 != 0 || p.cin != a.xC) return set_error("igemm: Cin=%d must be a multiple of 64", a.xC);

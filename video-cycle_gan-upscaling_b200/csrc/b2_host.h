@@ -37,6 +37,11 @@ int launch_conv_direct(const ConvIgemmArgs& a, cudaStream_t stream);
 bool conv_halo_applicable(const ConvIgemmArgs& a);
 int launch_conv_halo(const ConvIgemmArgs& a, cudaStream_t stream);
 
+// Row-stacked variant for Cout = 64 (b2_conv_stack.cu): R vertically adjacent output rows share one accumulator row, so
+// the MMAs run at N = 64..192 instead of 64.
+bool conv_stack_applicable(const ConvIgemmArgs& a);
+int launch_conv_stack(const ConvIgemmArgs& a, cudaStream_t stream);
+
 // Weight gradient (b2_conv_wgrad.cu): dw[wtap[t]][cx][cz] += sum_p x[p*in_mul + d(t), cx] * dz[p, cz], fp32 accumulate.
 struct WgradArgs {
     const void* x;   // [xB, xH, xW, cx] 16-bit

@@ -500,10 +500,13 @@ class UpscalerOrigNet(Net):
         tape["y"] = y
         return y, tape
 
-    def backward(self, tape, dz_final, sync=None):
+    def backward(self, tape, dz_final, sync=None, on_ready=None):
         """dz_final: fp32 (B,4H,4W,3) gradient w.r.t. the final conv's pre-tanh output (ops.tanh_bwd of the loss
-        gradients).  Accumulates every weight gradient into the flat gradient buffer."""
+        gradients).  Accumulates every weight gradient into the flat gradient buffer.  `on_ready(offset)` is called
+        whenever every gradient at flat offsets >= offset is final (the flat layout follows the graph order, backward
+        walks it from the tail), so a data-parallel caller can all-reduce that slice while the rest still runs."""
         self.ensure_grads()
+        ready = on_ready if on_ready is not None else (lambda off: None)
         k, f, dt = self.kernel_size, self.filters, self.train_dtype
         pk, w, g = self._packed["train"], self.weights, self.grads
         new = lambda shape: torch.empty(shape, dtype=dt, device=self.device)
@@ -534,6 +537,7 @@ class UpscalerOrigNet(Net):
             else:
                 d = ops.conv2d(d, pk[n + "#dgrad"], cin, k, k, stride=2, out=new(tuple(xin.shape)))
         dt_ = d      # gradient w.r.t. t = skip + BN(prefinal conv): flows into both the trunk and the head skip
+        ready(self.offsets[("upscaling/0/block/conv_transp", 0)][0])
         # ---- prefinal conv + BN
         dzp = self._bn_backward(tape, "prefinal", "prefinal/batch_norm", dt_, new(tuple(dt_.shape)), ops.ACT_NONE, sync=sync)
         m_in = tape["prefinal/in"]
@@ -550,6 +554,8 @@ class UpscalerOrigNet(Net):
                                     alpha=w[n + "/prelu"][0].reshape(-1), dalpha=g[n + "/prelu"][0].reshape(-1), sync=sync)
             ops.conv2d_wgrad(m_in, dz1, k, k, 1, g[n + "/conv_pre"][0])
             gm = ops.conv2d(dz1, pk[n + "/conv_pre#dgrad"], f, k, k, out=dh, residual=gm)
+            if i == self.res_block_num // 2:
+                ready(self.offsets[(n + "/conv_pre", 0)][0])
         # ---- head: PReLU backward (dbias = sum dy, dalpha), then the weight gradient of the row-folded 9x1 conv
         xp, u0 = tape["head"]
         a0 = w["initial/prelu"][0].reshape(-1)
@@ -561,6 +567,7 @@ class UpscalerOrigNet(Net):
         raw.zero_()
         ops.conv2d_wgrad(xp, dz0, 9, 1, 1, raw)
         ops.gather_f32(raw, self._head_wgrad_idx, g["initial/conv"][0], accumulate=True)
+        ready(0)
 
 
 class Vgg19Net(Net):
@@ -740,9 +747,11 @@ class DiscriminatorSimple512Net(Net):
     def forward_infer(self, x, out=None):
         return self.forward(x, False)[0]
 
-    def backward(self, tape, dscore, want_wgrad=True, want_input_grad=False, sync=None):
+    def backward(self, tape, dscore, want_wgrad=True, want_input_grad=False, sync=None, on_ready=None):
         """dscore: (n,1) fp32 gradient w.r.t. the scores.  Accumulates weight gradients unless the discriminator is
-        frozen (gan_train, model.py:1040); returns the gradient w.r.t. the input image (fp32) when asked."""
+        frozen (gan_train, model.py:1040); returns the gradient w.r.t. the input image (fp32) when asked.
+        `on_ready(offset)`: see UpscalerOrigNet.backward (the dense head, most of the parameters, is ready first)."""
+        ready = on_ready if (on_ready is not None and want_wgrad) else (lambda off: None)
         dt, pk, w = self.train_dtype, self._packed["train"], self.weights
         if want_wgrad:
             self.ensure_grads()
@@ -759,6 +768,7 @@ class DiscriminatorSimple512Net(Net):
             if want_wgrad:
                 ops.dense_bwd_weight(dins[j], d, g[name][0], g[name][1])
             d = ops.dense_bwd_data(d, w[name][0], torch.empty((n, c["cin"]), dtype=dt, device=self.device))
+        ready(self.offsets[(self._dense[0][0], 0)][0])
         ins = tape["ins"]
         last = self._conv_geom[-1]
         d = d.view(n, last[3][0], last[3][1], last[1]["cout"])
@@ -777,6 +787,7 @@ class DiscriminatorSimple512Net(Net):
                     raw.zero_()
                     ops.conv2d_wgrad(ins[0], dz, 1, 1, 1, raw)
                     ops.gather_f32(raw, self._first_wgrad_idx, g[name][0], accumulate=True)
+                ready(0)
                 if want_input_grad:
                     return ops.conv2d(dz, pk[name + "#dgrad"], c["cin"], 3, 3,
                                       out=torch.empty((n, h, w_, c["cin"]), dtype=torch.float32, device=self.device))

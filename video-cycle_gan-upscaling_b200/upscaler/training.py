@@ -91,27 +91,50 @@ def _make_sync():
 
 
 class GradReducer:
-    """Bucketed sum-all-reduce of a flat gradient buffer, overlapped with the rest of backward on a side stream."""
+    """Bucketed sum-all-reduce of a flat gradient buffer, overlapped with the rest of backward: the networks' backward
+    passes call `hook(offset)` when every gradient at flat offsets >= offset is final; the slice [offset, previous
+    offset) is then all-reduced on a side stream (ordered after the kernels already enqueued on the compute stream)
+    while backward keeps running.  Adam waits for the buckets' events.  Slices smaller than `min_elems` are merged
+    into the next bucket (launch latency, not link count, sizes a bucket on NVSwitch)."""
 
-    def __init__(self, n_buckets=3):
-        self.n_buckets = n_buckets
+    def __init__(self, min_elems=1 << 17):
+        self.min_elems = min_elems
         self.stream = None
         self.pending = []
+        self.log = []          # (lo, hi) of the buckets of the last step (tests, DESIGN.md)
+
+    def hook(self, flat, n):
+        """Returns on_ready(offset) for one backward pass over `flat[:n]`."""
+        state = {"hi": n}
+        self.log = []
+
+        def on_ready(offset):
+            lo, hi = int(offset), state["hi"]
+            if hi - lo < self.min_elems and lo > 0:
+                return
+            if hi > lo:
+                self.reduce_slice(flat, lo, hi)
+                state["hi"] = lo
+        return on_ready
 
     def reduce_slice(self, flat, lo, hi):
+        self.log.append((lo, hi))
         dist = _dist()
         if dist is None or hi <= lo:
             return
-        if self.stream is None:
-            self.stream = torch.cuda.Stream()
-        ev = torch.cuda.Event()
-        ev.record()
-        self.stream.wait_event(ev)
-        with torch.cuda.stream(self.stream):
+        if flat.is_cuda:
+            if self.stream is None:
+                self.stream = torch.cuda.Stream()
+            ev = torch.cuda.Event()
+            ev.record()
+            self.stream.wait_event(ev)
+            with torch.cuda.stream(self.stream):
+                dist.all_reduce(flat[lo:hi])
+                done = torch.cuda.Event()
+                done.record()
+            self.pending.append(done)
+        else:       # gloo (CPU tests of the host logic): synchronous
             dist.all_reduce(flat[lo:hi])
-            done = torch.cuda.Event()
-            done.record()
-        self.pending.append(done)
 
     def wait(self):
         for ev in self.pending:
@@ -181,14 +204,6 @@ class Compiled:
             grads.append(gpix)
         return grads
 
-    def _reduce_all(self, net):
-        """Sum-all-reduce of the flat gradients in graph-ordered buckets (no-op on one GPU)."""
-        if _dist() is None:
-            return
-        n, nb = net.n_trainable, self.reducer.n_buckets
-        for b in reversed(range(nb)):
-            self.reducer.reduce_slice(net.grad_flat, n * b // nb, n * (b + 1) // nb)
-
     # -------------------------------------------------------------- steps
     def step_gen(self, x, y_true):
         G = self.G
@@ -201,8 +216,7 @@ class Compiled:
         grads = self._content(y, yt, loss, 1.0)
         dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1] if len(grads) > 1 else None)
         G.ensure_grads().zero_()
-        G.backward(tape, dz, sync)
-        self._reduce_all(G)
+        G.backward(tape, dz, sync, on_ready=self.reducer.hook(G.grad_flat, G.n_trainable))
         self._adam(G)
         return self._mean_over_ranks(loss)[0]
 
@@ -219,8 +233,7 @@ class Compiled:
         dist = _dist()
         ops.mean_prod(scores, yd, loss, 1.0, 1.0 / (dist.get_world_size() if dist else 1), ds)
         D.ensure_grads().zero_()
-        D.backward(tape, ds, True, False, sync)
-        self._reduce_all(D)
+        D.backward(tape, ds, True, False, sync, on_ready=self.reducer.hook(D.grad_flat, D.n_trainable))
         self._adam(D)
         return self._mean_over_ranks(loss)[0]
 
@@ -244,8 +257,7 @@ class Compiled:
         grads.append(D.backward(dtape, ds, not self.d_frozen, True, sync))
         dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1], g3=grads[2] if len(grads) > 2 else None)
         G.ensure_grads().zero_()
-        G.backward(gtape, dz, sync)
-        self._reduce_all(G)
+        G.backward(gtape, dz, sync, on_ready=self.reducer.hook(G.grad_flat, G.n_trainable))
         self._adam(G)
         lc, la = self._mean_over_ranks(losses)
         return [cw * lc + dw * la, lc, la]
@@ -280,8 +292,9 @@ class Compiled:
         for scores, tape, coef in ((sr, tr, d_real), (sf, tf, d_fake)):
             ds = torch.empty_like(scores)
             ops.mean_prod(scores, None, None, 0.0, coef / world, ds, 1.0)
-            D.backward(tape, ds, True, False, sync)
-        self._reduce_all(D)
+            # the two passes accumulate into the same buffer: only the second one's slices are final
+            D.backward(tape, ds, True, False, sync,
+                       on_ready=self.reducer.hook(D.grad_flat, D.n_trainable) if scores is sf else None)
         self._adam(D)
         return val
 
@@ -310,8 +323,7 @@ class Compiled:
         grads.append(D.backward(dtape, ds, not self.d_frozen, True, sync))
         dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1], g3=grads[2] if len(grads) > 2 else None)
         G.ensure_grads().zero_()
-        G.backward(gtape, dz, sync)
-        self._reduce_all(G)
+        G.backward(gtape, dz, sync, on_ready=self.reducer.hook(G.grad_flat, G.n_trainable))
         self._adam(G)
         return [cw * lc + dw * la, lc, la]
 
