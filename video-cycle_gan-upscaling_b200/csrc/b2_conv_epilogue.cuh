@@ -11,11 +11,10 @@ constexpr int kMaxChan = 1024;  // widest layer on the path (discriminator Dense
 // 16-bit element helpers: the storage type is bf16 or IEEE fp16, chosen per launch (IgemmParams::f16).
 __device__ __forceinline__ uint32_t pack2(float a, float b, int f16) {
     if (f16) {
-        // clamp to the finite half range so a stray large activation saturates instead of becoming inf
-        a = fminf(fmaxf(a, -65504.f), 65504.f);
-        b = fminf(fmaxf(b, -65504.f), 65504.f);
-        const __half2 h = __floats2half2_rn(a, b);
-        return *reinterpret_cast<const uint32_t*>(&h);
+        // saturate to the finite half range (one F2FP.SATFINITE) so a stray large activation never becomes inf
+        uint32_t r;
+        asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+        return r;
     }
     const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<const uint32_t*>(&h);
@@ -75,46 +74,47 @@ __device__ __forceinline__ void epilogue_tile(const IgemmParams& p, uint32_t tad
             v[4 * g + 2] = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g + 2]), sc.z, sh.z), p.leaky, al.z);
             v[4 * g + 3] = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g + 3]), sc.w, sh.w), p.leaky, al.w);
         }
-        const bool vec = (!p.out_fp32) && ((p.out_ld & 7) == 0) && (n0 + c0 + CH <= p.n_valid);
+        // 32-byte accesses: this thread's pixel row shares no 128-byte line with its neighbours', so the LSU cost is per
+        // (instruction, line); 256-bit LDG/STG halve the instruction count (measured on the residual-trunk convs).
+        const bool vec = (!p.out_fp32) && ((p.out_ld & 15) == 0) && (n0 + c0 + CH <= p.n_valid);
         if (vec) {
             if (p.gate) {
-                const uint4* gp = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.gate) + obase + c0);
-                uint4 gv[CH / 8];
+                const __nv_bfloat16* gp = reinterpret_cast<const __nv_bfloat16*>(p.gate) + obase + c0;
+                uint8v gv[CH / 16];
 #pragma unroll
-                for (int g = 0; g < CH / 8; ++g) gv[g] = __ldg(gp + g);
+                for (int g = 0; g < CH / 16; ++g) gv[g] = ldg256(gp + 16 * g);
 #pragma unroll
-                for (int g = 0; g < CH / 8; ++g) {
+                for (int g = 0; g < CH / 16; ++g) {
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const float2 f = unpack2(reinterpret_cast<const uint32_t*>(&gv[g])[e], p.f16);
-                        if (!(f.x > 0.f)) v[g * 8 + 2 * e] *= p.gate_slope;
-                        if (!(f.y > 0.f)) v[g * 8 + 2 * e + 1] *= p.gate_slope;
+                    for (int e = 0; e < 8; ++e) {
+                        const float2 f = unpack2(gv[g].v[e], p.f16);
+                        if (!(f.x > 0.f)) v[g * 16 + 2 * e] *= p.gate_slope;
+                        if (!(f.y > 0.f)) v[g * 16 + 2 * e + 1] *= p.gate_slope;
                     }
                 }
             }
             if (p.residual) {
-                const uint4* rp = reinterpret_cast<const uint4*>(p.residual + obase + c0);
-                uint4 rv[CH / 8];
+                const __nv_bfloat16* rp = p.residual + obase + c0;
+                uint8v rv[CH / 16];
 #pragma unroll
-                for (int g = 0; g < CH / 8; ++g) rv[g] = __ldg(rp + g);
+                for (int g = 0; g < CH / 16; ++g) rv[g] = ldg256(rp + 16 * g);
 #pragma unroll
-                for (int g = 0; g < CH / 8; ++g) {
+                for (int g = 0; g < CH / 16; ++g) {
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const float2 f = unpack2(reinterpret_cast<const uint32_t*>(&rv[g])[e], p.f16);
-                        v[g * 8 + 2 * e] += f.x;
-                        v[g * 8 + 2 * e + 1] += f.y;
+                    for (int e = 0; e < 8; ++e) {
+                        const float2 f = unpack2(rv[g].v[e], p.f16);
+                        v[g * 16 + 2 * e] += f.x;
+                        v[g * 16 + 2 * e + 1] += f.y;
                     }
                 }
             }
-            uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + obase + c0);
+            __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + obase + c0;
 #pragma unroll
-            for (int g = 0; g < CH / 8; ++g) {
-                uint4 o;
-                uint32_t* h = reinterpret_cast<uint32_t*>(&o);
+            for (int g = 0; g < CH / 16; ++g) {
+                uint8v o;
 #pragma unroll
-                for (int e = 0; e < 4; ++e) h[e] = pack2(v[g * 8 + 2 * e], v[g * 8 + 2 * e + 1], p.f16);
-                op[g] = o;
+                for (int e = 0; e < 8; ++e) o.v[e] = pack2(v[g * 16 + 2 * e], v[g * 16 + 2 * e + 1], p.f16);
+                stg256(op + 16 * g, o);
             }
         } else {
 #pragma unroll

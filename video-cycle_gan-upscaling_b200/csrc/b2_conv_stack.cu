@@ -19,7 +19,8 @@
 // per instruction): the (dx = 0, cb = 0) strip is placed last in shared memory and followed by R-1 blocks of zeros, so
 // that group runs at N = 64R with B = [W(ky=0) | 0 | ... | 0]; every other MMA accumulates.
 //
-// Warp roles: 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..5 = epilogue (one TMEM lane quarter each).
+// Warp roles: 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..9 = epilogue (TMEM lane quarter = warp % 4, channel
+// half = (warp - 2) / 4).
 #include <string.h>
 
 #include "b2_conv_epilogue.cuh"
@@ -29,7 +30,7 @@
 
 namespace b2 {
 
-constexpr int kStackThreads = 192;
+constexpr int kStackThreads = 320;          // TMA warp, MMA warp, 8 epilogue warps
 constexpr int kStackTW = 8;                    // pixels per row group (one 8-row swizzle atom)
 constexpr int kStackGroups = 16;               // row groups per M = 128 tile
 constexpr int kStackMaxK = 9;                  // filter rows / columns supported
@@ -50,22 +51,78 @@ struct StackGeom {
     uint8_t i0[kStackMaxShifts];          //            first weight block of the descending-ky strip
 };
 
-// One 128 x 64 accumulator block -> one output pixel (64 channels) per thread.  `res` holds the pixel's residual row,
-// prefetched by the caller one block ahead so its global-memory latency hides behind the previous block's work.
-template <int ACT>
-__device__ __forceinline__ void stack_epilogue_block(const IgemmParams& p, uint32_t ta, bool valid, size_t obase,
-                                                     const uint4 (&res)[8], const float* s_scale, const float* s_shift,
-                                                     const float* s_alpha) {
+// Epilogue warp main loop.  Eight epilogue warps: warp (quarter, half) owns TMEM lanes [32*quarter, +32) and channels
+// [32*half, +32) of each of the R stacked output pixels of an accumulator row, so two warps per scheduler overlap one
+// another's TMEM-load and global-load latency.  The residual row of block j+1 is prefetched while block j is processed.
+// F16 / ACT are compile-time so the per-element path carries no uniform branches; the j loop stays rolled (a fully
+// unrolled epilogue measured 24 % of its stall samples as instruction-cache misses).
+template <int R, int ACT, int F16>
+__device__ __forceinline__ void stack_epilogue_loop(const IgemmParams& p, uint32_t tmem_base, uint64_t* tfull, uint64_t* tempty,
+                                                    int quarter, int half, int lane, const float* s_scale,
+                                                    const float* s_shift, const float* s_alpha) {
+    constexpr int kAccCols = 64 * R;
+    const int row = quarter * 32 + lane;
+    const int r_tx = row % kStackTW, r_g = row / kStackTW;
+    const float4* sc4 = reinterpret_cast<const float4*>(s_scale + 32 * half);
+    const float4* sh4 = reinterpret_cast<const float4*>(s_shift + 32 * half);
+    const float4* al4 = reinterpret_cast<const float4*>(s_alpha + 32 * half);
+    const bool has_res = p.residual != nullptr, has_gate = p.gate != nullptr;
+    const size_t row_pitch = size_t(p.OW) * size_t(p.out_ld);
+    int as = 0; uint32_t aph = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        int t = tile;
+        const int xt = t % p.tiles_x; t /= p.tiles_x;
+        const int yt = t % p.tiles_y; t /= p.tiles_y;
+        const int gx = xt * kStackTW + r_tx;
+        const int gy0 = yt * (kStackGroups * R) + r_g * R;
+        size_t obase = ((size_t(t) * p.OH + size_t(gy0)) * p.OW + size_t(gx)) * size_t(p.out_ld) + size_t(32 * half);
+        uint8v nxt[2];
 #pragma unroll
-    for (int half = 0; half < 2; ++half) {
-        uint32_t r[32];
-        tmem_ld32(ta + 32 * half, r);
-        tmem_ld_wait();
-        if (valid) {
+        for (int g = 0; g < 2; ++g)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) nxt[g].v[e] = 0;
+        if (has_res && gx < p.W && gy0 < p.H) {
+            nxt[0] = ldg256(p.residual + obase);
+            nxt[1] = ldg256(p.residual + obase + 16);
+        }
+        if (has_res && half == 0 && tile + int(gridDim.x) < p.num_tiles) {
+            // pull the NEXT tile's residual rows into L2 a whole tile ahead (they were written two layers ago and have
+            // usually left L2); the register prefetch one block ahead then only has to cover an L2 hit
+            int t2 = tile + int(gridDim.x);
+            const int xt2 = t2 % p.tiles_x; t2 /= p.tiles_x;
+            const int yt2 = t2 % p.tiles_y; t2 /= p.tiles_y;
+            const int gx2 = xt2 * kStackTW + r_tx, gy2 = yt2 * (kStackGroups * R) + r_g * R;
+            if (gx2 < p.W) {
+                const __nv_bfloat16* rp = p.residual + ((size_t(t2) * p.OH + size_t(gy2)) * p.OW + size_t(gx2)) * size_t(p.out_ld);
+#pragma unroll
+                for (int j = 0; j < R; ++j)
+                    if (gy2 + j < p.H) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + size_t(j) * row_pitch));
+            }
+        }
+        mbar_wait(&tfull[as], aph);
+        tc_fence_after();
+        uint32_t ta = tmem_base + (uint32_t(quarter * 32) << 16) + uint32_t(as * kAccCols + 32 * half);
+#pragma unroll 1
+        for (int j = 0; j < R; ++j, obase += row_pitch, ta += 64) {
+            uint32_t r[32];
+            __syncwarp();       // rows outside the image skip the tail of the previous iteration
+            tmem_ld32(ta, r);
+            uint8v cur[2];
+            cur[0] = nxt[0];
+            cur[1] = nxt[1];
+            const bool valid = gx < p.W && gy0 + j < p.H;
+            if (has_res && j + 1 < R && gx < p.W && gy0 + j + 1 < p.H) {
+                nxt[0] = ldg256(p.residual + obase + row_pitch);
+                nxt[1] = ldg256(p.residual + obase + row_pitch + 16);
+            }
+            uint8v gv[2];
+            if (has_gate && valid) {
+                gv[0] = ldg256(reinterpret_cast<const __nv_bfloat16*>(p.gate) + obase);
+                gv[1] = ldg256(reinterpret_cast<const __nv_bfloat16*>(p.gate) + obase + 16);
+            }
+            tmem_ld_wait();
+            if (!valid) continue;
             float v[32];
-            const float4* sc4 = reinterpret_cast<const float4*>(s_scale + 32 * half);
-            const float4* sh4 = reinterpret_cast<const float4*>(s_shift + 32 * half);
-            const float4* al4 = reinterpret_cast<const float4*>(s_alpha + 32 * half);
 #pragma unroll
             for (int g = 0; g < 8; ++g) {
                 const float4 sc = sc4[g], sh = sh4[g];
@@ -76,96 +133,63 @@ __device__ __forceinline__ void stack_epilogue_block(const IgemmParams& p, uint3
                 v[4 * g + 2] = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g + 2]), sc.z, sh.z), p.leaky, al.z);
                 v[4 * g + 3] = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g + 3]), sc.w, sh.w), p.leaky, al.w);
             }
-            if (p.gate) {
-                const uint4* gp = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.gate) + obase + 32 * half);
-                uint4 gv[4];
-#pragma unroll
-                for (int g = 0; g < 4; ++g) gv[g] = __ldg(gp + g);
+            if (has_gate) {
 #pragma unroll
                 for (int g = 0; g < 4; ++g)
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
-                        const float2 f = unpack2(reinterpret_cast<const uint32_t*>(&gv[g])[e], p.f16);
+                        const float2 f = unpack2(gv[g >> 1].v[(g & 1) * 4 + e], F16);
                         if (!(f.x > 0.f)) v[g * 8 + 2 * e] *= p.gate_slope;
                         if (!(f.y > 0.f)) v[g * 8 + 2 * e + 1] *= p.gate_slope;
                     }
             }
-            if (p.residual) {
+            if (has_res) {
 #pragma unroll
                 for (int g = 0; g < 4; ++g)
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
-                        const float2 f = unpack2(reinterpret_cast<const uint32_t*>(&res[4 * half + g])[e], p.f16);
+                        const float2 f = unpack2(cur[g >> 1].v[(g & 1) * 4 + e], F16);
                         v[g * 8 + 2 * e] += f.x;
                         v[g * 8 + 2 * e + 1] += f.y;
                     }
             }
             if (!p.out_fp32) {
-                uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + obase + 32 * half);
+                __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + obase;
 #pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    uint4 o;
-                    uint32_t* h = reinterpret_cast<uint32_t*>(&o);
+                for (int g = 0; g < 2; ++g) {
+                    uint8v o;
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) h[e] = pack2(v[g * 8 + 2 * e], v[g * 8 + 2 * e + 1], p.f16);
-                    op[g] = o;
+                    for (int e = 0; e < 8; ++e) o.v[e] = pack2(v[g * 16 + 2 * e], v[g * 16 + 2 * e + 1], F16);
+                    stg256(op + 16 * g, o);
                 }
             } else {
-                float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + obase + 32 * half);
+                float* op = reinterpret_cast<float*>(p.out) + obase;
 #pragma unroll
-                for (int g = 0; g < 8; ++g) op[g] = make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+                for (int g = 0; g < 4; ++g) {
+                    uint8v o;
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) o.v[e] = __float_as_uint(v[8 * g + e]);
+                    stg256(op + 8 * g, o);
+                }
             }
-        }
-    }
-}
-
-// Epilogue warp main loop: R output pixels (vertically adjacent) per accumulator row.
-template <int R, int ACT>
-__device__ __forceinline__ void stack_epilogue_loop(const IgemmParams& p, uint32_t tmem_base, uint64_t* tfull, uint64_t* tempty,
-                                                    int warp, int lane, const float* s_scale, const float* s_shift,
-                                                    const float* s_alpha) {
-    constexpr int kAccCols = 64 * R;
-    const int q = warp & 3;
-    const int row = q * 32 + lane;
-    const int r_tx = row % kStackTW, r_g = row / kStackTW;
-    int as = 0; uint32_t aph = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-        int t = tile;
-        const int xt = t % p.tiles_x; t /= p.tiles_x;
-        const int yt = t % p.tiles_y; t /= p.tiles_y;
-        const int gx = xt * kStackTW + r_tx;
-        const int gy0 = yt * (kStackGroups * R) + r_g * R;
-        const size_t obase0 = ((size_t(t) * p.OH + size_t(gy0)) * p.OW + size_t(gx)) * size_t(p.out_ld);
-        const size_t row_pitch = size_t(p.OW) * size_t(p.out_ld);
-        uint4 nxt[8];
-#pragma unroll
-        for (int g = 0; g < 8; ++g) nxt[g] = make_uint4(0, 0, 0, 0);
-        if (p.residual && gx < p.W && gy0 < p.H) {
-            const uint4* rp = reinterpret_cast<const uint4*>(p.residual + obase0);
-#pragma unroll
-            for (int g = 0; g < 8; ++g) nxt[g] = __ldg(rp + g);
-        }
-        mbar_wait(&tfull[as], aph);
-        tc_fence_after();
-        const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * kAccCols);
-#pragma unroll
-        for (int j = 0; j < R; ++j) {
-            uint4 cur[8];
-#pragma unroll
-            for (int g = 0; g < 8; ++g) cur[g] = nxt[g];
-            if (j + 1 < R && p.residual && gx < p.W && gy0 + j + 1 < p.H) {
-                const uint4* rp = reinterpret_cast<const uint4*>(p.residual + obase0 + size_t(j + 1) * row_pitch);
-#pragma unroll
-                for (int g = 0; g < 8; ++g) nxt[g] = __ldg(rp + g);
-            }
-            const bool valid = gx < p.W && gy0 + j < p.H;
-            stack_epilogue_block<ACT>(p, taddr + uint32_t(j * 64), valid, obase0 + size_t(j) * row_pitch, cur, s_scale, s_shift,
-                                      s_alpha);
         }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tempty[as]);
         if (++as == 2) { as = 0; aph ^= 1; }
+    }
+}
+
+template <int R, int F16>
+__device__ __forceinline__ void stack_epilogue_dispatch(const IgemmParams& p, uint32_t tmem_base, uint64_t* tfull, uint64_t* tempty,
+                                                        int quarter, int half, int lane, const float* s_scale,
+                                                        const float* s_shift, const float* s_alpha) {
+    switch (p.act) {
+        case ACT_RELU: stack_epilogue_loop<R, ACT_RELU, F16>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha); break;
+        case ACT_LEAKY: stack_epilogue_loop<R, ACT_LEAKY, F16>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha); break;
+        case ACT_PRELU: stack_epilogue_loop<R, ACT_PRELU, F16>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha); break;
+        case ACT_TANH: stack_epilogue_loop<R, ACT_TANH, F16>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha); break;
+        default: stack_epilogue_loop<R, ACT_NONE, F16>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha); break;
     }
 }
 
@@ -200,7 +224,7 @@ conv_stack_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         tma_prefetch_desc(&mapB);
         for (int s = 0; s < 4; ++s) { mbar_init(&afull[s], 1); mbar_init(&aempty[s], 1); }
         mbar_init(bfull, 1);
-        for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 4); }
+        for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 8); }
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc<kTmemCols>(tmem_slot);
@@ -298,13 +322,9 @@ conv_stack_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         }
     } else {
         // ------------------------------------------------------------ epilogue: R output pixels per accumulator row
-        switch (p.act) {
-            case ACT_RELU: stack_epilogue_loop<R, ACT_RELU>(p, tmem_base, tfull, tempty, warp, lane, s_scale, s_shift, s_alpha); break;
-            case ACT_LEAKY: stack_epilogue_loop<R, ACT_LEAKY>(p, tmem_base, tfull, tempty, warp, lane, s_scale, s_shift, s_alpha); break;
-            case ACT_PRELU: stack_epilogue_loop<R, ACT_PRELU>(p, tmem_base, tfull, tempty, warp, lane, s_scale, s_shift, s_alpha); break;
-            case ACT_TANH: stack_epilogue_loop<R, ACT_TANH>(p, tmem_base, tfull, tempty, warp, lane, s_scale, s_shift, s_alpha); break;
-            default: stack_epilogue_loop<R, ACT_NONE>(p, tmem_base, tfull, tempty, warp, lane, s_scale, s_shift, s_alpha); break;
-        }
+        const int quarter = warp & 3, half = (warp - 2) >> 2;
+        if (p.f16) stack_epilogue_dispatch<R, 1>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha);
+        else stack_epilogue_dispatch<R, 0>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha);
     }
 
     tc_fence_before();

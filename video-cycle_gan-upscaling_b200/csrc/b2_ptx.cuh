@@ -107,6 +107,23 @@ __device__ __forceinline__ void tma_store_wait_all() {
     asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
 }
 
+// 256-bit global accesses (sm_100: LDG/STG.E.ENL2.256).  A thread that owns one pixel row of an NHWC tensor touches a
+// different 128-byte line than its neighbours, so the LSU cost of the epilogues is per (instruction, line) pair:
+// 32-byte accesses halve the instruction count for the same bytes.  Pointers must be 32-byte aligned.
+struct alignas(32) uint8v { uint32_t v[8]; };
+__device__ __forceinline__ uint8v ldg256(const void* p) {
+    uint8v r;
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7])
+                 : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void stg256(void* p, const uint8v& r) {
+    asm volatile("st.global.v8.b32 [%8], {%0,%1,%2,%3,%4,%5,%6,%7};"
+                 ::"r"(r.v[0]), "r"(r.v[1]), "r"(r.v[2]), "r"(r.v[3]), "r"(r.v[4]), "r"(r.v[5]), "r"(r.v[6]), "r"(r.v[7]), "l"(p)
+                 : "memory");
+}
+
 // ------------------------------------------------------------------ tcgen05 / TMEM
 template <uint32_t kCols>
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst) {
