@@ -48,15 +48,21 @@ def predict_device(model, x_dev):
     return outs[0] if len(outs) == 1 else outs
 
 
+# Frames per pipeline stage of predict(): the device->host copy of stage i (24.9 MB per 1080p frame, PCIe) runs on a copy
+# stream while stage i+1 computes, and the host-side staging copy of stage i+1 overlaps the kernels of stage i.
+PIPELINE_FRAMES = 2
+
 _pinned_in = {}
+_dev_out = {}
+_copy_stream = {}
 
 
-def _stage_input(a):
-    """Host ndarray -> pinned staging buffer (cached per shape) so the H2D copy is a single async DMA."""
-    key = a.shape
+def _stage_input(a, slot):
+    """Host ndarray -> pinned staging buffer (cached per shape and pipeline slot) so the H2D copy is one async DMA."""
+    key = (a.shape, slot)
     buf = _pinned_in.get(key)
     if buf is None:
-        if len(_pinned_in) > 8:
+        if len(_pinned_in) > 16:
             _pinned_in.clear()
         buf = torch.empty(a.shape, dtype=torch.float32, pin_memory=True)
         _pinned_in[key] = buf
@@ -64,9 +70,24 @@ def _stage_input(a):
     return buf
 
 
+def _device_out(model, shape, dev):
+    """Device-side result buffer, cached per model and shape: the copy stream reads it after the compute stream has
+    moved on, so it must not go back to the caching allocator between calls."""
+    key = (id(model), tuple(shape), dev.index)
+    t = _dev_out.get(key)
+    if t is None:
+        if len(_dev_out) > 4:
+            _dev_out.clear()
+        t = torch.empty(shape, dtype=torch.float32, device=dev)
+        _dev_out[key] = t
+    return t
+
+
 def predict(model, x, batch_size=None):
     """Model.predict: host ndarray in, fresh host ndarray(s) out.  Results are copied device->host straight into a
-    pinned allocation (torch's caching host allocator recycles it once the caller drops the array)."""
+    pinned allocation (torch's caching host allocator recycles it once the caller drops the array).  Frames are
+    independent in inference (BatchNorm on moving statistics), so the batch is walked in stages of PIPELINE_FRAMES:
+    H2D + kernels on the current stream, D2H on a copy stream one stage behind."""
     if isinstance(x, (list, tuple)):
         if len(x) != 1:
             raise ValueError("predict on multi-input models is not part of the reference path")
@@ -76,16 +97,43 @@ def predict(model, x, batch_size=None):
     dev = _device()
     n = a.shape[0]
     bs = int(batch_size) if batch_size else 32  # Keras' predict default
-    outs = None
-    for i in range(0, n, bs):
-        h = _stage_input(a[i:i + bs])
-        y = predict_device(model, h.to(dev, non_blocking=True))
+    step = max(1, min(bs, PIPELINE_FRAMES))
+    main = torch.cuda.current_stream()
+    cs = _copy_stream.get(dev.index)
+    if cs is None:
+        cs = _copy_stream[dev.index] = torch.cuda.Stream(device=dev)
+    outs = devs = None
+    staged = []          # (pinned buffer, event after its H2D) of the two slots in flight
+    for ci, i in enumerate(range(0, n, step)):
+        slot = ci & 1
+        if len(staged) > slot and staged[slot] is not None:
+            staged[slot].synchronize()      # the H2D that last read this staging slot has finished
+        h = _stage_input(a[i:i + step], slot)
+        xd = h.to(dev, non_blocking=True)
+        ev_in = torch.cuda.Event()
+        ev_in.record(main)
+        if len(staged) <= slot:
+            staged.append(ev_in)
+        else:
+            staged[slot] = ev_in
+        if model._is_leaf and devs is not None:
+            y = model.net.forward_infer(xd, out=devs[0][i:i + xd.shape[0]])
+        else:
+            y = predict_device(model, xd)
         ys = y if isinstance(y, list) else [y]
         if outs is None:
             outs = [torch.empty((n,) + tuple(t.shape[1:]), dtype=torch.float32, pin_memory=True) for t in ys]
-        for o, t in zip(outs, ys):
-            o[i:i + t.shape[0]].copy_(t, non_blocking=True)
-        torch.cuda.current_stream().synchronize()  # the staging buffer is reused by the next chunk
+            if model._is_leaf and n > step and getattr(model.net, 'writes_out', False):
+                # later stages write straight into slices of one cached device buffer
+                devs = [_device_out(model, (n,) + tuple(ys[0].shape[1:]), dev)]
+        done = torch.cuda.Event()
+        done.record(main)
+        cs.wait_event(done)
+        with torch.cuda.stream(cs):
+            for o, t in zip(outs, ys):
+                o[i:i + t.shape[0]].copy_(t, non_blocking=True)
+                t.record_stream(cs)
+    cs.synchronize()
     res = [o.numpy() for o in outs]
     return res[0] if len(res) == 1 else res
 

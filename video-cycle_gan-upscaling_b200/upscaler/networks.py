@@ -318,6 +318,7 @@ class UpscalerOrigNet(Net):
     log2(factor) x (ConvT s2 + LeakyReLU 0.2) -> 9x9 conv -> tanh."""
 
     input_name = "initial/input"
+    writes_out = True      # forward_infer(x, out=...) writes its result into a caller-provided tensor (engine.predict)
     extra_layers = [("prefinal/tanh", "add"), ("final/tanh", "activation")]
 
     def __init__(self, kernel_size=5, filters=64, upscale_factor=4, res_block_num=16, weights=None, device="cuda",
