@@ -26,6 +26,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "video-cycle_gan-upscaling_b200"))
 
 GEN_FLOPS = {3: 1227.09e9, 5: 2942.77e9}      # per 270x480 frame, SURVEY.md 8(d)
+TRAIN_STEP_FLOPS = {3: 9.69e12, 5: 15.55e12}   # config 3 train step, B = 16 (3G + 3V per sample), SURVEY.md 8(d)
 CONVT2_FLOPS = {3: 611.5e9, 5: 1698.7e9}      # second Conv2DTranspose 256->256 at 540x960 -> 1080x1920
 H_LR, W_LR = 270, 480
 
@@ -134,6 +135,47 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def bench_train_step(args, rank, world, dev, barrier):
+    """Generator-only training step with the VGG19 content loss (train.py; BASELINE.json configs[2]): B = 16 LR patches
+    of 96x96 per GPU through compile_training_model(...).train_on_batch(host x, host y) -- forward with batch-statistics
+    BatchNorm, VGG19 loss, backward, Adam; data-parallel over NCCL when N > 1 (cross-replica BatchNorm sums, bucketed
+    gradient all-reduce overlapped with backward).  H2D of the batch and the D2H read of the loss are inside."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from upscaler import ops
+    from upscaler.model import VGG_MSE_LOSS, compile_training_model, make_upscaler_orig
+    B, lr, ks = 16, 96, args.kernel_size
+    up = make_upscaler_orig((4 * lr, 4 * lr, 3), kernel_size=ks)
+    tm = compile_training_model(up, VGG_MSE_LOSS((4 * lr, 4 * lr, 3), 1e-3).loss)
+    rng = np.random.default_rng(100 + rank)
+    hr = rng.uniform(-1, 1, (B, 4 * lr, 4 * lr, 3)).astype(np.float32)
+    x = hr.reshape(B, lr, 4, lr, 4, 3).mean(axis=(2, 4)).astype(np.float32)
+    for _ in range(3):
+        loss = tm.train_on_batch(x, hr)
+    barrier()
+    ops.reset_launch_count()
+    t0 = time.perf_counter()
+    for _ in range(args.train_steps):
+        loss = tm.train_on_batch(x, hr)       # returns the loss as a host float: the step's D2H read + sync
+    barrier()
+    t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = 1000.0 * float(t.item()) / args.train_steps
+    peaks = load_peaks()
+    tf = TRAIN_STEP_FLOPS[ks] * world / (ms * 1e-3) / 1e12
+    out = {"metric": "train samples/s", "value": world * B * 1000.0 / ms, "unit": "samples/s", "ms_per_step": ms,
+           "steps": args.train_steps, "config": "generator-only step, vgg-mse content loss, %d x (96x96 -> 384x384) per GPU, k=%d, "
+           "bf16 storage / fp32 accumulate / fp32 master weights + Adam%s" % (B, ks, ", NCCL data-parallel (SyncBN sums + bucketed gradient all-reduce)" if world > 1 else ""),
+           "algorithmic_tflops": tf, "frac_of_bf16_sustained_peak": tf / world / peaks["bf16_tflops_sustained"],
+           "gpu_launches_per_step": ops.launch_count() // args.train_steps, "loss": float(loss),
+           "h2d_bytes_per_step": int(x.nbytes + hr.nbytes), "d2h_bytes_per_step": 4}
+    del tm, up
+    torch.cuda.empty_cache()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -143,6 +185,8 @@ def main():
     ap.add_argument("--batch", type=int, default=8, help="frames per step per GPU")
     ap.add_argument("--kernel-size", type=int, default=3, dest="kernel_size")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-train", action="store_true", help="skip the training-step measurement (config 3)")
+    ap.add_argument("--train-steps", type=int, default=8, dest="train_steps")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -223,12 +267,17 @@ def main():
     e2e_value = world * B * e2e_steps / float(t_e2e.item())
     assert y.shape == (B, 4 * H_LR, 4 * W_LR, 3)
 
+    # ------------------------------------------------------------------ training step (BASELINE.json configs[2])
+    train = None
+    if not args.no_train:
+        train = bench_train_step(args, rank, world, dev, barrier)
+
     if rank == 0:
         peaks = load_peaks()
         dom = "upscaling/1/block/conv_transp"
         dom_ms = layer_ms.get(dom)
         achieved = CONVT2_FLOPS[ks] * B / (dom_ms * 1e-3) / 1e12 if dom_ms else None
-        roof = {"bound": "tensor", "kernel": "conv_igemm_kernel<256> (4 sub-pixel phases of " + dom + ")",
+        roof = {"bound": "tensor", "kernel": "conv_halo_kernel<256> x3 + conv_igemm_kernel<256> x1 (the 4 sub-pixel phases of " + dom + ")",
                 "achieved": achieved, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
                 "frac": (achieved / peaks["bf16_tflops_sustained"]) if achieved else None,
                 "peak_kind": "bf16 dense sustained, %s" % peaks["source"], "traffic": None,
@@ -249,7 +298,7 @@ def main():
                 "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": int(x_host.nbytes),
                         "d2h_bytes_per_step": int(y.nbytes), "api": "upscaler Model.predict(ndarray)->ndarray"},
                 "gpu_launches": launches,
-                "roofline": roof, "cpu_baseline": cpu,
+                "roofline": roof, "cpu_baseline": cpu, "train": train,
                 "layers_ms": {k: round(v, 4) for k, v in sorted(layer_ms.items(), key=lambda kv: -kv[1])[:8]}}
         print(json.dumps(line), flush=True)
     if world > 1:
