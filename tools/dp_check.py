@@ -37,13 +37,21 @@ def data(B, step):
     return x, hr
 
 
-def run(up, tm, lo, hi, steps, B):
-    losses = []
+def run(up, tm, lo, hi, steps, B, reverse=False):
+    """Returns the losses of `steps` steps and the (all-reduced) flat gradient of the FIRST step: Adam's update is
+    ~lr*sign(g) for the first steps, so weights after a few steps amplify bf16 round-off of near-zero gradients and
+    are not a meaningful comparison; the gradient itself is."""
+    losses, g0 = [], None
     for s in range(steps):
         x, hr = data(B, s)
+        if reverse:      # same batch, samples in reverse order: identical mathematics, different tiles and summation order
+            x, hr = x[::-1].copy(), hr[::-1].copy()
         losses.append(tm.train_on_batch(x[lo:hi], hr[lo:hi]))
+        if s == 0:
+            torch.cuda.synchronize()
+            g0 = up.net.grad_flat.detach().cpu().numpy().copy()
     torch.cuda.synchronize()
-    return np.array(losses), {k: [np.array(a) for a in v] for k, v in up.net.host_weights().items()}
+    return np.array(losses), g0
 
 
 def main():
@@ -77,15 +85,32 @@ def main():
     up1, tm1 = build()
     l_1, w_1 = run(up1, tm1, 0, B, steps, B)
     rel_l = np.abs(l_dp - l_1) / np.abs(l_1)
-    worst = 0.0
-    for k in w_1:
-        for a, b in zip(w_dp[k], w_1[k]):
-            d = np.abs(a - b).max() / (np.abs(b).max() + 1e-12)
-            worst = max(worst, float(d))
+    # Round-off floor: the same single-GPU step with the batch in reverse order (identical mathematics).  Gradients travel
+    # in bf16 through up to 37 layers, so two mathematically equal runs differ by a few per cent per tensor; the
+    # data-parallel run must agree with the single-GPU run as well as the single-GPU run agrees with itself.
+    up2, tm2 = build()
+    _, g_rev = run(up2, tm2, 0, B, 1, B, reverse=True)
+    bad, worst_cos, worst = [], 1.0, (0.0, 0.0, "")
+    net = up1.net
+    for (name, j), (o, n, shp) in net.offsets.items():
+        if o >= net.n_trainable:
+            continue
+        a, b, c = (v[o:o + n].astype(np.float64) for v in (w_dp, w_1, g_rev))
+        na, nb = float(np.linalg.norm(a)), float(np.linalg.norm(b))
+        if nb < 1e-6 * np.sqrt(n):        # analytically-zero gradients (conv bias in front of a train-mode BatchNorm)
+            continue
+        cos, ratio = float(np.vdot(a, b) / (na * nb)), na / nb
+        d_dp, d_floor = float(np.linalg.norm(a - b)) / nb, float(np.linalg.norm(c - b)) / nb
+        worst_cos = min(worst_cos, cos)
+        if d_dp > worst[0]:
+            worst = (d_dp, d_floor, "%s[%d]" % (name, j))
+        if cos < 0.97 or abs(ratio - 1) > 0.06 or d_dp > 2.0 * d_floor + 1e-2:
+            bad.append((name, j, round(cos, 4), round(ratio, 4), round(d_dp, 4), round(d_floor, 4)))
     print("DPCHECK world=%d losses dp %s single %s" % (world, np.round(l_dp, 6), np.round(l_1, 6)))
-    print("DPCHECK max rel loss diff %.2e, max weight diff / max|w| %.2e, replica drift %.2e, buckets %s" % (
-        rel_l.max(), worst, drift, buckets))
-    ok = rel_l.max() < 2e-3 and worst < 2e-2 and drift == 0.0
+    print("DPCHECK first-step loss rel diff %.2e, max rel loss diff over %d steps %.2e, first-step gradients: worst cosine "
+          "%.4f, worst per-tensor rel L2 diff %.3e (same tensor, reversed-batch floor %.3e: %s), out-of-tolerance %s, replica "
+          "drift %.2e, buckets %s" % (rel_l[0], steps, rel_l.max(), worst_cos, worst[0], worst[1], worst[2], bad, drift, buckets))
+    ok = rel_l[0] < 1e-3 and rel_l.max() < 2e-2 and not bad and drift == 0.0
     print("DPCHECK", "OK" if ok else "MISMATCH")
     sys.exit(0 if ok else 1)
 
