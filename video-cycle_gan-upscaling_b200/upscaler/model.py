@@ -9,6 +9,7 @@ from abc import ABCMeta, abstractmethod
 
 from .keras_compat import Adam, Input, Model  # noqa: F401  (re-exported: scripts import these from keras)
 from . import networks
+from .hdf5_io import load_model  # noqa: F401  (keras.models.load_model for the hot path's model families)
 
 
 def make_upscaler_orig(output_image_shape, kernel_size=5, filters=64, upscale_factor=4, res_block_num=16):
