@@ -101,6 +101,13 @@ int b2_fold_taps(const void* in, int in_fp32, int B, int H, int W, int Cin, int 
  * transpose, or the tap-folded layouts); this call refreshes the bf16 shadow copy from the fp32 master weights. */
 int b2_gather_cast(const float* src, const int32_t* idx, int64_t n, void* out, int f16, void* stream);
 
+/* Frame I/O edges (reference: upscaling/upscaler/data.py:253-270, used around Model.predict in data.py:314-363 and the
+ * frame-upscaling notebooks).  b2_u8_to_f32_norm: out[i] = float(in[i] / 127.5 - 1) (convert_image_series_to_array);
+ * b2_f32_to_u8_denorm: out[i] = uint8(around((in[i] + 1) * 127.5)), round-half-even (convert_array_to_image).  Both are
+ * bit-exact with the NumPy expressions; device buffers 16-byte aligned, n elements. */
+int b2_u8_to_f32_norm(const uint8_t* in, float* out, int64_t n, void* stream);
+int b2_f32_to_u8_denorm(const float* in, uint8_t* out, int64_t n, void* stream);
+
 /* ---------------------------------------------------------------------------------------------------------------
  * Training step (Model.train_on_batch of the models compile_training_model / make_and_compile_gan build,
  * model.py:1017-1137; call sites train.py:220, train_mini.py:232, train_gan.py:316-317, train_gan3.py:353-354).

@@ -73,6 +73,48 @@ inline int grid_for(long work, int threads) {
 
 }  // namespace
 
+// Frame I/O edges (reference: upscaling/upscaler/data.py:253-270).  Vectorised, coalesced: 16 pixels-channels per thread.
+//   u8 -> f32:  x / 127.5 - 1, evaluated in double like NumPy does on a uint8 array, then rounded once to float (what
+//               Keras feeds the network); bit-exact with convert_image_series_to_array(...).astype(float32).
+//   f32 -> u8:  uint8(around((a + 1) * 127.5)) in float32 with separate add and multiply (no FMA contraction) and
+//               round-half-to-even, bit-exact with convert_array_to_image on a float32 prediction.
+__global__ void u8_to_f32_norm_kernel(const uint8_t* __restrict__ in, float* __restrict__ out, long n) {
+    const long nv = n >> 4;
+    for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < nv; i += long(gridDim.x) * blockDim.x) {
+        const uint4 u = __ldg(reinterpret_cast<const uint4*>(in) + i);
+        const uint8_t* b = reinterpret_cast<const uint8_t*>(&u);
+        float4 o[4];
+        float* f = reinterpret_cast<float*>(o);
+#pragma unroll
+        for (int e = 0; e < 16; ++e) f[e] = float(__dsub_rn(__ddiv_rn(double(b[e]), 127.5), 1.0));
+#pragma unroll
+        for (int e = 0; e < 4; ++e) reinterpret_cast<float4*>(out)[i * 4 + e] = o[e];
+    }
+    for (long i = (nv << 4) + blockIdx.x * long(blockDim.x) + threadIdx.x; i < n; i += long(gridDim.x) * blockDim.x)
+        out[i] = float(__dsub_rn(__ddiv_rn(double(in[i]), 127.5), 1.0));
+}
+
+__device__ __forceinline__ uint8_t denorm_u8(float a) {
+    const float v = rintf(__fmul_rn(__fadd_rn(a, 1.0f), 127.5f));
+    return uint8_t(int(fminf(fmaxf(v, 0.f), 255.f)));
+}
+__global__ void f32_to_u8_denorm_kernel(const float* __restrict__ in, uint8_t* __restrict__ out, long n) {
+    const long nv = n >> 4;
+    for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < nv; i += long(gridDim.x) * blockDim.x) {
+        float4 v[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) v[e] = __ldg(reinterpret_cast<const float4*>(in) + i * 4 + e);
+        const float* f = reinterpret_cast<const float*>(v);
+        uint4 o;
+        uint8_t* b = reinterpret_cast<uint8_t*>(&o);
+#pragma unroll
+        for (int e = 0; e < 16; ++e) b[e] = denorm_u8(f[e]);
+        reinterpret_cast<uint4*>(out)[i] = o;
+    }
+    for (long i = (nv << 4) + blockIdx.x * long(blockDim.x) + threadIdx.x; i < n; i += long(gridDim.x) * blockDim.x)
+        out[i] = denorm_u8(in[i]);
+}
+
 extern "C" {
 
 int b2_fold_taps(const void* in, int in_fp32, int B, int H, int W, int Cin, int OH, int OW, int stride, int ntaps,
@@ -104,6 +146,26 @@ int b2_gather_cast(const float* src, const int32_t* idx, int64_t n, void* out, i
         src, idx, long(n), out, f16);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("b2_gather_cast launch: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+int b2_u8_to_f32_norm(const uint8_t* in, float* out, int64_t n, void* stream) {
+    if (!in || !out) return set_error("b2_u8_to_f32_norm: null pointer");
+    if ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) return set_error("b2_u8_to_f32_norm: buffers must be 16-byte aligned");
+    if (n <= 0) return 0;
+    u8_to_f32_norm_kernel<<<grid_for((n + 15) / 16, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(in, out, long(n));
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error("b2_u8_to_f32_norm launch: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+int b2_f32_to_u8_denorm(const float* in, uint8_t* out, int64_t n, void* stream) {
+    if (!in || !out) return set_error("b2_f32_to_u8_denorm: null pointer");
+    if ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) return set_error("b2_f32_to_u8_denorm: buffers must be 16-byte aligned");
+    if (n <= 0) return 0;
+    f32_to_u8_denorm_kernel<<<grid_for((n + 15) / 16, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(in, out, long(n));
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error("b2_f32_to_u8_denorm launch: %s", cudaGetErrorString(e));
     return 0;
 }
 

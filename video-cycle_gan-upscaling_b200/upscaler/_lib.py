@@ -51,6 +51,8 @@ _SIGNATURES = {
                      [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
     "b2_gather_cast": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int,
                                       ctypes.c_void_p]),
+    "b2_u8_to_f32_norm": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
+    "b2_f32_to_u8_denorm": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
     # ---- training step
     "b2_conv2d_s2_dgrad": (ctypes.c_int, [_P] + [_I] * 4 + [_P] + [_I] * 5 + [ctypes.POINTER(Epilogue), _P]),
     "b2_conv2d_wgrad": (ctypes.c_int, [_P] + [_I] * 4 + [_P] + [_I] * 4 + [_P, _I, _P]),

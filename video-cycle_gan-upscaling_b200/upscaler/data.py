@@ -29,3 +29,14 @@ def convert_image_series_to_array(image_series):
 def convert_imagesdf_to_arrays(images_df):
     """data.py:273-277."""
     return convert_image_series_to_array(images_df.image_hr), convert_image_series_to_array(images_df.image_lr)
+
+
+def upscale_images(images_series, upscaler, batch_size=8):
+    """The loop of save_img_predict / save_images_predicted (data.py:314, 338, 358-363) without the file writes:
+    PIL images (or uint8 HWC arrays) of one size -> list of upscaled PIL images.  The uint8 <-> float conversions run on
+    the device (Model.predict_uint8), the arithmetic and rounding are those of convert_image_series_to_array and
+    convert_array_to_image."""
+    from PIL import Image
+    frames = np.stack([np.asarray(img, dtype=np.uint8) for img in images_series])
+    out = upscaler.predict_uint8(frames, batch_size=batch_size)
+    return [Image.fromarray(o) for o in out]

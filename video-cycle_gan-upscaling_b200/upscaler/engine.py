@@ -58,13 +58,13 @@ _copy_stream = {}
 
 
 def _stage_input(a, slot):
-    """Host ndarray -> pinned staging buffer (cached per shape and pipeline slot) so the H2D copy is one async DMA."""
-    key = (a.shape, slot)
+    """Host ndarray -> pinned staging buffer (cached per shape, type and pipeline slot) so the H2D copy is one async DMA."""
+    key = (a.shape, slot, a.dtype.str)
     buf = _pinned_in.get(key)
     if buf is None:
         if len(_pinned_in) > 16:
             _pinned_in.clear()
-        buf = torch.empty(a.shape, dtype=torch.float32, pin_memory=True)
+        buf = torch.empty(a.shape, dtype=torch.uint8 if a.dtype == np.uint8 else torch.float32, pin_memory=True)
         _pinned_in[key] = buf
     buf.numpy()[...] = a
     return buf
@@ -83,7 +83,18 @@ def _device_out(model, shape, dev):
     return t
 
 
-def predict(model, x, batch_size=None):
+def predict_uint8(model, frames, batch_size=None):
+    """uint8 frames (N,H,W,3) -> uint8 upscaled frames: convert_image_series_to_array -> Model.predict ->
+    convert_array_to_image's arithmetic (data.py:253-270, save_img_predict data.py:358-363) with both conversions on
+    the device, so the PCIe traffic is the uint8 frames (a quarter of the float32 arrays) and the result is bit-identical
+    to doing the two conversions in NumPy around predict()."""
+    a = np.asarray(frames)
+    if a.dtype != np.uint8 or a.ndim != 4:
+        raise ValueError("predict_uint8 expects a uint8 array (frames, height, width, channels)")
+    return predict(model, np.ascontiguousarray(a), batch_size, u8=True)
+
+
+def predict(model, x, batch_size=None, u8=False):
     """Model.predict: host ndarray in, fresh host ndarray(s) out.  Results are copied device->host straight into a
     pinned allocation (torch's caching host allocator recycles it once the caller drops the array).  Frames are
     independent in inference (BatchNorm on moving statistics), so the batch is walked in stages of PIPELINE_FRAMES:
@@ -92,9 +103,10 @@ def predict(model, x, batch_size=None):
         if len(x) != 1:
             raise ValueError("predict on multi-input models is not part of the reference path")
         x = x[0]
-    a = as_batch(x)
+    a = x if u8 else as_batch(x)
     _check_input(model, a)
     dev = _device()
+    from . import ops
     n = a.shape[0]
     bs = int(batch_size) if batch_size else 32  # Keras' predict default
     step = max(1, min(bs, PIPELINE_FRAMES))
@@ -110,6 +122,8 @@ def predict(model, x, batch_size=None):
             staged[slot].synchronize()      # the H2D that last read this staging slot has finished
         h = _stage_input(a[i:i + step], slot)
         xd = h.to(dev, non_blocking=True)
+        if u8:
+            xd = ops.u8_to_f32_norm(xd)
         ev_in = torch.cuda.Event()
         ev_in.record(main)
         if len(staged) <= slot:
@@ -121,9 +135,12 @@ def predict(model, x, batch_size=None):
         else:
             y = predict_device(model, xd)
         ys = y if isinstance(y, list) else [y]
+        if u8:
+            ys = [ops.f32_to_u8_denorm(t.float().contiguous()) for t in ys]
         if outs is None:
-            outs = [torch.empty((n,) + tuple(t.shape[1:]), dtype=torch.float32, pin_memory=True) for t in ys]
-            if model._is_leaf and n > step and getattr(model.net, 'writes_out', False):
+            outs = [torch.empty((n,) + tuple(t.shape[1:]), dtype=torch.uint8 if u8 else torch.float32, pin_memory=True)
+                    for t in ys]
+            if model._is_leaf and n > step and getattr(model.net, 'writes_out', False) and not u8:
                 # later stages write straight into slices of one cached device buffer
                 devs = [_device_out(model, (n,) + tuple(ys[0].shape[1:]), dev)]
         done = torch.cuda.Event()

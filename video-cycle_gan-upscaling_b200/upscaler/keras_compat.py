@@ -175,6 +175,12 @@ class Model:
         from . import engine
         return engine.predict(self, x, batch_size)
 
+    def predict_uint8(self, frames, batch_size=None):
+        """Extension used by the frame-upscaling helpers (upscaler.data.upscale_images): uint8 frames in, uint8 frames
+        out, bit-identical to convert_image_series_to_array -> predict -> convert_array_to_image's arithmetic."""
+        from . import engine
+        return engine.predict_uint8(self, frames, batch_size)
+
     # ------------------------------------------------------------------ training
     def compile(self, loss=None, optimizer=None, loss_weights=None, **_):
         from . import engine

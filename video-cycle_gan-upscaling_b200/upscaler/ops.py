@@ -168,6 +168,32 @@ def fold_taps(x, taps, stride=1, out_hw=None, out=None, dtype=torch.bfloat16, ou
     return out
 
 
+def u8_to_f32_norm(x, out=None):
+    """uint8 frames -> float32 in [-1, 1]: x / 127.5 - 1 (data.py:266-270), bit-exact with NumPy's float64 evaluation."""
+    if x.dtype != torch.uint8:
+        raise ValueError("u8_to_f32_norm expects uint8 frames")
+    if out is None:
+        out = torch.empty(x.shape, dtype=torch.float32, device=x.device)
+    _require_cuda(x, out)
+    rc = _lib.load().b2_u8_to_f32_norm(_lib.ptr(x), _lib.ptr(out), x.numel(), _lib.stream_ptr())
+    _lib.check(rc, "b2_u8_to_f32_norm")
+    _count(1)
+    return out
+
+
+def f32_to_u8_denorm(x, out=None):
+    """float32 [-1, 1] -> uint8: uint8(around((x + 1) * 127.5)) (data.py:253-256), bit-exact with NumPy on float32."""
+    if x.dtype != torch.float32:
+        raise ValueError("f32_to_u8_denorm expects float32")
+    if out is None:
+        out = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
+    _require_cuda(x, out)
+    rc = _lib.load().b2_f32_to_u8_denorm(_lib.ptr(x), _lib.ptr(out), x.numel(), _lib.stream_ptr())
+    _lib.check(rc, "b2_f32_to_u8_denorm")
+    _count(1)
+    return out
+
+
 def gather_cast(src, idx, out=None, dtype=torch.bfloat16):
     """out[i] = idx[i] >= 0 ? cast(src.flat[idx[i]]) : 0 — refreshes a packed 16-bit weight copy from fp32 masters."""
     if src.dtype != torch.float32 or idx.dtype != torch.int32:
