@@ -1,5 +1,6 @@
 // b2_api.cu — the extern "C" boundary (include/b2srgan.h): turns layer-level geometry (kernel size, stride,
 // TensorFlow "same" padding, Conv2DTranspose phases) into tap lists for the implicit-GEMM kernels and launches them.
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/b2srgan.h"
@@ -81,19 +82,28 @@ static void convT_phase_taps(IgemmParams& p, int B, int Hout, int Wout, int Cin,
 // nothing (their outputs are zero only through the bias-free epilogue, so callers needing them pre-zero `out`).
 static int run_transposed(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw, int Hout,
                           int Wout, int pbh, int pbw, const b2_epilogue* ep, void* stream, bool direct) {
+    ConvIgemmArgs args[4];
+    int n = 0;
+    bool all = true;
     for (int ph = 0; ph < 4; ++ph) {
-        ConvIgemmArgs a;
+        ConvIgemmArgs& a = args[n];
         memset(&a, 0, sizeof(a));
         convT_phase_taps(a.p, B, Hout, Wout, Cin, kh, kw, pbh, pbw, ph >> 1, ph & 1);
-        if (a.p.H <= 0 || a.p.W <= 0) continue;
+        if (a.p.H <= 0 || a.p.W <= 0) { all = false; continue; }
         fill_epilogue(a.p, ep, Cout);
         a.x = reinterpret_cast<const __nv_bfloat16*>(x);
         a.xB = B; a.xH = H; a.xW = W; a.xC = Cin;
         a.w = reinterpret_cast<const __nv_bfloat16*>(w);
         a.w_rows = Cout; a.w_k = kh * kw * Cin;
         if (a.p.num_taps == 0) return set_error("transposed conv: phase %d has no taps (filter %dx%d)", ph, kh, kw);
-        int rc = direct ? launch_conv_direct(a, reinterpret_cast<cudaStream_t>(stream))
-                        : launch_conv_igemm(a, reinterpret_cast<cudaStream_t>(stream));
+        ++n;
+    }
+    static const bool no_fuse = getenv("B2_NO_PHASE_FUSION") != nullptr;      // A/B switch for profiling
+    if (!direct && !no_fuse && all && conv_phases_applicable(args, n))
+        return launch_conv_phases(args, n, reinterpret_cast<cudaStream_t>(stream));
+    for (int i = 0; i < n; ++i) {
+        int rc = direct ? launch_conv_direct(args[i], reinterpret_cast<cudaStream_t>(stream))
+                        : launch_conv_igemm(args[i], reinterpret_cast<cudaStream_t>(stream));
         if (rc) return rc;
     }
     return 0;
