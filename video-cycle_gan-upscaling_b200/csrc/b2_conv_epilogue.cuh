@@ -61,14 +61,15 @@ __device__ __forceinline__ void epilogue_tile(const IgemmParams& p, uint32_t tad
         tmem_ld_wait();
         if (!valid || n0 + c0 >= p.n_valid) continue;
         float v[CH];
-        const float4* sc4 = reinterpret_cast<const float4*>(s_scale + n0 + c0);
-        const float4* sh4 = reinterpret_cast<const float4*>(s_shift + n0 + c0);
-        const float4* al4 = reinterpret_cast<const float4*>(s_alpha + n0 + c0);
+        const uint32_t sc_a = smem_u32(s_scale + n0 + c0), sh_a = smem_u32(s_shift + n0 + c0), al_a = smem_u32(s_alpha + n0 + c0);
+        const bool unit_scale = p.scale == nullptr;      // bias-only layers (Conv2DTranspose): skip the scale loads
 #pragma unroll
         for (int g = 0; g < CH / 4; ++g) {
-            const float4 sc = sc4[g], sh = sh4[g];
+            float4 sc = make_float4(1.f, 1.f, 1.f, 1.f);
+            if (!unit_scale) sc = lds_f4(sc_a + 16 * g);
+            const float4 sh = lds_f4(sh_a + 16 * g);
             float4 al = make_float4(0.f, 0.f, 0.f, 0.f);
-            if constexpr (ACT == ACT_PRELU) al = al4[g];
+            if constexpr (ACT == ACT_PRELU) al = lds_f4(al_a + 16 * g);
             v[4 * g + 0] = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g + 0]), sc.x, sh.x), p.leaky, al.x);
             v[4 * g + 1] = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g + 1]), sc.y, sh.y), p.leaky, al.y);
             v[4 * g + 2] = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g + 2]), sc.z, sh.z), p.leaky, al.z);

@@ -63,9 +63,7 @@ __device__ __forceinline__ void stack_epilogue_loop(const IgemmParams& p, uint32
     constexpr int kAccCols = 64 * R;
     const int row = quarter * 32 + lane;
     const int r_tx = row % kStackTW, r_g = row / kStackTW;
-    const float4* sc4 = reinterpret_cast<const float4*>(s_scale + 32 * half);
-    const float4* sh4 = reinterpret_cast<const float4*>(s_shift + 32 * half);
-    const float4* al4 = reinterpret_cast<const float4*>(s_alpha + 32 * half);
+    const uint32_t sc_a = smem_u32(s_scale + 32 * half), sh_a = smem_u32(s_shift + 32 * half), al_a = smem_u32(s_alpha + 32 * half);
     const bool has_res = p.residual != nullptr, has_gate = p.gate != nullptr;
     const size_t row_pitch = size_t(p.OW) * size_t(p.out_ld);
     int as = 0; uint32_t aph = 0;
@@ -125,9 +123,9 @@ __device__ __forceinline__ void stack_epilogue_loop(const IgemmParams& p, uint32
             float v[32];
 #pragma unroll
             for (int g = 0; g < 8; ++g) {
-                const float4 sc = sc4[g], sh = sh4[g];
+                const float4 sc = lds_f4(sc_a + 16 * g), sh = lds_f4(sh_a + 16 * g);
                 float4 al = make_float4(0.f, 0.f, 0.f, 0.f);
-                if constexpr (ACT == ACT_PRELU) al = al4[g];
+                if constexpr (ACT == ACT_PRELU) al = lds_f4(al_a + 16 * g);
                 v[4 * g + 0] = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g + 0]), sc.x, sh.x), p.leaky, al.x);
                 v[4 * g + 1] = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g + 1]), sc.y, sh.y), p.leaky, al.y);
                 v[4 * g + 2] = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g + 2]), sc.z, sh.z), p.leaky, al.z);

@@ -16,40 +16,56 @@ struct FoldParams {
     int dy[kFoldMaxTaps], dx[kFoldMaxTaps];
 };
 
+// One CTA walks whole output rows (no per-element 64-bit divisions); the channel -> (tap, colour) map is decoded once
+// per CTA into shared memory.  Thread = (pixel, group of 8 channels): one 16-byte store, 8 L1-served scalar loads.
 template <typename TIn>
-__global__ void fold_taps_kernel(const TIn* __restrict__ in, void* __restrict__ out, FoldParams p) {
-    const long total = long(p.B) * p.OH * p.OW * 8;  // 8 groups of 8 channels per output pixel
-    const int used = p.ntaps * p.Cin;
-    for (long idx = blockIdx.x * long(blockDim.x) + threadIdx.x; idx < total; idx += long(gridDim.x) * blockDim.x) {
-        const int g = int(idx & 7);
-        long t = idx >> 3;
-        const int ox = int(t % p.OW); t /= p.OW;
-        const int oy = int(t % p.OH); t /= p.OH;
-        const int b = int(t);
-        float v[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            const int ch = g * 8 + e;
-            float f = 0.f;
-            if (ch < used) {
-                const int tap = ch / p.Cin, c = ch - tap * p.Cin;
-                const int iy = oy * p.stride + p.dy[tap], ix = ox * p.stride + p.dx[tap];
-                if (iy >= 0 && iy < p.H && ix >= 0 && ix < p.W)
-                    f = float(in[((size_t(b) * p.H + iy) * p.W + ix) * p.Cin + c]);
-            }
-            v[e] = f;
-        }
-        uint4 o;
-        if (p.f16) {
-            __half2* h = reinterpret_cast<__half2*>(&o);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) h[e] = __floats2half2_rn(v[2 * e], v[2 * e + 1]);
+__global__ void __launch_bounds__(256) fold_taps_kernel(const TIn* __restrict__ in, void* __restrict__ out, FoldParams p) {
+    // per output channel: x = element offset (dy * W + dx) * Cin + c from the stride-scaled output pixel,
+    //                     y = dy, z = dx (dy = -2^20 marks an unused channel: always out of range -> zero)
+    __shared__ int4 s_tab[64];     // index = (ch % 8) * 8 + ch / 8
+    if (threadIdx.x < 64) {
+        const int ch = threadIdx.x;
+        if (ch < p.ntaps * p.Cin) {
+            const int tap = ch / p.Cin, c = ch - tap * p.Cin;
+            s_tab[(ch & 7) * 8 + (ch >> 3)] = make_int4((p.dy[tap] * p.W + p.dx[tap]) * p.Cin + c, p.dy[tap], p.dx[tap], 0);
         } else {
-            __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+            s_tab[(ch & 7) * 8 + (ch >> 3)] = make_int4(0, -(1 << 20), 0, 0);
         }
-        *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(out) + (size_t(idx >> 3) * p.out_ld + p.out_c0 + g * 8)) = o;
+    }
+    __syncthreads();
+    const int rows = p.B * p.OH;
+    const int per_row = p.OW * 8;
+    for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+        const int b = row / p.OH, oy = row - b * p.OH;
+        const int iy0 = oy * p.stride;
+        const TIn* src = in + (size_t(b) * p.H + iy0) * p.W * p.Cin;
+        uint16_t* dst = reinterpret_cast<uint16_t*>(out) + size_t(row) * p.OW * p.out_ld + p.out_c0;
+        for (int i = threadIdx.x; i < per_row; i += blockDim.x) {
+            const int g = i & 7, ox = i >> 3;
+            const int ix0 = ox * p.stride;
+            const TIn* px = src + ix0 * p.Cin;
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int ch = g * 8 + e;
+                const int4 t = s_tab[e * 8 + g];      // transposed: the 8 groups of a warp hit 8 different bank quads
+                const int iy = iy0 + t.y, ix = ix0 + t.z;
+                float f = 0.f;
+                if (iy >= 0 && iy < p.H && ix >= 0 && ix < p.W) f = float(px[t.x]);
+                v[e] = f;
+            }
+            uint4 o;
+            if (p.f16) {
+                __half2* h = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) h[e] = __floats2half2_rn(v[2 * e], v[2 * e + 1]);
+            } else {
+                __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+            }
+            *reinterpret_cast<uint4*>(dst + size_t(ox) * p.out_ld + g * 8) = o;
+        }
     }
 }
 
@@ -126,14 +142,14 @@ int b2_fold_taps(const void* in, int in_fp32, int B, int H, int W, int Cin, int 
     p.B = B; p.H = H; p.W = W; p.Cin = Cin; p.OH = OH; p.OW = OW; p.stride = stride; p.ntaps = ntaps; p.f16 = f16;
     p.out_ld = out_ld; p.out_c0 = out_c0;
     for (int t = 0; t < ntaps; ++t) { p.dy[t] = dy[t]; p.dx[t] = dx[t]; }
-    const long total = long(B) * OH * OW * 8;
+    const int grid = grid_for(long(B) * OH * 256, 256);     // one CTA per output row, capped at 16 CTAs per SM
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     if (in_fp32)
-        fold_taps_kernel<float><<<grid_for(total, 256), 256, 0, s>>>(reinterpret_cast<const float*>(in), out, p);
+        fold_taps_kernel<float><<<grid, 256, 0, s>>>(reinterpret_cast<const float*>(in), out, p);
     else if (f16)
-        fold_taps_kernel<__half><<<grid_for(total, 256), 256, 0, s>>>(reinterpret_cast<const __half*>(in), out, p);
+        fold_taps_kernel<__half><<<grid, 256, 0, s>>>(reinterpret_cast<const __half*>(in), out, p);
     else
-        fold_taps_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>(
+        fold_taps_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(
             reinterpret_cast<const __nv_bfloat16*>(in), out, p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("b2_fold_taps launch: %s", cudaGetErrorString(e));

@@ -27,6 +27,15 @@ __device__ __forceinline__ uint32_t elect_one() {
     return pred;
 }
 
+// Broadcast 16-byte load from shared memory through an explicit shared-space address: LDS.128 (one wavefront for a
+// warp-uniform address) where a generic-pointer load compiles to LD.E.128 (two wavefronts, measured with ncu on the
+// conv epilogues where these per-channel vector loads were 47 % of all LSU wavefronts).
+__device__ __forceinline__ float4 lds_f4(uint32_t saddr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
+    return v;
+}
+
 // ------------------------------------------------------------------ mbarrier
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));

@@ -69,26 +69,48 @@ __device__ __forceinline__ void loadp8(const float* p, int c0, float (&v)[8], fl
     }
 }
 
-// Combine per-thread partial sums of NQ quantities x 8 channels: threads with the same channel group sit
-// `groups` apart in the block; reduce them through shared memory, then one atomicAdd per channel per block.
+// Combine per-thread partial sums of NQ quantities x 8 channels.  Threads with the same channel group sit `groups`
+// apart (groups is a power of two): lanes of one warp that share a group are folded with xor shuffles first, the
+// per-warp partials go through shared memory, and each block issues two 16-byte vector reductions per quantity and
+// channel group.  All blocks add into the same few cache lines and those reductions serialise in one L2 slice, so
+// their count (blocks x C/4 per quantity), not the bytes, is what this step costs: grids are kept at 2 blocks per SM.
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
 template <int NQ>
 __device__ __forceinline__ void block_combine(float (&acc)[NQ][8], int groups, int c0, float* const (&dst)[NQ]) {
     __shared__ float sh[NQ][kEwThreads][8];
+    for (int off = 16; off >= groups; off >>= 1)
 #pragma unroll
-    for (int q = 0; q < NQ; ++q)
+        for (int q = 0; q < NQ; ++q)
 #pragma unroll
-        for (int e = 0; e < 8; ++e) sh[q][threadIdx.x][e] = acc[q][e];
+            for (int e = 0; e < 8; ++e) acc[q][e] += __shfl_xor_sync(0xffffffffu, acc[q][e], off);
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+        *reinterpret_cast<float4*>(&sh[q][threadIdx.x][0]) = make_float4(acc[q][0], acc[q][1], acc[q][2], acc[q][3]);
+        *reinterpret_cast<float4*>(&sh[q][threadIdx.x][4]) = make_float4(acc[q][4], acc[q][5], acc[q][6], acc[q][7]);
+    }
     __syncthreads();
     if (int(threadIdx.x) < groups) {
+        const int step = groups < 32 ? 32 : groups;      // after the shuffles one partial per (warp, group) is left
 #pragma unroll
         for (int q = 0; q < NQ; ++q) {
             if (!dst[q]) continue;
             float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-            for (int t = threadIdx.x; t < kEwThreads; t += groups)
+            for (int t = threadIdx.x; t < kEwThreads; t += step) {
+                const float4 lo = *reinterpret_cast<const float4*>(&sh[q][t][0]);
+                const float4 hi = *reinterpret_cast<const float4*>(&sh[q][t][4]);
+                s[0] += lo.x; s[1] += lo.y; s[2] += lo.z; s[3] += lo.w;
+                s[4] += hi.x; s[5] += hi.y; s[6] += hi.z; s[7] += hi.w;
+            }
+            float* d = dst[q] + c0;
+            if ((reinterpret_cast<uintptr_t>(d) & 15) == 0) {
+                red_add_v4(d, s[0], s[1], s[2], s[3]);
+                red_add_v4(d + 4, s[4], s[5], s[6], s[7]);
+            } else {
 #pragma unroll
-                for (int e = 0; e < 8; ++e) s[e] += sh[q][t][e];
-#pragma unroll
-            for (int e = 0; e < 8; ++e) atomicAdd(dst[q] + c0 + e, s[e]);
+                for (int e = 0; e < 8; ++e) atomicAdd(d + e, s[e]);
+            }
         }
     }
 }
@@ -99,7 +121,18 @@ colstats_kernel(const void* __restrict__ x, long rows, int C, int f16, float* __
     const int groups = C >> 3, g = threadIdx.x % groups, c0 = g * 8;
     const int rpb = kEwThreads / groups;
     float acc[2][8] = {};
-    for (long r = long(blockIdx.x) * rpb + threadIdx.x / groups; r < rows; r += long(gridDim.x) * rpb) {
+    const long stride = long(gridDim.x) * rpb;
+    long r = long(blockIdx.x) * rpb + threadIdx.x / groups;
+    for (; r + 3 * stride < rows; r += 4 * stride) {       // four independent 16-byte loads in flight per thread
+        float v[4][8];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) load8(x, size_t(r + u * stride) * C + c0, f16, v[u]);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { acc[0][e] += v[u][e]; acc[1][e] = fmaf(v[u][e], v[u][e], acc[1][e]); }
+    }
+    for (; r < rows; r += stride) {
         float v[8];
         load8(x, size_t(r) * C + c0, f16, v);
 #pragma unroll
@@ -202,10 +235,9 @@ bn_bwd_reduce_kernel(const void* __restrict__ z, const void* __restrict__ gin, l
     loadp8(mean, c0, mu, 0.f);
     loadp8(invstd, c0, is, 1.f);
     float acc[3][8] = {};
-    for (long r = long(blockIdx.x) * rpb + threadIdx.x / groups; r < rows; r += long(gridDim.x) * rpb) {
-        float zv[8], gv[8];
-        load8(z, size_t(r) * C + c0, f16, zv);
-        load8(gin, size_t(r) * C + c0, f16, gv);
+    const long stride = long(gridDim.x) * rpb;
+    long r = long(blockIdx.x) * rpb + threadIdx.x / groups;
+    auto body = [&](const float (&zv)[8], const float (&gv)[8]) {
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
             const float u = fmaf(zv[e], sc[e], sh[e]);
@@ -214,6 +246,21 @@ bn_bwd_reduce_kernel(const void* __restrict__ z, const void* __restrict__ gin, l
             acc[1][e] = fmaf(dy, (zv[e] - mu[e]) * is[e], acc[1][e]);
             acc[2][e] = fmaf(gv[e], fminf(u, 0.f), acc[2][e]);
         }
+    };
+    for (; r + stride < rows; r += 2 * stride) {          // four independent 16-byte loads in flight per thread
+        float z0[8], g0[8], z1[8], g1[8];
+        load8(z, size_t(r) * C + c0, f16, z0);
+        load8(gin, size_t(r) * C + c0, f16, g0);
+        load8(z, size_t(r + stride) * C + c0, f16, z1);
+        load8(gin, size_t(r + stride) * C + c0, f16, g1);
+        body(z0, g0);
+        body(z1, g1);
+    }
+    for (; r < rows; r += stride) {
+        float zv[8], gv[8];
+        load8(z, size_t(r) * C + c0, f16, zv);
+        load8(gin, size_t(r) * C + c0, f16, gv);
+        body(zv, gv);
     }
     float* const dst[3] = {s1, s2, dalpha};
     block_combine<3>(acc, groups, c0, dst);
@@ -237,10 +284,9 @@ bn_bwd_apply_kernel(const void* __restrict__ z, const void* __restrict__ gin, lo
     loadp8(s2, c0, m2, 0.f);
 #pragma unroll
     for (int e = 0; e < 8; ++e) { m1[e] *= inv_count; m2[e] *= inv_count; }
-    for (long r = long(blockIdx.x) * rpb + threadIdx.x / groups; r < rows; r += long(gridDim.x) * rpb) {
-        float zv[8], gv[8];
-        load8(z, size_t(r) * C + c0, f16, zv);
-        load8(gin, size_t(r) * C + c0, f16, gv);
+    const long stride = long(gridDim.x) * rpb;
+    long r = long(blockIdx.x) * rpb + threadIdx.x / groups;
+    auto body = [&](const float (&zv)[8], float (&gv)[8]) {
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
             const float u = fmaf(zv[e], sc[e], sh[e]);
@@ -248,72 +294,97 @@ bn_bwd_apply_kernel(const void* __restrict__ z, const void* __restrict__ gin, lo
             const float xh = (zv[e] - mu[e]) * is[e];
             gv[e] = sc[e] * (dy - m1[e] - xh * m2[e]);
         }
+    };
+    for (; r + stride < rows; r += 2 * stride) {
+        float z0[8], g0[8], z1[8], g1[8];
+        load8(z, size_t(r) * C + c0, f16, z0);
+        load8(gin, size_t(r) * C + c0, f16, g0);
+        load8(z, size_t(r + stride) * C + c0, f16, z1);
+        load8(gin, size_t(r + stride) * C + c0, f16, g1);
+        body(z0, g0);
+        body(z1, g1);
+        store8(dz, size_t(r) * C + c0, f16, g0);
+        store8(dz, size_t(r + stride) * C + c0, f16, g1);
+    }
+    for (; r < rows; r += stride) {
+        float zv[8], gv[8];
+        load8(z, size_t(r) * C + c0, f16, zv);
+        load8(gin, size_t(r) * C + c0, f16, gv);
+        body(zv, gv);
         store8(dz, size_t(r) * C + c0, f16, gv);
     }
 }
 
 // ------------------------------------------------------------------------------------------------ max pooling (VGG19)
+// One CTA walks whole output rows (b, oy): no per-element 64-bit divisions, consecutive threads = consecutive 16-byte
+// channel groups of consecutive pixels, four independent loads per thread.
 __global__ void __launch_bounds__(kEwThreads)
 maxpool_fwd_kernel(const void* __restrict__ x, int B, int H, int W, int C, int f16, void* __restrict__ y) {
     const int OH = H >> 1, OW = W >> 1, groups = C >> 3;
-    const long total = long(B) * OH * OW * groups;
-    for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
-        const int g = int(i % groups);
-        long t = i / groups;
-        const int ox = int(t % OW); t /= OW;
-        const int oy = int(t % OH); t /= OH;
-        const size_t base = ((size_t(t) * H + 2 * oy) * W + 2 * ox) * C + g * 8;
-        float a[8], b[8];
-        load8(x, base, f16, a);
-        load8(x, base + C, f16, b);
+    const int per_row = OW * groups;
+    for (int row = blockIdx.x; row < B * OH; row += gridDim.x) {
+        const int b = row / OH, oy = row - b * OH;
+        const size_t in_row = (size_t(b) * H + 2 * oy) * W * C;
+        const size_t out_row = size_t(row) * OW * C;
+        for (int i = threadIdx.x; i < per_row; i += blockDim.x) {
+            const int ox = i / groups, g = i - ox * groups;
+            const size_t base = in_row + size_t(2 * ox) * C + g * 8;
+            float a[8], b1[8], c[8], d[8];
+            load8(x, base, f16, a);
+            load8(x, base + C, f16, b1);
+            load8(x, base + size_t(W) * C, f16, c);
+            load8(x, base + size_t(W) * C + C, f16, d);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) a[e] = fmaxf(a[e], b[e]);
-        load8(x, base + size_t(W) * C, f16, b);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) a[e] = fmaxf(a[e], b[e]);
-        load8(x, base + size_t(W) * C + C, f16, b);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) a[e] = fmaxf(a[e], b[e]);
-        store8(y, (size_t(i) / groups) * C + g * 8, f16, a);
+            for (int e = 0; e < 8; ++e) a[e] = fmaxf(fmaxf(a[e], b1[e]), fmaxf(c[e], d[e]));
+            store8(y, out_row + size_t(ox) * C + g * 8, f16, a);
+        }
     }
 }
 
 // dx = dy routed to the first element of each 2x2 window that equals the window maximum (TensorFlow's MaxPoolGrad);
 // rows / columns beyond the floor(H/2)*2 x floor(W/2)*2 region get zero.  Optional ReLU gate: dx *= (x > 0).
+// Thread = (window, 8 channels): reads the four inputs and dy once, writes the four gradients; the window maximum is
+// recomputed from the inputs (it equals the stored y bit for bit), so y is not read.
 __global__ void __launch_bounds__(kEwThreads)
 maxpool_bwd_kernel(const void* __restrict__ x, const void* __restrict__ y, const void* __restrict__ dy, int B, int H, int W,
                    int C, int f16, int relu_gate, void* __restrict__ dx) {
     const int OH = H >> 1, OW = W >> 1, groups = C >> 3;
-    const long total = long(B) * H * W * groups;
-    for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
-        const int g = int(i % groups);
-        long t = i / groups;
-        const int ix = int(t % W); t /= W;
-        const int iy = int(t % H); t /= H;
-        float o[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        const int oy = iy >> 1, ox = ix >> 1;
-        if (oy < OH && ox < OW) {
-            const size_t wbase = ((size_t(t) * H + 2 * oy) * W + 2 * ox) * C + g * 8;
-            const size_t obase = ((size_t(t) * OH + oy) * OW + ox) * C + g * 8;
-            float m[8], d[8], me[8];
-            load8(y, obase, f16, m);
-            load8(dy, obase, f16, d);
-            load8(x, (size_t(i) / groups) * C + g * 8, f16, me);
-            const int pos = (iy & 1) * 2 + (ix & 1);
-            bool earlier[8] = {false, false, false, false, false, false, false, false};
-            for (int q = 0; q < pos; ++q) {
-                float w[8];
-                load8(x, wbase + size_t(q >> 1) * W * C + size_t(q & 1) * C, f16, w);
+    const int WH = (H + 1) >> 1, WW = (W + 1) >> 1;       // windows including the zero-filled odd edge
+    const int per_row = WW * groups;
+    for (int row = blockIdx.x; row < B * WH; row += gridDim.x) {
+        const int b = row / WH, oy = row - b * WH;
+        const size_t in_row = (size_t(b) * H + 2 * oy) * W * C;
+        for (int i = threadIdx.x; i < per_row; i += blockDim.x) {
+            const int ox = i / groups, g = i - ox * groups;
+            const size_t base = in_row + size_t(2 * ox) * C + g * 8;
+            const bool has_x1 = 2 * ox + 1 < W, has_y1 = 2 * oy + 1 < H;
+            float o[4][8] = {};
+            if (oy < OH && ox < OW) {
+                float w[4][8], d[8];
+                load8(x, base, f16, w[0]);
+                load8(x, base + C, f16, w[1]);
+                load8(x, base + size_t(W) * C, f16, w[2]);
+                load8(x, base + size_t(W) * C + C, f16, w[3]);
+                load8(dy, ((size_t(b) * OH + oy) * OW + ox) * C + g * 8, f16, d);
 #pragma unroll
-                for (int e = 0; e < 8; ++e) earlier[e] = earlier[e] || (w[e] == m[e]);
+                for (int e = 0; e < 8; ++e) {
+                    const float m = fmaxf(fmaxf(w[0][e], w[1][e]), fmaxf(w[2][e], w[3][e]));
+                    bool found = false;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const bool hit = !found && w[q][e] == m;
+                        found = found || hit;
+                        o[q][e] = (hit && (!relu_gate || w[q][e] > 0.f)) ? d[e] : 0.f;
+                    }
+                }
             }
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                const bool take = (me[e] == m[e]) && !earlier[e] && (!relu_gate || me[e] > 0.f);
-                o[e] = take ? d[e] : 0.f;
+            store8(dx, base, f16, o[0]);
+            if (has_x1) store8(dx, base + C, f16, o[1]);
+            if (has_y1) {
+                store8(dx, base + size_t(W) * C, f16, o[2]);
+                if (has_x1) store8(dx, base + size_t(W) * C + C, f16, o[3]);
             }
         }
-        store8(dx, (size_t(i) / groups) * C + g * 8, f16, o);
     }
 }
 
@@ -523,7 +594,7 @@ extern "C" {
 int b2_colstats(const void* x, int64_t rows, int C, int f16, float* sum, float* sumsq, void* stream) {
     if (!x || !sum) return set_error("b2_colstats: null pointer");
     RowGrid g;
-    if (!row_grid(rows, C, g, 4)) return set_error("b2_colstats: C=%d unsupported (C/8 must divide %d)", C, kEwThreads);
+    if (!row_grid(rows, C, g, 2)) return set_error("b2_colstats: C=%d unsupported (C/8 must divide %d)", C, kEwThreads);
     colstats_kernel<<<g.blocks, kEwThreads, 0, B2_STREAM>>>(x, rows, C, f16, sum, sumsq);
     return launch_ok("b2_colstats");
 }
@@ -558,7 +629,7 @@ int b2_bn_bwd_reduce(const void* z, const void* g, int64_t rows, int C, int f16,
                      float* dalpha, void* stream) {
     if (!z || !g || !s1) return set_error("b2_bn_bwd_reduce: null pointer");
     RowGrid rg;
-    if (!row_grid(rows, C, rg, 4)) return set_error("b2_bn_bwd_reduce: C=%d unsupported", C);
+    if (!row_grid(rows, C, rg, 2)) return set_error("b2_bn_bwd_reduce: C=%d unsupported", C);
     bn_bwd_reduce_kernel<<<rg.blocks, kEwThreads, 0, B2_STREAM>>>(z, g, rows, C, f16, scale, shift, alpha, act, leaky, mean,
                                                                    invstd, s1, s2, dalpha);
     return launch_ok("b2_bn_bwd_reduce");
@@ -578,7 +649,7 @@ int b2_bn_bwd_apply(const void* z, const void* g, int64_t rows, int C, int f16, 
 int b2_maxpool2x2(const void* x, int B, int H, int W, int C, int f16, void* y, void* stream) {
     if (!x || !y) return set_error("b2_maxpool2x2: null pointer");
     if (C % 8 != 0 || H < 2 || W < 2) return set_error("b2_maxpool2x2: bad geometry %dx%dx%d", H, W, C);
-    maxpool_fwd_kernel<<<flat_grid(long(B) * (H / 2) * (W / 2) * (C / 8)), kEwThreads, 0, B2_STREAM>>>(x, B, H, W, C, f16, y);
+    maxpool_fwd_kernel<<<flat_grid(long(B) * (H / 2) * kEwThreads), kEwThreads, 0, B2_STREAM>>>(x, B, H, W, C, f16, y);
     return launch_ok("b2_maxpool2x2");
 }
 
@@ -586,7 +657,7 @@ int b2_maxpool2x2_bwd(const void* x, const void* y, const void* dy, int B, int H
                       void* dx, void* stream) {
     if (!x || !y || !dy || !dx) return set_error("b2_maxpool2x2_bwd: null pointer");
     if (C % 8 != 0 || H < 2 || W < 2) return set_error("b2_maxpool2x2_bwd: bad geometry %dx%dx%d", H, W, C);
-    maxpool_bwd_kernel<<<flat_grid(long(B) * H * W * (C / 8)), kEwThreads, 0, B2_STREAM>>>(x, y, dy, B, H, W, C, f16, relu_gate, dx);
+    maxpool_bwd_kernel<<<flat_grid(long(B) * ((H + 1) / 2) * kEwThreads), kEwThreads, 0, B2_STREAM>>>(x, y, dy, B, H, W, C, f16, relu_gate, dx);
     return launch_ok("b2_maxpool2x2_bwd");
 }
 
