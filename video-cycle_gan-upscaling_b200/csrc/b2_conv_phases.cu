@@ -13,8 +13,16 @@
 //     with the most taps is scheduled last and a short one first, which gives the loads the longest head start.
 //   * B ring: [256 x 64] weight blocks streamed from L2 in (phase, channel block, tap) order.
 //   * taps are shifted UMMA-descriptor views of the halo block, as in b2_conv_halo.cu.
+//   * Output: each epilogue warp owns a 4 x 8-pixel block of the tile and 128 of the 256 channels.  Writing a pixel row
+//     per thread straight to global memory costs one LSU wavefront per (thread, 32-byte piece) -- ncu showed the LSU data
+//     pipe 93 % busy on the 64 -> 256 block, half of it these stores.  Instead the warp packs 32 channels x 32 pixels into
+//     a 64-byte-swizzled 2 KB staging block (conflict-free 16-byte shared stores, 4 wavefronts per instruction) and one
+//     lane hands it to the TMA (cp.async.bulk.tensor store through a per-phase tensor map whose x / y strides skip the
+//     other parities).  Used when the staging blocks fit next to the rings and the layer has no gate / residual / fp32
+//     output; otherwise the shared register epilogue (b2_conv_epilogue.cuh) stores directly.
 // Warp roles: 0 = TMA producer (input), 1 = MMA issuer + TMEM owner, 2..9 = epilogue (lane quarter = warp % 4, column
 // half = (warp - 2) / 4), 10 = TMA producer (weights).
+#include <stdlib.h>
 #include <string.h>
 
 #include "b2_conv_epilogue.cuh"
@@ -42,16 +50,75 @@ struct PhaseGeom {
     int8_t oy[4], ox[4];     // output parity of the phase
     int8_t dy[kPhMaxTaps], dx[kPhMaxTaps];
     int16_t wtap[kPhMaxTaps];
+    int stage_bufs;          // 0: direct global stores; 1 / 2: staging blocks per epilogue warp for TMA stores
 };
+
+constexpr int kPhStageBytes = 32 * 64;     // 32 pixels x 32 channels x 2 bytes
+struct alignas(64) PhaseOutMaps { CUtensorMap m[4]; };   // per phase (execution order): [B][H][W][256] view of one output parity
+
+// TMA-store epilogue of one (tile, phase) for one epilogue warp: 128 accumulator columns of 32 pixel rows, in chunks of
+// 32 channels.  Staging block = TMA box {32 channels, 8 x, 4 y} with the 64-byte swizzle: pixel row `lane` is 64 bytes,
+// its 16-byte piece j sits at piece j ^ ((lane >> 1) & 3), which also makes the warp's shared stores conflict-free.
+template <int ACT>
+__device__ __forceinline__ void phase_epilogue_tma(const IgemmParams& p, uint32_t taddr, int half, int lane,
+                                                   const float* s_scale, const float* s_shift, const float* s_alpha,
+                                                   uint8_t* my_stage, int nbuf, int& sbuf, const CUtensorMap* map,
+                                                   int bx, int by, int b) {
+    const bool unit_scale = p.scale == nullptr;
+    const uint32_t swz = uint32_t((lane >> 1) & 3);
+#pragma unroll 1
+    for (int c0 = 0; c0 < 128; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld32(taddr + c0, r);
+        if (lane == 0) {                       // the store that last used this staging block must have read it
+            if (nbuf >= 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>();
+        }
+        __syncwarp();
+        tmem_ld_wait();
+        const int n = 128 * half + c0;
+        const uint32_t sc_a = smem_u32(s_scale + n), sh_a = smem_u32(s_shift + n), al_a = smem_u32(s_alpha + n);
+        const uint32_t row_a = smem_u32(my_stage + sbuf * kPhStageBytes) + uint32_t(lane) * 64u;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            uint32_t o[4];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int g4 = 2 * j + h;
+                float4 sc = make_float4(1.f, 1.f, 1.f, 1.f);
+                if (!unit_scale) sc = lds_f4(sc_a + 16 * g4);
+                const float4 sh = lds_f4(sh_a + 16 * g4);
+                float4 al = make_float4(0.f, 0.f, 0.f, 0.f);
+                if constexpr (ACT == ACT_PRELU) al = lds_f4(al_a + 16 * g4);
+                const float v0 = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g4 + 0]), sc.x, sh.x), p.leaky, al.x);
+                const float v1 = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g4 + 1]), sc.y, sh.y), p.leaky, al.y);
+                const float v2 = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g4 + 2]), sc.z, sh.z), p.leaky, al.z);
+                const float v3 = apply_act_t<ACT>(fmaf(__uint_as_float(r[4 * g4 + 3]), sc.w, sh.w), p.leaky, al.w);
+                o[2 * h] = pack2(v0, v1, p.f16);
+                o[2 * h + 1] = pack2(v2, v3, p.f16);
+            }
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row_a + ((uint32_t(j) ^ swz) << 4)), "r"(o[0]),
+                         "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+            tma_store_4d(map, my_stage + sbuf * kPhStageBytes, n, bx, by, b);
+            tma_store_commit();
+        }
+        if (++sbuf >= nbuf) sbuf = 0;
+    }
+}
 
 __global__ void __launch_bounds__(kPhThreads, 1)
 conv_phases_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
-                   const __grid_constant__ IgemmParams p, const __grid_constant__ PhaseGeom g) {
+                   const __grid_constant__ PhaseOutMaps mapO, const __grid_constant__ IgemmParams p,
+                   const __grid_constant__ PhaseGeom g) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smemB = smem;
     uint8_t* smemA = smem + kPhBStages * kPhBBlock;
-    uint8_t* tail = smemA + g.a_stages * g.a_block;
+    uint8_t* stage = smemA + g.a_stages * g.a_block;            // 8 warps x stage_bufs x 2 KB, 1024-aligned
+    uint8_t* tail = stage + 8 * g.stage_bufs * kPhStageBytes;
     uint64_t* bars = reinterpret_cast<uint64_t*>(tail);
     uint64_t* afull = bars;            // [8]
     uint64_t* aempty = bars + 8;       // [8]
@@ -171,6 +238,8 @@ conv_phases_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
         const int q = warp & 3, half = (warp - 2) >> 2;
         const int row = q * 32 + lane;
         const int r_tx = row % kPhTW, r_ty = row / kPhTW;
+        uint8_t* my_stage = stage + (warp - 2) * g.stage_bufs * kPhStageBytes;
+        int sbuf = 0;
         int as = 0; uint32_t aph = 0;
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
             int t = tile;
@@ -179,17 +248,28 @@ conv_phases_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
             const int gx = xt * kPhTW + r_tx, gy = yt * kPhTH + r_ty;
             const bool valid = gx < p.W && gy < p.H;
             for (int ph = 0; ph < g.nph; ++ph) {
-                const size_t pix = (size_t(t) * p.OH + size_t(gy * 2 + g.oy[ph])) * p.OW + size_t(gx * 2 + g.ox[ph]);
-                const size_t obase = pix * size_t(p.out_ld) + size_t(128 * half);
                 mbar_wait(&tfull[as], aph);
                 tc_fence_after();
                 const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * kPhBN + 128 * half);
-                switch (p.act) {
-                    case ACT_RELU: epilogue_tile<128, ACT_RELU>(p, taddr, valid, 128 * half, obase, s_scale, s_shift, s_alpha); break;
-                    case ACT_LEAKY: epilogue_tile<128, ACT_LEAKY>(p, taddr, valid, 128 * half, obase, s_scale, s_shift, s_alpha); break;
-                    case ACT_PRELU: epilogue_tile<128, ACT_PRELU>(p, taddr, valid, 128 * half, obase, s_scale, s_shift, s_alpha); break;
-                    case ACT_TANH: epilogue_tile<128, ACT_TANH>(p, taddr, valid, 128 * half, obase, s_scale, s_shift, s_alpha); break;
-                    default: epilogue_tile<128, ACT_NONE>(p, taddr, valid, 128 * half, obase, s_scale, s_shift, s_alpha); break;
+                if (g.stage_bufs) {
+                    const int bx = xt * kPhTW, by = yt * kPhTH + 4 * q;
+                    switch (p.act) {
+                        case ACT_RELU: phase_epilogue_tma<ACT_RELU>(p, taddr, half, lane, s_scale, s_shift, s_alpha, my_stage, g.stage_bufs, sbuf, &mapO.m[ph], bx, by, t); break;
+                        case ACT_LEAKY: phase_epilogue_tma<ACT_LEAKY>(p, taddr, half, lane, s_scale, s_shift, s_alpha, my_stage, g.stage_bufs, sbuf, &mapO.m[ph], bx, by, t); break;
+                        case ACT_PRELU: phase_epilogue_tma<ACT_PRELU>(p, taddr, half, lane, s_scale, s_shift, s_alpha, my_stage, g.stage_bufs, sbuf, &mapO.m[ph], bx, by, t); break;
+                        case ACT_TANH: phase_epilogue_tma<ACT_TANH>(p, taddr, half, lane, s_scale, s_shift, s_alpha, my_stage, g.stage_bufs, sbuf, &mapO.m[ph], bx, by, t); break;
+                        default: phase_epilogue_tma<ACT_NONE>(p, taddr, half, lane, s_scale, s_shift, s_alpha, my_stage, g.stage_bufs, sbuf, &mapO.m[ph], bx, by, t); break;
+                    }
+                } else {
+                    const size_t pix = (size_t(t) * p.OH + size_t(gy * 2 + g.oy[ph])) * p.OW + size_t(gx * 2 + g.ox[ph]);
+                    const size_t obase = pix * size_t(p.out_ld) + size_t(128 * half);
+                    switch (p.act) {
+                        case ACT_RELU: epilogue_tile<128, ACT_RELU>(p, taddr, valid, 128 * half, obase, s_scale, s_shift, s_alpha); break;
+                        case ACT_LEAKY: epilogue_tile<128, ACT_LEAKY>(p, taddr, valid, 128 * half, obase, s_scale, s_shift, s_alpha); break;
+                        case ACT_PRELU: epilogue_tile<128, ACT_PRELU>(p, taddr, valid, 128 * half, obase, s_scale, s_shift, s_alpha); break;
+                        case ACT_TANH: epilogue_tile<128, ACT_TANH>(p, taddr, valid, 128 * half, obase, s_scale, s_shift, s_alpha); break;
+                        default: epilogue_tile<128, ACT_NONE>(p, taddr, valid, 128 * half, obase, s_scale, s_shift, s_alpha); break;
+                    }
                 }
                 tc_fence_before();
                 __syncwarp();
@@ -197,6 +277,7 @@ conv_phases_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
                 if (++as == 2) { as = 0; aph ^= 1; }
             }
         }
+        if (g.stage_bufs && lane == 0) tma_store_wait_all<0>();   // the staging blocks must outlive the stores' reads
     }
 
     tc_fence_before();
@@ -257,10 +338,20 @@ int launch_conv_phases(const ConvIgemmArgs* ph, int nph, cudaStream_t stream) {
     g.a_block = ((g.HH * g.HW * 128) + 1023) & ~1023;
     const int cbs = p.cin / 64;
     const int tail_bytes = 256 + 3 * kPhBN * 4;
-    g.a_stages = (kPhSmemMax - 1024 - kPhBStages * kPhBBlock - tail_bytes) / g.a_block;
+    const int avail = kPhSmemMax - 1024 - kPhBStages * kPhBBlock - tail_bytes;
+    // staging blocks for the TMA-store epilogue: two per epilogue warp if they fit beside the minimum input ring, else one
+    const bool can_stage = !p.out_fp32 && !p.gate && !p.residual && p.OH == 2 * p.H && p.OW == 2 * p.W;
+    static const int force_bufs = getenv("B2_PHASES_STAGE_BUFS") ? atoi(getenv("B2_PHASES_STAGE_BUFS")) : -1;
+    g.stage_bufs = 0;
+    if (can_stage) {
+        for (int nb = 2; nb >= 1; --nb)
+            if (avail - 8 * nb * kPhStageBytes >= (cbs + 1) * g.a_block) { g.stage_bufs = nb; break; }
+        if (force_bufs >= 0 && force_bufs < g.stage_bufs) g.stage_bufs = force_bufs;
+    }
+    g.a_stages = (avail - 8 * g.stage_bufs * kPhStageBytes) / g.a_block;
     if (g.a_stages > 8) g.a_stages = 8;
     if (g.a_stages < cbs + 1) return set_error("conv_phases: %d input blocks of %d bytes do not fit", cbs, g.a_block);
-    const int smem_bytes = 1024 + kPhBStages * kPhBBlock + g.a_stages * g.a_block + tail_bytes;
+    const int smem_bytes = 1024 + kPhBStages * kPhBBlock + g.a_stages * g.a_block + 8 * g.stage_bufs * kPhStageBytes + tail_bytes;
     p.TB = 1; p.TH = kPhTH; p.TW = kPhTW;
     p.tiles_x = (p.W + kPhTW - 1) / kPhTW;
     p.tiles_y = (p.H + kPhTH - 1) / kPhTH;
@@ -286,6 +377,19 @@ int launch_conv_phases(const ConvIgemmArgs* ph, int nph, cudaStream_t stream) {
         int rc = encode_tensor_map(&mapB, a.w, 2, dims, strides, box, estr);
         if (rc) return rc;
     }
+    PhaseOutMaps mapO;
+    memset(&mapO, 0, sizeof(mapO));
+    if (g.stage_bufs) {
+        for (int i = 0; i < 4; ++i) {
+            const char* base = reinterpret_cast<const char*>(p.out) + (size_t(g.oy[i]) * p.OW + size_t(g.ox[i])) * size_t(p.out_ld) * 2;
+            cuuint64_t dims[4] = {cuuint64_t(kPhBN), cuuint64_t(p.W), cuuint64_t(p.H), cuuint64_t(p.B)};
+            cuuint64_t strides[3] = {cuuint64_t(p.out_ld) * 4, cuuint64_t(p.OW) * p.out_ld * 4, cuuint64_t(p.OH) * p.OW * p.out_ld * 2};
+            cuuint32_t box[4] = {32, cuuint32_t(kPhTW), 4, 1};
+            cuuint32_t estr[4] = {1, 1, 1, 1};
+            int rc = encode_tensor_map(&mapO.m[i], base, 4, dims, strides, box, estr, 64);
+            if (rc) return rc;
+        }
+    }
     static int attr_smem = 0;
     if (attr_smem < smem_bytes) {
         cudaError_t e = cudaFuncSetAttribute(conv_phases_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
@@ -294,7 +398,7 @@ int launch_conv_phases(const ConvIgemmArgs* ph, int nph, cudaStream_t stream) {
     }
     const int sms = device_sm_count();
     const int grid = p.num_tiles < sms ? p.num_tiles : sms;
-    conv_phases_kernel<<<grid, kPhThreads, smem_bytes, stream>>>(mapA, mapB, p, g);
+    conv_phases_kernel<<<grid, kPhThreads, smem_bytes, stream>>>(mapA, mapB, mapO, p, g);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("conv_phases launch: %s", cudaGetErrorString(e));
     return 0;

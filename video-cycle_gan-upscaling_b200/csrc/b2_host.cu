@@ -46,11 +46,13 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 int encode_tensor_map(CUtensorMap* map, const void* base, int rank, const cuuint64_t* dims,
-                      const cuuint64_t* strides_bytes, const cuuint32_t* box, const cuuint32_t* elem_strides) {
+                      const cuuint64_t* strides_bytes, const cuuint32_t* box, const cuuint32_t* elem_strides,
+                      int swizzle_bytes) {
     EncodeTiledFn fn = get_encode_fn();
     if (!fn) return set_error("cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
     CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, cuuint32_t(rank), const_cast<void*>(base), dims,
-                    strides_bytes, box, elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    strides_bytes, box, elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS)
         return set_error("cuTensorMapEncodeTiled failed (%d): rank=%d dims=[%llu,%llu,..] box=[%u,%u,..]", int(r), rank,

@@ -19,7 +19,7 @@ int device_sm_count();
 // rank-`rank` bf16 tensor, 128-byte swizzle, zero fill for out-of-bounds elements.
 int encode_tensor_map(CUtensorMap* map, const void* base, int rank, const cuuint64_t* dims,
                       const cuuint64_t* strides_bytes /* rank-1 entries */, const cuuint32_t* box,
-                      const cuuint32_t* elem_strides);
+                      const cuuint32_t* elem_strides, int swizzle_bytes = 128 /* 128 or 64 */);
 
 struct ConvIgemmArgs {
     const __nv_bfloat16* x;  // input NHWC
