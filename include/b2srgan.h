@@ -29,6 +29,9 @@ enum { B2_ACT_NONE = 0, B2_ACT_RELU = 1, B2_ACT_LEAKY = 2, B2_ACT_PRELU = 3, B2_
 
 const char* b2_last_error(void);
 int b2_version(void);
+/* Switches the CTA-pair (tcgen05 cta_group::2) kernels on or off for subsequent calls; returns the previous setting.
+ * Both settings compute the same results; the switch exists for A/B measurements and tests. */
+int b2_set_pair_kernels(int enable);
 
 /* Epilogue shared by every convolution entry point:
  *   out = act(acc * scale[c] + shift[c]) + residual

@@ -83,6 +83,33 @@ def test_conv2d_transpose_s2(k, Cin, H, W):
     _close(y.float().cpu().numpy(), ref, 4e-3, 1e-2)
 
 
+@pytest.mark.parametrize("k,Cin,B,H,W", [(3, 64, 2, 32, 24), (3, 256, 1, 48, 24), (3, 256, 3, 47, 23), (5, 64, 1, 33, 31),
+                                         (3, 128, 5, 16, 8)])
+@pytest.mark.parametrize("pair", [True, False])
+def test_conv2d_transpose_s2_fused_phases(k, Cin, B, H, W, pair):
+    """Images large enough for the fused-phase kernels (b2_conv_phases2.cu over CTA pairs, b2_conv_phases.cu single CTA):
+    odd tile counts (the last pair's second CTA idles), ragged right / bottom edges, TMA-store epilogue."""
+    from upscaler import ops
+    dtype = torch.float16
+    rng = np.random.default_rng(k * 1000 + Cin + H)
+    x = _rnd((B, H, W, Cin), rng)
+    kern = _rnd((k, k, 256, Cin), rng, 1.0 / np.sqrt(k * k * Cin / 4))
+    bias = _rnd((256,), rng, 0.1)
+    ref = O.leaky(O.conv2d_transpose_same_s2(_q(x, dtype).permute(0, 3, 1, 2), _q(kern, dtype), torch.from_numpy(bias)),
+                  0.2).permute(0, 2, 3, 1).numpy()
+    idx = torch.from_numpy(ops.convT_pack_index(k, k, Cin, 256)).cuda()
+    wp = ops.gather_cast(torch.from_numpy(kern).cuda(), idx, dtype=dtype)
+    ops.set_pair_kernels(pair)
+    try:
+        y = ops.conv2d_transpose_s2(torch.from_numpy(x).cuda().to(dtype), wp, 256, k, k, shift=torch.from_numpy(bias).cuda(),
+                                    act=ops.ACT_LEAKY, leaky=0.2)
+        torch.cuda.synchronize()
+    finally:
+        ops.set_pair_kernels(True)
+    assert tuple(y.shape) == (B, 2 * H, 2 * W, 256)
+    _close(y.float().cpu().numpy(), ref, 4e-3, 1e-2)
+
+
 @pytest.mark.parametrize("shape", [(1, 24, 40), (2, 9, 150), (1, 3, 5), (1, 20, 128), (1, 31, 257)])
 def test_final_conv_rows(shape):
     """final/conv 9x9 256->3 + tanh, row-streaming kernel, ragged widths (strip edges) and heights < filter."""

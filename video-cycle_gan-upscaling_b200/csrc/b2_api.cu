@@ -8,6 +8,9 @@
 
 using namespace b2;
 
+// CTA-pair (cta_group::2) kernels on/off: A/B switch for tests and profiling (env B2_NO_PAIR=1 starts with them off)
+static int g_pair_kernels = getenv("B2_NO_PAIR") ? 0 : 1;
+
 static void fill_epilogue(IgemmParams& p, const b2_epilogue* ep, int Cout) {
     p.scale = ep->scale;
     p.shift = ep->shift;
@@ -99,8 +102,14 @@ static int run_transposed(const void* x, int B, int H, int W, int Cin, const voi
         ++n;
     }
     static const bool no_fuse = getenv("B2_NO_PHASE_FUSION") != nullptr;      // A/B switch for profiling
-    if (!direct && !no_fuse && all && conv_phases_applicable(args, n))
-        return launch_conv_phases(args, n, reinterpret_cast<cudaStream_t>(stream));
+    if (!direct && !no_fuse && all) {
+        // CTA-pair kernel first (half the weight traffic per SM); -2 = its rings do not fit this geometry
+        if (g_pair_kernels && conv_phases2_applicable(args, n)) {
+            const int rc = launch_conv_phases2(args, n, reinterpret_cast<cudaStream_t>(stream));
+            if (rc != -2) return rc;
+        }
+        if (conv_phases_applicable(args, n)) return launch_conv_phases(args, n, reinterpret_cast<cudaStream_t>(stream));
+    }
     for (int i = 0; i < n; ++i) {
         int rc = direct ? launch_conv_direct(args[i], reinterpret_cast<cudaStream_t>(stream))
                         : launch_conv_igemm(args[i], reinterpret_cast<cudaStream_t>(stream));
@@ -113,6 +122,12 @@ extern "C" {
 
 const char* b2_last_error(void) { return last_error(); }
 int b2_version(void) { return 1; }
+
+int b2_set_pair_kernels(int enable) {
+    const int old = g_pair_kernels;
+    g_pair_kernels = enable ? 1 : 0;
+    return old;
+}
 
 int b2_conv2d_fprop(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw, int stride,
                     const b2_epilogue* ep, void* stream) {

@@ -45,6 +45,9 @@ int launch_conv_stack(const ConvIgemmArgs& a, cudaStream_t stream);
 // All sub-pixel phases of a stride-2 transposed conv with Cout = 256 in one persistent kernel (b2_conv_phases.cu).
 bool conv_phases_applicable(const ConvIgemmArgs* phases, int nph);
 int launch_conv_phases(const ConvIgemmArgs* phases, int nph, cudaStream_t stream);
+// The same over CTA pairs (tcgen05 cta_group::2, b2_conv_phases2.cu); returns -2 when its rings do not fit.
+bool conv_phases2_applicable(const ConvIgemmArgs* phases, int nph);
+int launch_conv_phases2(const ConvIgemmArgs* phases, int nph, cudaStream_t stream);
 
 // Weight gradient (b2_conv_wgrad.cu): dw[wtap[t]][cx][cz] += sum_p x[p*in_mul + d(t), cx] * dz[p, cz], fp32 accumulate.
 struct WgradArgs {

@@ -37,6 +37,7 @@ _P, _I, _L, _F = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float
 _SIGNATURES = {
     "b2_last_error": (ctypes.c_char_p, []),
     "b2_version": (ctypes.c_int, []),
+    "b2_set_pair_kernels": (ctypes.c_int, [ctypes.c_int]),
     "b2_conv2d_fprop": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p] + [ctypes.c_int] * 4 +
                         [ctypes.POINTER(Epilogue), ctypes.c_void_p]),
     "b2_conv2d_transpose_s2_fprop": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p] +

@@ -24,6 +24,11 @@ def launch_count():
     return _launches
 
 
+def set_pair_kernels(enable):
+    """A/B switch for the CTA-pair (cta_group::2) kernels; returns the previous setting."""
+    return bool(_lib.load().b2_set_pair_kernels(1 if enable else 0))
+
+
 def _count(n):
     global _launches
     _launches += n
