@@ -293,10 +293,14 @@ def main():
         dom = "upscaling/1/block/conv_transp"
         dom_ms = layer_ms.get(dom)
         achieved = CONVT2_FLOPS[ks] * B / (dom_ms * 1e-3) / 1e12 if dom_ms else None
-        roof = {"bound": "tensor", "kernel": "conv_halo_kernel<256> x3 + conv_igemm_kernel<256> x1 (the 4 sub-pixel phases of " + dom + ")",
+        # DRAM bytes of that launch from `ncu --set full` (profiles/r01_s22_ncu_full_conv_phases2_convT2_summary.txt,
+        # B = 8, k = 3): 2.17 GB read + 8.44 GB written; algorithmic = 2.12 GB input + 8.49 GB output -> no wasted re-reads
+        traffic = 10.61e9 * B / 8 if ks == 3 else None
+        roof = {"bound": "tensor", "kernel": "conv_phases2_kernel (all 4 sub-pixel phases of " + dom + " in one persistent CTA-pair launch)",
                 "achieved": achieved, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
                 "frac": (achieved / peaks["bf16_tflops_sustained"]) if achieved else None,
-                "peak_kind": "bf16 dense sustained, %s" % peaks["source"], "traffic": None,
+                "peak_kind": "bf16 dense sustained, %s" % peaks["source"], "traffic": traffic,
+                "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)",
                 "share_of_step": (dom_ms / ms_step) if dom_ms else None}
         whole = GEN_FLOPS[ks] * world * B / (ms_step * 1e-3) / 1e12
         cpu = None
