@@ -206,6 +206,9 @@ STACK_CASES = [
     (2, 47, 16, 9, 1, "prelu"),        # the folded 9x1 head conv
     (1, 48, 40, 3, 3, "gate"),         # dgrad form: ReLU gate + residual, bf16
     (1, 144, 8, 1, 3, "fp32"),         # 1x3 filter, fp32 output, several tiles per column strip
+    (2, 64, 24, 5, 5, "prelu"),        # 5x5 (the reference's default kernel size): 200 KB of weights, streamed strips, R = 2
+    (1, 70, 19, 5, 5, "residual"),     # 5x5 streamed, ragged edges, several tiles per CTA ring wrap
+    (1, 45, 16, 5, 3, "gate"),         # 5x3 streamed (120 KB of weights), dgrad-form epilogue
 ]
 
 

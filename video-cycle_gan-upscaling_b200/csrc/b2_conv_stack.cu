@@ -14,13 +14,16 @@
 //   M tile   = 16 row-groups x 8 pixels; group g covers output rows y0 + R*g .. y0 + R*g + R-1 -> 16R x 8 output pixels
 //   A tile   = (16R + kh - 1) x (8 + kw - 1) pixels x 64 channels (128-byte swizzled rows, one TMA box per 64 channels),
 //              view of shift (s, dx): start + (s*HW + dx)*128 B, 8-row-group stride R*HW*128 B
-//   weights  = all kh*kw*(Cin/64) blocks of [64 x 64] resident in shared memory (<= 96 KB)
+//   weights  = all kh*kw*(Cin/64) blocks of [64 x 64] resident in shared memory (<= 96 KB), or -- 5x5 filters: 200 KB --
+//              STREAMED: a ring of strip slots (one per-dx strip of kh blocks + R-1 zero blocks each), filled by a
+//              second producer warp in the order the MMA warp walks (cb, dx); 200 KB per 32x8-pixel tile from L2 is
+//              ~20 B/clk/SM, far below what the MMAs of the tile take
 // The very first MMA group of a tile must overwrite all R*64 accumulator columns (tcgen05.mma has one accumulate flag
 // per instruction): the (dx = 0, cb = 0) strip is placed last in shared memory and followed by R-1 blocks of zeros, so
 // that group runs at N = 64R with B = [W(ky=0) | 0 | ... | 0]; every other MMA accumulates.
 //
-// Warp roles: 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..9 = epilogue (TMEM lane quarter = warp % 4, channel
-// half = (warp - 2) / 4).
+// Warp roles: 0 = TMA producer (input tiles; resident weights), 1 = MMA issuer + TMEM owner, 2..9 = epilogue (TMEM lane
+// quarter = warp % 4, channel half = (warp - 2) / 4), 10 = TMA producer of streamed weight strips.
 #include <string.h>
 
 #include "b2_conv_epilogue.cuh"
@@ -30,7 +33,7 @@
 
 namespace b2 {
 
-constexpr int kStackThreads = 320;          // TMA warp, MMA warp, 8 epilogue warps
+constexpr int kStackThreads = 320;          // TMA warp, MMA warp, 8 epilogue warps (+ a weight-strip warp when streaming: 352)
 constexpr int kStackTW = 8;                    // pixels per row group (one 8-row swizzle atom)
 constexpr int kStackGroups = 16;               // row groups per M = 128 tile
 constexpr int kStackMaxK = 9;                  // filter rows / columns supported
@@ -45,6 +48,8 @@ struct StackGeom {
     int a_stages;
     int b_bytes;         // resident weights + zero blocks
     int nshift;          // kh + R - 1
+    int b_slots;         // 0: weights resident; >= 2: weight strips streamed through a ring of this many slots
+    int slot_bytes;      // (kh + R - 1) blocks of 8 KB
     int16_t wt[kStackMaxK][kStackMaxK];   // [ky][dxi] -> index of the tap's [Cout x Cin] slab in the packed weights
     uint8_t cnt[kStackMaxShifts];         // per shift: number of stacked output rows it feeds
     uint8_t jlo[kStackMaxShifts];         //            first of them
@@ -191,11 +196,12 @@ __device__ __forceinline__ void stack_epilogue_dispatch(const IgemmParams& p, ui
     }
 }
 
-template <int R>
-__global__ void __launch_bounds__(kStackThreads, 1)
+template <int R, bool STREAM>
+__global__ void __launch_bounds__(STREAM ? kStackThreads + 32 : kStackThreads, 1)
 conv_stack_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                   const __grid_constant__ IgemmParams p, const __grid_constant__ StackGeom g) {
     constexpr int kBlk = 64 * 128;            // one [64 cout x 64 k] weight block
+    constexpr int kThreads = STREAM ? kStackThreads + 32 : kStackThreads;
     constexpr int kAccCols = 64 * R;
     constexpr uint32_t kTmemCols = (2 * kAccCols) <= 128 ? 128 : ((2 * kAccCols) <= 256 ? 256 : 512);
     extern __shared__ uint8_t smem_raw[];
@@ -210,7 +216,9 @@ conv_stack_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     uint64_t* tfull = bars + 9;        // [2]
     uint64_t* tempty = bars + 11;      // [2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
-    float* s_scale = reinterpret_cast<float*>(tail + 128);
+    uint64_t* sfull = bars + 16;       // [4] streamed weight strips
+    uint64_t* sempty = bars + 20;      // [4]
+    float* s_scale = reinterpret_cast<float*>(tail + 256);
     float* s_shift = s_scale + 64;
     float* s_alpha = s_shift + 64;
 
@@ -222,16 +230,23 @@ conv_stack_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         tma_prefetch_desc(&mapB);
         for (int s = 0; s < 4; ++s) { mbar_init(&afull[s], 1); mbar_init(&aempty[s], 1); }
         mbar_init(bfull, 1);
+        for (int s = 0; s < 4; ++s) { mbar_init(&sfull[s], 1); mbar_init(&sempty[s], 1); }
         for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 8); }
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc<kTmemCols>(tmem_slot);
-    {   // zero blocks behind the last strip (B operand of the tile-opening MMA group)
+    if constexpr (!STREAM) {   // zero blocks behind the last strip (B operand of the tile-opening MMA group)
         uint4* z = reinterpret_cast<uint4*>(smemB + nstrips * g.kh * kBlk);
-        for (int i = threadIdx.x; i < (R - 1) * kBlk / 16; i += kStackThreads) z[i] = make_uint4(0, 0, 0, 0);
+        for (int i = threadIdx.x; i < (R - 1) * kBlk / 16; i += kThreads) z[i] = make_uint4(0, 0, 0, 0);
+        fence_proxy_async();
+    } else {                // streamed: every ring slot ends in R-1 zero blocks the strip loads never touch
+        for (int sl = 0; sl < g.b_slots; ++sl) {
+            uint4* z = reinterpret_cast<uint4*>(smemB + sl * g.slot_bytes + g.kh * kBlk);
+            for (int i = threadIdx.x; i < (R - 1) * kBlk / 16; i += kThreads) z[i] = make_uint4(0, 0, 0, 0);
+        }
         fence_proxy_async();
     }
-    for (int c = threadIdx.x; c < 64; c += kStackThreads) {
+    for (int c = threadIdx.x; c < 64; c += kThreads) {
         s_scale[c] = p.scale ? p.scale[c] : 1.f;
         s_shift[c] = p.shift ? p.shift[c] : 0.f;
         s_alpha[c] = p.alpha ? p.alpha[c] : 0.f;
@@ -244,7 +259,7 @@ conv_stack_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 
     if (warp == 0) {
         // ------------------------------------------------------------ producer: resident weights, then halo tiles
-        if (lane == 0) {
+        if (lane == 0 && !STREAM) {
             mbar_expect_tx(bfull, uint32_t(nstrips * g.kh) * kBlk);
             for (int dxi = 0; dxi < g.kw; ++dxi)
                 for (int cb = 0; cb < cbs; ++cb) {
@@ -280,7 +295,9 @@ conv_stack_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         const uint32_t a_lo0 = sdesc_lo(smem_u32(smemA)), b_lo0 = sdesc_lo(smem_u32(smemB));
         int sa = 0; uint32_t pa = 0;
         int as = 0; uint32_t aph = 0;
-        mbar_wait(bfull, 0);
+        int sb = 0; uint32_t pb = 0;
+        constexpr bool streamed = STREAM;
+        if (!streamed) mbar_wait(bfull, 0);
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
             mbar_wait(&tempty[as], aph ^ 1);
             tc_fence_after();
@@ -292,7 +309,12 @@ conv_stack_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                 for (int dxi = 0; dxi < g.kw; ++dxi) {
                     const int q = dxi * cbs + cb;
                     const int pos = q == 0 ? nstrips - 1 : q - 1;
-                    const uint32_t b_lo_strip = b_lo0 + uint32_t(pos * g.kh) * (kBlk >> 4);
+                    uint32_t b_lo_strip = b_lo0 + uint32_t(pos * g.kh) * (kBlk >> 4);
+                    if (streamed) {
+                        mbar_wait(&sfull[sb], pb);
+                        tc_fence_after();
+                        b_lo_strip = b_lo0 + uint32_t(sb) * uint32_t(g.slot_bytes >> 4);
+                    }
                     for (int s = 0; s < g.nshift; ++s) {
                         const bool opening = (q | s) == 0;          // first MMA group of the tile: overwrite all R blocks
                         const uint32_t cnt = opening ? uint32_t(R) : uint32_t(g.cnt[s]);
@@ -306,6 +328,7 @@ conv_stack_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                             umma_f16_lohi(d, a_lo + 2, a_hi, b_lo + 2, b_hi, idesc, 1);
                             umma_f16_lohi(d, a_lo + 4, a_hi, b_lo + 4, b_hi, idesc, 1);
                             umma_f16_lohi(d, a_lo + 6, a_hi, b_lo + 6, b_hi, idesc, 1);
+                            if (streamed && s == g.nshift - 1) umma_commit(&sempty[sb]);
                             if (last) {
                                 umma_commit(&aempty[sa]);
                                 if (cb == cbs - 1) umma_commit(&tfull[as]);
@@ -313,10 +336,29 @@ conv_stack_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                         }
                         __syncwarp();
                     }
+                    if (streamed && ++sb == g.b_slots) { sb = 0; pb ^= 1; }
                 }
                 if (++sa == g.a_stages) { sa = 0; pa ^= 1; }
             }
             if (++as == 2) { as = 0; aph ^= 1; }
+        }
+    } else if (STREAM && warp == 10) {
+        // ------------------------------------------------------------ producer: streamed weight strips, (cb, dx) order
+        {
+            int sb = 0; uint32_t pb = 0;
+            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x)
+                for (int cb = 0; cb < cbs; ++cb)
+                    for (int dxi = 0; dxi < g.kw; ++dxi) {
+                        mbar_wait(&sempty[sb], pb ^ 1);
+                        if (lane == 0) {
+                            mbar_expect_tx(&sfull[sb], uint32_t(g.kh) * kBlk);
+                            for (int i = 0; i < g.kh; ++i)                      // descending ky
+                                tma_load_2d(smemB + sb * g.slot_bytes + i * kBlk, &mapB, &sfull[sb],
+                                            int(g.wt[g.kh - 1 - i][dxi]) * p.cin + cb * 64, 0);
+                        }
+                        __syncwarp();
+                        if (++sb == g.b_slots) { sb = 0; pb ^= 1; }
+                    }
         }
     } else {
         // ------------------------------------------------------------ epilogue: R output pixels per accumulator row
@@ -354,19 +396,23 @@ static bool stack_rect(const IgemmParams& p, int& kh, int& kw, int& dy0, int& dx
 
 // Rows stacked per accumulator row for an image of H rows: the largest R in {3, 2} whose 16R-row tiles waste at most
 // ~15 % of the MMA rows and whose operands fit in shared memory; 0 when the kernel does not apply.
-static int stack_pick_r(const ConvIgemmArgs& a, int kh, int kw) {
+static int stack_pick_r(const ConvIgemmArgs& a, int kh, int kw, bool* streamed = nullptr) {
     const IgemmParams& p = a.p;
     const int cbs = p.cin / 64;
     const int wbytes = kh * kw * cbs * 64 * 128;
-    if (wbytes > 96 * 1024) return 0;
     const int tw = (p.W + kStackTW - 1) / kStackTW * kStackTW;
-    for (int R = 3; R >= 2; --R) {
-        const int th = kStackGroups * R;
-        const long covered = long((p.H + th - 1) / th) * th * tw;
-        if (long(p.H) * p.W * 100 < covered * 85) continue;
-        const int a_block = (((th + kh - 1) * (kStackTW + kw - 1) * 128) + 1023) & ~1023;
-        if (wbytes + (R - 1) * 8192 + 2 * a_block + 2048 > kStackSmemMax) continue;
-        return R;
+    for (int pass = 0; pass < 2; ++pass) {           // resident weights first, then streamed strips
+        if (pass == 0 && wbytes > 96 * 1024) continue;
+        for (int R = 3; R >= 2; --R) {
+            const int th = kStackGroups * R;
+            const long covered = long((p.H + th - 1) / th) * th * tw;
+            if (long(p.H) * p.W * 100 < covered * 85) continue;
+            const int a_block = (((th + kh - 1) * (kStackTW + kw - 1) * 128) + 1023) & ~1023;
+            const int b_bytes = pass == 0 ? wbytes + (R - 1) * 8192 : 2 * (kh + R - 1) * 8192;
+            if (b_bytes + 2 * a_block + 2048 > kStackSmemMax) continue;
+            if (streamed) *streamed = pass == 1;
+            return R;
+        }
     }
     return 0;
 }
@@ -381,18 +427,18 @@ bool conv_stack_applicable(const ConvIgemmArgs& a) {
     return stack_pick_r(a, kh, kw) != 0;
 }
 
-template <int R>
+template <int R, bool STREAM>
 static int launch_stack_r(const CUtensorMap& mapA, const CUtensorMap& mapB, const IgemmParams& p, const StackGeom& g,
                           int smem_bytes, cudaStream_t stream) {
     static int attr_smem = 0;
     if (attr_smem < smem_bytes) {
-        cudaError_t e = cudaFuncSetAttribute(conv_stack_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+        cudaError_t e = cudaFuncSetAttribute(conv_stack_kernel<R, STREAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
         if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(conv_stack): %s", cudaGetErrorString(e));
         attr_smem = smem_bytes;
     }
     const int sms = device_sm_count();
     const int grid = p.num_tiles < sms ? p.num_tiles : sms;
-    conv_stack_kernel<R><<<grid, kStackThreads, smem_bytes, stream>>>(mapA, mapB, p, g);
+    conv_stack_kernel<R, STREAM><<<grid, STREAM ? kStackThreads + 32 : kStackThreads, smem_bytes, stream>>>(mapA, mapB, p, g);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("conv_stack launch: %s", cudaGetErrorString(e));
     return 0;
@@ -403,7 +449,8 @@ int launch_conv_stack(const ConvIgemmArgs& a, cudaStream_t stream) {
     StackGeom g;
     memset(&g, 0, sizeof(g));
     if (!stack_rect(p, g.kh, g.kw, g.dy_min, g.dx_min)) return set_error("conv_stack: taps are not a full rectangle");
-    const int R = stack_pick_r(a, g.kh, g.kw);
+    bool streamed = false;
+    const int R = stack_pick_r(a, g.kh, g.kw, &streamed);
     if (R == 0) return set_error("conv_stack: not applicable to %dx%d, Cin=%d, %dx%d taps", p.H, p.W, p.cin, g.kh, g.kw);
     for (int t = 0; t < p.num_taps; ++t) g.wt[p.dy[t] - g.dy_min][p.dx[t] - g.dx_min] = p.wtap[t];
     g.nshift = g.kh + R - 1;
@@ -420,6 +467,13 @@ int launch_conv_stack(const ConvIgemmArgs& a, cudaStream_t stream) {
     g.HW = kStackTW + g.kw - 1;
     g.a_block = ((g.HH * g.HW * 128) + 1023) & ~1023;
     g.b_bytes = (g.kh * g.kw * cbs + (R - 1)) * 64 * 128;
+    if (streamed) {
+        g.slot_bytes = (g.kh + R - 1) * 64 * 128;
+        g.b_slots = (kStackSmemMax - 2048 - 2 * g.a_block) / g.slot_bytes;
+        if (g.b_slots > 4) g.b_slots = 4;
+        if (g.b_slots > g.kw * cbs) g.b_slots = g.kw * cbs < 2 ? 2 : g.kw * cbs;
+        g.b_bytes = g.b_slots * g.slot_bytes;
+    }
     g.a_stages = (kStackSmemMax - 2048 - g.b_bytes) / g.a_block;
     if (g.a_stages > 4) g.a_stages = 4;
     if (g.a_stages < 2) return set_error("conv_stack: no room for double buffering");
@@ -448,7 +502,9 @@ int launch_conv_stack(const ConvIgemmArgs& a, cudaStream_t stream) {
         int rc = encode_tensor_map(&mapB, a.w, 2, dims, strides, box, estr);
         if (rc) return rc;
     }
-    return R == 3 ? launch_stack_r<3>(mapA, mapB, p, g, smem_bytes, stream) : launch_stack_r<2>(mapA, mapB, p, g, smem_bytes, stream);
+    if (streamed)
+        return R == 3 ? launch_stack_r<3, true>(mapA, mapB, p, g, smem_bytes, stream) : launch_stack_r<2, true>(mapA, mapB, p, g, smem_bytes, stream);
+    return R == 3 ? launch_stack_r<3, false>(mapA, mapB, p, g, smem_bytes, stream) : launch_stack_r<2, false>(mapA, mapB, p, g, smem_bytes, stream);
 }
 
 }  // namespace b2
