@@ -168,11 +168,15 @@ def init_vgg19_weights(seed=4321):
 DISC_FILTERS = [64, 128, 256, 512, 512, 512, 512, 512, 512]
 
 
-def init_discriminator_simple_512_weights(seed=99, input_shape=(512, 512, 3), randomize=True):
+DISC_THIN_FILTERS = [64, 128, 128, 128, 128, 128, 128, 128, 128]     # make_discriminator_thin_512, model.py:901-939
+
+
+def init_discriminator_simple_512_weights(seed=99, input_shape=(512, 512, 3), randomize=True, filters=None):
+    """`filters`: DISC_FILTERS (simple_512, default) or DISC_THIN_FILTERS (thin_512); the forward pass is the same."""
     rng = np.random.default_rng(seed)
     w, cin = {}, input_shape[2]
     h, wd = input_shape[0], input_shape[1]
-    for i, c in enumerate(DISC_FILTERS):
+    for i, c in enumerate(filters or DISC_FILTERS):
         w["discriminator/block_%d/Conv2d" % (i + 1)] = _conv_w(rng, 3, 3, cin, c, 0.02 if randomize else 0.0)
         w["discriminator/block_%d/BatchNorm" % (i + 1)] = _bn_w(rng, c, randomize)
         if i > 0:
@@ -312,7 +316,8 @@ def gan_losses(family, act, real_out, fake_out):
 
 # ------------------------------------------------------------------------------------------------ discriminator
 def discriminator_simple_512_forward(w, x_nhwc, activation="none", training=False, stats_out=None):
-    """make_discriminator_simple_512 (model.py:836-896); returns (n, 1)."""
+    """make_discriminator_simple_512 (model.py:836-896) and make_discriminator_thin_512 (model.py:901-960: same graph,
+    narrower blocks -- the widths come with the weights); returns (n, 1)."""
     x = _t(x_nhwc).permute(0, 3, 1, 2)
     for i in range(9):
         x = conv2d_same(x, *w["discriminator/block_%d/Conv2d" % (i + 1)], stride=1 if i == 0 else 2)

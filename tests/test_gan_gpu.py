@@ -155,3 +155,37 @@ def test_gan2_step_train_gan3_py(family, act):
     print("%s/%s gan losses %s vs oracle %s" % (family, act, np.round(lg, 5), np.round(lg_ref, 5)))
     assert abs(lg[1] - lg_ref[1]) <= 1e-2 * abs(lg_ref[1])
     assert abs(lg[2] - lg_ref[2]) <= 3e-2 * abs(lg_ref[2]) + ADV_ATOL
+
+
+def test_discriminator_thin_512_forward_backward():
+    """make_discriminator_thin_512 (model.py:901-960): same kernels, 128-wide blocks; scores and gradients vs the oracle."""
+    from upscaler.networks import DiscriminatorThin512Net
+    from upscaler import ops
+    n, H, W = 8, 64, 64
+    dw = O.init_discriminator_simple_512_weights(seed=5, input_shape=(H, W, 3), filters=O.DISC_THIN_FILTERS)
+    x = np.random.default_rng(2).uniform(-1, 1, (n, H, W, 3)).astype(np.float32)
+    lab = np.where(np.arange(n) % 2 == 0, 1.0, -1.0).astype(np.float32)
+    w = O.to_torch(dw, requires_grad=True)
+    with torch.no_grad():
+        inf_ref = O.discriminator_simple_512_forward(w, x, "none", False).numpy()
+    out = O.discriminator_simple_512_forward(w, torch.from_numpy(x), "none", True, [])
+    O.wasserstein_loss(torch.from_numpy(lab).reshape(-1, 1), out).backward()
+    net = DiscriminatorThin512Net((H, W, 3), weights=dw, dtype=torch.float16)
+    assert sum(int(np.prod(t.shape)) for v in dw.values() for t in v) == sum(int(t.numel()) for v in net.weights.values() for t in v)
+    xd = torch.from_numpy(x).cuda()
+    inf = net.forward(xd, False)[0]
+    scores, tape = net.forward(xd, True)
+    lb = torch.zeros(1, device="cuda")
+    ds = torch.empty_like(scores)
+    ops.mean_prod(scores, torch.from_numpy(lab).cuda(), lb, 1.0, 1.0, ds)
+    net.ensure_grads().zero_()
+    net.backward(tape, ds, True, False)
+    torch.cuda.synchronize()
+    assert _rel(inf.cpu().numpy(), inf_ref) < 5e-3
+    assert _rel(scores.cpu().numpy(), out.detach().numpy()) < 1e-2
+    for name in ("discriminator/block_2/Conv2d", "discriminator/block_5/Conv2d", "discriminator/final/Dense_1"):
+        ref = w[name][0].grad.numpy()
+        got = net.grads[name][0].cpu().numpy().reshape(ref.shape)
+        cos = float(np.vdot(got, ref) / (np.linalg.norm(got) * np.linalg.norm(ref)))
+        print("thin_512 grad %s cos %.4f norm ratio %.4f" % (name, cos, np.linalg.norm(got) / np.linalg.norm(ref)))
+        assert cos > 0.97 and abs(np.linalg.norm(got) / np.linalg.norm(ref) - 1) < 0.06

@@ -675,7 +675,9 @@ def load_model(filepath, custom_objects=None, compile=False):
     elif "discriminator/block_1/Conv2d" in names:
         if in_shape is None:
             raise ValueError("discriminator file without model_config: the input shape cannot be recovered")
-        m = M.make_discriminator_simple_512(tuple(in_shape), activation=arch.get("activation", "none"))
+        thin = int(weights["discriminator/block_3/Conv2d"][0].shape[3]) == 128      # thin_512 vs simple_512 (256)
+        make = M.make_discriminator_thin_512 if thin else M.make_discriminator_simple_512
+        m = make(tuple(in_shape), activation=arch.get("activation", "none"))
     elif "block1_conv1" in names and "block5_conv4" in names:
         net = networks.Vgg19Net()
         m = Model(net=net, input_shape=tuple(in_shape) if in_shape else (None, None, 3), name="vgg19")

@@ -30,6 +30,12 @@ def make_discriminator_simple_512(input_shape, activation='none'):
     return Model(net=net, input_shape=tuple(input_shape), name="model_2")
 
 
+def make_discriminator_thin_512(input_shape, activation='none'):
+    """model.py:901-960 — make_discriminator_simple_512 with 128 filters in blocks 2..9."""
+    net = networks.DiscriminatorThin512Net(tuple(input_shape), activation=activation)
+    return Model(net=net, input_shape=tuple(input_shape), name="model_2")
+
+
 # ------------------------------------------------------------------------------------------------ content losses
 class _VggLossBase(object):
     """Frozen VGG19 -> block5_conv4 features of y_true and y_pred (model.py:101-157).  `vgg19` may be a Model wrapping

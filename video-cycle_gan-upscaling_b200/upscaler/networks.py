@@ -67,13 +67,14 @@ def vgg19_layer_specs():
     return specs
 
 
-DISC_FILTERS = [64, 128, 256, 512, 512, 512, 512, 512, 512]
+DISC_FILTERS = [64, 128, 256, 512, 512, 512, 512, 512, 512]          # make_discriminator_simple_512, model.py:839-873
+DISC_THIN_FILTERS = [64, 128, 128, 128, 128, 128, 128, 128, 128]     # make_discriminator_thin_512, model.py:901-939
 
 
-def discriminator_simple_512_layer_specs(input_shape):
+def discriminator_simple_512_layer_specs(input_shape, filters=None):
     h, w, cin = input_shape
     specs = []
-    for i, c in enumerate(DISC_FILTERS):
+    for i, c in enumerate(filters or DISC_FILTERS):
         specs.append(("discriminator/block_%d/Conv2d" % (i + 1), "conv", dict(kh=3, kw=3, cin=cin, cout=c, stride=1 if i == 0 else 2)))
         specs.append(("discriminator/block_%d/BatchNorm" % (i + 1), "bn", dict(c=c)))
         if i > 0:
@@ -664,13 +665,14 @@ class DiscriminatorSimple512Net(Net):
     Flatten -> Dense 1024 - BN - LReLU -> Dense 32 - BN - LReLU -> Dense 1 -> optional activation."""
 
     input_name = "discriminator/input"
+    filters = DISC_FILTERS
 
     def __init__(self, input_shape, activation="none", weights=None, device="cuda", seed=None, dtype=None):
         self.input_shape = tuple(input_shape)
         self.activation = activation
         if dtype is not None:       # fp16 storage is offered for numerics checks; bf16 (default) has the range a
             self.train_dtype = dtype  # diverging Wasserstein critic needs (gan_test.ipynb cell 17: |D| up to 2e11)
-        specs = discriminator_simple_512_layer_specs(self.input_shape)
+        specs = discriminator_simple_512_layer_specs(self.input_shape, self.filters)
         super().__init__(specs, weights, seed, device)
         self.extra_layers = [("discriminator/final/Flatten", "flatten")]
         h, w = self.input_shape[:2]
@@ -793,3 +795,9 @@ class DiscriminatorSimple512Net(Net):
                     return ops.conv2d(dz, pk[name + "#dgrad"], c["cin"], 3, 3,
                                       out=torch.empty((n, h, w_, c["cin"]), dtype=torch.float32, device=self.device))
         return None
+
+
+class DiscriminatorThin512Net(DiscriminatorSimple512Net):
+    """make_discriminator_thin_512 (model.py:901-960): the same graph with 128-wide blocks 2..9."""
+
+    filters = DISC_THIN_FILTERS
