@@ -20,6 +20,7 @@ buckets, launched on a side stream as soon as backward has finished the slice (t
 order, so the tail of the network — whose gradients are ready first — is the last slice).
 """
 import math
+import os
 
 import numpy as np
 import torch
@@ -84,8 +85,11 @@ def _make_sync():
         return None
     world = dist.get_world_size()
 
+    skip = bool(os.environ.get("B2_DP_NO_BN_SYNC"))       # timing experiments only: replicas keep local statistics
+
     def sync(buf, rows):
-        dist.all_reduce(buf)
+        if not skip:
+            dist.all_reduce(buf)
         return rows * world if rows is not None else world
     return sync
 
@@ -120,7 +124,7 @@ class GradReducer:
     def reduce_slice(self, flat, lo, hi):
         self.log.append((lo, hi))
         dist = _dist()
-        if dist is None or hi <= lo:
+        if dist is None or hi <= lo or os.environ.get("B2_DP_NO_GRAD_SYNC"):
             return
         if flat.is_cuda:
             if self.stream is None:
