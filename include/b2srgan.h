@@ -109,6 +109,12 @@ int b2_gather_cast(const float* src, const int32_t* idx, int64_t n, void* out, i
  * b2_f32_to_u8_denorm: out[i] = uint8(around((in[i] + 1) * 127.5)), round-half-even (convert_array_to_image).  Both are
  * bit-exact with the NumPy expressions; device buffers 16-byte aligned, n elements. */
 int b2_u8_to_f32_norm(const uint8_t* in, float* out, int64_t n, void* stream);
+/* Bilinear x`factor` enlargement of an fp32 NHWC image (TensorFlow 1.x resize_bilinear, align_corners = False: what
+ * K.resize_images(..., "bilinear") lowers to in make_upscaler_skip_con, reference upscaling/upscaler/model.py:357),
+ * written as 16-bit elements into channels [c0, c0 + C) of an NHWC tensor with `ld` channels per pixel -- the
+ * Concatenate of model.py:358 becomes a channel slice of the final conv's input. */
+int b2_resize_bilinear_into(const float* in, int B, int H, int W, int C, int factor, void* out, int ld, int c0, int f16,
+                            void* stream);
 int b2_f32_to_u8_denorm(const float* in, uint8_t* out, int64_t n, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------------

@@ -233,6 +233,54 @@ def upscaler_orig_forward(w, x_nhwc, training=False, stats_out=None, upscale_fac
     return m.permute(0, 2, 3, 1)
 
 
+def resize_bilinear_tf1(x_nchw, factor):
+    """K.resize_images(x, factor, factor, 'channels_last', 'bilinear') as Keras 2.2 / TF 1.14 evaluate it (reference
+    model.py:357): tf.image.resize_bilinear with align_corners=False and no half-pixel centres -- source coordinate =
+    out * in/out, y0 = floor, y1 = min(y0+1, in-1), lerp in x then y.  (NOT torch's F.interpolate, which uses half-pixel
+    centres.)"""
+    B, C, H, W = x_nchw.shape
+    sy = torch.arange(H * factor, dtype=torch.float32) / factor
+    sx = torch.arange(W * factor, dtype=torch.float32) / factor
+    y0, x0 = sy.floor().long(), sx.floor().long()
+    y1, x1 = torch.clamp(y0 + 1, max=H - 1), torch.clamp(x0 + 1, max=W - 1)
+    fy, fx = (sy - y0.float()).view(1, 1, -1, 1), (sx - x0.float()).view(1, 1, 1, -1)
+    top = x_nchw[:, :, y0][:, :, :, x0] + (x_nchw[:, :, y0][:, :, :, x1] - x_nchw[:, :, y0][:, :, :, x0]) * fx
+    bot = x_nchw[:, :, y1][:, :, :, x0] + (x_nchw[:, :, y1][:, :, :, x1] - x_nchw[:, :, y1][:, :, :, x0]) * fx
+    return top + (bot - top) * fy
+
+
+def init_upscaler_skip_con_weights(seed=1234, kernel_size=5, upscale_factor=4, randomize=True):
+    """make_upscaler_skip_con (model.py:332-363) in Keras layout under make_upscaler_orig's layer names."""
+    w = init_upscaler_orig_weights(seed=seed, kernel_size=kernel_size, upscale_factor=upscale_factor, randomize=randomize)
+    rng = np.random.default_rng(seed + 77)
+    w["prefinal/conv2d"] = _conv_w(rng, 3, 3, 64, 64, 0.02 if randomize else 0.0)
+    cin = 64
+    for i in range(int(math.log(upscale_factor, 2))):
+        k = glorot_uniform(rng, (3, 3, 224, cin), 9 * cin, 9 * 224)         # Conv2DTranspose kernel: (kh, kw, Cout, Cin)
+        w["upscaling/%d/block/conv_transp" % i] = [k, (rng.normal(0, 0.02, 224) if randomize else np.zeros(224)).astype(np.float32)]
+        cin = 224
+    w["final/conv"] = _conv_w(rng, 9, 9, 227, 3, 0.02 if randomize else 0.0)
+    return w
+
+
+def upscaler_skip_con_forward(w, x_nhwc, upscale_factor=4, res_block_num=16):
+    """make_upscaler_skip_con (model.py:332-363), inference phase (BatchNorm on moving statistics)."""
+    x = _t(x_nhwc).permute(0, 3, 1, 2)
+    m = prelu(conv2d_same(x, *w["initial/conv"]), w["initial/prelu"][0])
+    skip = m
+    for i in range(res_block_num):
+        n = "res_block/%d" % i
+        h = conv2d_same(m, *w[n + "/conv_pre"])
+        h = prelu(batch_norm(h, *w[n + "/batch_norm_pre"], False), w[n + "/prelu"][0])
+        h = batch_norm(conv2d_same(h, *w[n + "/conv_post"]), *w[n + "/batch_norm_post"], False)
+        m = m + h
+    m = skip + batch_norm(conv2d_same(m, *w["prefinal/conv2d"]), *w["prefinal/batch_norm"], False)
+    for i in range(int(math.log(upscale_factor, 2))):
+        m = leaky(conv2d_transpose_same_s2(m, *w["upscaling/%d/block/conv_transp" % i]), 0.2)
+    m = torch.cat([resize_bilinear_tf1(x, upscale_factor), m], dim=1)      # Concatenate(axis=3) in NHWC
+    return torch.tanh(conv2d_same(m, *w["final/conv"])).permute(0, 2, 3, 1)
+
+
 def upscaler_bn_names(res_block_num=16):
     names = []
     for i in range(res_block_num):

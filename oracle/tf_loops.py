@@ -49,3 +49,24 @@ def conv2d_transpose_same_s2_loops(x, kernel):
                     if 0 <= y < 2 * H and 0 <= xx < 2 * W:
                         out[y, xx] += kernel[ky, kx].astype(np.float64) @ x[iy, ix].astype(np.float64)
     return out
+
+
+def resize_bilinear_tf1_loops(img, factor):
+    """tf.image.resize_bilinear (TF 1.x, align_corners=False, no half-pixel centres) as plain loops over an (H, W)
+    list-of-lists image: the independent restatement oracle.resize_bilinear_tf1 is checked against."""
+    H, W = len(img), len(img[0])
+    out = [[0.0] * (W * factor) for _ in range(H * factor)]
+    for oy in range(H * factor):
+        sy = oy * (H / float(H * factor))
+        y0 = int(sy)
+        y1 = min(y0 + 1, H - 1)
+        fy = sy - y0
+        for ox in range(W * factor):
+            sx = ox * (W / float(W * factor))
+            x0 = int(sx)
+            x1 = min(x0 + 1, W - 1)
+            fx = sx - x0
+            top = img[y0][x0] + (img[y0][x1] - img[y0][x0]) * fx
+            bot = img[y1][x0] + (img[y1][x1] - img[y1][x0]) * fx
+            out[oy][ox] = top + (bot - top) * fy
+    return out

@@ -148,3 +148,30 @@ def test_trainers_run_and_decrease_loss():
     losses = [tr.train_on_batch(x, y) for _ in range(6)]
     assert losses[-1] < losses[0]
     assert tr.opt.iterations == 6
+
+
+def test_resize_bilinear_tf1_known_answers_and_loops():
+    """K.resize_images(..., 'bilinear') of make_upscaler_skip_con (model.py:357) = TF 1.x resize_bilinear without
+    half-pixel centres: [0, 1] enlarged x2 is [0, 0.5, 1, 1] (the last sample clamps), not torch's [0, 0.25, 0.75, 1]."""
+    import torch
+    from oracle import tf_loops
+    x = torch.tensor([[[[0.0, 1.0]]]])
+    assert O.resize_bilinear_tf1(x, 2)[0, 0].tolist() == [[0.0, 0.5, 1.0, 1.0], [0.0, 0.5, 1.0, 1.0]]
+    rng = np.random.default_rng(0)
+    img = rng.uniform(-1, 1, (5, 7)).astype(np.float32)
+    got = O.resize_bilinear_tf1(torch.from_numpy(img)[None, None], 4)[0, 0].numpy()
+    want = np.array(tf_loops.resize_bilinear_tf1_loops(img.tolist(), 4), np.float32)
+    assert got.shape == (20, 28) and np.abs(got - want).max() < 1e-6
+
+
+def test_skip_con_oracle_shapes_and_param_count():
+    w = O.init_upscaler_skip_con_weights(seed=3, kernel_size=3)
+    # orig trunk (k=3) up to the after-res block, then 3x3x64x224 + 224, 3x3x224x224 + 224, 9x9x227x3 + 3
+    trunk = O.count_params({k: v for k, v in O.init_upscaler_orig_weights(seed=3, kernel_size=3).items()
+                            if not k.startswith("upscaling") and k != "final/conv"})
+    assert O.count_params(w) == trunk + (9 * 64 * 224 + 224) + (9 * 224 * 224 + 224) + (81 * 227 * 3 + 3)
+    x = np.random.default_rng(1).uniform(-1, 1, (1, 6, 5, 3)).astype(np.float32)
+    import torch
+    with torch.no_grad():
+        y = O.upscaler_skip_con_forward(O.to_torch(w), x)
+    assert tuple(y.shape) == (1, 24, 20, 3) and float(y.abs().max()) <= 1.0

@@ -79,6 +79,41 @@ __global__ void gather_cast_kernel(const float* __restrict__ src, const int32_t*
     }
 }
 
+// K.resize_images(x, f, f, "channels_last", "bilinear") of make_upscaler_skip_con (reference model.py:357) = TensorFlow 1.x
+// tf.image.resize_bilinear with align_corners = False and no half-pixel centres: source coordinate = out * (in / out),
+// y0 = floor, y1 = min(y0 + 1, in - 1), top/bottom rows lerped in x, then in y -- all in fp32.  The result is written as
+// 16-bit elements into channels [c0, c0 + C) of an NHWC tensor with `ld` channels per pixel (the Concatenate of model.py:358
+// becomes a channel slice of the tensor the final conv reads).  One thread per output pixel.
+__global__ void __launch_bounds__(256)
+resize_bilinear_into_kernel(const float* __restrict__ in, int B, int H, int W, int C, int factor, void* __restrict__ out,
+                            int ld, int c0, int f16) {
+    const int OH = H * factor, OW = W * factor;
+    const float inv = 1.0f / float(factor);
+    for (int row = blockIdx.x; row < B * OH; row += gridDim.x) {
+        const int b = row / OH, oy = row - b * OH;
+        const float sy = float(oy) * inv;
+        const int y0 = int(floorf(sy)), y1 = min(y0 + 1, H - 1);
+        const float fy = sy - float(y0);
+        const float* r0 = in + (size_t(b) * H + y0) * W * C;
+        const float* r1 = in + (size_t(b) * H + y1) * W * C;
+        uint16_t* dst = reinterpret_cast<uint16_t*>(out) + size_t(row) * OW * ld + c0;
+        for (int ox = threadIdx.x; ox < OW; ox += blockDim.x) {
+            const float sx = float(ox) * inv;
+            const int x0 = int(floorf(sx)), x1 = min(x0 + 1, W - 1);
+            const float fx = sx - float(x0);
+            for (int c = 0; c < C; ++c) {
+                const float tl = r0[x0 * C + c], tr = r0[x1 * C + c], bl = r1[x0 * C + c], br = r1[x1 * C + c];
+                const float top = tl + (tr - tl) * fx, bot = bl + (br - bl) * fx;
+                const float v = top + (bot - top) * fy;
+                uint16_t h;
+                if (f16) { const __half t = __float2half_rn(v); h = *reinterpret_cast<const uint16_t*>(&t); }
+                else { const __nv_bfloat16 t = __float2bfloat16_rn(v); h = *reinterpret_cast<const uint16_t*>(&t); }
+                dst[size_t(ox) * ld + c] = h;
+            }
+        }
+    }
+}
+
 inline int grid_for(long work, int threads) {
     long blocks = (work + threads - 1) / threads;
     const long cap = long(device_sm_count()) * 16;
@@ -172,6 +207,18 @@ int b2_u8_to_f32_norm(const uint8_t* in, float* out, int64_t n, void* stream) {
     u8_to_f32_norm_kernel<<<grid_for((n + 15) / 16, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(in, out, long(n));
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("b2_u8_to_f32_norm launch: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+int b2_resize_bilinear_into(const float* in, int B, int H, int W, int C, int factor, void* out, int ld, int c0, int f16,
+                            void* stream) {
+    if (!in || !out) return set_error("b2_resize_bilinear_into: null pointer");
+    if (B < 1 || H < 1 || W < 1 || C < 1 || factor < 1 || c0 < 0 || c0 + C > ld)
+        return set_error("b2_resize_bilinear_into: bad geometry (%d,%d,%d,%d) x%d into channels [%d,%d) of %d", B, H, W, C, factor, c0, c0 + C, ld);
+    resize_bilinear_into_kernel<<<grid_for(long(B) * H * factor * 256, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        in, B, H, W, C, factor, out, ld, c0, f16);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error("b2_resize_bilinear_into launch: %s", cudaGetErrorString(e));
     return 0;
 }
 

@@ -24,6 +24,15 @@ def make_upscaler_orig(output_image_shape, kernel_size=5, filters=64, upscale_fa
     return Model(net=net, input_shape=input_image_shape, name="model_1")
 
 
+def make_upscaler_skip_con(output_image_shape, kernel_size=5, filters=64, upscale_factor=4):
+    """model.py:332-363 — skip-connection upscaler: orig trunk (16 residual blocks), 3x3 after-res conv, 224-filter 3x3
+    Conv2DTranspose blocks, final conv over the concatenation of the bilinearly enlarged input and the features.
+    Inference on the B200 path; train_on_batch raises NotImplementedError."""
+    h, w, c = output_image_shape
+    net = networks.UpscalerSkipConNet(kernel_size=kernel_size, filters=filters, upscale_factor=upscale_factor, res_block_num=16)
+    return Model(net=net, input_shape=(h // upscale_factor, w // upscale_factor, c), name="model_1")
+
+
 def make_discriminator_simple_512(input_shape, activation='none'):
     """model.py:836-896 — 9 conv-BN-LeakyReLU(0.1) blocks (s1 then 8 x s2), Flatten, Dense 1024/32/1."""
     net = networks.DiscriminatorSimple512Net(tuple(input_shape), activation=activation)

@@ -29,9 +29,13 @@ def glorot_uniform(rng, shape, fan_in, fan_out):
     return rng.uniform(-lim, lim, size=shape).astype(np.float32)
 
 
-def upscaler_orig_layer_specs(kernel_size=5, filters=64, upscale_factor=4, res_block_num=16):
-    """(name, kind, config) in graph order, with the reference's layer names."""
+def upscaler_orig_layer_specs(kernel_size=5, filters=64, upscale_factor=4, res_block_num=16, up_filters=256,
+                              up_kernel=None, prefinal_kernel=None, concat_input=False):
+    """(name, kind, config) in graph order, with the reference's layer names.  The keyword variants describe
+    make_upscaler_skip_con (model.py:332-363): 3x3 after-res conv, 3x3 Conv2DTranspose with 224 filters, and the final
+    conv reading Concatenate([bilinear x4 input (3), upsampled features (224)])."""
     k = kernel_size
+    uk, pk_ = up_kernel or k, prefinal_kernel or k
     specs = [("initial/conv", "conv", dict(kh=9, kw=9, cin=3, cout=filters)),
              ("initial/prelu", "prelu", dict(c=filters))]
     for i in range(res_block_num):
@@ -41,13 +45,13 @@ def upscaler_orig_layer_specs(kernel_size=5, filters=64, upscale_factor=4, res_b
                   (n + "/prelu", "prelu", dict(c=filters)),
                   (n + "/conv_post", "conv", dict(kh=k, kw=k, cin=filters, cout=filters)),
                   (n + "/batch_norm_post", "bn", dict(c=filters))]
-    specs += [("prefinal/conv2d", "conv", dict(kh=k, kw=k, cin=filters, cout=64)),
+    specs += [("prefinal/conv2d", "conv", dict(kh=pk_, kw=pk_, cin=filters, cout=64)),
               ("prefinal/batch_norm", "bn", dict(c=64))]
     cin = 64
     for i in range(int(math.log(upscale_factor, 2))):
-        specs.append(("upscaling/%d/block/conv_transp" % i, "convT", dict(kh=k, kw=k, cin=cin, cout=256)))
-        cin = 256
-    specs.append(("final/conv", "conv", dict(kh=9, kw=9, cin=cin, cout=3)))
+        specs.append(("upscaling/%d/block/conv_transp" % i, "convT", dict(kh=uk, kw=uk, cin=cin, cout=up_filters)))
+        cin = up_filters
+    specs.append(("final/conv", "conv", dict(kh=9, kw=9, cin=cin + (3 if concat_input else 0), cout=3)))
     return specs
 
 
@@ -322,6 +326,9 @@ class UpscalerOrigNet(Net):
     writes_out = True      # forward_infer(x, out=...) writes its result into a caller-provided tensor (engine.predict)
     extra_layers = [("prefinal/tanh", "add"), ("final/tanh", "activation")]
 
+    # graph variant (overridden by UpscalerSkipConNet)
+    up_filters, up_kernel, prefinal_kernel, concat_input, supports_training = 256, None, None, False, True
+
     def __init__(self, kernel_size=5, filters=64, upscale_factor=4, res_block_num=16, weights=None, device="cuda",
                  seed=None, infer_dtype=torch.float16):
         if filters != 64:
@@ -332,7 +339,10 @@ class UpscalerOrigNet(Net):
         # 16-bit storage type of the inference path (activations + packed weights): fp16 keeps 11 significand bits,
         # which is what holds max-abs error under 2e-2 across 37 layers; bf16 is accepted and ~8x noisier.
         self.infer_dtype = infer_dtype
-        super().__init__(upscaler_orig_layer_specs(kernel_size, filters, upscale_factor, res_block_num), weights, seed, device)
+        self.up_kernel = self.up_kernel or kernel_size
+        self.prefinal_kernel = self.prefinal_kernel or kernel_size
+        super().__init__(upscaler_orig_layer_specs(kernel_size, filters, upscale_factor, res_block_num, self.up_filters,
+                                                   self.up_kernel, self.prefinal_kernel, self.concat_input), weights, seed, device)
         self._infer = {}
         self._final_rows = False
         self._build_index_maps()
@@ -342,9 +352,19 @@ class UpscalerOrigNet(Net):
     # ---------------------------------------------------------------- weights
     def _build_index_maps(self):
         k = self.kernel_size
+        pad64 = lambda n: -(-n // 64) * 64
         for name, kind, c in self.specs:
             if kind == "conv":
-                if name == "final/conv" and c["kh"] == 9 and c["kw"] == 9 and c["cout"] == 3 and c["cin"] % 64 == 0 and c["cin"] <= 256:
+                if name == "final/conv" and self.concat_input:
+                    # our tensor: channels [0, F) = upsampled features, [F, F+3) = resized input, rest zero padding;
+                    # Keras: Concatenate([resized input (3), features (F)]) (model.py:358)
+                    F = self.up_filters
+                    cm = -np.ones(pad64(F + 3), np.int64)
+                    cm[:F] = 3 + np.arange(F)
+                    cm[F:F + 3] = np.arange(3)
+                    idx = ops.conv_scatter_pack_index(c["kh"], c["kw"], c["cin"], c["cout"], chan_map=cm)
+                    self._final_rows = True
+                elif name == "final/conv" and c["kh"] == 9 and c["kw"] == 9 and c["cout"] == 3 and c["cin"] % 64 == 0 and c["cin"] <= 256:
                     idx = ops.conv_scatter_pack_index(c["kh"], c["kw"], c["cin"], c["cout"])
                     self._final_rows = True
                 elif c["cin"] < 64:
@@ -352,10 +372,12 @@ class UpscalerOrigNet(Net):
                 else:
                     idx = ops.conv_pack_index(c["kh"], c["kw"], c["cin"], c["cout"])
             elif kind == "convT":
-                idx = ops.convT_pack_index(c["kh"], c["kw"], c["cin"], c["cout"])
+                idx = ops.convT_pack_index(c["kh"], c["kw"], c["cin"], c["cout"], pad64(c["cin"]), pad64(c["cout"]))
             else:
                 continue
             self.add_pack("infer", name, name, idx)
+            if not self.supports_training:
+                continue
             self.add_pack("train", name, name, idx)
             # data-gradient layouts (training only)
             if kind == "conv" and c["cin"] >= 64 and name != "final/conv":
@@ -364,11 +386,13 @@ class UpscalerOrigNet(Net):
                 self.add_pack("train", name + "#dgrad", name, ops.convT_dgrad_pack_index(c["kh"], c["kw"], c["cin"], c["cout"]))
             elif name == "final/conv":
                 self.add_pack("train", name + "#dgrad", name, ops.final_dgrad_pack_index(c["kh"], c["kw"], c["cin"], c["cout"]))
-        self.build_packs({"infer": self.infer_dtype, "train": self.train_dtype})
+        self.build_packs({"infer": self.infer_dtype, "train": self.train_dtype} if self.supports_training else
+                         {"infer": self.infer_dtype})
         c0 = self.specs[0][2]
         self._head_wgrad_idx = torch.from_numpy(ops.rowfold_wgrad_gather_index(c0["kh"], c0["kw"], c0["cin"], c0["cout"])).to(self.device)
         cf = self.specs[-1][2]
-        self._final_wgrad_idx = torch.from_numpy(ops.final_wgrad_gather_index(cf["kh"], cf["kw"], cf["cin"], cf["cout"])).to(self.device)
+        if self.supports_training:
+            self._final_wgrad_idx = torch.from_numpy(ops.final_wgrad_gather_index(cf["kh"], cf["kw"], cf["cin"], cf["cout"])).to(self.device)
 
     def refresh(self, sets=("infer",)):
         """Re-derive packed 16-bit weights (and, for inference, the folded BatchNorm epilogues) from the fp32 masters."""
@@ -401,7 +425,12 @@ class UpscalerOrigNet(Net):
         inf["prefinal/conv2d"] = (s, b, None)
         for i in range(self.upscale_times):
             n = "upscaling/%d/block/conv_transp" % i
-            inf[n] = (None, w[n][1], None)
+            bias = w[n][1]
+            if bias.numel() % 64:                       # padded output channels: zero bias -> LeakyReLU(0) = 0
+                pb = self._vec("bias_pad/" + n, -(-bias.numel() // 64) * 64, zero=True)
+                pb[:bias.numel()].copy_(bias)
+                bias = pb
+            inf[n] = (None, bias, None)
         inf["final/conv"] = (None, w["final/conv"][1], None)
         self._infer = inf
 
@@ -443,15 +472,19 @@ class UpscalerOrigNet(Net):
                                                               shift=b, residual=m))
         free = [t for t in ping if t is not m]
         s, b, _ = inf["prefinal/conv2d"]
-        m = T("prefinal/conv2d", lambda: ops.conv2d(m, pk["prefinal/conv2d"], 64, k, k, out=free[0], scale=s, shift=b,
+        kp, ku = self.prefinal_kernel, self.up_kernel
+        upc = -(-self.up_filters // 64) * 64           # 224 -> 256: padded channels carry zeros
+        m = T("prefinal/conv2d", lambda: ops.conv2d(m, pk["prefinal/conv2d"], 64, kp, kp, out=free[0], scale=s, shift=b,
                                                     residual=skip))
         h, w_ = H, W
         for i in range(self.upscale_times):
             n = "upscaling/%d/block/conv_transp" % i
             _, b, _ = inf[n]
-            ob = self._buf("up%d" % i, (B, 2 * h, 2 * w_, 256), dt)
-            m = T(n, lambda: ops.conv2d_transpose_s2(m, pk[n], 256, k, k, out=ob, shift=b, act=ops.ACT_LEAKY, leaky=0.2))
+            ob = self._buf("up%d" % i, (B, 2 * h, 2 * w_, upc), dt)
+            m = T(n, lambda: ops.conv2d_transpose_s2(m, pk[n], upc, ku, ku, out=ob, shift=b, act=ops.ACT_LEAKY, leaky=0.2))
             h, w_ = 2 * h, 2 * w_
+        if self.concat_input:      # Concatenate([bilinear-resized input, features]) = three of the padding channels
+            T("final/resize_input", lambda: ops.resize_bilinear_into(x, m, self.up_filters, 2 ** self.upscale_times))
         _, b, _ = inf["final/conv"]
         if out is None:
             out = torch.empty((B, h, w_, 3), dtype=torch.float32, device=self.device)
@@ -464,6 +497,8 @@ class UpscalerOrigNet(Net):
         """Training-phase forward (BatchNorm on batch statistics, moving statistics updated).  Returns
         (y fp32 (B,4H,4W,3), tape).  Packed 'train' weights must be current (refresh(('train',)))."""
         self._need_gpu()
+        if not self.supports_training:
+            raise NotImplementedError("%s: inference only on the B200 path so far (training covers make_upscaler_orig)" % type(self).__name__)
         if not self._final_rows:
             raise RuntimeError("training needs the row-streaming final conv (Cin <= 256)")
         B, H, W, _ = x.shape
@@ -570,6 +605,17 @@ class UpscalerOrigNet(Net):
         ops.conv2d_wgrad(xp, dz0, 9, 1, 1, raw)
         ops.gather_f32(raw, self._head_wgrad_idx, g["initial/conv"][0], accumulate=True)
         ready(0)
+
+
+class UpscalerSkipConNet(UpscalerOrigNet):
+    """make_upscaler_skip_con (model.py:332-363): the `orig` trunk, a 3x3 after-res conv, two 3x3 Conv2DTranspose blocks
+    with 224 filters, and a final 9x9 conv over Concatenate([bilinear x4 input, features]) (227 channels).  The reference
+    builds it with unnamed (hence duplicate-named) blocks, which Keras rejects; the layers carry make_upscaler_orig's names
+    here.  On the B200 path the 224 channels are padded to 256 with zero weights (LeakyReLU(0) = 0), the resized input is
+    written into three of the padding channels, and the final conv's packed weights are permuted accordingly -- so every
+    kernel of the `orig` inference path is reused.  Inference only so far."""
+
+    up_filters, up_kernel, prefinal_kernel, concat_input, supports_training = 224, 3, 3, True, False
 
 
 class Vgg19Net(Net):

@@ -186,6 +186,22 @@ def u8_to_f32_norm(x, out=None):
     return out
 
 
+def resize_bilinear_into(x, out, c0, factor):
+    """K.resize_images(x, factor, factor, 'channels_last', 'bilinear') (model.py:357; TF 1.x legacy bilinear) of the fp32
+    NHWC image x, written into channels [c0, c0+C) of the 16-bit NHWC tensor `out` (B, H*factor, W*factor, ld)."""
+    B, H, W, C = x.shape
+    if x.dtype != torch.float32 or out.dtype not in (torch.float16, torch.bfloat16):
+        raise ValueError("resize_bilinear_into: fp32 input and a 16-bit output tensor expected")
+    if tuple(out.shape[:3]) != (B, H * factor, W * factor):
+        raise ValueError("resize_bilinear_into: output %s does not match %s x%d" % (tuple(out.shape), tuple(x.shape), factor))
+    _require_cuda(x, out)
+    rc = _lib.load().b2_resize_bilinear_into(_lib.ptr(x), B, H, W, C, factor, _lib.ptr(out), out.shape[3], c0,
+                                             1 if out.dtype == torch.float16 else 0, _lib.stream_ptr())
+    _lib.check(rc, "b2_resize_bilinear_into")
+    _count(1)
+    return out
+
+
 def f32_to_u8_denorm(x, out=None):
     """float32 [-1, 1] -> uint8: uint8(around((x + 1) * 127.5)) (data.py:253-256), bit-exact with NumPy on float32."""
     if x.dtype != torch.float32:
@@ -507,13 +523,18 @@ def conv_pack_index(kh, kw, cin, cout, cin_pad=None):
     return idx.astype(np.int32)
 
 
-def convT_pack_index(kh, kw, cin, cout):
-    """Keras Conv2DTranspose kernel (kh,kw,Cout,Cin) -> packed [Cout][kh*kw][Cin]."""
+def convT_pack_index(kh, kw, cin, cout, cin_pad=None, cout_pad=None):
+    """Keras Conv2DTranspose kernel (kh,kw,Cout,Cin) -> packed [cout_pad][kh*kw][cin_pad] (-1 = zero: padded channels)."""
     T = kh * kw
     t = np.arange(T)[None, :, None]
     c = np.arange(cin)[None, None, :]
     co = np.arange(cout)[:, None, None]
-    return ((t * cout + co) * cin + c).astype(np.int32)
+    idx = ((t * cout + co) * cin + c).astype(np.int64)
+    if (cin_pad or cin) == cin and (cout_pad or cout) == cout:
+        return idx.astype(np.int32)
+    full = -np.ones((cout_pad or cout, T, cin_pad or cin), np.int64)
+    full[:cout, :, :cin] = idx
+    return full.astype(np.int32)
 
 
 def conv_rowfold_pack_index(kh, kw, cin, cout):
@@ -543,15 +564,19 @@ def conv_fullfold_pack_index(kh, kw, cin, cout):
     return idx.astype(np.int32)
 
 
-def conv_scatter_pack_index(kh, kw, cin, cout):
-    """Keras Conv2D kernel (kh,kw,Cin,Cout) -> packed [256][Cin] for conv2d_scatter: row n = (dy*kw + dx)*Cout + co."""
+def conv_scatter_pack_index(kh, kw, cin, cout, chan_map=None):
+    """Keras Conv2D kernel (kh,kw,Cin,Cout) -> packed [256][Cin'] for conv2d_scatter: row n = (dy*kw + dx)*Cout + co.
+    `chan_map` (length Cin', optional): our input channel j reads Keras input channel chan_map[j] (-1 = zero padding) --
+    used when the tensor the conv reads is a padded / permuted form of the Keras one (skip-con's Concatenate)."""
     if kh * kw * cout > 256:
         raise ValueError("conv_scatter needs kh*kw*Cout <= 256")
-    idx = -np.ones((256, cin), np.int64)
+    cm = np.arange(cin) if chan_map is None else np.asarray(chan_map, np.int64)
+    idx = -np.ones((256, cm.size), np.int64)
     t = np.arange(kh * kw)[:, None, None]
     co = np.arange(cout)[None, :, None]
-    c = np.arange(cin)[None, None, :]
-    idx[:kh * kw * cout] = ((t * cin + c) * cout + co).reshape(kh * kw * cout, cin)
+    c = cm[None, None, :]
+    full = np.where(c >= 0, (t * cin + c) * cout + co, -1)
+    idx[:kh * kw * cout] = full.reshape(kh * kw * cout, cm.size)
     return idx.astype(np.int32)
 
 
