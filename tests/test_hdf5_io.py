@@ -150,3 +150,22 @@ def test_model_save_and_load_model_round_trip(tmp_path):
     assert d2.input_shape == (None, 32, 32, 3) and d2.net.activation == "sigmoid" and d2.count_params() == d.count_params()
     a, b = d.net.host_weights(), d2.net.host_weights()
     assert all(np.array_equal(x, y) for k in a for x, y in zip(a[k], b[k]))
+
+
+def test_save_and_load_model_pick_the_variant_from_the_weight_shapes(tmp_path):
+    """skip-con generator (final conv over 227 channels) and thin discriminator (128-wide blocks) survive save -> load_model."""
+    from upscaler.model import load_model, make_discriminator_thin_512, make_upscaler_skip_con
+    from upscaler import networks
+    up = make_upscaler_skip_con((64, 96, 3), kernel_size=3)
+    p = str(tmp_path / "skip_con.h5")
+    up.save(p)
+    m2 = load_model(p)
+    assert isinstance(m2.net, networks.UpscalerSkipConNet) and m2.output_shape == (None, 64, 96, 3)
+    a, b = up.net.host_weights(), m2.net.host_weights()
+    assert a["final/conv"][0].shape == (9, 9, 227, 3) and a["upscaling/1/block/conv_transp"][0].shape == (3, 3, 224, 224)
+    assert all(np.array_equal(x, y) for k in a for x, y in zip(a[k], b[k]))
+    d = make_discriminator_thin_512((32, 32, 3))
+    pd = str(tmp_path / "thin.h5")
+    d.save(pd)
+    d2 = load_model(pd)
+    assert isinstance(d2.net, networks.DiscriminatorThin512Net) and d2.count_params() == d.count_params()
