@@ -5,6 +5,11 @@ sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "video-cycle_gan
 import numpy as np, torch
 from upscaler.model import VGG_MSE_LOSS, compile_training_model, make_upscaler_orig
 from upscaler import ops, training
+if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+    import torch.distributed as dist
+    torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+    dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+RANK = int(os.environ.get("RANK", "0"))
 B, lr = 16, 96
 up = make_upscaler_orig((4 * lr, 4 * lr, 3), kernel_size=3)
 tm = compile_training_model(up, VGG_MSE_LOSS((4 * lr, 4 * lr, 3), 1e-3).loss)
@@ -25,16 +30,20 @@ comp = comp[0] if comp else None
 print("compiled:", comp)
 if comp is not None:
     wrap(comp.G, "forward_train"); wrap(comp.G, "backward"); wrap(comp, "_content"); wrap(comp, "_adam")
-    wrap(training._uploader, "now"); wrap(training._uploader, "later")
-for it in range(3):
+    wrap(comp, "_mean_over_ranks"); wrap(comp.reducer, "wait")
+for it in range(4):
     marks.clear()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     l = tm.train_on_batch(x, hr)
     tot = (time.perf_counter() - t0) * 1e3
-    print("step %.2f ms: " % tot + ", ".join("%s %.2f" % m for m in marks))
+    if RANK == 0:
+        print("step %.2f ms: " % tot + ", ".join("%s %.2f" % m for m in marks))
 # GPU-only time of the same step: launch everything, then sync
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record(); l = tm.train_on_batch(x, hr); e1.record(); torch.cuda.synchronize()
-print("event-timed step: %.2f ms" % e0.elapsed_time(e1))
+ops.reset_launch_count(); tm.train_on_batch(x, hr)      # every rank: the step holds collectives
+if RANK == 0:
+    print("event-timed step: %.2f ms" % e0.elapsed_time(e1))
+    print("launches per step:", ops.launch_count())
