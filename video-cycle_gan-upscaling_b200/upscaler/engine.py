@@ -108,6 +108,15 @@ def predict(model, x, batch_size=None, u8=False):
     dev = _device()
     from . import ops
     n = a.shape[0]
+    if n == 0:                                   # Keras returns an empty array of the output shape
+        shapes = model.output_shape if isinstance(model.output_shape, list) else [model.output_shape]
+        res = []
+        for shp in shapes:
+            dims = tuple(shp[1:])
+            if any(d is None for d in dims):     # fully-convolutional model: derive from the input's spatial size
+                dims = tuple(model.net.output_shape_for(tuple(a.shape[1:]))) if model._is_leaf else dims
+            res.append(np.zeros((0,) + tuple(int(d) for d in dims), np.uint8 if u8 else np.float32))
+        return res[0] if len(res) == 1 else res
     bs = int(batch_size) if batch_size else 32  # Keras' predict default
     step = max(1, min(bs, PIPELINE_FRAMES))
     main = torch.cuda.current_stream()
