@@ -176,6 +176,63 @@ def bench_train_step(args, rank, world, dev, barrier):
     return out
 
 
+GAN_STEP_FLOPS_PER_IMAGE = {3: 4 * 155.1e9 + 8 * 36.34e9 + 3 * 203.84e9, 5: 2.39e12}   # 4G + 8D + 3V at HR 512^2, SURVEY.md 8(d)
+
+
+def bench_gan_step(args, rank, world, dev, barrier):
+    """Full SRGAN adversarial step (BASELINE.json configs[3]; train_gan.py:296-321 with its defaults HR 512x512, bs 2 -> n = 6
+    LR images of 128x128): gen_train.predict(x) -> host concat [real, fake] -> disc_train.train_on_batch -> gan_train
+    .train_on_batch(x, [hr, +1]) through make_and_compile_gan(...), VGG19 content loss + Wasserstein adversarial loss, one
+    shared Adam; host arrays in and out exactly as the reference's loop moves them; NCCL data-parallel when N > 1."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from upscaler import ops
+    from upscaler.model import (VGG_MSE_LOSS, make_and_compile_gan, make_discriminator_simple_512, make_upscaler_orig,
+                                wasserstein_loss)
+    n, lr, ks = 6, 128, args.kernel_size
+    hr_shape = (4 * lr, 4 * lr, 3)
+    G = make_upscaler_orig(hr_shape, kernel_size=ks)
+    D = make_discriminator_simple_512(hr_shape, activation="none")
+    gen_train, disc_train, gan_train = make_and_compile_gan(G, D, (lr, lr, 3), hr_shape, VGG_MSE_LOSS(hr_shape, 1e-3).loss, 1,
+                                                           wasserstein_loss, 1e-5)
+    rng = np.random.default_rng(200 + rank)
+    hr = rng.uniform(-1, 1, (n,) + hr_shape).astype(np.float32)
+    x = hr.reshape(n, lr, 4, lr, 4, 3).mean(axis=(2, 4)).astype(np.float32)
+    d_y = np.concatenate((np.ones(n), -np.ones(n))).astype(np.float32)
+    ones = np.ones(n, np.float32)
+
+    def step():
+        gen = gen_train.predict(x)
+        ld = disc_train.train_on_batch(np.concatenate((hr, gen), axis=0), d_y)
+        lg = gan_train.train_on_batch(x, [hr, ones])
+        return ld, lg
+
+    for _ in range(3):
+        step()
+    barrier()
+    ops.reset_launch_count()
+    steps = max(3, args.train_steps // 2)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        ld, lg = step()
+    barrier()
+    t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = 1000.0 * float(t.item()) / steps
+    peaks = load_peaks()
+    tf = GAN_STEP_FLOPS_PER_IMAGE[ks] * n * world / (ms * 1e-3) / 1e12
+    out = {"metric": "GAN train LR images/s", "value": world * n * 1000.0 / ms, "unit": "samples/s", "ms_per_step": ms, "steps": steps,
+           "config": "train_gan.py step: predict + discriminator step (2n images) + GAN step, n = %d LR images of 128x128 -> 512x512 per GPU, "
+                     "k=%d, simple_512 discriminator, vgg-mse + Wasserstein, shared Adam%s" % (n, ks, ", NCCL data-parallel" if world > 1 else ""),
+           "algorithmic_tflops": tf, "frac_of_bf16_sustained_peak": tf / world / peaks["bf16_tflops_sustained"],
+           "gpu_launches_per_step": ops.launch_count() // steps, "loss_disc": float(ld), "loss_gan": [float(v) for v in lg]}
+    del gen_train, disc_train, gan_train, G, D
+    torch.cuda.empty_cache()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -284,9 +341,10 @@ def main():
     e2e_u8 = world * B * e2e_steps / float(t_u8.item())
 
     # ------------------------------------------------------------------ training step (BASELINE.json configs[2])
-    train = None
+    train = train_gan = None
     if not args.no_train:
         train = bench_train_step(args, rank, world, dev, barrier)
+        train_gan = bench_gan_step(args, rank, world, dev, barrier)
 
     if rank == 0:
         peaks = load_peaks()
@@ -321,7 +379,7 @@ def main():
                               "d2h_bytes_per_step": int(yu.nbytes),
                               "api": "Model.predict_uint8(uint8 frames)->uint8 frames (data.py:253-270 conversions fused on the device)"},
                 "gpu_launches": launches,
-                "roofline": roof, "cpu_baseline": cpu, "train": train,
+                "roofline": roof, "cpu_baseline": cpu, "train": train, "train_gan": train_gan,
                 "layers_ms": {k: round(v, 4) for k, v in sorted(layer_ms.items(), key=lambda kv: -kv[1])[:8]}}
         print(json.dumps(line), flush=True)
     if world > 1:
