@@ -491,14 +491,37 @@ __device__ __forceinline__ void st_any(void* p, size_t i, int dtype, float v) {
 }
 
 // Dense head of the discriminator: batch-sized M, so plain CUDA-core loops over the fp32 master weights.
-__global__ void dense_fwd_kernel(const void* x, int xd, int n, int K, int N, const float* __restrict__ W, const float* b,
-                                 void* out, int od) {
-    const long total = long(n) * N;
-    for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
-        const int o = int(i % N), r = int(i / N);
-        float acc = b ? b[o] : 0.f;
-        for (int k = 0; k < K; ++k) acc = fmaf(ld_any(x, size_t(r) * K + k, xd), W[size_t(k) * N + o], acc);
-        st_any(out, i, od, acc);
+// Forward: a block owns 32 output columns; its 8 warps stride over K (each warp-load of W is one 128-byte row piece), every
+// thread keeps up to 8 batch rows in registers so W is read once per 8 rows, partial sums meet in shared memory.  (The
+// thread-per-output form needed K = 2048 dependent L2 round trips: 380 us for 12 x 2048 x 1024.)
+__global__ void __launch_bounds__(256)
+dense_fwd_kernel(const void* x, int xd, int n, int K, int N, const float* __restrict__ W, const float* b, void* out, int od) {
+    __shared__ float red[8][8][33];
+    const int col = threadIdx.x & 31, ks = threadIdx.x >> 5;
+    const int o = blockIdx.x * 32 + col;
+    for (int r0 = 0; r0 < n; r0 += 8) {
+        const int nr = min(8, n - r0);
+        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (o < N) {
+#pragma unroll 4
+            for (int k = ks; k < K; k += 8) {
+                const float w = W[size_t(k) * N + o];
+#pragma unroll
+                for (int r = 0; r < 8; ++r)
+                    if (r < nr) acc[r] = fmaf(ld_any(x, size_t(r0 + r) * K + k, xd), w, acc[r]);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 8; ++r) red[ks][r][col] = acc[r];
+        __syncthreads();
+        const int r = ks;                     // thread (r, col) finishes row r0 + r
+        if (o < N && r < nr) {
+            float sum = b ? b[o] : 0.f;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) sum += red[q][r][col];
+            st_any(out, size_t(r0 + r) * N + o, od, sum);
+        }
+        __syncthreads();
     }
 }
 __global__ void dense_bwd_data_kernel(const void* dy, int yd, int n, int K, int N, const float* __restrict__ W, void* dx, int xd) {
@@ -697,7 +720,7 @@ int b2_colsum_f32(const float* x, int64_t rows, int C, float* sum, void* stream)
 int b2_dense_fwd(const void* x, int x_dtype, int n, int K, int N, const float* W, const float* b, void* out, int out_dtype,
                  void* stream) {
     if (!x || !W || !out) return set_error("b2_dense_fwd: null pointer");
-    dense_fwd_kernel<<<flat_grid(long(n) * N), kEwThreads, 0, B2_STREAM>>>(x, x_dtype, n, K, N, W, b, out, out_dtype);
+    dense_fwd_kernel<<<(N + 31) / 32, 256, 0, B2_STREAM>>>(x, x_dtype, n, K, N, W, b, out, out_dtype);
     return launch_ok("b2_dense_fwd");
 }
 int b2_dense_bwd_data(const void* dy, int dy_dtype, int n, int K, int N, const float* W, void* dx, int dx_dtype, void* stream) {
