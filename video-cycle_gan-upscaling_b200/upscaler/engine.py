@@ -50,6 +50,8 @@ def predict_device(model, x_dev):
 
 # Frames per pipeline stage of predict(): the device->host copy of stage i (24.9 MB per 1080p frame, PCIe) runs on a copy
 # stream while stage i+1 computes, and the host-side staging copy of stage i+1 overlaps the kernels of stage i.
+# (Measured alternative: stages shrinking towards the end of the batch, 8 frames -> 4, 2, 1, 1, to expose less of the last
+# copy: 584 frames/s against 610 with uniform stages of 2 -- one-frame stages run the kernels at 560 frames/s.)
 PIPELINE_FRAMES = 2
 
 _pinned_in = {}
