@@ -263,18 +263,19 @@ def init_upscaler_skip_con_weights(seed=1234, kernel_size=5, upscale_factor=4, r
     return w
 
 
-def upscaler_skip_con_forward(w, x_nhwc, upscale_factor=4, res_block_num=16):
-    """make_upscaler_skip_con (model.py:332-363), inference phase (BatchNorm on moving statistics)."""
+def upscaler_skip_con_forward(w, x_nhwc, training=False, stats_out=None, upscale_factor=4, res_block_num=16):
+    """make_upscaler_skip_con (model.py:332-363); `training` selects batch statistics (with `stats_out` collecting them in
+    graph order, as upscaler_orig_forward does) or moving statistics."""
     x = _t(x_nhwc).permute(0, 3, 1, 2)
     m = prelu(conv2d_same(x, *w["initial/conv"]), w["initial/prelu"][0])
     skip = m
     for i in range(res_block_num):
         n = "res_block/%d" % i
         h = conv2d_same(m, *w[n + "/conv_pre"])
-        h = prelu(batch_norm(h, *w[n + "/batch_norm_pre"], False), w[n + "/prelu"][0])
-        h = batch_norm(conv2d_same(h, *w[n + "/conv_post"]), *w[n + "/batch_norm_post"], False)
+        h = prelu(batch_norm(h, *w[n + "/batch_norm_pre"], training, stats_out), w[n + "/prelu"][0])
+        h = batch_norm(conv2d_same(h, *w[n + "/conv_post"]), *w[n + "/batch_norm_post"], training, stats_out)
         m = m + h
-    m = skip + batch_norm(conv2d_same(m, *w["prefinal/conv2d"]), *w["prefinal/batch_norm"], False)
+    m = skip + batch_norm(conv2d_same(m, *w["prefinal/conv2d"]), *w["prefinal/batch_norm"], training, stats_out)
     for i in range(int(math.log(upscale_factor, 2))):
         m = leaky(conv2d_transpose_same_s2(m, *w["upscaling/%d/block/conv_transp" % i]), 0.2)
     m = torch.cat([resize_bilinear_tf1(x, upscale_factor), m], dim=1)      # Concatenate(axis=3) in NHWC
@@ -435,7 +436,8 @@ class GeneratorTrainer:
     """compile_training_model + train_on_batch (model.py:1130-1137; train_mini.py:232)."""
 
     def __init__(self, gen_weights, vgg_weights, loss_kind="vgg-mse", rate=1e-3, optimizer=None, res_block_num=16,
-                 upscale_factor=4):
+                 upscale_factor=4, forward=None):
+        self.forward = forward or upscaler_orig_forward        # or upscaler_skip_con_forward (same signature)
         self.w = to_torch(gen_weights, requires_grad=True)
         self.vw = to_torch(vgg_weights) if vgg_weights is not None else None
         self.kind, self.rate = loss_kind, rate
@@ -444,7 +446,7 @@ class GeneratorTrainer:
 
     def train_on_batch(self, x_lr, y_hr):
         stats = []
-        y = upscaler_orig_forward(self.w, x_lr, True, stats, self.uf, self.rbn)
+        y = self.forward(self.w, x_lr, True, stats, self.uf, self.rbn)
         loss = content_loss(self.kind, self.vw, _t(y_hr), y, self.rate)
         loss.backward()
         self.opt.apply(_trainable(self.w, "g"))
@@ -453,7 +455,7 @@ class GeneratorTrainer:
 
     def predict(self, x_lr):
         with torch.no_grad():
-            return upscaler_orig_forward(self.w, x_lr, False, None, self.uf, self.rbn).numpy()
+            return self.forward(self.w, x_lr, False, None, self.uf, self.rbn).numpy()
 
 
 class GanTrainer:

@@ -212,3 +212,67 @@ def test_generator_loss_curve_200_steps_free_running():
     # (a run that ends below the oracle is not a defect: the lower side of the band is wider; seen 0.0045 vs 0.0070)
     assert late_w / 2.0 < late_g < late_w * 1.4
     assert np.all(win_g < 2.0 * win_w) and np.all(win_g > win_w / 3.0)
+
+
+def test_skip_con_train_forward_backward():
+    """make_upscaler_skip_con (model.py:332-363): forward_train output and EVERY weight gradient vs autograd, same protocol
+    as test_generator_train_forward_backward (pixel-MSE upstream gradient, 2 residual blocks): covers the 224-filter ConvT
+    layers (gradients gathered back from the 256-channel padded layout) and the 227-channel final conv (permuted)."""
+    from upscaler.networks import UpscalerSkipConNet
+    from upscaler import ops
+    rbn = 2
+    gw = O.init_upscaler_skip_con_weights(seed=5, kernel_size=3)
+    gw = {k: v for k, v in gw.items() if not k.startswith("res_block/") or int(k.split("/")[1]) < rbn}
+    x, hr = _data(2, 12, seed=9)
+    w = O.to_torch(gw, requires_grad=True)
+    y = O.upscaler_skip_con_forward(w, x, True, [], 4, rbn)
+    loss = torch.mean((y - torch.from_numpy(hr)) ** 2)
+    loss.backward()
+    net = UpscalerSkipConNet(kernel_size=3, res_block_num=rbn, weights=gw)
+    net.refresh(("train",))
+    yd, tape = net.forward_train(torch.from_numpy(x).cuda())
+    buf = torch.zeros(1, device="cuda")
+    gpix = torch.empty_like(yd)
+    ops.loss_pair(yd, torch.from_numpy(hr).cuda(), buf, grad=gpix)
+    dz = ops.tanh_bwd(yd, gpix, torch.empty_like(yd))
+    net.ensure_grads().zero_()
+    net.backward(tape, dz)
+    torch.cuda.synchronize()
+    assert _rel(yd.cpu().numpy(), y.detach().numpy()) < 3e-2
+    assert abs(float(buf) - float(loss)) <= 1e-2 * float(loss)
+    bad = []
+    for name, kind, cfg in net.specs:
+        for j, gt in enumerate(net.grads[name]):
+            ref = w[name][j].grad
+            if ref is None:
+                continue
+            ref = ref.numpy()
+            got = gt.cpu().numpy().reshape(ref.shape)
+            if kind == "conv" and j == 1 and name not in ("initial/conv", "final/conv"):
+                assert np.abs(got).max() <= 1e-6 + 1e-3 * np.abs(ref).max() + 1e-7
+                continue
+            nr = np.linalg.norm(got) / np.linalg.norm(ref)
+            cos = float(np.vdot(got, ref) / (np.linalg.norm(got) * np.linalg.norm(ref)))
+            print("   skip-con grad %-36s[%d] norm ratio %.4f cos %.4f" % (name, j, nr, cos))
+            if abs(nr - 1) > 5e-2 or cos < 0.98:
+                bad.append((name, j, nr, cos))
+    assert not bad, bad
+
+
+def test_skip_con_train_on_batch_losses():
+    """skip-con through compile_training_model / train_on_batch with the VGG19 content loss: losses within 1 % of the oracle
+    from identical weights (teacher forcing), 16 residual blocks."""
+    from upscaler.keras_compat import Adam
+    from upscaler.model import VGG_MSE_LOSS, compile_training_model, make_upscaler_skip_con
+    gw, vw = O.init_upscaler_skip_con_weights(seed=31, kernel_size=3), O.init_vgg19_weights()
+    up = make_upscaler_skip_con((64, 64, 3), kernel_size=3)
+    up.net.set_weights(gw)
+    tm = compile_training_model(up, VGG_MSE_LOSS((64, 64, 3), 1e-3, vgg19=vw).loss, optimizer=Adam())
+    ref = O.GeneratorTrainer(gw, vw, "vgg-mse", 1e-3, forward=O.upscaler_skip_con_forward)
+    for step in range(5):
+        xs, hs = _data(2, 16, seed=50 + step)
+        _sync_weights(up, ref)
+        got = tm.train_on_batch(xs, hs)
+        want = ref.train_on_batch(xs, hs)
+        print("skip-con step %d loss %.5f vs oracle %.5f" % (step, got, want))
+        assert abs(got - want) <= 1e-2 * want

@@ -27,7 +27,8 @@ def make_upscaler_orig(output_image_shape, kernel_size=5, filters=64, upscale_fa
 def make_upscaler_skip_con(output_image_shape, kernel_size=5, filters=64, upscale_factor=4):
     """model.py:332-363 — skip-connection upscaler: orig trunk (16 residual blocks), 3x3 after-res conv, 224-filter 3x3
     Conv2DTranspose blocks, final conv over the concatenation of the bilinearly enlarged input and the features.
-    Inference on the B200 path; train_on_batch raises NotImplementedError."""
+    Inference and training (compile_training_model / make_and_compile_gan*) run on the kernels of the `orig` path with the
+    224-filter layers padded to 256 channels."""
     h, w, c = output_image_shape
     net = networks.UpscalerSkipConNet(kernel_size=kernel_size, filters=filters, upscale_factor=upscale_factor, res_block_num=16)
     return Model(net=net, input_shape=(h // upscale_factor, w // upscale_factor, c), name="model_1")

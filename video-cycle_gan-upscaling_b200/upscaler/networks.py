@@ -353,6 +353,7 @@ class UpscalerOrigNet(Net):
     def _build_index_maps(self):
         k = self.kernel_size
         pad64 = lambda n: -(-n // 64) * 64
+        self._final_chan_map, self._convT_wgrad_idx, self._convT_bias_idx = None, {}, {}
         for name, kind, c in self.specs:
             if kind == "conv":
                 if name == "final/conv" and self.concat_input:
@@ -364,6 +365,7 @@ class UpscalerOrigNet(Net):
                     cm[F:F + 3] = np.arange(3)
                     idx = ops.conv_scatter_pack_index(c["kh"], c["kw"], c["cin"], c["cout"], chan_map=cm)
                     self._final_rows = True
+                    self._final_chan_map = cm
                 elif name == "final/conv" and c["kh"] == 9 and c["kw"] == 9 and c["cout"] == 3 and c["cin"] % 64 == 0 and c["cin"] <= 256:
                     idx = ops.conv_scatter_pack_index(c["kh"], c["kw"], c["cin"], c["cout"])
                     self._final_rows = True
@@ -383,16 +385,23 @@ class UpscalerOrigNet(Net):
             if kind == "conv" and c["cin"] >= 64 and name != "final/conv":
                 self.add_pack("train", name + "#dgrad", name, ops.conv_dgrad_pack_index(c["kh"], c["kw"], c["cin"], c["cout"]))
             elif kind == "convT":
-                self.add_pack("train", name + "#dgrad", name, ops.convT_dgrad_pack_index(c["kh"], c["kw"], c["cin"], c["cout"]))
+                self.add_pack("train", name + "#dgrad", name, ops.convT_dgrad_pack_index(c["kh"], c["kw"], c["cin"], c["cout"],
+                                                                                         pad64(c["cin"]), pad64(c["cout"])))
+                if c["cout"] % 64 or c["cin"] % 64:       # weight / bias gradients come out in the padded layout
+                    self._convT_bias_idx[name] = torch.arange(c["cout"], dtype=torch.int32, device=self.device)
+                    self._convT_wgrad_idx[name] = torch.from_numpy(ops.padded_gather_index(
+                        (c["kh"], c["kw"], c["cout"], c["cin"]), (c["kh"], c["kw"], pad64(c["cout"]), pad64(c["cin"])))).to(self.device)
             elif name == "final/conv":
-                self.add_pack("train", name + "#dgrad", name, ops.final_dgrad_pack_index(c["kh"], c["kw"], c["cin"], c["cout"]))
+                self.add_pack("train", name + "#dgrad", name, ops.final_dgrad_pack_index(c["kh"], c["kw"], c["cin"], c["cout"],
+                                                                                         chan_map=self._final_chan_map))
         self.build_packs({"infer": self.infer_dtype, "train": self.train_dtype} if self.supports_training else
                          {"infer": self.infer_dtype})
         c0 = self.specs[0][2]
         self._head_wgrad_idx = torch.from_numpy(ops.rowfold_wgrad_gather_index(c0["kh"], c0["kw"], c0["cin"], c0["cout"])).to(self.device)
         cf = self.specs[-1][2]
         if self.supports_training:
-            self._final_wgrad_idx = torch.from_numpy(ops.final_wgrad_gather_index(cf["kh"], cf["kw"], cf["cin"], cf["cout"])).to(self.device)
+            self._final_wgrad_idx = torch.from_numpy(ops.final_wgrad_gather_index(cf["kh"], cf["kw"], cf["cin"], cf["cout"],
+                                                                                  chan_map=self._final_chan_map)).to(self.device)
 
     def refresh(self, sets=("infer",)):
         """Re-derive packed 16-bit weights (and, for inference, the folded BatchNorm epilogues) from the fp32 masters."""
@@ -522,16 +531,25 @@ class UpscalerOrigNet(Net):
                                   sync=sync)
             tape[n] = (m, h)
             m = mo
-        zp = ops.conv2d(m, pk["prefinal/conv2d"], 64, k, k, out=new((B, H, W, 64)), shift=w["prefinal/conv2d"][1])
+        kp, ku = self.prefinal_kernel, self.up_kernel
+        upc = -(-self.up_filters // 64) * 64
+        zp = ops.conv2d(m, pk["prefinal/conv2d"], 64, kp, kp, out=new((B, H, W, 64)), shift=w["prefinal/conv2d"][1])
         t = self._bn_forward(tape, "prefinal", "prefinal/batch_norm", zp, new((B, H, W, 64)), ops.ACT_NONE, residual=skip, sync=sync)
         tape["prefinal/in"] = m
         ups, h_, w_ = [t], H, W
         for i in range(self.upscale_times):
             n = "upscaling/%d/block/conv_transp" % i
-            u = ops.conv2d_transpose_s2(ups[-1], pk[n], 256, k, k, out=new((B, 2 * h_, 2 * w_, 256)), shift=w[n][1],
+            bias = w[n][1]
+            if bias.numel() != upc:                     # padded output channels: zero bias -> LeakyReLU(0) = 0
+                pb = self._vec("bias_pad/" + n, upc, zero=True)
+                ops.cast_scale(bias, pb[:bias.numel()], 1.0)
+                bias = pb
+            u = ops.conv2d_transpose_s2(ups[-1], pk[n], upc, ku, ku, out=new((B, 2 * h_, 2 * w_, upc)), shift=bias,
                                         act=ops.ACT_LEAKY, leaky=0.2)
             ups.append(u)
             h_, w_ = 2 * h_, 2 * w_
+        if self.concat_input:       # Concatenate([bilinear-resized input, features]): three of the padding channels
+            ops.resize_bilinear_into(x, ups[-1], self.up_filters, 2 ** self.upscale_times)
         tape["ups"] = ups
         y = ops.conv2d_scatter(ups[-1], pk["final/conv"], 3, 9, 9, bias=w["final/conv"][1], act=ops.ACT_TANH)
         tape["y"] = y
@@ -560,26 +578,38 @@ class UpscalerOrigNet(Net):
         raw.zero_()
         ops.conv2d_wgrad(ups[-1], F, 1, 1, 1, raw)
         ops.gather_f32(raw, self._final_wgrad_idx, g["final/conv"][0], accumulate=True)
-        d = ops.conv2d(F, pk["final/conv#dgrad"], 256, 1, 1, out=new((B, HH, WW, 256)), gate=ups[-1], gate_slope=0.2)
+        kp, ku = self.prefinal_kernel, self.up_kernel
+        upc = ups[-1].shape[-1]
+        # (padding / resized-input channels of `d` meet zero rows of the packed ConvT weights below: their values are moot)
+        d = ops.conv2d(F, pk["final/conv#dgrad"], upc, 1, 1, out=new((B, HH, WW, upc)), gate=ups[-1], gate_slope=0.2)
         del F
         # ---- upsampling blocks (Conv2DTranspose stride 2 + LeakyReLU 0.2), last to first
         for i in reversed(range(self.upscale_times)):
             n = "upscaling/%d/block/conv_transp" % i
             xin = ups[i]
-            ops.colstats(d, g[n][1])
-            ops.conv2d_wgrad(d, xin, k, k, 2, g[n][0])
             cin = xin.shape[-1]
-            if i > 0:
-                d = ops.conv2d(d, pk[n + "#dgrad"], cin, k, k, stride=2, out=new(tuple(xin.shape)), gate=xin, gate_slope=0.2)
+            if n in self._convT_wgrad_idx:              # padded channels: raw gradients in the padded layout, then gather
+                braw = self._vec("bias_raw/" + n, upc, zero=True)
+                ops.colstats(d, braw)
+                ops.gather_f32(braw, self._convT_bias_idx[n], g[n][1], accumulate=True)
+                raw = self._buf("convT_raw/" + n, (ku * ku * upc * cin,), torch.float32)
+                raw.zero_()
+                ops.conv2d_wgrad(d, xin, ku, ku, 2, raw)
+                ops.gather_f32(raw, self._convT_wgrad_idx[n], g[n][0], accumulate=True)
             else:
-                d = ops.conv2d(d, pk[n + "#dgrad"], cin, k, k, stride=2, out=new(tuple(xin.shape)))
+                ops.colstats(d, g[n][1])
+                ops.conv2d_wgrad(d, xin, ku, ku, 2, g[n][0])
+            if i > 0:
+                d = ops.conv2d(d, pk[n + "#dgrad"], cin, ku, ku, stride=2, out=new(tuple(xin.shape)), gate=xin, gate_slope=0.2)
+            else:
+                d = ops.conv2d(d, pk[n + "#dgrad"], cin, ku, ku, stride=2, out=new(tuple(xin.shape)))
         dt_ = d      # gradient w.r.t. t = skip + BN(prefinal conv): flows into both the trunk and the head skip
         ready(self.offsets[("upscaling/0/block/conv_transp", 0)][0])
         # ---- prefinal conv + BN
         dzp = self._bn_backward(tape, "prefinal", "prefinal/batch_norm", dt_, new(tuple(dt_.shape)), ops.ACT_NONE, sync=sync)
         m_in = tape["prefinal/in"]
-        ops.conv2d_wgrad(m_in, dzp, k, k, 1, g["prefinal/conv2d"][0])
-        gm = ops.conv2d(dzp, pk["prefinal/conv2d#dgrad"], f, k, k, out=new(tuple(m_in.shape)))
+        ops.conv2d_wgrad(m_in, dzp, kp, kp, 1, g["prefinal/conv2d"][0])
+        gm = ops.conv2d(dzp, pk["prefinal/conv2d#dgrad"], f, kp, kp, out=new(tuple(m_in.shape)))
         # ---- residual blocks, last to first; gm is the gradient w.r.t. each block's output (the residual stream)
         for i in reversed(range(self.res_block_num)):
             n = "res_block/%d" % i
@@ -613,9 +643,10 @@ class UpscalerSkipConNet(UpscalerOrigNet):
     builds it with unnamed (hence duplicate-named) blocks, which Keras rejects; the layers carry make_upscaler_orig's names
     here.  On the B200 path the 224 channels are padded to 256 with zero weights (LeakyReLU(0) = 0), the resized input is
     written into three of the padding channels, and the final conv's packed weights are permuted accordingly -- so every
-    kernel of the `orig` inference path is reused.  Inference only so far."""
+    kernel of the `orig` path is reused, in training too (weight gradients of the padded layers are produced in the padded
+    layout and gathered back into the Keras one)."""
 
-    up_filters, up_kernel, prefinal_kernel, concat_input, supports_training = 224, 3, 3, True, False
+    up_filters, up_kernel, prefinal_kernel, concat_input, supports_training = 224, 3, 3, True, True
 
 
 class Vgg19Net(Net):

@@ -443,28 +443,46 @@ def _final_fold_channel(t, co, cout):
     return 64 * (t // FINAL_TAPS_PER_GROUP) + (t % FINAL_TAPS_PER_GROUP) * cout + co
 
 
-def final_dgrad_pack_index(kh, kw, cin, cout):
+def final_dgrad_pack_index(kh, kw, cin, cout, chan_map=None):
     """Data gradient of the final Conv2D(3, 9x9) (model.py:290) as a 1x1 conv over the tap-folded output gradient F
-    (F[q, f(t,co)] = dz[q - d(t), co]): packed [Cin rows][256 folded channels], entry = W[t, c, co]."""
+    (F[q, f(t,co)] = dz[q - d(t), co]): packed [rows = our input channels][256 folded channels], entry = W[t, c, co].
+    `chan_map`: our channel j is Keras input channel chan_map[j] (-1 = padding), see conv_scatter_pack_index."""
     T = kh * kw
-    idx = -np.ones((cin, 64 * (-(-T // FINAL_TAPS_PER_GROUP))), np.int64)
-    c = np.arange(cin)
+    cm = np.arange(cin) if chan_map is None else np.asarray(chan_map, np.int64)
+    idx = -np.ones((cm.size, 64 * (-(-T // FINAL_TAPS_PER_GROUP))), np.int64)
     for t in range(T):
         for co in range(cout):
-            idx[:, _final_fold_channel(t, co, cout)] = (t * cin + c) * cout + co
+            idx[:, _final_fold_channel(t, co, cout)] = np.where(cm >= 0, (t * cin + cm) * cout + co, -1)
     return idx.astype(np.int32)
 
 
-def final_wgrad_gather_index(kh, kw, cin, cout):
-    """Keras (kh,kw,Cin,Cout) gradient of the final conv <- raw[c][f] = sum_p X[p,c] * F[p,f] (raw row pitch 256)."""
+def final_wgrad_gather_index(kh, kw, cin, cout, chan_map=None):
+    """Keras (kh,kw,Cin,Cout) gradient of the final conv <- raw[j][f] = sum_p X[p,j] * F[p,f] (raw row pitch 256), j = our
+    channel holding Keras channel c (the inverse of `chan_map`)."""
     T = kh * kw
     nf = 64 * (-(-T // FINAL_TAPS_PER_GROUP))
     idx = np.zeros((T, cin, cout), np.int64)
-    c = np.arange(cin)[:, None]
+    if chan_map is None:
+        row = np.arange(cin)
+    else:
+        cm = np.asarray(chan_map, np.int64)
+        row = np.zeros(cin, np.int64)
+        row[cm[cm >= 0]] = np.nonzero(cm >= 0)[0]
+    c = row[:, None]
     for t in range(T):
         f = np.array([_final_fold_channel(t, co, cout) for co in range(cout)])[None, :]
         idx[t] = c * nf + f
     return idx.astype(np.int32)
+
+
+def padded_gather_index(true_shape, padded_shape):
+    """Flat positions, in a tensor of `padded_shape`, of the leading `true_shape` block (same rank): the weight gradient of
+    a layer run with zero-padded channels is produced in the padded layout and gathered back into the Keras one."""
+    grids = np.meshgrid(*[np.arange(n) for n in true_shape], indexing="ij")
+    flat = np.zeros(true_shape, np.int64)
+    for g, n in zip(grids, padded_shape):
+        flat = flat * n + g
+    return flat.astype(np.int32)
 
 
 def rowfold_wgrad_gather_index(kh, kw, cin, cout):
@@ -501,13 +519,18 @@ def conv_s2_dgrad_pack_index(kh, kw, cin, cout):
     return ((t * cin + ci) * cout + co).astype(np.int32)
 
 
-def convT_dgrad_pack_index(kh, kw, cin, cout):
-    """Keras Conv2DTranspose kernel (kh,kw,Cout,Cin) -> packed [Cin][kh*kw][Cout]: the data gradient of
-    Conv2DTranspose(stride 2) is a stride-2 'same' conv2d of the output gradient with this weight."""
+def convT_dgrad_pack_index(kh, kw, cin, cout, cin_pad=None, cout_pad=None):
+    """Keras Conv2DTranspose kernel (kh,kw,Cout,Cin) -> packed [cin_pad][kh*kw][cout_pad] (-1 = zero): the data gradient
+    of Conv2DTranspose(stride 2) is a stride-2 'same' conv2d of the output gradient with this weight."""
     t = np.arange(kh * kw)[None, :, None]
     ci = np.arange(cin)[:, None, None]
     co = np.arange(cout)[None, None, :]
-    return ((t * cout + co) * cin + ci).astype(np.int32)
+    idx = ((t * cout + co) * cin + ci).astype(np.int64)
+    if (cin_pad or cin) == cin and (cout_pad or cout) == cout:
+        return idx.astype(np.int32)
+    full = -np.ones((cin_pad or cin, kh * kw, cout_pad or cout), np.int64)
+    full[:cin, :, :cout] = idx
+    return full.astype(np.int32)
 
 
 
