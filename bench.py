@@ -135,7 +135,7 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
-def bench_train_step(args, rank, world, dev, barrier):
+def bench_train_step(args, rank, world, dev, barrier, B=16, hw=(96, 96)):
     """Generator-only training step with the VGG19 content loss (train.py; BASELINE.json configs[2]): B = 16 LR patches
     of 96x96 per GPU through compile_training_model(...).train_on_batch(host x, host y) -- forward with batch-statistics
     BatchNorm, VGG19 loss, backward, Adam; data-parallel over NCCL when N > 1 (cross-replica BatchNorm sums, bucketed
@@ -145,12 +145,13 @@ def bench_train_step(args, rank, world, dev, barrier):
     import torch.distributed as dist
     from upscaler import ops
     from upscaler.model import VGG_MSE_LOSS, compile_training_model, make_upscaler_orig
-    B, lr, ks = 16, 96, args.kernel_size
-    up = make_upscaler_orig((4 * lr, 4 * lr, 3), kernel_size=ks)
-    tm = compile_training_model(up, VGG_MSE_LOSS((4 * lr, 4 * lr, 3), 1e-3).loss)
+    ks = args.kernel_size
+    h, w_ = hw
+    up = make_upscaler_orig((4 * h, 4 * w_, 3), kernel_size=ks)
+    tm = compile_training_model(up, VGG_MSE_LOSS((4 * h, 4 * w_, 3), 1e-3).loss)
     rng = np.random.default_rng(100 + rank)
-    hr = rng.uniform(-1, 1, (B, 4 * lr, 4 * lr, 3)).astype(np.float32)
-    x = hr.reshape(B, lr, 4, lr, 4, 3).mean(axis=(2, 4)).astype(np.float32)
+    hr = rng.uniform(-1, 1, (B, 4 * h, 4 * w_, 3)).astype(np.float32)
+    x = hr.reshape(B, h, 4, w_, 4, 3).mean(axis=(2, 4)).astype(np.float32)
     for _ in range(3):
         loss = tm.train_on_batch(x, hr)
     barrier()
@@ -164,10 +165,14 @@ def bench_train_step(args, rank, world, dev, barrier):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = 1000.0 * float(t.item()) / args.train_steps
     peaks = load_peaks()
-    tf = TRAIN_STEP_FLOPS[ks] * world / (ms * 1e-3) / 1e12
+    # 3 G + 3 V per sample; V scales with the HR pixel count (114.66 GFLOP at 384 x 384)
+    flops = B * 3 * (GEN_FLOPS[ks] * (h * w_) / float(H_LR * W_LR) + 114.66e9 * (16 * h * w_) / float(384 * 384))
+    if (B, hw) == (16, (96, 96)):
+        flops = TRAIN_STEP_FLOPS[ks]
+    tf = flops * world / (ms * 1e-3) / 1e12
     out = {"metric": "train samples/s", "value": world * B * 1000.0 / ms, "unit": "samples/s", "ms_per_step": ms,
-           "steps": args.train_steps, "config": "generator-only step, vgg-mse content loss, %d x (96x96 -> 384x384) per GPU, k=%d, "
-           "bf16 storage / fp32 accumulate / fp32 master weights + Adam%s" % (B, ks, ", NCCL data-parallel (SyncBN sums + bucketed gradient all-reduce)" if world > 1 else ""),
+           "steps": args.train_steps, "config": "generator-only step, vgg-mse content loss, %d x (%dx%d -> %dx%d) per GPU, k=%d, "
+           "bf16 storage / fp32 accumulate / fp32 master weights + Adam%s" % (B, h, w_, 4 * h, 4 * w_, ks, ", NCCL data-parallel (SyncBN sums + bucketed gradient all-reduce)" if world > 1 else ""),
            "algorithmic_tflops": tf, "frac_of_bf16_sustained_peak": tf / world / peaks["bf16_tflops_sustained"],
            "gpu_launches_per_step": ops.launch_count() // args.train_steps, "loss": float(loss),
            "h2d_bytes_per_step": int(x.nbytes + hr.nbytes), "d2h_bytes_per_step": 4}
@@ -341,10 +346,13 @@ def main():
     e2e_u8 = world * B * e2e_steps / float(t_u8.item())
 
     # ------------------------------------------------------------------ training step (BASELINE.json configs[2])
-    train = train_gan = None
+    train = train_gan = train_full = None
     if not args.no_train:
         train = bench_train_step(args, rank, world, dev, barrier)
         train_gan = bench_gan_step(args, rank, world, dev, barrier)
+        # train.py's own workload and one of the three steps of a train_cgc.py iteration (configs[4]):
+        # batch 1 of a full 270x480 -> 1080x1920 frame
+        train_full = bench_train_step(args, rank, world, dev, barrier, B=1, hw=(H_LR, W_LR))
 
     if rank == 0:
         peaks = load_peaks()
@@ -379,7 +387,7 @@ def main():
                               "d2h_bytes_per_step": int(yu.nbytes),
                               "api": "Model.predict_uint8(uint8 frames)->uint8 frames (data.py:253-270 conversions fused on the device)"},
                 "gpu_launches": launches,
-                "roofline": roof, "cpu_baseline": cpu, "train": train, "train_gan": train_gan,
+                "roofline": roof, "cpu_baseline": cpu, "train": train, "train_gan": train_gan, "train_full_frame": train_full,
                 "layers_ms": {k: round(v, 4) for k, v in sorted(layer_ms.items(), key=lambda kv: -kv[1])[:8]}}
         print(json.dumps(line), flush=True)
     if world > 1:
