@@ -359,8 +359,8 @@ def main():
         dom = "upscaling/1/block/conv_transp"
         dom_ms = layer_ms.get(dom)
         achieved = CONVT2_FLOPS[ks] * B / (dom_ms * 1e-3) / 1e12 if dom_ms else None
-        # DRAM bytes of that launch from `ncu --set full` (profiles/r01_s24_ncu_full_conv_phases2_convT2_summary.txt,
-        # B = 8, k = 3): 2.17 GB read + 8.44 GB written, tensor pipe 69 % active at 1.46 GHz under ncu; algorithmic = 2.12 GB input + 8.49 GB output -> no wasted re-reads
+        # DRAM bytes of that launch from `ncu --set full` (profiles/r01_s40_ncu_full_conv_phases2_convT2_summary.txt,
+        # B = 8, k = 3): 2.17 GB read + 8.44 GB written, tensor pipe 67 % active under ncu; algorithmic = 2.12 GB input + 8.49 GB output -> no wasted re-reads
         traffic = 10.61e9 * B / 8 if ks == 3 else None
         roof = {"bound": "tensor", "kernel": "conv_phases2_kernel (all 4 sub-pixel phases of " + dom + " in one persistent CTA-pair launch)",
                 "achieved": achieved, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
