@@ -188,6 +188,10 @@ int b2_loss_pair(const void* a, const void* b, int64_t n, int dtype, int mae, fl
 int b2_mean_prod(const float* x, const float* y, float yconst, int64_t n, float weight, float gscale, float* loss, float* grad,
                  void* stream);
 
+/* Discriminator output activation (model.py:885-892, 950-957, 1003-1010; train_gan3.py -da) on the (n,1) scores.
+ * kind: 1 sigmoid, 2 log-sigm, 3 tanh, 4 bi-log.  dy == NULL: out = f(z); otherwise out = dy * f'(z).  fp32. */
+int b2_score_act(const float* z, const float* dy, float* out, int64_t n, int kind, void* stream);
+
 /* Backward of the generator's final tanh (model.py:291): dz = (g1 + g2 + g3) * (1 - y*y); g2, g3 may be null. fp32. */
 int b2_tanh_bwd(const float* y, const float* g1, const float* g2, const float* g3, int64_t n, float* dz, void* stream);
 

@@ -85,6 +85,63 @@ def test_discriminator_forward_backward(shape, dtype):
     assert abs(nr - 1) < tol_n and cos > tol_c
 
 
+@pytest.mark.parametrize("act", ["sigmoid", "log-sigm", "tanh", "bi-log"])
+def test_score_activation_kernel(act):
+    """b2_score_act (discriminator output layer, model.py:885-892; train_gan3.py -da) against autograd of the oracle's
+    restatement: fp32, so tight."""
+    from upscaler import ops
+    z = np.concatenate((np.linspace(-12, 12, 97), [0.0, 1e-4, -1e-4, 40.0, -40.0])).astype(np.float32).reshape(-1, 1)
+    dy = np.random.default_rng(1).normal(size=z.shape).astype(np.float32)
+    zt = torch.from_numpy(z).requires_grad_(True)
+    ref = O.loss_activation(act, zt)
+    ref.backward(torch.from_numpy(dy))
+    zd = torch.from_numpy(z).cuda()
+    got = ops.score_act(zd, act).cpu().numpy()
+    gback = ops.score_act(zd, act, dy=torch.from_numpy(dy).cuda()).cpu().numpy()
+    # float32 log(sigmoid(x)) loses everything below -17 or so in the oracle's two-step form; compare where it is exact
+    ok = np.abs(z) <= 12 if act == "log-sigm" else np.ones_like(z, bool)
+    assert np.allclose(got[ok], ref.detach().numpy()[ok], rtol=2e-5, atol=2e-6)
+    assert np.allclose(gback[ok], zt.grad.numpy()[ok], rtol=2e-5, atol=2e-6)
+    assert np.isfinite(got).all() and np.isfinite(gback).all()
+
+
+@pytest.mark.parametrize("act", ["sigmoid", "log-sigm", "tanh", "bi-log"])
+def test_discriminator_output_activation(act):
+    """make_discriminator_simple_512(..., activation=act): scores and the image gradient through the output layer."""
+    from upscaler import ops
+    from upscaler.model import make_discriminator_simple_512
+    n, H, W = 16, 64, 64
+    dw = O.init_discriminator_simple_512_weights(seed=5, input_shape=(H, W, 3))
+    x = np.random.default_rng(2).uniform(-1, 1, (n, H, W, 3)).astype(np.float32)
+    lab = np.where(np.arange(n) % 2 == 0, 1.0, -1.0).astype(np.float32)
+    w = O.to_torch(dw, requires_grad=True)
+    xt = torch.from_numpy(x).requires_grad_(True)
+    with torch.no_grad():
+        inf_ref = O.discriminator_simple_512_forward(w, x, act, False).numpy()
+    out = O.discriminator_simple_512_forward(w, xt, act, True, [])
+    O.wasserstein_loss(torch.from_numpy(lab).reshape(-1, 1), out).backward()
+    D = make_discriminator_simple_512((H, W, 3), activation=act)
+    D.net.set_weights(dw)
+    assert np.abs(D.predict(x) - inf_ref).max() < 3e-2 * max(1.0, np.abs(inf_ref).max())
+    xd = torch.from_numpy(x).cuda()
+    scores, tape = D.net.forward(xd, True)
+    ds = torch.empty_like(scores)
+    ops.mean_prod(scores, torch.from_numpy(lab).cuda(), torch.zeros(1, device="cuda"), 1.0, 1.0, ds)
+    D.net.ensure_grads().zero_()
+    dimg = D.net.backward(tape, ds, True, True).cpu().numpy()
+    ref_s = out.detach().numpy()
+    print("%s: train scores max abs err %.4f (|ref| max %.3f)" % (act, np.abs(scores.cpu().numpy() - ref_s).max(), np.abs(ref_s).max()))
+    assert np.abs(scores.cpu().numpy() - ref_s).max() < 8e-2 * max(1.0, np.abs(ref_s).max())
+    gi = xt.grad.numpy()
+    nr = np.linalg.norm(dimg) / np.linalg.norm(gi)
+    cos = float(np.vdot(dimg, gi) / (np.linalg.norm(dimg) * np.linalg.norm(gi)))
+    print("   input gradient norm ratio %.4f cos %.4f" % (nr, cos))
+    assert abs(nr - 1) < 0.2 and cos > 0.9
+    gw = D.net.grads["discriminator/final/Dense_3"][0].cpu().numpy().ravel()
+    rw = w["discriminator/final/Dense_3"][0].grad.numpy().ravel()
+    assert abs(np.linalg.norm(gw) / np.linalg.norm(rw) - 1) < 0.2
+
+
 def _gan_models(kind2=False, family="relativistic", act="log-sigm"):
     from upscaler.model import (RelativisticLosses, VGG_MSE_LOSS, WassersteinLosses, make_and_compile_gan,
                                 make_and_compile_gan2, make_discriminator_simple_512, make_upscaler_orig, wasserstein_loss)

@@ -447,6 +447,31 @@ __global__ void mean_prod_kernel(const float* x, const float* y, float yconst, l
     }
 }
 
+// Discriminator output activation (model.py:885-892, 950-957, 1003-1010) on the (n,1) scores and its backward.
+// kind: 1 sigmoid, 2 log(sigmoid), 3 tanh, 4 bi-log = x/(1+|x|) * log(|x|+2).  dy == nullptr: out = f(z); else
+// out = dy * f'(z).  fp32; n = batch size.
+__global__ void score_act_kernel(const float* z, const float* dy, float* out, long n, int kind) {
+    for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < n; i += long(gridDim.x) * blockDim.x) {
+        const float x = z[i];
+        float f, d;
+        if (kind == 1) {
+            f = 1.f / (1.f + expf(-x));
+            d = f * (1.f - f);
+        } else if (kind == 2) {
+            f = fminf(x, 0.f) - log1pf(expf(-fabsf(x)));
+            d = 1.f / (1.f + expf(x));
+        } else if (kind == 3) {
+            f = tanhf(x);
+            d = 1.f - f * f;
+        } else {
+            const float a = fabsf(x), r = x / (1.f + a), l = logf(a + 2.f);
+            f = r * l;
+            d = l / ((1.f + a) * (1.f + a)) + a / ((1.f + a) * (a + 2.f));
+        }
+        out[i] = dy ? dy[i] * d : f;
+    }
+}
+
 // dz = (g1 + g2 + g3) * (1 - y^2): backward of the generator's final tanh (model.py:291) with up to three incoming
 // gradients (pixel loss, VGG image gradient, discriminator image gradient); all fp32.
 __global__ void tanh_bwd_kernel(const float* __restrict__ y, const float* __restrict__ g1, const float* __restrict__ g2,
@@ -695,6 +720,14 @@ int b2_loss_pair(const void* a, const void* b, int64_t n, int dtype, int mae, fl
     else
         loss_pair_kernel<__nv_bfloat16><<<grid, kEwThreads, 0, B2_STREAM>>>(reinterpret_cast<const __nv_bfloat16*>(a), reinterpret_cast<const __nv_bfloat16*>(b), n, mae, weight, gscale, loss, reinterpret_cast<__nv_bfloat16*>(grad));
     return launch_ok("b2_loss_pair");
+}
+
+int b2_score_act(const float* z, const float* dy, float* out, int64_t n, int kind, void* stream) {
+    if (!z || !out) return set_error("b2_score_act: null pointer");
+    if (kind < 1 || kind > 4) return set_error("b2_score_act: kind must be 1 (sigmoid), 2 (log-sigm), 3 (tanh) or 4 (bi-log)");
+    if (n == 0) return 0;
+    score_act_kernel<<<int((n + 255) / 256 < 148 ? (n + 255) / 256 : 148), 256, 0, B2_STREAM>>>(z, dy, out, n, kind);
+    return launch_ok("b2_score_act");
 }
 
 int b2_mean_prod(const float* x, const float* y, float yconst, int64_t n, float weight, float gscale, float* loss, float* grad,

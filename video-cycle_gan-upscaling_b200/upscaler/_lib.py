@@ -68,6 +68,7 @@ _SIGNATURES = {
     "b2_maxpool2x2_bwd": (ctypes.c_int, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
     "b2_loss_pair": (ctypes.c_int, [_P, _P, _L, _I, _I, _F, _F, _P, _P, _P]),
     "b2_mean_prod": (ctypes.c_int, [_P, _P, _F, _L, _F, _F, _P, _P, _P]),
+    "b2_score_act": (ctypes.c_int, [_P, _P, _P, _L, _I, _P]),
     "b2_tanh_bwd": (ctypes.c_int, [_P, _P, _P, _P, _L, _P, _P]),
     "b2_gather_f32": (ctypes.c_int, [_P, _P, _L, _P, _I, _P]),
     "b2_colsum_f32": (ctypes.c_int, [_P, _L, _I, _P, _P]),

@@ -797,8 +797,6 @@ class DiscriminatorSimple512Net(Net):
         """x: (n,H,W,3) fp32 -> ((n,1) fp32 scores, tape).  training=True normalises with batch statistics (and updates
         the moving ones, as Keras does even for a frozen discriminator inside the GAN model); False = Model.predict."""
         self._need_gpu()
-        if self.activation not in ("none", "log", "linear", None):
-            raise NotImplementedError("discriminator output activation %r (model.py:885-892) is not built yet" % self.activation)
         dt, pk, w = self.train_dtype, self._packed["train"], self.weights
         n = x.shape[0]
         if tuple(x.shape[1:]) != self.input_shape:
@@ -822,6 +820,9 @@ class DiscriminatorSimple512Net(Net):
                               torch.empty((n, c["cout"]), dtype=torch.float32 if last else dt, device=self.device))
             a = z if last else self._bn_act(tape, "discriminator/final/BatchNorm_%d" % (j + 1), z, training, sync)
         tape["dins"] = dins
+        if self.activation in ops.SCORE_ACTS:                   # model.py:885-892; any other string: no output layer
+            tape["score_pre"] = a
+            a = ops.score_act(a, self.activation)
         return a, tape
 
     def forward_infer(self, x, out=None):
@@ -839,6 +840,8 @@ class DiscriminatorSimple512Net(Net):
         n = dscore.shape[0]
         dins = tape["dins"]
         d = dscore
+        if "score_pre" in tape:
+            d = ops.score_act(tape["score_pre"], self.activation, dy=dscore.contiguous())
         for j in reversed(range(len(self._dense))):
             name, c = self._dense[j]
             if j < len(self._dense) - 1:

@@ -365,6 +365,20 @@ def loss_pair(a, b, loss, mae=False, weight=1.0, gscale=1.0, grad=None):
     _count(1)
 
 
+SCORE_ACTS = {"sigmoid": 1, "log-sigm": 2, "tanh": 3, "bi-log": 4}
+
+
+def score_act(z, kind, dy=None, out=None):
+    """Discriminator output activation (model.py:885-892) of the fp32 scores z; with dy: its backward dy * f'(z)."""
+    if out is None:
+        out = torch.empty_like(z)
+    _require_cuda(z, out, dy)
+    rc = _lib.load().b2_score_act(_lib.ptr(z), _lib.ptr(dy), _lib.ptr(out), z.numel(), SCORE_ACTS[kind], _lib.stream_ptr())
+    _lib.check(rc, "b2_score_act")
+    _count(1)
+    return out
+
+
 def mean_prod(x, y, loss, weight=1.0, gscale=1.0, grad=None, yconst=1.0):
     rc = _lib.load().b2_mean_prod(_lib.ptr(x), _lib.ptr(y), yconst, x.numel(), weight, gscale, _lib.ptr(loss), _lib.ptr(grad),
                                   _lib.stream_ptr())
