@@ -130,6 +130,25 @@ int b2_f32_to_u8_denorm(const float* in, uint8_t* out, int64_t n, void* stream);
 int b2_conv2d_s2_dgrad(const void* dz, int B, int OH, int OW, int Cout, const void* w, int Cin, int kh, int kw, int H, int W,
                        const b2_epilogue* ep, void* stream);
 
+/* Conv2D with explicit zero padding and output grid — keras Conv2D(padding='valid', strides 1 or 3) of
+ * make_discriminator_sparse_512 (model.py:967-989: pad 0, OH = (H - kh) / stride + 1), and, with pad = k - 1 and
+ * flipped/transposed weights, the data gradient of its stride-1 first block.
+ *   out[b,oy,ox,:] = sum_{ky,kx} x[b, oy*stride + ky - pad_h, ox*stride + kx - pad_w, :] . w[:, ky, kx, :]   (0 outside x)
+ *   x: [B,H,W,Cin] 16-bit, Cin a multiple of 64; w packed [Cout][kh*kw*Cin]; ep->out: [B,OH,OW,Cout]; stride 1..3. */
+int b2_conv2d_fprop_pad(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw, int stride,
+                        int pad_h, int pad_w, int OH, int OW, const b2_epilogue* ep, void* stream);
+
+/* Data gradient of that convolution for stride 2 or 3 (TF conv2d_backprop_input behind model.py:971-989), run as
+ * stride*stride sub-pixel phases.  dz: [B,OH,OW,Cout]; w packed [Cin][kh*kw*Cout] (taps un-flipped, channels
+ * transposed: conv_s2_dgrad_pack_index); ep->out: [B,H,W,Cin], every element written (rows the forward never read get 0). */
+int b2_conv2d_strided_dgrad(const void* dz, int B, int OH, int OW, int Cout, const void* w, int Cin, int kh, int kw, int stride,
+                            int pad_h, int pad_w, int H, int W, const b2_epilogue* ep, void* stream);
+
+/* Weight gradient of that convolution (see b2_conv2d_wgrad): dw[ky][kx][cx][cz] += sum_p x[p*stride + (ky,kx) - pad, cx] *
+ * dz[p, cz] over the (OH, OW) grid of dz. */
+int b2_conv2d_wgrad_pad(const void* x, int B, int H, int W, int Cx, const void* dz, int OH, int OW, int Cz, int kh, int kw,
+                        int stride, int pad_h, int pad_w, float* dw, int f16, void* stream);
+
 /* Weight gradient — TF conv2d_backprop_filter:  dw[ky][kx][cx][cz] += sum_p x[p*stride + (ky,kx) - pad, cx] * dz[p, cz],
  * fp32, ACCUMULATED into dw (zero it first), tcgen05 with the pixel dimension as GEMM K and split-K over pixels.
  *   Conv2D:           x = layer input [B,H,W,Cin],  dz = gradient of the layer output [B,ceil(H/s),ceil(W/s),Cout]

@@ -264,3 +264,52 @@ def test_adam_matches_keras_adam():
         ops.adam(p, torch.from_numpy(g * 4).cuda(), m, v, float(lr_t), 0.9, 0.999, 1e-7, gscale=0.25)
     torch.cuda.synchronize()
     _close(p.cpu().numpy(), pt.numpy(), 1e-6, 1e-5, "adam")
+
+
+VALID_CASES = [
+    # B, H, W, Cin, Cout, k, stride       (make_discriminator_sparse_512, model.py:967-989: 5x5 'valid', strides 1 / 3)
+    (2, 40, 37, 64, 128, 5, 3),
+    (1, 168, 100, 64, 128, 5, 3),         # wide rows: the strided TMA box limits the tile width
+    (3, 17, 17, 128, 256, 5, 3),
+    (4, 5, 5, 256, 256, 5, 3),            # 5x5 -> 1x1
+    (2, 20, 23, 64, 64, 5, 1),
+    (2, 19, 22, 64, 128, 3, 2),
+]
+
+
+@pytest.mark.parametrize("case", VALID_CASES)
+def test_conv2d_valid_forward_dgrad_wgrad(case):
+    """b2_conv2d_fprop_pad / b2_conv2d_strided_dgrad / b2_conv2d_wgrad_pad against autograd of a plain fp32
+    conv2d(padding=0) on the same bf16-rounded operands."""
+    import torch.nn.functional as F
+    from upscaler import ops
+    B, H, W, Cin, Cout, k, s = case
+    rng = np.random.default_rng(abs(hash(case)) % 2 ** 31)
+    OH, OW = (H - k) // s + 1, (W - k) // s + 1
+    x = _rnd((B, H, W, Cin), rng)
+    dz = _rnd((B, OH, OW, Cout), rng)
+    kern_np = _rnd((k, k, Cin, Cout), rng, 1.0 / np.sqrt(k * k * Cin))
+    bias = _rnd((Cout,), rng, 0.1)
+    xt = _q(x).permute(0, 3, 1, 2).clone().requires_grad_(True)
+    kt = _q(kern_np).requires_grad_(True)
+    y = F.conv2d(xt, kt.permute(3, 2, 0, 1), torch.from_numpy(bias), stride=s)
+    assert tuple(y.shape) == (B, Cout, OH, OW)
+    (y * _q(dz).permute(0, 3, 1, 2)).sum().backward()
+    kd = torch.from_numpy(kern_np).cuda()
+    wp = ops.gather_cast(kd, torch.from_numpy(ops.conv_pack_index(k, k, Cin, Cout)).cuda(), dtype=BF)
+    got = ops.conv2d_pad(_dev(x), wp, Cout, k, k, s, (0, 0), (OH, OW), shift=torch.from_numpy(bias).cuda())
+    ref = y.detach().permute(0, 2, 3, 1).numpy()
+    _close(got.float().cpu().numpy(), ref, 4e-3 * np.abs(ref).max(), 1e-2, "valid fprop")
+    ref_dx = xt.grad.permute(0, 2, 3, 1).numpy()
+    if s > 1:
+        wt = ops.gather_cast(kd, torch.from_numpy(ops.conv_s2_dgrad_pack_index(k, k, Cin, Cout)).cuda(), dtype=BF)
+        dx = ops.conv2d_strided_dgrad(_dev(dz), wt, Cin, k, k, s, (0, 0), (H, W))
+    else:
+        wt = ops.gather_cast(kd, torch.from_numpy(ops.conv_dgrad_pack_index(k, k, Cin, Cout)).cuda(), dtype=BF)
+        dx = ops.conv2d_pad(_dev(dz), wt, Cin, k, k, 1, (k - 1, k - 1), (H, W))
+    _close(dx.float().cpu().numpy(), ref_dx, 4e-3 * np.abs(ref_dx).max(), 1e-2, "valid dgrad")
+    dw = torch.zeros((k, k, Cin, Cout), device="cuda")
+    ops.conv2d_wgrad_pad(_dev(x), _dev(dz), k, k, s, (0, 0), dw)
+    torch.cuda.synchronize()
+    ref_dw = kt.grad.numpy()
+    _close(dw.cpu().numpy(), ref_dw, 2e-3 * np.abs(ref_dw).max(), 2e-3, "valid wgrad")

@@ -56,6 +56,52 @@ static int conv_taps(IgemmParams& p, int B, int H, int W, int Cin, int kh, int k
     return 0;
 }
 
+// Explicit-padding form (Conv2D(padding='valid'), and the 'full' correlation that is its stride-1 data gradient):
+// out[oy] = sum_ky x[oy*stride + ky - pad]; the output grid (OH, OW) is the caller's.
+static int conv_taps_pad(IgemmParams& p, int B, int Cin, int kh, int kw, int stride, int pad_h, int pad_w, int OH, int OW) {
+    if (kh * kw > kMaxTaps) return set_error("conv: %dx%d filter exceeds %d taps", kh, kw, kMaxTaps);
+    if (pad_h < 0 || pad_w < 0 || pad_h > 100 || pad_w > 100) return set_error("conv: bad padding %d,%d", pad_h, pad_w);
+    p.B = B; p.H = OH; p.W = OW;
+    p.cin = Cin;
+    p.in_mul = stride;
+    p.num_taps = kh * kw;
+    for (int ky = 0; ky < kh; ++ky)
+        for (int kx = 0; kx < kw; ++kx) {
+            const int t = ky * kw + kx;
+            p.dy[t] = int8_t(ky - pad_h);
+            p.dx[t] = int8_t(kx - pad_w);
+            p.wtap[t] = int16_t(t);
+        }
+    p.OH = OH; p.OW = OW;
+    p.out_sy = 1; p.out_sx = 1; p.out_oy = 0; p.out_ox = 0;
+    return 0;
+}
+
+// Data gradient of a stride-s convolution as s*s sub-pixel phases: x position y = s*j + py receives
+// sum over ky = py + pad - s*d of dz[j + d] * W[ky]  (the stride-2 SAME case above is convT_phase_taps).
+static void strided_phase_taps(IgemmParams& p, int B, int H, int W, int Cz, int kh, int kw, int s, int pad_h, int pad_w,
+                               int py, int px) {
+    p.B = B; p.H = (H - py + s - 1) / s; p.W = (W - px + s - 1) / s;
+    p.cin = Cz;
+    p.in_mul = 1;
+    int nt = 0;
+    for (int ky = 0; ky < kh; ++ky) {
+        const int ny = py + pad_h - ky;
+        if (((ny % s) + s) % s != 0) continue;
+        for (int kx = 0; kx < kw; ++kx) {
+            const int nx = px + pad_w - kx;
+            if (((nx % s) + s) % s != 0) continue;
+            p.dy[nt] = int8_t(ny >= 0 ? ny / s : -((-ny) / s));
+            p.dx[nt] = int8_t(nx >= 0 ? nx / s : -((-nx) / s));
+            p.wtap[nt] = int16_t(ky * kw + kx);
+            ++nt;
+        }
+    }
+    p.num_taps = nt;
+    p.OH = H; p.OW = W;
+    p.out_sy = s; p.out_sx = s; p.out_oy = py; p.out_ox = px;
+}
+
 // Conv2DTranspose(stride 2, same) is the input-gradient of a SAME stride-2 conv: out[y] = sum_i x[i] * W[y - 2i + pb],
 // pb = the forward conv's pad_before ((k-2)/2 when out = 2*in).  For output parity py: y = 2j + py, i = j + d
 // =>  ky = py + pb - 2d.  The same tap lists give the data gradient of a stride-2 Conv2D (discriminator, model.py:843-871)
@@ -180,6 +226,67 @@ int b2_conv2d_wgrad(const void* x, int B, int H, int W, int Cx, const void* dz, 
             const int t = ky * kw + kx;
             a.dy[t] = int8_t(ky - pbh);
             a.dx[t] = int8_t(kx - pbw);
+            a.wtap[t] = int16_t(t);
+        }
+    a.dw = dw;
+    a.f16 = f16;
+    return launch_conv_wgrad(a, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b2_conv2d_fprop_pad(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw, int stride,
+                        int pad_h, int pad_w, int OH, int OW, const b2_epilogue* ep, void* stream) {
+    if (!x || !w || !ep || !ep->out) return set_error("b2_conv2d_fprop_pad: null pointer");
+    if (stride < 1 || stride > 3) return set_error("b2_conv2d_fprop_pad: stride %d unsupported", stride);
+    if (OH < 1 || OW < 1) return set_error("b2_conv2d_fprop_pad: empty output %dx%d", OH, OW);
+    ConvIgemmArgs a;
+    memset(&a, 0, sizeof(a));
+    if (conv_taps_pad(a.p, B, Cin, kh, kw, stride, pad_h, pad_w, OH, OW)) return -1;
+    fill_epilogue(a.p, ep, Cout);
+    a.x = reinterpret_cast<const __nv_bfloat16*>(x);
+    a.xB = B; a.xH = H; a.xW = W; a.xC = Cin;
+    a.w = reinterpret_cast<const __nv_bfloat16*>(w);
+    a.w_rows = Cout; a.w_k = kh * kw * Cin;
+    return launch_conv_igemm(a, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b2_conv2d_strided_dgrad(const void* dz, int B, int OH, int OW, int Cout, const void* w, int Cin, int kh, int kw, int stride,
+                            int pad_h, int pad_w, int H, int W, const b2_epilogue* ep, void* stream) {
+    if (!dz || !w || !ep || !ep->out) return set_error("b2_conv2d_strided_dgrad: null pointer");
+    if (stride < 2 || stride > 3) return set_error("b2_conv2d_strided_dgrad: stride %d unsupported", stride);
+    if (kh < stride || kw < stride || kh * kw > kMaxTaps)
+        return set_error("b2_conv2d_strided_dgrad: filter %dx%d must cover the stride and have at most %d taps", kh, kw, kMaxTaps);
+    for (int ph = 0; ph < stride * stride; ++ph) {
+        ConvIgemmArgs a;
+        memset(&a, 0, sizeof(a));
+        strided_phase_taps(a.p, B, H, W, Cout, kh, kw, stride, pad_h, pad_w, ph / stride, ph % stride);
+        if (a.p.H <= 0 || a.p.W <= 0) continue;
+        fill_epilogue(a.p, ep, Cin);
+        a.x = reinterpret_cast<const __nv_bfloat16*>(dz);
+        a.xB = B; a.xH = OH; a.xW = OW; a.xC = Cout;
+        a.w = reinterpret_cast<const __nv_bfloat16*>(w);
+        a.w_rows = Cin; a.w_k = kh * kw * Cout;
+        const int rc = launch_conv_igemm(a, reinterpret_cast<cudaStream_t>(stream));
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int b2_conv2d_wgrad_pad(const void* x, int B, int H, int W, int Cx, const void* dz, int OH, int OW, int Cz, int kh, int kw,
+                        int stride, int pad_h, int pad_w, float* dw, int f16, void* stream) {
+    if (!x || !dz || !dw) return set_error("b2_conv2d_wgrad_pad: null pointer");
+    if (stride < 1 || stride > 3) return set_error("b2_conv2d_wgrad_pad: stride %d unsupported", stride);
+    if (kh * kw > kMaxTaps) return set_error("b2_conv2d_wgrad_pad: %dx%d filter exceeds %d taps", kh, kw, kMaxTaps);
+    if (pad_h < 0 || pad_w < 0 || pad_h > 100 || pad_w > 100) return set_error("b2_conv2d_wgrad_pad: bad padding");
+    WgradArgs a;
+    memset(&a, 0, sizeof(a));
+    a.x = x; a.xB = B; a.xH = H; a.xW = W; a.cx = Cx;
+    a.dz = dz; a.zB = B; a.zH = OH; a.zW = OW; a.cz = Cz;
+    a.num_taps = kh * kw; a.in_mul = stride;
+    for (int ky = 0; ky < kh; ++ky)
+        for (int kx = 0; kx < kw; ++kx) {
+            const int t = ky * kw + kx;
+            a.dy[t] = int8_t(ky - pad_h);
+            a.dx[t] = int8_t(kx - pad_w);
             a.wtap[t] = int16_t(t);
         }
     a.dw = dw;

@@ -202,13 +202,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
 
 // ---------------------------------------------------------------------------------------------- host side
 
-static void choose_tile(int B, int H, int W, int& TB, int& TH, int& TW) {
+static void choose_tile(int B, int H, int W, int& TB, int& TH, int& TW, int ext_max = 128) {
     double best = -1.0;
     TB = TH = TW = 1;
-    const int wmax = W < 128 ? W : 128;
+    const int wmax = W < ext_max ? W : ext_max;    // ext_max: a strided TMA box spans tile * stride <= 256 elements
     for (int tw = 1; tw <= wmax; ++tw) {
         int th = 128 / tw;
         if (th > H) th = H;
+        if (th > ext_max) th = ext_max;
         if (th < 1) continue;
         int tb = 128 / (tw * th);
         if (tb > B) tb = B;
@@ -247,8 +248,8 @@ int launch_conv_igemm(const ConvIgemmArgs& a, cudaStream_t stream) {
     IgemmParams p = a.p;
     if (a.xC % 64 != 0 || p.cin != a.xC) return set_error("igemm: Cin=%d must be a multiple of 64", a.xC);
     if (p.num_taps < 1 || p.num_taps > kMaxTaps) return set_error("igemm: bad tap count %d", p.num_taps);
-    if (p.in_mul != 1 && p.in_mul != 2) return set_error("igemm: in_mul must be 1 or 2");
-    choose_tile(p.B, p.H, p.W, p.TB, p.TH, p.TW);
+    if (p.in_mul < 1 || p.in_mul > 3) return set_error("igemm: in_mul must be 1, 2 or 3");
+    choose_tile(p.B, p.H, p.W, p.TB, p.TH, p.TW, p.in_mul <= 2 ? 128 : 256 / p.in_mul);
     int BN = 256;
     if (p.n_valid <= 16) BN = 16;
     else if (p.n_valid <= 32) BN = 32;

@@ -259,13 +259,14 @@ static int launch_wgrad_bn(const CUtensorMap& mapX, const CUtensorMap& mapZ, con
 }
 
 // Same tile chooser as the forward kernel: the box of <= 128 pixels that wastes the fewest MMA rows.
-static void wgrad_choose_tile(int B, int H, int W, int& TB, int& TH, int& TW) {
+static void wgrad_choose_tile(int B, int H, int W, int& TB, int& TH, int& TW, int ext_max = 128) {
     double best = -1.0;
     TB = TH = TW = 1;
-    const int wmax = W < 128 ? W : 128;
+    const int wmax = W < ext_max ? W : ext_max;
     for (int tw = 1; tw <= wmax; ++tw) {
         int th = 128 / tw;
         if (th > H) th = H;
+        if (th > ext_max) th = ext_max;
         if (th < 1) continue;
         int tb = 128 / (tw * th);
         if (tb > B) tb = B;
@@ -283,14 +284,14 @@ int launch_conv_wgrad(const WgradArgs& a, cudaStream_t stream) {
     memset(&p, 0, sizeof(p));
     if (a.cx % 64 != 0 || a.cz % 64 != 0) return set_error("wgrad: channel counts %d / %d must be multiples of 64", a.cx, a.cz);
     if (a.num_taps < 1 || a.num_taps > kMaxTaps) return set_error("wgrad: bad tap count %d", a.num_taps);
-    if (a.in_mul != 1 && a.in_mul != 2) return set_error("wgrad: stride must be 1 or 2");
+    if (a.in_mul < 1 || a.in_mul > 3) return set_error("wgrad: stride must be 1, 2 or 3");
     p.B = a.zB; p.H = a.zH; p.W = a.zW;
     p.cx = a.cx; p.cz = a.cz;
     p.num_taps = a.num_taps; p.in_mul = a.in_mul;
     for (int t = 0; t < a.num_taps; ++t) { p.dy[t] = a.dy[t]; p.dx[t] = a.dx[t]; p.wtap[t] = a.wtap[t]; }
     p.dw = a.dw;
     p.f16 = a.f16;
-    wgrad_choose_tile(p.B, p.H, p.W, p.TB, p.TH, p.TW);
+    wgrad_choose_tile(p.B, p.H, p.W, p.TB, p.TH, p.TW, a.in_mul <= 2 ? 128 : 256 / a.in_mul);
     p.tiles_x = (p.W + p.TW - 1) / p.TW;
     p.tiles_y = (p.H + p.TH - 1) / p.TH;
     p.tiles_b = (p.B + p.TB - 1) / p.TB;

@@ -58,6 +58,9 @@ _SIGNATURES = {
     # ---- training step
     "b2_conv2d_s2_dgrad": (ctypes.c_int, [_P] + [_I] * 4 + [_P] + [_I] * 5 + [ctypes.POINTER(Epilogue), _P]),
     "b2_conv2d_wgrad": (ctypes.c_int, [_P] + [_I] * 4 + [_P] + [_I] * 4 + [_P, _I, _P]),
+    "b2_conv2d_fprop_pad": (ctypes.c_int, [_P] + [_I] * 4 + [_P] + [_I] * 8 + [ctypes.POINTER(Epilogue), _P]),
+    "b2_conv2d_strided_dgrad": (ctypes.c_int, [_P] + [_I] * 4 + [_P] + [_I] * 8 + [ctypes.POINTER(Epilogue), _P]),
+    "b2_conv2d_wgrad_pad": (ctypes.c_int, [_P] + [_I] * 4 + [_P] + [_I] * 8 + [_P, _I, _P]),
     "b2_colstats": (ctypes.c_int, [_P, _L, _I, _I, _P, _P, _P]),
     "b2_bn_finalize": (ctypes.c_int, [_P, _P, _F, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _I, _P]),
     "b2_bn_fold": (ctypes.c_int, [_P, _P, _P, _P, _P, _F, _P, _P, _I, _P]),

@@ -257,6 +257,59 @@ def conv2d_s2_dgrad(dz, w_packed_t, cin, kh, kw, in_hw, out=None, gate=None, gat
     return out
 
 
+def conv2d_pad(x, w_packed, cout, kh, kw, stride, pad, out_hw, out=None, out_dtype=None, shift=None, gate=None,
+               gate_slope=0.0):
+    """Conv2D with explicit zero padding `pad` = (pad_h, pad_w) on an explicit output grid: padding='valid' (pad 0,
+    out = (in - k) // stride + 1; make_discriminator_sparse_512, model.py:967-989) or the 'full' correlation (pad k-1)."""
+    B, H, W, Cin = x.shape
+    OH, OW = out_hw
+    f16 = _elem_flag(x, w_packed)
+    if Cin % 64 != 0 or w_packed.numel() != cout * kh * kw * Cin:
+        raise ValueError("conv2d_pad: Cin must be a multiple of 64 and the packed weight [Cout][kh*kw*Cin]")
+    if out is None:
+        out = torch.empty((B, OH, OW, cout), dtype=out_dtype or x.dtype, device=x.device)
+    _require_cuda(x, w_packed, out, shift, gate)
+    ep = _lib.make_epilogue(out, None, shift, None, ACT_NONE, 0.0, None, f16, gate, gate_slope)
+    rc = _lib.load().b2_conv2d_fprop_pad(_lib.ptr(x), B, H, W, Cin, _lib.ptr(w_packed), cout, kh, kw, stride, pad[0], pad[1],
+                                         OH, OW, ctypes.byref(ep), _lib.stream_ptr())
+    _lib.check(rc, "b2_conv2d_fprop_pad")
+    _count(1)
+    return out
+
+
+def conv2d_strided_dgrad(dz, w_packed_t, cin, kh, kw, stride, pad, in_hw, out=None):
+    """Data gradient of conv2d_pad for stride 2 or 3: dz (B,OH,OW,Cout) -> (B,H,W,Cin); `w_packed_t` from
+    conv_s2_dgrad_pack_index."""
+    B, OH, OW, Cout = dz.shape
+    H, W = in_hw
+    f16 = _elem_flag(dz, w_packed_t)
+    if out is None:
+        out = torch.empty((B, H, W, cin), dtype=dz.dtype, device=dz.device)
+    _require_cuda(dz, w_packed_t, out)
+    ep = _lib.make_epilogue(out, None, None, None, ACT_NONE, 0.0, None, f16, None, 0.0)
+    rc = _lib.load().b2_conv2d_strided_dgrad(_lib.ptr(dz), B, OH, OW, Cout, _lib.ptr(w_packed_t), cin, kh, kw, stride,
+                                             pad[0], pad[1], H, W, ctypes.byref(ep), _lib.stream_ptr())
+    _lib.check(rc, "b2_conv2d_strided_dgrad")
+    _count(stride * stride)
+    return out
+
+
+def conv2d_wgrad_pad(x, dz, kh, kw, stride, pad, dw):
+    """conv2d_wgrad for conv2d_pad's geometry: dw (kh,kw,Cx,Cz) fp32 += sum_p x[p*stride + tap - pad] (x) dz[p]."""
+    B, H, W, Cx = x.shape
+    _, OH, OW, Cz = dz.shape
+    if x.dtype != dz.dtype or x.dtype not in (torch.bfloat16, torch.float16):
+        raise ValueError("conv2d_wgrad_pad: x and dz must share a 16-bit dtype")
+    if dw.dtype != torch.float32 or dw.numel() != kh * kw * Cx * Cz:
+        raise ValueError("conv2d_wgrad_pad: dw must be float32 with %d elements" % (kh * kw * Cx * Cz))
+    _require_cuda(x, dz, dw)
+    rc = _lib.load().b2_conv2d_wgrad_pad(_lib.ptr(x), B, H, W, Cx, _lib.ptr(dz), OH, OW, Cz, kh, kw, stride, pad[0], pad[1],
+                                         _lib.ptr(dw), 1 if x.dtype == torch.float16 else 0, _lib.stream_ptr())
+    _lib.check(rc, "b2_conv2d_wgrad_pad")
+    _count(1)
+    return dw
+
+
 def conv2d_wgrad(x, dz, kh, kw, stride, dw):
     """dw (kh,kw,Cx,Cz) fp32 += sum_p x[p*stride + tap - pad] (x) dz[p]  (Conv2D: x = input, dz = output gradient;
     Conv2DTranspose: x = output gradient, dz = input, stride 2)."""
