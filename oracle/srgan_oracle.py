@@ -190,6 +190,37 @@ def init_discriminator_simple_512_weights(seed=99, input_shape=(512, 512, 3), ra
     return w
 
 
+DISC_SPARSE_FILTERS = [64, 128, 256, 256, 256, 256]       # make_discriminator_sparse_512, model.py:967-989
+DISC_SPARSE_STRIDES = [1, 3, 3, 3, 3, 3]                   # 5x5 kernels, padding='valid': 512 -> 508 -> 168 -> 55 -> 17 -> 5 -> 1
+
+
+def sparse_512_conv_sizes(h, w):
+    """Spatial sizes after each 'valid' 5x5 block of make_discriminator_sparse_512 (model.py:967-989)."""
+    out = []
+    for s in DISC_SPARSE_STRIDES:
+        h, w = (h - 5) // s + 1, (w - 5) // s + 1
+        if h < 1 or w < 1:
+            raise ValueError("input too small for make_discriminator_sparse_512")
+        out.append((h, w))
+    return out
+
+
+def init_discriminator_sparse_512_weights(seed=98, input_shape=(512, 512, 3), randomize=True):
+    rng = np.random.default_rng(seed)
+    w, cin = {}, input_shape[2]
+    for i, c in enumerate(DISC_SPARSE_FILTERS):
+        w["discriminator/block_%d/Conv2d" % (i + 1)] = _conv_w(rng, 5, 5, cin, c, 0.02 if randomize else 0.0)
+        w["discriminator/block_%d/BatchNorm" % (i + 1)] = _bn_w(rng, c, randomize)
+        cin = c
+    h, wd = sparse_512_conv_sizes(input_shape[0], input_shape[1])[-1]
+    flat = h * wd * cin
+    for j, (fi, fo) in enumerate([(flat, 128), (128, 32), (32, 1)]):      # model.py:992-1000
+        w["discriminator/final/Dense_%d" % (j + 1)] = [glorot_uniform(rng, (fi, fo), fi, fo), np.zeros(fo, np.float32)]
+        if j < 2:
+            w["discriminator/final/BatchNorm_%d" % (j + 1)] = _bn_w(rng, fo, randomize)
+    return w
+
+
 def to_torch(weights, requires_grad=False):
     out = {}
     for k, arrs in weights.items():
@@ -373,6 +404,26 @@ def discriminator_simple_512_forward(w, x_nhwc, activation="none", training=Fals
         x = batch_norm(x, *w["discriminator/block_%d/BatchNorm" % (i + 1)], training, stats_out)
         x = leaky(x, 0.1)
     x = x.permute(0, 2, 3, 1).reshape(x.shape[0], -1)  # Keras Flatten of an NHWC tensor
+    for j in range(2):
+        k, b = w["discriminator/final/Dense_%d" % (j + 1)]
+        x = x @ k + b
+        x = batch_norm(x, *w["discriminator/final/BatchNorm_%d" % (j + 1)], training, stats_out)
+        x = leaky(x, 0.1)
+    k, b = w["discriminator/final/Dense_3"]
+    x = x @ k + b
+    return loss_activation(activation, x) if activation in ("sigmoid", "log-sigm", "tanh", "bi-log") else x
+
+
+def discriminator_sparse_512_forward(w, x_nhwc, activation="none", training=False, stats_out=None):
+    """make_discriminator_sparse_512 (model.py:964-1012): six 5x5 padding='valid' blocks (strides 1,3,3,3,3,3) + the
+    Dense 128 / 32 / 1 head; returns (n, 1)."""
+    x = _t(x_nhwc).permute(0, 3, 1, 2)
+    for i, s in enumerate(DISC_SPARSE_STRIDES):
+        k, b = w["discriminator/block_%d/Conv2d" % (i + 1)]
+        x = F.conv2d(x, k.permute(3, 2, 0, 1), b, stride=s)
+        x = batch_norm(x, *w["discriminator/block_%d/BatchNorm" % (i + 1)], training, stats_out)
+        x = leaky(x, 0.1)
+    x = x.permute(0, 2, 3, 1).reshape(x.shape[0], -1)
     for j in range(2):
         k, b = w["discriminator/final/Dense_%d" % (j + 1)]
         x = x @ k + b

@@ -246,3 +246,44 @@ def test_discriminator_thin_512_forward_backward():
         cos = float(np.vdot(got, ref) / (np.linalg.norm(got) * np.linalg.norm(ref)))
         print("thin_512 grad %s cos %.4f norm ratio %.4f" % (name, cos, np.linalg.norm(got) / np.linalg.norm(ref)))
         assert cos > 0.97 and abs(np.linalg.norm(got) / np.linalg.norm(ref) - 1) < 0.06
+
+
+def test_discriminator_sparse_512_forward_backward():
+    """make_discriminator_sparse_512 (model.py:964-1012): 5x5 'valid' blocks with strides 1,3,3,3,3,3 at the smallest
+    input it accepts in one dimension (489) and a ragged other one; scores, weight gradients and the image gradient."""
+    from upscaler.networks import DiscriminatorSparse512Net
+    from upscaler import ops
+    n, H, W = 6, 489, 500
+    dw = O.init_discriminator_sparse_512_weights(seed=7, input_shape=(H, W, 3))
+    x = np.random.default_rng(3).uniform(-1, 1, (n, H, W, 3)).astype(np.float32)
+    lab = np.where(np.arange(n) % 2 == 0, 1.0, -1.0).astype(np.float32)
+    w = O.to_torch(dw, requires_grad=True)
+    xt = torch.from_numpy(x).requires_grad_(True)
+    with torch.no_grad():
+        inf_ref = O.discriminator_sparse_512_forward(w, x, "none", False).numpy()
+    out = O.discriminator_sparse_512_forward(w, xt, "none", True, [])
+    O.wasserstein_loss(torch.from_numpy(lab).reshape(-1, 1), out).backward()
+    net = DiscriminatorSparse512Net((H, W, 3), weights=dw, dtype=torch.float16)
+    assert sum(int(np.prod(t.shape)) for v in dw.values() for t in v) == sum(int(t.numel()) for v in net.weights.values() for t in v)
+    xd = torch.from_numpy(x).cuda()
+    inf = net.forward(xd, False)[0]
+    scores, tape = net.forward(xd, True)
+    ds = torch.empty_like(scores)
+    ops.mean_prod(scores, torch.from_numpy(lab).cuda(), torch.zeros(1, device="cuda"), 1.0, 1.0, ds)
+    net.ensure_grads().zero_()
+    dimg = net.backward(tape, ds, True, True).cpu().numpy()
+    torch.cuda.synchronize()
+    print("sparse_512: inference rel err %.4f, train rel err %.4f" % (
+        _rel(inf.cpu().numpy(), inf_ref), _rel(scores.cpu().numpy(), out.detach().numpy())))
+    assert _rel(inf.cpu().numpy(), inf_ref) < 5e-3
+    assert _rel(scores.cpu().numpy(), out.detach().numpy()) < 2e-2
+    for name in ["discriminator/block_%d/Conv2d" % i for i in range(1, 7)] + ["discriminator/final/Dense_1"]:
+        ref = w[name][0].grad.numpy()
+        got = net.grads[name][0].cpu().numpy().reshape(ref.shape)
+        cos = float(np.vdot(got, ref) / (np.linalg.norm(got) * np.linalg.norm(ref)))
+        print("sparse_512 grad %s cos %.4f norm ratio %.4f" % (name, cos, np.linalg.norm(got) / np.linalg.norm(ref)))
+        assert cos > 0.97 and abs(np.linalg.norm(got) / np.linalg.norm(ref) - 1) < 0.06
+    gi = xt.grad.numpy()
+    cos = float(np.vdot(dimg, gi) / (np.linalg.norm(dimg) * np.linalg.norm(gi)))
+    print("sparse_512 image gradient cos %.4f norm ratio %.4f" % (cos, np.linalg.norm(dimg) / np.linalg.norm(gi)))
+    assert cos > 0.97 and abs(np.linalg.norm(dimg) / np.linalg.norm(gi) - 1) < 0.06

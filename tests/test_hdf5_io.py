@@ -169,3 +169,15 @@ def test_save_and_load_model_pick_the_variant_from_the_weight_shapes(tmp_path):
     d.save(pd)
     d2 = load_model(pd)
     assert isinstance(d2.net, networks.DiscriminatorThin512Net) and d2.count_params() == d.count_params()
+    from upscaler.model import make_discriminator_sparse_512
+    ds = make_discriminator_sparse_512((512, 512, 3), activation="tanh")
+    assert ds.count_params() == 5987777          # Keras summary of model.py:964-1012 at (512, 512, 3)
+    ps = str(tmp_path / "sparse.h5")
+    ds.save(ps)
+    ds2 = load_model(ps)
+    assert isinstance(ds2.net, networks.DiscriminatorSparse512Net) and ds2.net.activation == "tanh"
+    a, b = ds.net.host_weights(), ds2.net.host_weights()
+    assert a["discriminator/block_2/Conv2d"][0].shape == (5, 5, 64, 128) and a["discriminator/final/Dense_1"][0].shape == (256, 128)
+    assert all(np.array_equal(x, y) for k in a for x, y in zip(a[k], b[k]))
+    with pytest.raises(ValueError):
+        make_discriminator_sparse_512((256, 256, 3))

@@ -528,7 +528,7 @@ def _layer_config(name, kind, cfg):
     c = {"name": name, "trainable": True}
     if kind in ("conv", "convT"):
         s = int(cfg.get("stride", 2 if kind == "convT" else 1))
-        c.update(filters=int(cfg["cout"]), kernel_size=[int(cfg["kh"]), int(cfg["kw"])], strides=[s, s], padding="same",
+        c.update(filters=int(cfg["cout"]), kernel_size=[int(cfg["kh"]), int(cfg["kw"])], strides=[s, s], padding=cfg.get("padding", "same"),
                  data_format="channels_last", dilation_rate=[1, 1], activation="linear", use_bias=True)
     elif kind == "dense":
         c.update(units=int(cfg["cout"]), activation="linear", use_bias=True)
@@ -680,6 +680,8 @@ def load_model(filepath, custom_objects=None, compile=False):
             raise ValueError("discriminator file without model_config: the input shape cannot be recovered")
         thin = int(weights["discriminator/block_3/Conv2d"][0].shape[3]) == 128      # thin_512 vs simple_512 (256)
         make = M.make_discriminator_thin_512 if thin else M.make_discriminator_simple_512
+        if int(weights["discriminator/block_1/Conv2d"][0].shape[0]) == 5:           # 5x5 'valid' blocks: sparse_512
+            make = M.make_discriminator_sparse_512
         m = make(tuple(in_shape), activation=arch.get("activation", "none"))
     elif "block1_conv1" in names and "block5_conv4" in names:
         net = networks.Vgg19Net()

@@ -46,6 +46,13 @@ def make_discriminator_thin_512(input_shape, activation='none'):
     return Model(net=net, input_shape=tuple(input_shape), name="model_2")
 
 
+def make_discriminator_sparse_512(input_shape, activation='none'):
+    """model.py:964-1012 — six 5x5 padding='valid' conv-BN-LeakyReLU(0.1) blocks (strides 1,3,3,3,3,3), Flatten,
+    Dense 128/32/1.  Inputs of at least 489 x 489."""
+    net = networks.DiscriminatorSparse512Net(tuple(input_shape), activation=activation)
+    return Model(net=net, input_shape=tuple(input_shape), name="model_2")
+
+
 # ------------------------------------------------------------------------------------------------ content losses
 class _VggLossBase(object):
     """Frozen VGG19 -> block5_conv4 features of y_true and y_pred (model.py:101-157).  `vgg19` may be a Model wrapping

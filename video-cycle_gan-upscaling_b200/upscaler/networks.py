@@ -92,6 +92,29 @@ def discriminator_simple_512_layer_specs(input_shape, filters=None):
     return specs
 
 
+DISC_SPARSE_FILTERS = [64, 128, 256, 256, 256, 256]      # make_discriminator_sparse_512, model.py:967-989
+DISC_SPARSE_STRIDES = [1, 3, 3, 3, 3, 3]
+
+
+def discriminator_sparse_512_layer_specs(input_shape):
+    """5x5 padding='valid' blocks (512 -> 508 -> 168 -> 55 -> 17 -> 5 -> 1), Dense 128 / 32 / 1 (model.py:964-1000)."""
+    h, w, cin = input_shape
+    specs = []
+    for i, (c, st) in enumerate(zip(DISC_SPARSE_FILTERS, DISC_SPARSE_STRIDES)):
+        specs.append(("discriminator/block_%d/Conv2d" % (i + 1), "conv", dict(kh=5, kw=5, cin=cin, cout=c, stride=st, padding="valid")))
+        specs.append(("discriminator/block_%d/BatchNorm" % (i + 1), "bn", dict(c=c)))
+        h, w = (h - 5) // st + 1, (w - 5) // st + 1
+        if h < 1 or w < 1:
+            raise ValueError("make_discriminator_sparse_512 needs inputs of at least 489 x 489, got %s" % (tuple(input_shape),))
+        cin = c
+    flat = h * w * cin
+    for j, (fi, fo) in enumerate([(flat, 128), (128, 32), (32, 1)]):
+        specs.append(("discriminator/final/Dense_%d" % (j + 1), "dense", dict(cin=fi, cout=fo)))
+        if j < 2:
+            specs.append(("discriminator/final/BatchNorm_%d" % (j + 1), "bn", dict(c=fo)))
+    return specs
+
+
 def init_keras_weights(specs, seed=None):
     """Keras initialisers: glorot_uniform kernels, zero biases, BN (1,0,0,1), PReLU alpha 0 (model.py:21; Keras
     default for :276)."""
@@ -749,9 +772,19 @@ class DiscriminatorSimple512Net(Net):
         self.activation = activation
         if dtype is not None:       # fp16 storage is offered for numerics checks; bf16 (default) has the range a
             self.train_dtype = dtype  # diverging Wasserstein critic needs (gan_test.ipynb cell 17: |D| up to 2e11)
-        specs = discriminator_simple_512_layer_specs(self.input_shape, self.filters)
+        specs = self._layer_specs()
         super().__init__(specs, weights, seed, device)
         self.extra_layers = [("discriminator/final/Flatten", "flatten")]
+        self._setup_convs(specs)
+        self._dense = [(n, c) for n, kind, c in specs if kind == "dense"]
+        self.build_packs({"train": self.train_dtype})
+        if self.on_gpu:
+            self.refresh()
+
+    def _layer_specs(self):
+        return discriminator_simple_512_layer_specs(self.input_shape, self.filters)
+
+    def _setup_convs(self, specs):
         h, w = self.input_shape[:2]
         self._conv_geom = []
         for name, kind, c in specs:
@@ -768,12 +801,8 @@ class DiscriminatorSimple512Net(Net):
                 self.add_pack("train", name, name, ops.conv_pack_index(3, 3, c["cin"], c["cout"]))
                 self.add_pack("train", name + "#dgrad", name, ops.conv_s2_dgrad_pack_index(3, 3, c["cin"], c["cout"]))
         self._flat_hw = (h, w)
-        self._dense = [(n, c) for n, kind, c in specs if kind == "dense"]
-        self.build_packs({"train": self.train_dtype})
         c1 = specs[0][2]
         self._first_wgrad_idx = torch.from_numpy(ops.fullfold_wgrad_gather_index(3, 3, c1["cin"], c1["cout"])).to(self.device)
-        if self.on_gpu:
-            self.refresh()
 
     def refresh(self, sets=("train",)):
         for s in sets:
@@ -802,15 +831,7 @@ class DiscriminatorSimple512Net(Net):
         if tuple(x.shape[1:]) != self.input_shape:
             raise ValueError("discriminator expects input %s, got %s" % (self.input_shape, tuple(x.shape[1:])))
         tape = {}
-        taps = [(ky - 1, kx - 1) for ky in range(3) for kx in range(3)]
-        a = ops.fold_taps(x, taps, dtype=dt)
-        ins = []
-        for bi, (name, c, _, _) in enumerate(self._conv_geom):
-            kk = 1 if bi == 0 else 3
-            ins.append(a)
-            z = ops.conv2d(a, pk[name], c["cout"], kk, kk, stride=c["stride"], shift=w[name][1])
-            a = self._bn_act(tape, name.replace("Conv2d", "BatchNorm"), z, training, sync)
-        tape["ins"] = ins
+        a = self._conv_forward(x, tape, training, sync)
         a = a.reshape(n, -1)                                   # Keras Flatten of an NHWC tensor
         dins = []
         for j, (name, c) in enumerate(self._dense):
@@ -824,6 +845,20 @@ class DiscriminatorSimple512Net(Net):
             tape["score_pre"] = a
             a = ops.score_act(a, self.activation)
         return a, tape
+
+    def _conv_forward(self, x, tape, training, sync):
+        """The convolutional blocks: block_1 with all nine taps folded into channels, then 3x3 'same' convs."""
+        dt, pk, w = self.train_dtype, self._packed["train"], self.weights
+        taps = [(ky - 1, kx - 1) for ky in range(3) for kx in range(3)]
+        a = ops.fold_taps(x, taps, dtype=dt)
+        ins = []
+        for bi, (name, c, _, _) in enumerate(self._conv_geom):
+            kk = 1 if bi == 0 else 3
+            ins.append(a)
+            z = ops.conv2d(a, pk[name], c["cout"], kk, kk, stride=c["stride"], shift=w[name][1])
+            a = self._bn_act(tape, name.replace("Conv2d", "BatchNorm"), z, training, sync)
+        tape["ins"] = ins
+        return a
 
     def forward_infer(self, x, out=None):
         return self.forward(x, False)[0]
@@ -852,9 +887,15 @@ class DiscriminatorSimple512Net(Net):
                 ops.dense_bwd_weight(dins[j], d, g[name][0], g[name][1])
             d = ops.dense_bwd_data(d, w[name][0], torch.empty((n, c["cin"]), dtype=dt, device=self.device))
         ready(self.offsets[(self._dense[0][0], 0)][0])
-        ins = tape["ins"]
         last = self._conv_geom[-1]
         d = d.view(n, last[3][0], last[3][1], last[1]["cout"])
+        return self._conv_backward(tape, d, want_wgrad, want_input_grad, sync, ready)
+
+    def _conv_backward(self, tape, d, want_wgrad, want_input_grad, sync, ready):
+        dt, pk, w = self.train_dtype, self._packed["train"], self.weights
+        g = self.grads
+        n = d.shape[0]
+        ins = tape["ins"]
         for bi in reversed(range(len(self._conv_geom))):
             name, c, (h, w_), _ = self._conv_geom[bi]
             bn = name.replace("Conv2d", "BatchNorm")
@@ -881,3 +922,71 @@ class DiscriminatorThin512Net(DiscriminatorSimple512Net):
     """make_discriminator_thin_512 (model.py:901-960): the same graph with 128-wide blocks 2..9."""
 
     filters = DISC_THIN_FILTERS
+
+
+class DiscriminatorSparse512Net(DiscriminatorSimple512Net):
+    """make_discriminator_sparse_512 (model.py:964-1012): six 5x5 padding='valid' blocks with strides 1,3,3,3,3,3 and a
+    Dense 128 / 32 / 1 head.  block_1 (Cin = 3) runs as a 5x1 conv over the input with its 5 filter columns folded into
+    channels; the stride-3 blocks run on b2_conv2d_fprop_pad / b2_conv2d_strided_dgrad / b2_conv2d_wgrad_pad."""
+
+    filters = DISC_SPARSE_FILTERS
+
+    def _layer_specs(self):
+        return discriminator_sparse_512_layer_specs(self.input_shape)
+
+    def _setup_convs(self, specs):
+        h, w = self.input_shape[:2]
+        self._conv_geom = []
+        for name, kind, c in specs:
+            if kind != "conv":
+                continue
+            s = c["stride"]
+            oh, ow = (h - 5) // s + 1, (w - 5) // s + 1
+            self._conv_geom.append((name, c, (h, w), (oh, ow)))
+            h, w = oh, ow
+            if c["cin"] < 64:
+                self.add_pack("train", name, name, ops.conv_rowfold_pack_index(5, 5, c["cin"], c["cout"]))
+                self.add_pack("train", name + "#dgrad", name, ops.conv_dgrad_pack_index(5, 5, c["cin"], c["cout"]))
+            else:
+                self.add_pack("train", name, name, ops.conv_pack_index(5, 5, c["cin"], c["cout"]))
+                self.add_pack("train", name + "#dgrad", name, ops.conv_s2_dgrad_pack_index(5, 5, c["cin"], c["cout"]))
+        self._flat_hw = (h, w)
+        c1 = specs[0][2]
+        self._first_wgrad_idx = torch.from_numpy(ops.rowfold_wgrad_gather_index(5, 5, c1["cin"], c1["cout"])).to(self.device)
+
+    def _conv_forward(self, x, tape, training, sync):
+        dt, pk, w = self.train_dtype, self._packed["train"], self.weights
+        H, W = self.input_shape[:2]
+        a = ops.fold_taps(x, [(0, kx) for kx in range(5)], out_hw=(H, W - 4), dtype=dt)
+        ins = []
+        for bi, (name, c, _, ohw) in enumerate(self._conv_geom):
+            ins.append(a)
+            z = ops.conv2d_pad(a, pk[name], c["cout"], 5, 1 if bi == 0 else 5, c["stride"], (0, 0), ohw, shift=w[name][1])
+            a = self._bn_act(tape, name.replace("Conv2d", "BatchNorm"), z, training, sync)
+        tape["ins"] = ins
+        return a
+
+    def _conv_backward(self, tape, d, want_wgrad, want_input_grad, sync, ready):
+        pk, g = self._packed["train"], self.grads
+        n = d.shape[0]
+        ins = tape["ins"]
+        for bi in reversed(range(len(self._conv_geom))):
+            name, c, (h, w_), _ = self._conv_geom[bi]
+            bn = name.replace("Conv2d", "BatchNorm")
+            dz = self._bn_backward(tape, bn, bn, d, torch.empty_like(d), ops.ACT_LEAKY, leaky=0.1, sync=sync,
+                                   want_param_grads=want_wgrad)
+            if bi > 0:
+                if want_wgrad:
+                    ops.conv2d_wgrad_pad(ins[bi], dz, 5, 5, c["stride"], (0, 0), g[name][0])
+                d = ops.conv2d_strided_dgrad(dz, pk[name + "#dgrad"], c["cin"], 5, 5, c["stride"], (0, 0), (h, w_))
+            else:
+                if want_wgrad:
+                    raw = self._buf("first_raw", (5 * 64 * c["cout"],), torch.float32)
+                    raw.zero_()
+                    ops.conv2d_wgrad_pad(ins[0], dz, 5, 1, 1, (0, 0), raw)
+                    ops.gather_f32(raw, self._first_wgrad_idx, g[name][0], accumulate=True)
+                ready(0)
+                if want_input_grad:
+                    return ops.conv2d_pad(dz, pk[name + "#dgrad"], c["cin"], 5, 5, 1, (4, 4), (h, w_),
+                                          out=torch.empty((n, h, w_, c["cin"]), dtype=torch.float32, device=self.device))
+        return None
