@@ -434,8 +434,10 @@ def discriminator_sparse_512_forward(w, x_nhwc, activation="none", training=Fals
     return loss_activation(activation, x) if activation in ("sigmoid", "log-sigm", "tanh", "bi-log") else x
 
 
-def discriminator_bn_names():
-    return ["discriminator/block_%d/BatchNorm" % (i + 1) for i in range(9)] + \
+def discriminator_bn_names(weights=None):
+    """BatchNormalization layers in graph order; the block count (9, or 6 for sparse_512) is read from `weights`."""
+    nb = 9 if weights is None else len([k for k in weights if k.startswith("discriminator/block_") and k.endswith("/BatchNorm")])
+    return ["discriminator/block_%d/BatchNorm" % (i + 1) for i in range(nb)] + \
            ["discriminator/final/BatchNorm_1", "discriminator/final/BatchNorm_2"]
 
 
@@ -516,7 +518,8 @@ class GanTrainer:
 
     def __init__(self, gen_weights, disc_weights, vgg_weights, content_kind="vgg-mse", rate=1e-3, content_weight=1.0,
                  disc_loss_weight=1e-10, disc_activation="none", share_adam_counter=True, res_block_num=16,
-                 upscale_factor=4):
+                 upscale_factor=4, disc_forward=None):
+        self.dfwd = disc_forward or discriminator_simple_512_forward     # or discriminator_sparse_512_forward
         self.g = to_torch(gen_weights, requires_grad=True)
         self.d = to_torch(disc_weights, requires_grad=True)
         self.vw = to_torch(vgg_weights) if vgg_weights is not None else None
@@ -532,17 +535,17 @@ class GanTrainer:
 
     def disc_train_on_batch(self, d_in, d_y):
         stats = []
-        out = discriminator_simple_512_forward(self.d, d_in, self.dact, True, stats)
+        out = self.dfwd(self.d, d_in, self.dact, True, stats)
         loss = wasserstein_loss(_t(d_y).reshape(-1, 1), out)
         loss.backward()
         self.opt_d.apply(_trainable(self.d, "d"))
-        _apply_moving(self.d, discriminator_bn_names(), stats)
+        _apply_moving(self.d, discriminator_bn_names(self.d), stats)
         return float(loss.detach())
 
     def gan_train_on_batch(self, x_lr, y_hr, adv_y):
         gstats, dstats = [], []
         y = upscaler_orig_forward(self.g, x_lr, True, gstats, self.uf, self.rbn)
-        dout = discriminator_simple_512_forward(self.d, y, self.dact, True, dstats)
+        dout = self.dfwd(self.d, y, self.dact, True, dstats)
         lc = content_loss(self.kind, self.vw, _t(y_hr), y, self.rate)
         la = wasserstein_loss(_t(adv_y).reshape(-1, 1), dout)
         total = self.cw * lc + self.dw * la
@@ -553,7 +556,7 @@ class GanTrainer:
         self.opt_g.apply(_trainable(self.g, "g"))
         _apply_moving(self.g, upscaler_bn_names(self.rbn), gstats)
         # Keras: a frozen model's BatchNormalization still runs in training phase and still updates its moving stats
-        _apply_moving(self.d, discriminator_bn_names(), dstats)
+        _apply_moving(self.d, discriminator_bn_names(self.d), dstats)
         return [float(total.detach()), float(lc.detach()), float(la.detach())]
 
     def step(self, x_lr, y_hr):
@@ -579,20 +582,20 @@ class Gan2Trainer(GanTrainer):
 
     def disc_train_on_batch2(self, real, fake):
         s1, s2 = [], []
-        r = discriminator_simple_512_forward(self.d, real, self.dact, True, s1)
-        f = discriminator_simple_512_forward(self.d, fake, self.dact, True, s2)
+        r = self.dfwd(self.d, real, self.dact, True, s1)
+        f = self.dfwd(self.d, fake, self.dact, True, s2)
         loss, _ = gan_losses(self.family, self.loss_act, r, f)
         loss.backward()
         self.opt_d.apply(_trainable(self.d, "d"))
-        _apply_moving(self.d, discriminator_bn_names(), s1)
-        _apply_moving(self.d, discriminator_bn_names(), s2)
+        _apply_moving(self.d, discriminator_bn_names(self.d), s1)
+        _apply_moving(self.d, discriminator_bn_names(self.d), s2)
         return float(loss.detach())
 
     def gan_train_on_batch2(self, x_lr, real, y_hr):
         gstats, s1, s2 = [], [], []
-        r = discriminator_simple_512_forward(self.d, real, self.dact, True, s1)
+        r = self.dfwd(self.d, real, self.dact, True, s1)
         y = upscaler_orig_forward(self.g, x_lr, True, gstats, self.uf, self.rbn)
-        f = discriminator_simple_512_forward(self.d, y, self.dact, True, s2)
+        f = self.dfwd(self.d, y, self.dact, True, s2)
         lc = content_loss(self.kind, self.vw, _t(y_hr), y, self.rate)
         _, la = gan_losses(self.family, self.loss_act, r, f)
         total = self.cw * lc + self.dw * la
@@ -602,8 +605,8 @@ class Gan2Trainer(GanTrainer):
                 t.grad = None
         self.opt_g.apply(_trainable(self.g, "g"))
         _apply_moving(self.g, upscaler_bn_names(self.rbn), gstats)
-        _apply_moving(self.d, discriminator_bn_names(), s1)
-        _apply_moving(self.d, discriminator_bn_names(), s2)
+        _apply_moving(self.d, discriminator_bn_names(self.d), s1)
+        _apply_moving(self.d, discriminator_bn_names(self.d), s2)
         return [float(total.detach()), float(lc.detach()), float(la.detach())]
 
 

@@ -142,27 +142,34 @@ def test_discriminator_output_activation(act):
     assert abs(np.linalg.norm(gw) / np.linalg.norm(rw) - 1) < 0.2
 
 
-def _gan_models(kind2=False, family="relativistic", act="log-sigm"):
+def _gan_models(kind2=False, family="relativistic", act="log-sigm", disc="simple", HR=HR, dact="none"):
     from upscaler.model import (RelativisticLosses, VGG_MSE_LOSS, WassersteinLosses, make_and_compile_gan,
-                                make_and_compile_gan2, make_discriminator_simple_512, make_upscaler_orig, wasserstein_loss)
+                                make_and_compile_gan2, make_discriminator_simple_512, make_discriminator_sparse_512,
+                                make_upscaler_orig, wasserstein_loss)
     from upscaler.keras_compat import Adam
     rbn = 1
     gw = O.init_upscaler_orig_weights(seed=21, kernel_size=3, res_block_num=rbn)
-    dw = O.init_discriminator_simple_512_weights(seed=22, input_shape=(HR, HR, 3))
+    if disc == "sparse":
+        dw = O.init_discriminator_sparse_512_weights(seed=22, input_shape=(HR, HR, 3))
+        make_d, dfwd = make_discriminator_sparse_512, O.discriminator_sparse_512_forward
+    else:
+        dw = O.init_discriminator_simple_512_weights(seed=22, input_shape=(HR, HR, 3))
+        make_d, dfwd = make_discriminator_simple_512, O.discriminator_simple_512_forward
     vw = O.init_vgg19_weights()
     G = make_upscaler_orig((HR, HR, 3), kernel_size=3, res_block_num=rbn)
     G.net.set_weights(gw)
-    D = make_discriminator_simple_512((HR, HR, 3), activation="none")
+    D = make_d((HR, HR, 3), activation=dact)
     D.net.set_weights(dw)
     content = VGG_MSE_LOSS((HR, HR, 3), 1e-3, vgg19=vw).loss
     dlw = 1e-3     # large enough for the adversarial term to matter in the comparison (reference default 1e-10 / 1e-5)
     if not kind2:
         models = make_and_compile_gan(G, D, (HR // 4, HR // 4, 3), (HR, HR, 3), content, 1, wasserstein_loss, dlw, optimizer=Adam())
-        ref = O.GanTrainer(gw, dw, vw, "vgg-mse", 1e-3, 1.0, dlw, res_block_num=rbn)
+        ref = O.GanTrainer(gw, dw, vw, "vgg-mse", 1e-3, 1.0, dlw, res_block_num=rbn, disc_activation=dact, disc_forward=dfwd)
     else:
         mk = (lambda: WassersteinLosses()) if family == "wasserstein" else (lambda: RelativisticLosses(loss_activation=act))
         models = make_and_compile_gan2(G, D, (HR // 4, HR // 4, 3), (HR, HR, 3), content, 1, mk, dlw, optimizer=Adam())
-        ref = O.Gan2Trainer(gw, dw, vw, "vgg-mse", 1e-3, 1.0, dlw, res_block_num=rbn, family=family, loss_act=act)
+        ref = O.Gan2Trainer(gw, dw, vw, "vgg-mse", 1e-3, 1.0, dlw, res_block_num=rbn, family=family, loss_act=act,
+                            disc_activation=dact, disc_forward=dfwd)
     return G, D, models, ref
 
 
@@ -287,3 +294,29 @@ def test_discriminator_sparse_512_forward_backward():
     cos = float(np.vdot(dimg, gi) / (np.linalg.norm(dimg) * np.linalg.norm(gi)))
     print("sparse_512 image gradient cos %.4f norm ratio %.4f" % (cos, np.linalg.norm(dimg) / np.linalg.norm(gi)))
     assert cos > 0.97 and abs(np.linalg.norm(dimg) / np.linalg.norm(gi) - 1) < 0.06
+
+
+def test_gan2_step_sparse_discriminator_with_output_activation():
+    """train_gan3.py:339-354 at BASELINE config 4's shapes (128x128 -> 512x512) with make_discriminator_sparse_512 and
+    a tanh output layer (-da tanh) under the relativistic log-sigm loss (-dla log-sigm)."""
+    G, D, (gen_train, disc_train, gan_train), ref = _gan_models(True, "relativistic", "log-sigm", disc="sparse", HR=512, dact="tanh")
+    x, hr = _data(4, 128, seed=9)
+    n = x.shape[0]
+    gen = gen_train.predict(x)
+    ld = disc_train.train_on_batch([hr, gen], -np.ones(n))
+    ld_ref = ref.disc_train_on_batch2(hr, gen)
+    print("sparse/tanh disc loss %.5f vs oracle %.5f" % (ld, ld_ref))
+    assert abs(ld - ld_ref) <= 3e-2 * abs(ld_ref) + ADV_ATOL
+    D.net.set_weights({k: [t.detach().numpy() for t in ts] for k, ts in ref.d.items()})
+    lg = gan_train.train_on_batch([x, hr], [hr, -np.ones(n)])
+    lg_ref = ref.gan_train_on_batch2(x, hr, hr)
+    print("sparse/tanh gan losses %s vs oracle %s" % (np.round(lg, 5), np.round(lg_ref, 5)))
+    assert abs(lg[1] - lg_ref[1]) <= 1e-2 * abs(lg_ref[1])
+    assert abs(lg[2] - lg_ref[2]) <= 3e-2 * abs(lg_ref[2]) + ADV_ATOL
+    # the generator moved the same way: its first conv after the step, against the oracle's
+    k = "initial/conv"
+    w0 = O.init_upscaler_orig_weights(seed=21, kernel_size=3, res_block_num=1)[k][0]
+    ua, ub = G.net.host_weights()[k][0] - w0, ref.g[k][0].detach().numpy() - w0
+    agree = float(np.mean(np.sign(ua) == np.sign(ub)))
+    print("initial/conv first Adam step: %.3f of the entries moved the same way" % agree)
+    assert np.abs(ua).max() < 1.1e-3 and agree > 0.8      # sign-like first step of size lr = 1e-3 (see test_training_gpu)
