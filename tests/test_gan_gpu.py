@@ -9,8 +9,11 @@ from oracle import srgan_oracle as O
 
 pytestmark = pytest.mark.gpu
 HR = 64
-# adversarial losses are (differences of) batch means of critic scores of magnitude O(1) that carry ~3 % bf16 noise each
-ADV_ATOL = 3e-2
+# adversarial losses are (differences of) batch means of critic scores of magnitude O(1); with bf16 activation storage (the
+# production type: the critic's range needs it) each mean carries a few % of rounding error through eleven batch-statistics
+# BatchNorms over 8 samples.  Measured over repeated runs: offsets of 0.021-0.033 with +-0.006 of atomic-order noise
+# (profiles/r01_s46_gan2_repeat.log); with fp16 storage the offset is 0.005-0.007 (test_gan2_disc_loss_fp16_storage).
+ADV_ATOL = 5e-2
 
 
 def _rel(got, ref):
@@ -142,7 +145,7 @@ def test_discriminator_output_activation(act):
     assert abs(np.linalg.norm(gw) / np.linalg.norm(rw) - 1) < 0.2
 
 
-def _gan_models(kind2=False, family="relativistic", act="log-sigm", disc="simple", HR=HR, dact="none"):
+def _gan_models(kind2=False, family="relativistic", act="log-sigm", disc="simple", HR=HR, dact="none", ddtype=None):
     from upscaler.model import (RelativisticLosses, VGG_MSE_LOSS, WassersteinLosses, make_and_compile_gan,
                                 make_and_compile_gan2, make_discriminator_simple_512, make_discriminator_sparse_512,
                                 make_upscaler_orig, wasserstein_loss)
@@ -159,6 +162,9 @@ def _gan_models(kind2=False, family="relativistic", act="log-sigm", disc="simple
     G = make_upscaler_orig((HR, HR, 3), kernel_size=3, res_block_num=rbn)
     G.net.set_weights(gw)
     D = make_d((HR, HR, 3), activation=dact)
+    if ddtype is not None:
+        from upscaler.keras_compat import Model
+        D = Model(net=type(D.net)((HR, HR, 3), activation=dact, dtype=ddtype), input_shape=(HR, HR, 3), name="model_2")
     D.net.set_weights(dw)
     content = VGG_MSE_LOSS((HR, HR, 3), 1e-3, vgg19=vw).loss
     dlw = 1e-3     # large enough for the adversarial term to matter in the comparison (reference default 1e-10 / 1e-5)
@@ -320,3 +326,16 @@ def test_gan2_step_sparse_discriminator_with_output_activation():
     agree = float(np.mean(np.sign(ua) == np.sign(ub)))
     print("initial/conv first Adam step: %.3f of the entries moved the same way" % agree)
     assert np.abs(ua).max() < 1.1e-3 and agree > 0.8      # sign-like first step of size lr = 1e-3 (see test_training_gpu)
+
+
+def test_gan2_disc_loss_fp16_storage():
+    """The offset ADV_ATOL allows for is activation-storage rounding, not arithmetic: with fp16 storage (11-bit
+    significand) in the critic the offset of the Wasserstein loss of the same batches drops from ~0.025 to 0.005-0.007
+    (the generated batch still comes from the bf16 generator)."""
+    G, D, (gen_train, disc_train, gan_train), ref = _gan_models(True, "wasserstein", "none", ddtype=torch.float16)
+    x, hr = _data(8, HR // 4, seed=6)
+    gen = gen_train.predict(x)
+    ld = disc_train.train_on_batch([hr, gen], -np.ones(x.shape[0]))
+    ld_ref = ref.disc_train_on_batch2(hr, gen)
+    print("wasserstein, fp16 critic: disc loss %.5f vs oracle %.5f" % (ld, ld_ref))
+    assert abs(ld - ld_ref) <= 1.5e-2
