@@ -4,13 +4,15 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "video-cycle_gan-upscaling_b200"))
 import numpy as np, torch
 from upscaler import ops
-from upscaler.model import (VGG_MSE_LOSS, make_and_compile_gan, make_discriminator_simple_512, make_upscaler_orig, wasserstein_loss)
+from upscaler import model as M
+from upscaler.model import VGG_MSE_LOSS, make_and_compile_gan, make_upscaler_orig, wasserstein_loss
 ks = int(sys.argv[1]) if len(sys.argv) > 1 else 3
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+disc = sys.argv[3] if len(sys.argv) > 3 else "simple"          # simple | thin | sparse
 n, lr = 6, 128
 hr_shape = (4 * lr, 4 * lr, 3)
 G = make_upscaler_orig(hr_shape, kernel_size=ks)
-D = make_discriminator_simple_512(hr_shape, activation="none")
+D = getattr(M, "make_discriminator_%s_512" % disc)(hr_shape, activation="none")
 gen_train, disc_train, gan_train = make_and_compile_gan(G, D, (lr, lr, 3), hr_shape, VGG_MSE_LOSS(hr_shape, 1e-3).loss, 1, wasserstein_loss, 1e-5)
 rng = np.random.default_rng(0)
 hr = rng.uniform(-1, 1, (n,) + hr_shape).astype(np.float32)
