@@ -217,6 +217,19 @@ int b2_tanh_bwd(const float* y, const float* g1, const float* g2, const float* g
 /* sum[c] += sum over rows of x[rows][C], fp32, C <= 8 (bias gradient of the 3-channel final conv, model.py:290). */
 int b2_colsum_f32(const float* x, int64_t rows, int C, float* sum, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * Data-parallel training: sum-all-reduce of small fp32 vectors (the cross-replica BatchNormalization sums,
+ * model.py:20, 23, 284, 840-872 seen by N replicas) over NVLink peer memory, one single-CTA launch on the compute
+ * stream.  Every rank allocates one region (b2_peer_alloc), sends the 64-byte CUDA IPC handle to its peers (the host
+ * side uses torch.distributed for that), opens theirs (b2_peer_open) and passes the `world` region pointers, indexed by
+ * rank, to every call.  `epoch` starts at 1 and increases by one per call, identically on all ranks.  n <= b2_peer_max_elems().
+ * ------------------------------------------------------------------------------------------------------------- */
+int b2_peer_max_elems(void);
+int b2_peer_alloc(void** region, unsigned char* handle64);
+int b2_peer_open(const unsigned char* handle64, void** region);
+int b2_peer_close(void* region, int opened);
+int b2_peer_allreduce_f32(float* data, int n, void* const* regions, int rank, int world, unsigned epoch, void* stream);
+
 /* Dense layers of the discriminator head (model.py:876-884; batch-sized M, negligible FLOPs) on CUDA cores, reading
  * the fp32 master weights in Keras layout W[K][N] directly.  x / dy / dx / out are 16-bit unless the dtype code
  * (0 bf16, 1 fp16, 2 fp32) says otherwise.

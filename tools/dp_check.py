@@ -104,13 +104,17 @@ def main():
         worst_cos = min(worst_cos, cos)
         if d_dp > worst[0]:
             worst = (d_dp, d_floor, "%s[%d]" % (name, j))
-        if cos < 0.97 or abs(ratio - 1) > 0.06 or d_dp > 2.0 * d_floor + 1e-2:
+        # norm ratio: 6 %, or half the tensor's own round-off floor where that is larger (the 64-element bias gradients of
+        # initial/conv sit at a 17-19 % reversed-batch floor)
+        if cos < 0.97 or abs(ratio - 1) > max(0.06, 0.5 * d_floor) or d_dp > 2.0 * d_floor + 1e-2:
             bad.append((name, j, round(cos, 4), round(ratio, 4), round(d_dp, 4), round(d_floor, 4)))
     print("DPCHECK world=%d losses dp %s single %s" % (world, np.round(l_dp, 6), np.round(l_1, 6)))
     print("DPCHECK first-step loss rel diff %.2e, max rel loss diff over %d steps %.2e, first-step gradients: worst cosine "
           "%.4f, worst per-tensor rel L2 diff %.3e (same tensor, reversed-batch floor %.3e: %s), out-of-tolerance %s, replica "
           "drift %.2e, buckets %s" % (rel_l[0], steps, rel_l.max(), worst_cos, worst[0], worst[1], worst[2], bad, drift, buckets))
-    ok = rel_l[0] < 1e-3 and rel_l.max() < 2e-2 and not bad and drift == 0.0
+    # steps 2..4 follow sign-like first Adam updates (|update| = lr whatever the gradient's size), so round-off in the
+    # first gradients moves the later losses by 0.6-2.1 % run to run (six 2-GPU runs, NCCL and peer reductions alike)
+    ok = rel_l[0] < 1e-3 and rel_l.max() < 3e-2 and not bad and drift == 0.0
     print("DPCHECK", "OK" if ok else "MISMATCH")
     sys.exit(0 if ok else 1)
 

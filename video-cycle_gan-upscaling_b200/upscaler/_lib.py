@@ -72,6 +72,11 @@ _SIGNATURES = {
     "b2_loss_pair": (ctypes.c_int, [_P, _P, _L, _I, _I, _F, _F, _P, _P, _P]),
     "b2_mean_prod": (ctypes.c_int, [_P, _P, _F, _L, _F, _F, _P, _P, _P]),
     "b2_score_act": (ctypes.c_int, [_P, _P, _P, _L, _I, _P]),
+    "b2_peer_max_elems": (ctypes.c_int, []),
+    "b2_peer_alloc": (ctypes.c_int, [ctypes.POINTER(ctypes.c_void_p), ctypes.c_char_p]),
+    "b2_peer_open": (ctypes.c_int, [ctypes.c_char_p, ctypes.POINTER(ctypes.c_void_p)]),
+    "b2_peer_close": (ctypes.c_int, [_P, _I]),
+    "b2_peer_allreduce_f32": (ctypes.c_int, [_P, _I, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _P]),
     "b2_tanh_bwd": (ctypes.c_int, [_P, _P, _P, _P, _L, _P, _P]),
     "b2_gather_f32": (ctypes.c_int, [_P, _P, _L, _P, _I, _P]),
     "b2_colsum_f32": (ctypes.c_int, [_P, _L, _I, _P, _P]),

@@ -1,0 +1,81 @@
+"""Cross-replica sums of small fp32 vectors over NVLink peer memory (csrc/b2_peer.cu) for the data-parallel training
+step: the BatchNormalization statistics of N replicas, ~70 latency-bound reductions per step that sit on the
+critical path.  torch.distributed carries the one-time exchange of the CUDA IPC handles; every reduction afterwards is one
+single-CTA kernel on the compute stream.  B2_DP_NO_PEER=1 keeps these reductions on NCCL (A/B timing)."""
+import ctypes
+import os
+
+from . import _lib
+
+_state = {"reducer": None, "tried": False}
+
+
+class PeerReducer:
+    def __init__(self, dist, device):
+        import torch
+        lib = _lib.load()
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        self.max_elems = lib.b2_peer_max_elems()
+        with torch.cuda.device(device):
+            own = ctypes.c_void_p()
+            handle = ctypes.create_string_buffer(64)
+            _lib.check(lib.b2_peer_alloc(ctypes.byref(own), handle), "b2_peer_alloc")
+            handles = [None] * self.world
+            dist.all_gather_object(handles, bytes(handle.raw))
+            self.regions = (ctypes.c_void_p * self.world)()
+            for p in range(self.world):
+                if p == self.rank:
+                    self.regions[p] = own.value
+                else:
+                    q = ctypes.c_void_p()
+                    _lib.check(lib.b2_peer_open(handles[p], ctypes.byref(q)), "b2_peer_open")
+                    self.regions[p] = q.value
+        dist.barrier()
+        self.epoch = 0
+        self.calls = 0
+
+    def all_reduce(self, buf):
+        """In-place sum over the ranks of a contiguous float32 CUDA tensor of at most max_elems elements."""
+        import torch
+        if buf.dtype != torch.float32 or not buf.is_cuda or not buf.is_contiguous() or buf.numel() > self.max_elems:
+            raise ValueError("peer all-reduce takes contiguous float32 CUDA tensors of at most %d elements" % self.max_elems)
+        self.epoch = (self.epoch % 0x7FFFFFFE) + 1
+        rc = _lib.load().b2_peer_allreduce_f32(_lib.ptr(buf), buf.numel(), self.regions, self.rank, self.world, self.epoch,
+                                               _lib.stream_ptr())
+        _lib.check(rc, "b2_peer_allreduce_f32")
+        self.calls += 1
+        from . import ops
+        ops._count(1)
+        return buf
+
+
+def reducer(dist, device):
+    """The process-wide PeerReducer, or None when the ranks cannot reach each other's memory (then NCCL is used).  The
+    decision is collective: every rank reports whether it could open all regions, and all follow the minimum."""
+    if _state["tried"]:
+        return _state["reducer"]
+    _state["tried"] = True
+    import torch
+    ok, red = 1, None
+    if os.environ.get("B2_DP_NO_PEER") or dist.get_backend() != "nccl" or dist.get_world_size() > 8:
+        ok = 0
+    if ok:
+        dev = torch.device(device)
+        n = torch.cuda.device_count()
+        if dist.get_world_size() > n or not all(torch.cuda.can_device_access_peer(dev.index, j) for j in range(n) if j != dev.index):
+            ok = 0
+    flag = torch.tensor([ok], device=device, dtype=torch.int32)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if int(flag.item()) == 1:
+        try:
+            red = PeerReducer(dist, device)
+            good = 1
+        except _lib.B2Error as e:            # e.g. IPC disabled in the container: say so once, stay on NCCL
+            print("[b2] peer all-reduce unavailable (%s); BatchNorm sums stay on NCCL" % e, flush=True)
+            good = 0
+        flag.fill_(good)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) != 1:
+            red = None
+    _state["reducer"] = red
+    return red

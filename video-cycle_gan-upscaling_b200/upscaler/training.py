@@ -86,10 +86,18 @@ def _make_sync():
     world = dist.get_world_size()
 
     skip = bool(os.environ.get("B2_DP_NO_BN_SYNC"))       # timing experiments only: replicas keep local statistics
+    red = {"r": None, "asked": False}
 
     def sync(buf, rows):
         if not skip:
-            dist.all_reduce(buf)
+            if not red["asked"] and buf.is_cuda:           # NVLink peer-memory reduction (csrc/b2_peer.cu) where available
+                from . import peer
+                red["r"], red["asked"] = peer.reducer(dist, buf.device), True
+            r = red["r"]
+            if r is not None and buf.is_cuda and buf.dtype == torch.float32 and buf.is_contiguous() and buf.numel() <= r.max_elems:
+                r.all_reduce(buf)
+            else:
+                dist.all_reduce(buf)
         return rows * world if rows is not None else world
     return sync
 
