@@ -53,7 +53,19 @@ typedef struct {
      * is (same geometry as out, 16-bit).  Null = no gating. */
     const void* gate;
     float gate_slope;
+    /* Train-mode BatchNormalization statistics fused into the producing convolution (model.py:19-20, 22-23, 283-284,
+     * 839-872): when set, every CTA adds its share of the per-channel sums of the fp32 values it stores (after scale / shift /
+     * activation / residual) and writes them to ITS row stats_part[cta][0..Cout) = sum, [Cout..2*Cout) = sum of squares;
+     * rows beyond the launch's grid up to b2_sm_count() are written as zeros, so b2_bn_fwd_finalize(part, b2_sm_count(), ...)
+     * follows without a separate statistics pass.  Supported by the stride-1 Cout = 64 kernels (the residual trunk) and the
+     * generic implicit-GEMM kernels; entry points that cannot honour it return an error.  Null = off. */
+    float* stats_part;
 } b2_epilogue;
+
+/* Layout self-description for foreign-function binders (checked against the ctypes mirror in tests/test_abi_layout.py). */
+int b2_sizeof_epilogue(void);
+int b2_epilogue_field_count(void);
+int b2_epilogue_field_offset(int field); /* fields in declaration order; -1 when out of range */
 
 /* Conv2D(padding='same') forward on tcgen05 tensor cores — replaces the TF conv2d behind keras.layers.Conv2D at
  * model.py:19, 22, 275, 283, 290, 839-871 and the VGG19 convs behind model.py:108-113.
@@ -116,6 +128,12 @@ int b2_u8_to_f32_norm(const uint8_t* in, float* out, int64_t n, void* stream);
 int b2_resize_bilinear_into(const float* in, int B, int H, int W, int C, int factor, void* out, int ld, int c0, int f16,
                             void* stream);
 int b2_f32_to_u8_denorm(const float* in, uint8_t* out, int64_t n, void* stream);
+
+/* Saturation guard of the 16-bit storage: *count += number of elements of x[n] at the edge of their type -- fp16 (f16 != 0):
+ * |x| >= 65504 (the value the convolution epilogues' saturating conversion stores for anything larger), inf or NaN; bf16:
+ * inf or NaN.  The host runs it over every layer output of the first inference pass after a weight change (and on
+ * request), so a network whose activations leave the fp16 range is reported instead of silently clipped. */
+int b2_count_saturated(const void* x, int64_t n, int f16, unsigned int* count, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------------
  * Training step (Model.train_on_batch of the models compile_training_model / make_and_compile_gan build,
@@ -190,6 +208,37 @@ int b2_bn_bwd_reduce(const void* z, const void* g, int64_t rows, int C, int f16,
 int b2_bn_bwd_apply(const void* z, const void* g, int64_t rows, int C, int f16, const float* scale, const float* shift,
                     const float* alpha, int act, float leaky, const float* mean, const float* invstd, const float* s1,
                     const float* s2, float count, void* dz, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Train-mode BatchNormalization statistics, deterministic two-stage form (what the training step uses; b2_colstats /
+ * b2_bn_finalize / b2_bn_bwd_reduce above remain for one-off reductions such as bias gradients).
+ * Stage 1 writes partial per-channel sums with plain stores, one row per CTA: part[row][q*C + c].  Producers: the two
+ * kernels below, or a convolution's epilogue (b2_epilogue.stats_part, rows = b2_sm_count()).  `*nparts` receives the
+ * number of rows written (<= b2_bn_part_rows()).  Stage 2 is one single-CTA launch that adds the rows in a fixed order,
+ * optionally sum-exchanges the result with the data-parallel replicas over NVLink peer memory (peer_regions / rank /
+ * world / epoch as in b2_peer_allreduce_f32; peer_regions == NULL or world <= 1: no exchange) and finishes the layer.
+ * No atomics: results are bit-reproducible and identical on every replica.
+ * ------------------------------------------------------------------------------------------------------------- */
+int b2_sm_count(void);
+int b2_bn_part_rows(void);
+/* forward stage 1: part[row] = [sum x | sum x^2] over the rows of a [rows][C] 16-bit tensor. */
+int b2_bn_stats_partial(const void* x, int64_t rows, int C, int f16, float* part, int* nparts, void* stream);
+/* forward stage 2: sums (x world) -> mean, biased variance -> aff = [scale | shift | mean | invstd] (4*C floats, owned by
+ * the caller's tape), Keras moving-statistics update when moving_mean / moving_var are given (momentum 0.99, variance
+ * n/(n-(1+eps))).  `count` = rows over ALL replicas.  sums_out (2*C, nullable) receives the summed statistics; with
+ * aff == NULL nothing else is computed (NCCL fallback: all-reduce sums_out, call again with nparts = 1). */
+int b2_bn_fwd_finalize(const float* part, int nparts, int C, float count, void* const* peer_regions, int rank, int world,
+                       unsigned epoch, float* sums_out, const float* gamma, const float* beta, float eps, float momentum,
+                       float* moving_mean, float* moving_var, float* aff, void* stream);
+/* backward stage 1 through y = act(u), u = z*scale + shift (aff from the forward tape): with dy = g*act'(u),
+ * part[row] = [sum dy | sum dy*xhat | sum g*min(u,0)]. */
+int b2_bn_bwd_partial(const void* z, const void* g, int64_t rows, int C, int f16, const float* aff, const float* alpha, int act,
+                      float leaky, float* part, int* nparts, void* stream);
+/* backward stage 2: sums = [s1 | s2] over all replicas (input of b2_bn_bwd_apply); dbeta += s1*gscale, dgamma += s2*gscale,
+ * dalpha += this replica's third sum (each nullable).  raw_out != NULL: only write the 3*C local sums there and return
+ * (NCCL fallback; call again on the all-reduced buffer with nparts = 1). */
+int b2_bn_bwd_finalize(const float* part, int nparts, int C, void* const* peer_regions, int rank, int world, unsigned epoch,
+                       float* raw_out, float* sums, float* dgamma, float* dbeta, float* dalpha, float gscale, void* stream);
 
 /* MaxPooling2D(2,2) 'valid' of VGG19 (keras.applications behind model.py:108) and its gradient (first maximum of each
  * window takes the gradient; relu_gate != 0 additionally zeroes it where x <= 0, i.e. the ReLU of the conv below). */

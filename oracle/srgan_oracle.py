@@ -395,20 +395,24 @@ def gan_losses(family, act, real_out, fake_out):
 
 
 # ------------------------------------------------------------------------------------------------ discriminator
-def discriminator_simple_512_forward(w, x_nhwc, activation="none", training=False, stats_out=None):
+def discriminator_simple_512_forward(w, x_nhwc, activation="none", training=False, stats_out=None, q=None):
     """make_discriminator_simple_512 (model.py:836-896) and make_discriminator_thin_512 (model.py:901-960: same graph,
-    narrower blocks -- the widths come with the weights); returns (n, 1)."""
-    x = _t(x_nhwc).permute(0, 3, 1, 2)
+    narrower blocks -- the widths come with the weights); returns (n, 1).  `q` (tests only): applied to every tensor the
+    CUDA path stores in 16 bits (conv / dense outputs and activations, conv weights), e.g. f16_ste -- the fp32 oracle's own
+    sensitivity to storage rounding, from which the adversarial-loss tolerances of the GAN tests are derived."""
+    qq = q if q is not None else (lambda t: t)
+    x = qq(_t(x_nhwc).permute(0, 3, 1, 2))
     for i in range(9):
-        x = conv2d_same(x, *w["discriminator/block_%d/Conv2d" % (i + 1)], stride=1 if i == 0 else 2)
+        k, b = w["discriminator/block_%d/Conv2d" % (i + 1)]
+        x = qq(conv2d_same(x, qq(k), b, stride=1 if i == 0 else 2))
         x = batch_norm(x, *w["discriminator/block_%d/BatchNorm" % (i + 1)], training, stats_out)
-        x = leaky(x, 0.1)
+        x = qq(leaky(x, 0.1))
     x = x.permute(0, 2, 3, 1).reshape(x.shape[0], -1)  # Keras Flatten of an NHWC tensor
     for j in range(2):
         k, b = w["discriminator/final/Dense_%d" % (j + 1)]
-        x = x @ k + b
+        x = qq(x @ k + b)
         x = batch_norm(x, *w["discriminator/final/BatchNorm_%d" % (j + 1)], training, stats_out)
-        x = leaky(x, 0.1)
+        x = qq(leaky(x, 0.1))
     k, b = w["discriminator/final/Dense_3"]
     x = x @ k + b
     return loss_activation(activation, x) if activation in ("sigmoid", "log-sigm", "tanh", "bi-log") else x
@@ -518,7 +522,12 @@ class GanTrainer:
 
     def __init__(self, gen_weights, disc_weights, vgg_weights, content_kind="vgg-mse", rate=1e-3, content_weight=1.0,
                  disc_loss_weight=1e-10, disc_activation="none", share_adam_counter=True, res_block_num=16,
-                 upscale_factor=4, disc_forward=None):
+                 upscale_factor=4, disc_forward=None, frozen_updates_moving=False):
+        # frozen_updates_moving: whether the discriminator's BatchNorm moving statistics follow the training-phase passes.
+        # UNPINNED Keras behaviour (no Keras here): from 2.1.3 on, Layer.updates / Network.updates are [] while `trainable` is
+        # False, the train functions are built at the first train_on_batch, and make_and_compile_gan* leave
+        # discriminator.trainable = False (model.py:1040, 1101) -> False is the default reading; True = pre-2.1.3.
+        self.d_moves = frozen_updates_moving
         self.dfwd = disc_forward or discriminator_simple_512_forward     # or discriminator_sparse_512_forward
         self.g = to_torch(gen_weights, requires_grad=True)
         self.d = to_torch(disc_weights, requires_grad=True)
@@ -538,8 +547,10 @@ class GanTrainer:
         out = self.dfwd(self.d, d_in, self.dact, True, stats)
         loss = wasserstein_loss(_t(d_y).reshape(-1, 1), out)
         loss.backward()
+        self.last_d_grads = {k: [None if t.grad is None else t.grad.detach().clone() for t in ts] for k, ts in self.d.items()}
         self.opt_d.apply(_trainable(self.d, "d"))
-        _apply_moving(self.d, discriminator_bn_names(self.d), stats)
+        if self.d_moves:
+            _apply_moving(self.d, discriminator_bn_names(self.d), stats)
         return float(loss.detach())
 
     def gan_train_on_batch(self, x_lr, y_hr, adv_y):
@@ -555,8 +566,9 @@ class GanTrainer:
                 t.grad = None
         self.opt_g.apply(_trainable(self.g, "g"))
         _apply_moving(self.g, upscaler_bn_names(self.rbn), gstats)
-        # Keras: a frozen model's BatchNormalization still runs in training phase and still updates its moving stats
-        _apply_moving(self.d, discriminator_bn_names(self.d), dstats)
+        # a frozen model's BatchNormalization still normalises with batch statistics (learning phase 1)
+        if self.d_moves:
+            _apply_moving(self.d, discriminator_bn_names(self.d), dstats)
         return [float(total.detach()), float(lc.detach()), float(la.detach())]
 
     def step(self, x_lr, y_hr):
@@ -586,9 +598,11 @@ class Gan2Trainer(GanTrainer):
         f = self.dfwd(self.d, fake, self.dact, True, s2)
         loss, _ = gan_losses(self.family, self.loss_act, r, f)
         loss.backward()
+        self.last_d_grads = {k: [None if t.grad is None else t.grad.detach().clone() for t in ts] for k, ts in self.d.items()}
         self.opt_d.apply(_trainable(self.d, "d"))
-        _apply_moving(self.d, discriminator_bn_names(self.d), s1)
-        _apply_moving(self.d, discriminator_bn_names(self.d), s2)
+        if self.d_moves:
+            _apply_moving(self.d, discriminator_bn_names(self.d), s1)
+            _apply_moving(self.d, discriminator_bn_names(self.d), s2)
         return float(loss.detach())
 
     def gan_train_on_batch2(self, x_lr, real, y_hr):
@@ -605,8 +619,9 @@ class Gan2Trainer(GanTrainer):
                 t.grad = None
         self.opt_g.apply(_trainable(self.g, "g"))
         _apply_moving(self.g, upscaler_bn_names(self.rbn), gstats)
-        _apply_moving(self.d, discriminator_bn_names(self.d), s1)
-        _apply_moving(self.d, discriminator_bn_names(self.d), s2)
+        if self.d_moves:
+            _apply_moving(self.d, discriminator_bn_names(self.d), s1)
+            _apply_moving(self.d, discriminator_bn_names(self.d), s2)
         return [float(total.detach()), float(lc.detach()), float(la.detach())]
 
 

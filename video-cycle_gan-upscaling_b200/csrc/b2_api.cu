@@ -1,5 +1,6 @@
 // b2_api.cu — the extern "C" boundary (include/b2srgan.h): turns layer-level geometry (kernel size, stride,
 // TensorFlow "same" padding, Conv2DTranspose phases) into tap lists for the implicit-GEMM kernels and launches them.
+#include <stddef.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -9,7 +10,7 @@
 using namespace b2;
 
 // CTA-pair (cta_group::2) kernels on/off: A/B switch for tests and profiling (env B2_NO_PAIR=1 starts with them off)
-static int g_pair_kernels = getenv("B2_NO_PAIR") ? 0 : 1;
+static int g_pair_kernels = B2_PROF_ENV("B2_NO_PAIR") ? 0 : 1;
 
 static void fill_epilogue(IgemmParams& p, const b2_epilogue* ep, int Cout) {
     p.scale = ep->scale;
@@ -20,6 +21,8 @@ static void fill_epilogue(IgemmParams& p, const b2_epilogue* ep, int Cout) {
     p.residual = reinterpret_cast<const __nv_bfloat16*>(ep->residual);
     p.gate = ep->gate;
     p.gate_slope = ep->gate_slope;
+    p.stats_part = ep->stats_part;
+    p.stats_rows = 2 * device_sm_count();
     p.out = ep->out;
     p.out_fp32 = ep->out_fp32;
     p.f16 = ep->f16;
@@ -131,6 +134,7 @@ static void convT_phase_taps(IgemmParams& p, int B, int Hout, int Wout, int Cin,
 // nothing (their outputs are zero only through the bias-free epilogue, so callers needing them pre-zero `out`).
 static int run_transposed(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw, int Hout,
                           int Wout, int pbh, int pbw, const b2_epilogue* ep, void* stream, bool direct) {
+    if (ep->stats_part) return set_error("b2_epilogue.stats_part is only honoured by b2_conv2d_fprop");
     ConvIgemmArgs args[4];
     int n = 0;
     bool all = true;
@@ -147,7 +151,7 @@ static int run_transposed(const void* x, int B, int H, int W, int Cin, const voi
         if (a.p.num_taps == 0) return set_error("transposed conv: phase %d has no taps (filter %dx%d)", ph, kh, kw);
         ++n;
     }
-    static const bool no_fuse = getenv("B2_NO_PHASE_FUSION") != nullptr;      // A/B switch for profiling
+    static const bool no_fuse = B2_PROF_ENV("B2_NO_PHASE_FUSION") != nullptr;      // A/B switch for profiling
     if (!direct && !no_fuse && all) {
         // CTA-pair kernel first (half the weight traffic per SM); -2 = its rings do not fit this geometry
         if (g_pair_kernels && conv_phases2_applicable(args, n)) {
@@ -167,7 +171,27 @@ static int run_transposed(const void* x, int B, int H, int W, int Cin, const voi
 extern "C" {
 
 const char* b2_last_error(void) { return last_error(); }
-int b2_version(void) { return 1; }
+int b2_version(void) { return 2; }
+
+int b2_sizeof_epilogue(void) { return int(sizeof(b2_epilogue)); }
+int b2_epilogue_field_count(void) { return 12; }
+int b2_epilogue_field_offset(int field) {
+    switch (field) {
+        case 0: return int(offsetof(b2_epilogue, scale));
+        case 1: return int(offsetof(b2_epilogue, shift));
+        case 2: return int(offsetof(b2_epilogue, alpha));
+        case 3: return int(offsetof(b2_epilogue, act));
+        case 4: return int(offsetof(b2_epilogue, leaky));
+        case 5: return int(offsetof(b2_epilogue, residual));
+        case 6: return int(offsetof(b2_epilogue, out));
+        case 7: return int(offsetof(b2_epilogue, out_fp32));
+        case 8: return int(offsetof(b2_epilogue, f16));
+        case 9: return int(offsetof(b2_epilogue, gate));
+        case 10: return int(offsetof(b2_epilogue, gate_slope));
+        case 11: return int(offsetof(b2_epilogue, stats_part));
+        default: return -1;
+    }
+}
 
 int b2_set_pair_kernels(int enable) {
     const int old = g_pair_kernels;
@@ -236,6 +260,7 @@ int b2_conv2d_wgrad(const void* x, int B, int H, int W, int Cx, const void* dz, 
 int b2_conv2d_fprop_pad(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw, int stride,
                         int pad_h, int pad_w, int OH, int OW, const b2_epilogue* ep, void* stream) {
     if (!x || !w || !ep || !ep->out) return set_error("b2_conv2d_fprop_pad: null pointer");
+    if (ep->stats_part) return set_error("b2_epilogue.stats_part is only honoured by b2_conv2d_fprop");
     if (stride < 1 || stride > 3) return set_error("b2_conv2d_fprop_pad: stride %d unsupported", stride);
     if (OH < 1 || OW < 1) return set_error("b2_conv2d_fprop_pad: empty output %dx%d", OH, OW);
     ConvIgemmArgs a;
@@ -252,6 +277,7 @@ int b2_conv2d_fprop_pad(const void* x, int B, int H, int W, int Cin, const void*
 int b2_conv2d_strided_dgrad(const void* dz, int B, int OH, int OW, int Cout, const void* w, int Cin, int kh, int kw, int stride,
                             int pad_h, int pad_w, int H, int W, const b2_epilogue* ep, void* stream) {
     if (!dz || !w || !ep || !ep->out) return set_error("b2_conv2d_strided_dgrad: null pointer");
+    if (ep->stats_part) return set_error("b2_epilogue.stats_part is only honoured by b2_conv2d_fprop");
     if (stride < 2 || stride > 3) return set_error("b2_conv2d_strided_dgrad: stride %d unsupported", stride);
     if (kh < stride || kw < stride || kh * kw > kMaxTaps)
         return set_error("b2_conv2d_strided_dgrad: filter %dx%d must cover the stride and have at most %d taps", kh, kw, kMaxTaps);
@@ -309,6 +335,7 @@ int b2_conv2d_scatter_fprop(const void* x, int B, int H, int W, int Cin, const v
 int b2_conv2d_direct(const void* x, int B, int H, int W, int Cin, const void* w, int Cout, int kh, int kw, int stride,
                      int transposed, const b2_epilogue* ep, void* stream) {
     if (!x || !w || !ep || !ep->out) return set_error("b2_conv2d_direct: null pointer");
+    if (ep->stats_part) return set_error("b2_epilogue.stats_part is only honoured by b2_conv2d_fprop");
     if (transposed)
         return run_transposed(x, B, H, W, Cin, w, Cout, kh, kw, 2 * H, 2 * W, (kh - 2) / 2, (kw - 2) / 2, ep, stream, true);
     ConvIgemmArgs a;

@@ -240,9 +240,24 @@ static int launch_bn(const CUtensorMap& mapA, const CUtensorMap& mapB, const Ige
     return 0;
 }
 
+static int launch_conv_igemm_nostats(const ConvIgemmArgs& a, cudaStream_t stream);
+
 int launch_conv_igemm(const ConvIgemmArgs& a, cudaStream_t stream) {
-    static const bool no_halo = getenv("B2_NO_HALO") != nullptr;   // A/B switch for profiling the two main loops
-    static const bool no_stack = getenv("B2_NO_STACK") != nullptr;
+    if (!a.p.stats_part) return launch_conv_igemm_nostats(a, stream);
+    // Train-mode BatchNorm statistics of the output: fused into the row-stacked kernel's epilogue where that kernel runs
+    // (the residual trunk), otherwise one statistics pass over the finished tensor -- same contract for the caller.
+    if (a.p.out_fp32 || a.p.out_sy != 1 || a.p.out_sx != 1 || a.p.out_ld != a.p.n_valid)
+        return set_error("conv: BatchNorm statistics need a dense 16-bit output");
+    if (conv_stack_applicable(a)) return launch_conv_stack(a, stream);
+    ConvIgemmArgs b = a;
+    b.p.stats_part = nullptr;
+    if (int rc = launch_conv_igemm_nostats(b, stream)) return rc;
+    return launch_bn_stats_all_rows(a.p.out, long(a.p.B) * a.p.OH * a.p.OW, a.p.n_valid, a.p.f16, a.p.stats_part, stream);
+}
+
+static int launch_conv_igemm_nostats(const ConvIgemmArgs& a, cudaStream_t stream) {
+    static const bool no_halo = B2_PROF_ENV("B2_NO_HALO") != nullptr;   // A/B switch for profiling the two main loops
+    static const bool no_stack = B2_PROF_ENV("B2_NO_STACK") != nullptr;
     if (!no_halo && !no_stack && conv_stack_applicable(a)) return launch_conv_stack(a, stream);
     if (!no_halo && conv_halo_applicable(a)) return launch_conv_halo(a, stream);
     IgemmParams p = a.p;

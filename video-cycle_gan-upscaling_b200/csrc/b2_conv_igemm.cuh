@@ -37,6 +37,8 @@ struct IgemmParams {
     const __nv_bfloat16* residual;  // added after the activation; same geometry as out; may be null
     const void* gate;     // backward of ReLU / LeakyReLU fused into a dgrad: value *= (gate > 0 ? 1 : gate_slope); same
     float gate_slope;     //   geometry and element type as out's 16-bit form; may be null
+    float* stats_part;    // train-mode BatchNorm statistics fused into the epilogue: per-CTA rows [2 * n_valid]; may be null
+    int stats_rows;       //   rows the producer must leave valid (b2_bn_part_rows(); rows beyond the grid are zeroed)
     void* out;
     int out_fp32;  // 1: out is float, 0: out is the 16-bit element type
     int f16;       // 16-bit element type of x / w / residual / out: 0 = bf16, 1 = fp16 (IEEE half)

@@ -341,7 +341,7 @@ int launch_conv_phases(const ConvIgemmArgs* ph, int nph, cudaStream_t stream) {
     const int avail = kPhSmemMax - 1024 - kPhBStages * kPhBBlock - tail_bytes;
     // staging blocks for the TMA-store epilogue: two per epilogue warp if they fit beside the minimum input ring, else one
     const bool can_stage = !p.out_fp32 && !p.gate && !p.residual && p.OH == 2 * p.H && p.OW == 2 * p.W;
-    static const int force_bufs = getenv("B2_PHASES_STAGE_BUFS") ? atoi(getenv("B2_PHASES_STAGE_BUFS")) : -1;
+    static const int force_bufs = B2_PROF_ENV("B2_PHASES_STAGE_BUFS") ? atoi(B2_PROF_ENV("B2_PHASES_STAGE_BUFS")) : -1;
     g.stage_bufs = 0;
     if (can_stage) {
         for (int nb = 2; nb >= 1; --nb)

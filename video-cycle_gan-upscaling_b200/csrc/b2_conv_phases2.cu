@@ -392,8 +392,8 @@ int launch_conv_phases2(const ConvIgemmArgs* ph, int nph, cudaStream_t stream) {
     // staging blocks for the TMA-store epilogue: two per epilogue warp if they fit beside the minimum input ring, else one
     const bool can_stage = !p.out_fp32 && !p.gate && !p.residual && p.OH == 2 * p.H && p.OW == 2 * p.W &&
                            (p.act != ACT_LEAKY || (p.leaky >= 0.f && p.leaky <= 1.f));
-    static const int force_bufs = getenv("B2_PHASES2_STAGE_BUFS") ? atoi(getenv("B2_PHASES2_STAGE_BUFS")) : -1;
-    static const int dbg = getenv("B2_PH2_DEBUG") ? atoi(getenv("B2_PH2_DEBUG")) : 0;
+    static const int force_bufs = B2_PROF_ENV("B2_PHASES2_STAGE_BUFS") ? atoi(B2_PROF_ENV("B2_PHASES2_STAGE_BUFS")) : -1;
+    static const int dbg = B2_PROF_ENV("B2_PH2_DEBUG") ? atoi(B2_PROF_ENV("B2_PH2_DEBUG")) : 0;
     g.dbg = dbg;
     g.stage_bufs = 0;
     if (can_stage) {

@@ -56,20 +56,45 @@ struct StackGeom {
     uint8_t i0[kStackMaxShifts];          //            first weight block of the descending-ky strip
 };
 
+// Sum of v[e] over the 32 lanes of a warp for all 32 elements at once ("reduce-scatter" butterfly: 16 + 8 + 4 + 2 + 1
+// shuffles): on return lane l holds the total of element l in v[0].  A lane with bit b set keeps the upper half.
+__device__ __forceinline__ void warp_reduce_scatter32(float (&v)[32], int lane) {
+#pragma unroll
+    for (int half = 16; half >= 1; half >>= 1) {
+        const bool hi = (lane & half) != 0;
+#pragma unroll
+        for (int i = 0; i < half; ++i) {
+            const float send = hi ? v[i] : v[i + half];
+            const float keep = hi ? v[i + half] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, half);
+        }
+    }
+}
+
 // Epilogue warp main loop.  Eight epilogue warps: warp (quarter, half) owns TMEM lanes [32*quarter, +32) and channels
 // [32*half, +32) of each of the R stacked output pixels of an accumulator row, so two warps per scheduler overlap one
 // another's TMEM-load and global-load latency.  The residual row of block j+1 is prefetched while block j is processed.
 // F16 / ACT are compile-time so the per-element path carries no uniform branches; the j loop stays rolled (a fully
 // unrolled epilogue measured 24 % of its stall samples as instruction-cache misses).
-template <int R, int ACT, int F16>
+// STATS (train-mode BatchNorm statistics fused into the conv that feeds it, b2_epilogue.stats_part): every thread keeps
+// running sums of v and v*v for its 32 channels over all the pixels it stores (fp32 values, before the 16-bit rounding);
+// at the end the lanes of a warp are combined with the reduce-scatter above and lane l leaves channel 32*half + l's
+// (sum, sum of squares) in s_stats[warp][l] for the CTA-level combine at the end of the kernel.  Residual / gate do not
+// occur in front of a BatchNorm, so they are compiled out of this variant.
+template <int R, int ACT, int F16, bool STATS>
 __device__ __forceinline__ void stack_epilogue_loop(const IgemmParams& p, uint32_t tmem_base, uint64_t* tfull, uint64_t* tempty,
                                                     int quarter, int half, int lane, const float* s_scale,
-                                                    const float* s_shift, const float* s_alpha) {
+                                                    const float* s_shift, const float* s_alpha, float2* s_stats) {
     constexpr int kAccCols = 64 * R;
     const int row = quarter * 32 + lane;
     const int r_tx = row % kStackTW, r_g = row / kStackTW;
     const uint32_t sc_a = smem_u32(s_scale + 32 * half), sh_a = smem_u32(s_shift + 32 * half), al_a = smem_u32(s_alpha + 32 * half);
-    const bool has_res = p.residual != nullptr, has_gate = p.gate != nullptr;
+    const bool has_res = !STATS && p.residual != nullptr, has_gate = !STATS && p.gate != nullptr;
+    float st_sum[STATS ? 32 : 1], st_sq[STATS ? 32 : 1];
+    if constexpr (STATS) {
+#pragma unroll
+        for (int e = 0; e < 32; ++e) { st_sum[e] = 0.f; st_sq[e] = 0.f; }
+    }
     const size_t row_pitch = size_t(p.OW) * size_t(p.out_ld);
     int as = 0; uint32_t aph = 0;
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
@@ -156,6 +181,10 @@ __device__ __forceinline__ void stack_epilogue_loop(const IgemmParams& p, uint32
                         v[g * 8 + 2 * e + 1] += f.y;
                     }
             }
+            if constexpr (STATS) {
+#pragma unroll
+                for (int e = 0; e < 32; ++e) { st_sum[e] += v[e]; st_sq[e] = fmaf(v[e], v[e], st_sq[e]); }
+            }
             if (!p.out_fp32) {
                 __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + obase;
 #pragma unroll
@@ -181,18 +210,28 @@ __device__ __forceinline__ void stack_epilogue_loop(const IgemmParams& p, uint32
         if (lane == 0) mbar_arrive(&tempty[as]);
         if (++as == 2) { as = 0; aph ^= 1; }
     }
+    if constexpr (STATS) {
+        __syncwarp();
+        warp_reduce_scatter32(st_sum, lane);
+        warp_reduce_scatter32(st_sq, lane);
+        s_stats[(half * 4 + quarter) * 32 + lane] = make_float2(st_sum[0], st_sq[0]);
+    }
 }
 
 template <int R, int F16>
 __device__ __forceinline__ void stack_epilogue_dispatch(const IgemmParams& p, uint32_t tmem_base, uint64_t* tfull, uint64_t* tempty,
                                                         int quarter, int half, int lane, const float* s_scale,
-                                                        const float* s_shift, const float* s_alpha) {
+                                                        const float* s_shift, const float* s_alpha, float2* s_stats) {
+    if (p.stats_part) {      // only offered for act == none without residual / gate (checked by the launcher)
+        stack_epilogue_loop<R, ACT_NONE, F16, true>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha, s_stats);
+        return;
+    }
     switch (p.act) {
-        case ACT_RELU: stack_epilogue_loop<R, ACT_RELU, F16>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha); break;
-        case ACT_LEAKY: stack_epilogue_loop<R, ACT_LEAKY, F16>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha); break;
-        case ACT_PRELU: stack_epilogue_loop<R, ACT_PRELU, F16>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha); break;
-        case ACT_TANH: stack_epilogue_loop<R, ACT_TANH, F16>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha); break;
-        default: stack_epilogue_loop<R, ACT_NONE, F16>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha); break;
+        case ACT_RELU: stack_epilogue_loop<R, ACT_RELU, F16, false>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha, s_stats); break;
+        case ACT_LEAKY: stack_epilogue_loop<R, ACT_LEAKY, F16, false>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha, s_stats); break;
+        case ACT_PRELU: stack_epilogue_loop<R, ACT_PRELU, F16, false>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha, s_stats); break;
+        case ACT_TANH: stack_epilogue_loop<R, ACT_TANH, F16, false>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha, s_stats); break;
+        default: stack_epilogue_loop<R, ACT_NONE, F16, false>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha, s_stats); break;
     }
 }
 
@@ -221,6 +260,7 @@ conv_stack_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     float* s_scale = reinterpret_cast<float*>(tail + 256);
     float* s_shift = s_scale + 64;
     float* s_alpha = s_shift + 64;
+    float2* s_stats = reinterpret_cast<float2*>(s_alpha + 64);     // [8 epilogue warps][32 lanes] (sum, sum of squares)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int cbs = p.cin >> 6;
@@ -363,8 +403,8 @@ conv_stack_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     } else {
         // ------------------------------------------------------------ epilogue: R output pixels per accumulator row
         const int quarter = warp & 3, half = (warp - 2) >> 2;
-        if (p.f16) stack_epilogue_dispatch<R, 1>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha);
-        else stack_epilogue_dispatch<R, 0>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha);
+        if (p.f16) stack_epilogue_dispatch<R, 1>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha, s_stats);
+        else stack_epilogue_dispatch<R, 0>(p, tmem_base, tfull, tempty, quarter, half, lane, s_scale, s_shift, s_alpha, s_stats);
     }
 
     tc_fence_before();
@@ -372,6 +412,24 @@ conv_stack_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc<kTmemCols>(tmem_base);
+    }
+    if (p.stats_part) {
+        // this CTA's row of partial sums: the four lane-quarter warps of each channel half added in a fixed order; rows
+        // of CTAs that do not exist in this launch (grid < stats_rows) are written as zeros
+        if (threadIdx.x < 64) {
+            const int c = threadIdx.x, hf = c >> 5, l = c & 31;
+            float sm = 0.f, sq = 0.f;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float2 t = s_stats[(hf * 4 + q) * 32 + l];
+                sm += t.x; sq += t.y;
+            }
+            float* rowp = p.stats_part + size_t(blockIdx.x) * 128;
+            rowp[c] = sm;
+            rowp[64 + c] = sq;
+        }
+        for (int r = int(gridDim.x) + int(blockIdx.x); r < p.stats_rows; r += int(gridDim.x))
+            for (int i = threadIdx.x; i < 128; i += kThreads) p.stats_part[size_t(r) * 128 + i] = 0.f;
     }
 }
 
@@ -409,7 +467,7 @@ static int stack_pick_r(const ConvIgemmArgs& a, int kh, int kw, bool* streamed =
             if (long(p.H) * p.W * 100 < covered * 85) continue;
             const int a_block = (((th + kh - 1) * (kStackTW + kw - 1) * 128) + 1023) & ~1023;
             const int b_bytes = pass == 0 ? wbytes + (R - 1) * 8192 : 2 * (kh + R - 1) * 8192;
-            if (b_bytes + 2 * a_block + 2048 > kStackSmemMax) continue;
+            if (b_bytes + 2 * a_block + 4096 > kStackSmemMax) continue;
             if (streamed) *streamed = pass == 1;
             return R;
         }
@@ -419,6 +477,7 @@ static int stack_pick_r(const ConvIgemmArgs& a, int kh, int kw, bool* streamed =
 
 bool conv_stack_applicable(const ConvIgemmArgs& a) {
     const IgemmParams& p = a.p;
+    if (p.stats_part && (p.act != ACT_NONE || p.residual || p.gate || p.out_fp32)) return false;
     if (p.in_mul != 1 || p.n_valid != 64 || p.out_ld != 64 || a.w_rows != 64) return false;
     if (p.out_sy != 1 || p.out_sx != 1 || p.out_oy != 0 || p.out_ox != 0) return false;
     if (a.xC % 64 != 0 || p.cin != a.xC || p.num_taps < 2) return false;
@@ -469,15 +528,15 @@ int launch_conv_stack(const ConvIgemmArgs& a, cudaStream_t stream) {
     g.b_bytes = (g.kh * g.kw * cbs + (R - 1)) * 64 * 128;
     if (streamed) {
         g.slot_bytes = (g.kh + R - 1) * 64 * 128;
-        g.b_slots = (kStackSmemMax - 2048 - 2 * g.a_block) / g.slot_bytes;
+        g.b_slots = (kStackSmemMax - 4096 - 2 * g.a_block) / g.slot_bytes;
         if (g.b_slots > 4) g.b_slots = 4;
         if (g.b_slots > g.kw * cbs) g.b_slots = g.kw * cbs < 2 ? 2 : g.kw * cbs;
         g.b_bytes = g.b_slots * g.slot_bytes;
     }
-    g.a_stages = (kStackSmemMax - 2048 - g.b_bytes) / g.a_block;
+    g.a_stages = (kStackSmemMax - 4096 - g.b_bytes) / g.a_block;
     if (g.a_stages > 4) g.a_stages = 4;
     if (g.a_stages < 2) return set_error("conv_stack: no room for double buffering");
-    const int smem_bytes = g.b_bytes + g.a_stages * g.a_block + 1024 + 1024;
+    const int smem_bytes = g.b_bytes + g.a_stages * g.a_block + 1024 + 3072;   // alignment slack + barriers, epilogue vectors, statistics
     p.TB = 1; p.TH = th; p.TW = kStackTW;
     p.tiles_x = (p.W + kStackTW - 1) / kStackTW;
     p.tiles_y = (p.H + th - 1) / th;

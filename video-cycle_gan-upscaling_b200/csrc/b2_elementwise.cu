@@ -166,7 +166,46 @@ __global__ void f32_to_u8_denorm_kernel(const float* __restrict__ in, uint8_t* _
         out[i] = denorm_u8(in[i]);
 }
 
+// Counts the elements of a 16-bit tensor that sit at the edge of their type: fp16 |x| >= 65504 (what the conv epilogues'
+// cvt.rn.satfinite stores for anything larger), inf or NaN; bf16 inf or NaN.  One atomic per CTA, and only when non-zero.
+__global__ void count_saturated_kernel(const uint4* __restrict__ x, long n8, const uint16_t* __restrict__ tail, int ntail,
+                                       uint32_t limit, unsigned int* __restrict__ count) {
+    unsigned int c = 0;
+    for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < n8; i += long(gridDim.x) * blockDim.x) {
+        const uint4 v = __ldg(x + i);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            c += ((w[e] & 0x7FFFu) >= limit) ? 1u : 0u;
+            c += (((w[e] >> 16) & 0x7FFFu) >= limit) ? 1u : 0u;
+        }
+    }
+    if (blockIdx.x == 0 && int(threadIdx.x) < ntail) c += ((tail[threadIdx.x] & 0x7FFFu) >= limit) ? 1u : 0u;
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    __shared__ unsigned int sh[8];
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned int t = 0;
+        for (int w = 0; w < int(blockDim.x >> 5); ++w) t += sh[w];
+        if (t) atomicAdd(count, t);
+    }
+}
+
 extern "C" {
+
+int b2_count_saturated(const void* x, int64_t n, int f16, unsigned int* count, void* stream) {
+    if (!x || !count) return set_error("b2_count_saturated: null pointer");
+    if (reinterpret_cast<uintptr_t>(x) & 15) return set_error("b2_count_saturated: tensor must be 16-byte aligned");
+    if (n <= 0) return 0;
+    const long n8 = n >> 3;
+    count_saturated_kernel<<<grid_for(n8 > 0 ? n8 : 1, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const uint4*>(x), n8, reinterpret_cast<const uint16_t*>(x) + (n8 << 3), int(n & 7),
+        f16 ? 0x7BFFu : 0x7F80u, count);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error("b2_count_saturated launch: %s", cudaGetErrorString(e));
+    return 0;
+}
 
 int b2_fold_taps(const void* in, int in_fp32, int B, int H, int W, int Cin, int OH, int OW, int stride, int ntaps,
                  const int* dy, const int* dx, void* out, int f16, int out_ld, int out_c0, void* stream) {

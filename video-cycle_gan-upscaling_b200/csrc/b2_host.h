@@ -8,6 +8,15 @@
 
 #include "b2_conv_igemm.cuh"
 
+// A/B switches read from the environment exist only in profiling builds (B2_BUILD_PROFILING=1 python -m upscaler._build ->
+// -DB2_PROFILING, used by tools/): the shipped library reads no environment variables and has no hidden state.
+#ifdef B2_PROFILING
+#include <stdlib.h>
+#define B2_PROF_ENV(name) getenv(name)
+#else
+#define B2_PROF_ENV(name) (static_cast<const char*>(nullptr))
+#endif
+
 namespace b2 {
 
 // Records a printf-style message retrievable through b2_last_error() and returns -1.
@@ -30,6 +39,8 @@ struct ConvIgemmArgs {
 };
 
 int launch_conv_igemm(const ConvIgemmArgs& a, cudaStream_t stream);
+// b2_bn_train.cu: [sum | sum of squares] of a finished [rows][C] 16-bit tensor into all 2 * SM-count rows of `part`.
+int launch_bn_stats_all_rows(const void* x, long rows, int C, int f16, float* part, cudaStream_t stream);
 // CUDA-core cross-check with identical semantics (tests only).
 int launch_conv_direct(const ConvIgemmArgs& a, cudaStream_t stream);
 

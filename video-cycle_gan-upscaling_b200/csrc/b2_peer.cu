@@ -14,55 +14,42 @@
 //      same order on every rank, so all replicas get identical bits.
 // Two parities suffice: a rank reaches epoch e+2 only after every peer has delivered e+1, i.e. has finished reading e.
 #include "b2_host.h"
+#include "b2_peer.cuh"
 
 #include <string.h>
 
 namespace {
 
 using b2::set_error;
+using b2::kPeerMaxElems;
+using b2::kPeerMaxWorld;
+using b2::kPeerRegionBytes;
 
-constexpr int kPeerMaxWorld = 8;
-constexpr int kPeerMaxElems = 4096;
-constexpr size_t kPeerRegionBytes = size_t(2) * kPeerMaxWorld * kPeerMaxElems * sizeof(uint2);
-
-struct PeerBases {
-    unsigned char* base[kPeerMaxWorld];
-};
-
-__device__ __forceinline__ void st_pair(uint2* p, unsigned v, unsigned flag) {
-    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(v), "r"(flag) : "memory");
-}
-__device__ __forceinline__ uint2 ld_pair(const uint2* p) {
-    uint2 v;
-    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
-    return v;
-}
-
-__global__ void __launch_bounds__(512) peer_allreduce_kernel(float* data, int n, PeerBases peers, int rank, int world,
-                                                              unsigned epoch) {
-    const size_t par = size_t(epoch & 1u) * kPeerMaxWorld * kPeerMaxElems;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        const unsigned v = __float_as_uint(data[i]);
-        for (int p = 1; p <= world; ++p) {                      // peers first, own region last
-            const int q = (rank + p) % world;
-            st_pair(reinterpret_cast<uint2*>(peers.base[q]) + par + size_t(rank) * kPeerMaxElems + i, v, epoch);
-        }
-    }
-    const uint2* mine = reinterpret_cast<const uint2*>(peers.base[rank]) + par;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        float s = 0.f;
-        for (int q = 0; q < world; ++q) {
-            uint2 w;
-            do {
-                w = ld_pair(mine + size_t(q) * kPeerMaxElems + i);
-            } while (w.y != epoch);
-            s += __uint_as_float(w.x);
-        }
-        data[i] = s;
-    }
+__global__ void __launch_bounds__(512) peer_allreduce_kernel(float* data, int n, b2::PeerBases pb) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) b2::peer_put(pb, i, data[i]);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) data[i] = b2::peer_get_sum(pb, i);
 }
 
 }  // namespace
+
+namespace b2 {
+int make_peer_bases(void* const* regions, int rank, int world, unsigned epoch, PeerBases* out) {
+    memset(out, 0, sizeof(*out));
+    out->rank = 0; out->world = 1; out->epoch = epoch;
+    if (!regions || world <= 1) {
+        if (regions && world == 1 && regions[0]) out->base[0] = reinterpret_cast<unsigned char*>(regions[0]);
+        return 0;
+    }
+    if (world > kPeerMaxWorld || rank < 0 || rank >= world)
+        return set_error("peer exchange: rank %d of %d (at most %d peers)", rank, world, kPeerMaxWorld);
+    for (int p = 0; p < world; ++p) {
+        if (!regions[p]) return set_error("peer exchange: region of rank %d is null", p);
+        out->base[p] = reinterpret_cast<unsigned char*>(regions[p]);
+    }
+    out->rank = rank; out->world = world;
+    return 0;
+}
+}  // namespace b2
 
 extern "C" {
 
@@ -107,18 +94,14 @@ int b2_peer_close(void* region, int opened) {
 
 int b2_peer_allreduce_f32(float* data, int n, void* const* regions, int rank, int world, unsigned epoch, void* stream) {
     if (!data || !regions) return set_error("b2_peer_allreduce_f32: null pointer");
-    if (world < 1 || world > kPeerMaxWorld || rank < 0 || rank >= world)
-        return set_error("b2_peer_allreduce_f32: rank %d of %d (at most %d peers)", rank, world, kPeerMaxWorld);
     if (n < 0 || n > kPeerMaxElems) return set_error("b2_peer_allreduce_f32: %d elements exceed %d", n, kPeerMaxElems);
+    b2::PeerBases pb;
+    if (world < 1) return set_error("b2_peer_allreduce_f32: rank %d of %d (at most %d peers)", rank, world, kPeerMaxWorld);
+    if (int rc = b2::make_peer_bases(regions, rank, world, epoch, &pb)) return rc;
+    pb.world = world;      // world == 1 still runs the exchange through the own region (identity; exercised by the tests)
     if (n == 0) return 0;
-    PeerBases pb;
-    memset(&pb, 0, sizeof(pb));
-    for (int p = 0; p < world; ++p) {
-        if (!regions[p]) return set_error("b2_peer_allreduce_f32: region of rank %d is null", p);
-        pb.base[p] = reinterpret_cast<unsigned char*>(regions[p]);
-    }
     const int threads = n >= 512 ? 512 : ((n + 31) / 32) * 32;
-    peer_allreduce_kernel<<<1, threads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(data, n, pb, rank, world, epoch);
+    peer_allreduce_kernel<<<1, threads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(data, n, pb);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("b2_peer_allreduce_f32 launch: %s", cudaGetErrorString(e));
     return 0;

@@ -29,6 +29,7 @@ class Epilogue(ctypes.Structure):
         ("f16", ctypes.c_int),
         ("gate", ctypes.c_void_p),
         ("gate_slope", ctypes.c_float),
+        ("stats_part", ctypes.c_void_p),
     ]
 
 
@@ -37,6 +38,9 @@ _P, _I, _L, _F = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float
 _SIGNATURES = {
     "b2_last_error": (ctypes.c_char_p, []),
     "b2_version": (ctypes.c_int, []),
+    "b2_sizeof_epilogue": (ctypes.c_int, []),
+    "b2_epilogue_field_count": (ctypes.c_int, []),
+    "b2_epilogue_field_offset": (ctypes.c_int, [ctypes.c_int]),
     "b2_set_pair_kernels": (ctypes.c_int, [ctypes.c_int]),
     "b2_conv2d_fprop": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p] + [ctypes.c_int] * 4 +
                         [ctypes.POINTER(Epilogue), ctypes.c_void_p]),
@@ -54,6 +58,7 @@ _SIGNATURES = {
                                       ctypes.c_void_p]),
     "b2_resize_bilinear_into": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 5 + [ctypes.c_void_p] + [ctypes.c_int] * 3 + [ctypes.c_void_p]),
     "b2_u8_to_f32_norm": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
+    "b2_count_saturated": (ctypes.c_int, [_P, _L, _I, _P, _P]),
     "b2_f32_to_u8_denorm": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
     # ---- training step
     "b2_conv2d_s2_dgrad": (ctypes.c_int, [_P] + [_I] * 4 + [_P] + [_I] * 5 + [ctypes.POINTER(Epilogue), _P]),
@@ -67,6 +72,14 @@ _SIGNATURES = {
     "b2_affine_act": (ctypes.c_int, [_P, _L, _I, _I, _P, _P, _P, _I, _F, _P, _P, _P]),
     "b2_bn_bwd_reduce": (ctypes.c_int, [_P, _P, _L, _I, _I, _P, _P, _P, _I, _F, _P, _P, _P, _P, _P, _P]),
     "b2_bn_bwd_apply": (ctypes.c_int, [_P, _P, _L, _I, _I, _P, _P, _P, _I, _F, _P, _P, _P, _P, _F, _P, _P]),
+    "b2_sm_count": (ctypes.c_int, []),
+    "b2_bn_part_rows": (ctypes.c_int, []),
+    "b2_bn_stats_partial": (ctypes.c_int, [_P, _L, _I, _I, _P, ctypes.POINTER(ctypes.c_int), _P]),
+    "b2_bn_fwd_finalize": (ctypes.c_int, [_P, _I, _I, _F, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _P, _P, _P, _F, _F,
+                                          _P, _P, _P, _P]),
+    "b2_bn_bwd_partial": (ctypes.c_int, [_P, _P, _L, _I, _I, _P, _P, _I, _F, _P, ctypes.POINTER(ctypes.c_int), _P]),
+    "b2_bn_bwd_finalize": (ctypes.c_int, [_P, _I, _I, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _P, _P, _P, _P, _P,
+                                          _F, _P]),
     "b2_maxpool2x2": (ctypes.c_int, [_P, _I, _I, _I, _I, _I, _P, _P]),
     "b2_maxpool2x2_bwd": (ctypes.c_int, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
     "b2_loss_pair": (ctypes.c_int, [_P, _P, _L, _I, _I, _F, _F, _P, _P, _P]),
@@ -133,7 +146,7 @@ def stream_ptr():
 
 
 def make_epilogue(out, scale=None, shift=None, alpha=None, act=ACT_NONE, leaky=0.0, residual=None, f16=0, gate=None,
-                  gate_slope=0.0):
+                  gate_slope=0.0, stats_part=None):
     import torch
     ep = Epilogue()
     ep.scale = scale.data_ptr() if scale is not None else None
@@ -147,4 +160,5 @@ def make_epilogue(out, scale=None, shift=None, alpha=None, act=ACT_NONE, leaky=0
     ep.f16 = int(f16)
     ep.gate = gate.data_ptr() if gate is not None else None
     ep.gate_slope = gate_slope
+    ep.stats_part = stats_part.data_ptr() if stats_part is not None else None
     return ep

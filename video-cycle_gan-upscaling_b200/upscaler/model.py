@@ -34,6 +34,44 @@ def make_upscaler_skip_con(output_image_shape, kernel_size=5, filters=64, upscal
     return Model(net=net, input_shape=(h // upscale_factor, w // upscale_factor, c), name="model_1")
 
 
+def _not_built(name, lines):
+    raise NotImplementedError(
+        "%s (reference upscaling/upscaler/model.py:%s) is not built on the B200 path yet; the generators that run are "
+        "make_upscaler_orig and make_upscaler_skip_con (SURVEY.md 8f-3 lists the rest as next)" % (name, lines))
+
+
+def make_upscaler_unetish(output_image_shape, kernel_size=5, upscale_factor=4, step_size=4, downscale_times=5,
+                          initial_step_filter_count=32, dropout_rate=0.1):
+    """model.py:563-636 (U-Net-ish generator with Dropout / Cropping2D / Concatenate).  Importable so that the reference
+    scripts start (train.py:5, train_gan3.py:4); raises when called."""
+    _not_built("make_upscaler_unetish", "563-636")
+
+
+def make_upscaler_unetish_add(output_image_shape, kernel_size=5, upscale_factor=4, step_size=4, downscale_times=5,
+                              initial_step_filter_count=48, dropout_rate=0.1):
+    """model.py:642-722; raises when called."""
+    _not_built("make_upscaler_unetish_add", "642-722")
+
+
+def make_upscaler_unetish_complex(output_image_shape, kernel_size=5, upscale_factor=4, step_size=4, downscale_times=3,
+                                  initial_step_filter_count=32, dropout_rate=0.1):
+    """model.py:748-832; raises when called."""
+    _not_built("make_upscaler_unetish_complex", "748-832")
+
+
+def make_upscaler_attention(output_image_shape, kernel_size=5, filters=64, upscale_factor=4, res_block_num=16):
+    """model.py:296-328 (sigmoid-gated residual blocks, atanh skip, Conv2DTranspose with kernel scale+1 / stride scale);
+    raises when called."""
+    _not_built("make_upscaler_attention", "296-328")
+
+
+def make_upscaler_incep_resnet(output_image_shape, filters=64, upscale_factor=4, a_block_type='3path', a_block_num=5,
+                               a_block_kernel=3, b_block_type='2path', b_block_num=10, b_block_kernel=7,
+                               c_block_type='2path', c_block_num=5, c_block_kernel=3):
+    """model.py:445-497 (inception-style residual blocks with 1x1, 1xk, kx1 convs); raises when called."""
+    _not_built("make_upscaler_incep_resnet", "445-497")
+
+
 def make_discriminator_simple_512(input_shape, activation='none'):
     """model.py:836-896 — 9 conv-BN-LeakyReLU(0.1) blocks (s1 then 8 x s2), Flatten, Dense 1024/32/1."""
     net = networks.DiscriminatorSimple512Net(tuple(input_shape), activation=activation)

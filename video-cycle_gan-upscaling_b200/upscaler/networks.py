@@ -19,6 +19,11 @@ import torch
 
 from . import ops
 
+# 16-bit storage type of the TRAINING passes of the generator and the discriminators (activations, packed weights and
+# gradients; every kernel takes the element type per call).  fp16 keeps 11 significand bits against bf16's 8; its narrow
+# range is handled by carrying the gradients multiplied by a power-of-two-free scale chosen per step (training.py).
+TRAIN_DTYPE = torch.bfloat16
+
 BN_EPS = 1e-3       # keras BatchNormalization defaults, model.py:20
 BN_MOMENTUM = 0.99
 ALIGN = 64          # floats; keeps every tensor (and its gradient) 256-byte aligned inside the flat buffers
@@ -304,40 +309,54 @@ class Net:
             raise RuntimeError("this network runs on hand-written sm_100a kernels only; no CUDA device is available")
 
     # ---------------------------------------------------------------- train-mode BatchNormalization helpers
-    def _bn_forward(self, tape, key, bn_name, z, out, act, alpha=None, leaky=0.0, residual=None, sync=None):
-        """Batch statistics of z (+ optional cross-replica sum), moving-stat update, out = act(BN(z)) + residual."""
+    def _bn_forward(self, tape, key, bn_name, z, out, act, alpha=None, leaky=0.0, residual=None, sync=None, stats=None,
+                    update_moving=True):
+        """Batch statistics of z (+ the other replicas' when `sync` is given), moving-statistics update,
+        out = act(BN(z)) + residual.  `stats` = (part, nparts) when the kernel that produced z already wrote the partial
+        sums (conv epilogue).  The statistics vectors are allocated per call and owned by the tape: a second forward
+        through the same layer before the first one's backward (real / fake batches, train_gan3.py:353) keeps its own."""
         C = z.shape[-1]
-        st = self._vec("st/" + key, 2 * C, zero=True)
-        ops.colstats(z, st[:C], st[C:])
         rows = z.numel() // C
-        if sync is not None:
-            rows = sync(st, rows)
-        aff = self._vec("aff/" + key, 4 * C)
-        scale, shift, mean, invstd = aff[:C], aff[C:2 * C], aff[2 * C:3 * C], aff[3 * C:]
+        part, nparts = stats if stats is not None else ops.bn_stats_partial(z)
+        aff = torch.empty(4 * C, dtype=torch.float32, device=z.device)       # scale | shift | mean | invstd
         gamma, beta, mm, mv = self.weights[bn_name]
-        ops.bn_finalize(st[:C], st[C:], rows, gamma, beta, scale, shift, mean, invstd, mm, mv, BN_EPS, BN_MOMENTUM)
-        ops.affine_act(z, out, scale, shift, alpha, act, leaky, residual)
-        tape[key] = (z, scale, shift, mean, invstd, rows)
+        if not update_moving:
+            mm = mv = None
+        world = sync.world if sync is not None else 1
+        peer = sync.peer_for(z.device) if sync is not None else None
+        if sync is None or peer is not None:
+            ops.bn_fwd_finalize(part, nparts, C, rows * world, gamma, beta, aff, mm, mv, peer=peer, eps=BN_EPS, momentum=BN_MOMENTUM)
+        else:                   # replicas that cannot map each other's memory: sums over NCCL, two stage-2 launches
+            sums = torch.empty(2 * C, dtype=torch.float32, device=z.device)
+            ops.bn_fwd_finalize(part, nparts, C, rows, None, None, None, sums_out=sums)
+            sync.all_reduce(sums)
+            ops.bn_fwd_finalize(sums, 1, C, rows * world, gamma, beta, aff, mm, mv, eps=BN_EPS, momentum=BN_MOMENTUM)
+        ops.affine_act(z, out, aff[:C], aff[C:2 * C], alpha, act, leaky, residual)
+        tape[key] = (z, aff, rows * world)
         return out
 
-    def _bn_backward(self, tape, key, bn_name, g, dz, act, alpha=None, leaky=0.0, dalpha=None, sync=None, want_param_grads=True):
-        """g = gradient w.r.t. act(BN(z)); writes dgamma / dbeta (and dalpha) into the gradient views, returns dz."""
-        z, scale, shift, mean, invstd, rows = tape[key]
+    def _bn_backward(self, tape, key, bn_name, g, dz, act, alpha=None, leaky=0.0, dalpha=None, sync=None, want_param_grads=True,
+                     stats=None):
+        """g = gradient w.r.t. act(BN(z)); ACCUMULATES dgamma / dbeta (and dalpha) into the gradient views, returns dz.
+        The two reductions go through a per-call scratch (never through the gradient accumulators), so several backward
+        passes may add into the same gradient buffer."""
+        z, aff, rows = tape[key]
         C = z.shape[-1]
-        if want_param_grads and sync is None:
-            s2, s1 = self.grads[bn_name][0], self.grads[bn_name][1]     # dgamma = sum dy*xhat, dbeta = sum dy
-            da = dalpha
+        part, nparts = stats if stats is not None else ops.bn_bwd_partial(z, g, aff, alpha, act, leaky)
+        sums = torch.empty(2 * C, dtype=torch.float32, device=z.device)
+        dgamma, dbeta = (self.grads[bn_name][0], self.grads[bn_name][1]) if want_param_grads else (None, None)
+        da = dalpha if want_param_grads else None
+        world = sync.world if sync is not None else 1
+        peer = sync.peer_for(z.device) if sync is not None else None
+        # dgamma / dbeta come from sums over ALL replicas; the final gradient all-reduce sums the replicas again: 1/world
+        if sync is None or peer is not None:
+            ops.bn_bwd_finalize(part, nparts, C, sums, dgamma, dbeta, da, 1.0 / world, peer=peer)
         else:
-            tmp = self._vec("bwd/" + key, 2 * C, zero=True)
-            s1, s2, da = tmp[:C], tmp[C:], (dalpha if want_param_grads else None)
-        ops.bn_bwd_reduce(z, g, scale, shift, alpha, act, leaky, mean, invstd, s1, s2, da)
-        if sync is not None:
-            world = sync(tmp, None)
-            if want_param_grads:
-                # the final gradient all-reduce sums over replicas: hand it 1/world of the global sums
-                ops.cast_scale(s2, self.grads[bn_name][0], 1.0 / world)
-                ops.cast_scale(s1, self.grads[bn_name][1], 1.0 / world)
-        ops.bn_bwd_apply(z, g, scale, shift, alpha, act, leaky, mean, invstd, s1, s2, rows, dz)
+            raw = torch.empty(3 * C, dtype=torch.float32, device=z.device)
+            ops.bn_bwd_finalize(part, nparts, C, None, raw_out=raw)
+            sync.all_reduce(raw[:2 * C])
+            ops.bn_bwd_finalize(raw, 1, C, sums, dgamma, dbeta, da, 1.0 / world)
+        ops.bn_bwd_apply(z, g, aff[:C], aff[C:2 * C], alpha, act, leaky, aff[2 * C:3 * C], aff[3 * C:], sums[:C], sums[C:], rows, dz)
         return dz
 
 
@@ -347,13 +366,19 @@ class UpscalerOrigNet(Net):
 
     input_name = "initial/input"
     writes_out = True      # forward_infer(x, out=...) writes its result into a caller-provided tensor (engine.predict)
+    # Saturation guard of the fp16 inference path: the conv epilogues store with a saturating conversion (+-65504), so the
+    # FIRST forward pass after every weight change (and any pass with check_saturation=True) counts, layer by layer, the
+    # stored activations that sit at that edge.  A non-zero count is never silent: "fallback" warns, switches this
+    # network's inference storage to bf16 (fp32's range, 3 fewer significand bits) and reruns the batch; "raise" raises
+    # FloatingPointError.  `saturation_report` keeps the last per-layer counts.
+    on_saturation = "fallback"
     extra_layers = [("prefinal/tanh", "add"), ("final/tanh", "activation")]
 
     # graph variant (overridden by UpscalerSkipConNet)
     up_filters, up_kernel, prefinal_kernel, concat_input, supports_training = 256, None, None, False, True
 
     def __init__(self, kernel_size=5, filters=64, upscale_factor=4, res_block_num=16, weights=None, device="cuda",
-                 seed=None, infer_dtype=torch.float16):
+                 seed=None, infer_dtype=torch.float16, train_dtype=None):
         if filters != 64:
             raise ValueError("the B200 path is built for filters=64 (reference default, model.py:267)")
         self.kernel_size, self.filters = kernel_size, filters
@@ -362,12 +387,14 @@ class UpscalerOrigNet(Net):
         # 16-bit storage type of the inference path (activations + packed weights): fp16 keeps 11 significand bits,
         # which is what holds max-abs error under 2e-2 across 37 layers; bf16 is accepted and ~8x noisier.
         self.infer_dtype = infer_dtype
+        self.train_dtype = train_dtype or TRAIN_DTYPE
         self.up_kernel = self.up_kernel or kernel_size
         self.prefinal_kernel = self.prefinal_kernel or kernel_size
         super().__init__(upscaler_orig_layer_specs(kernel_size, filters, upscale_factor, res_block_num, self.up_filters,
                                                    self.up_kernel, self.prefinal_kernel, self.concat_input), weights, seed, device)
         self._infer = {}
         self._final_rows = False
+        self._sat_pending, self.saturation_report = True, {}
         self._build_index_maps()
         if self.on_gpu:
             self.refresh()
@@ -433,6 +460,7 @@ class UpscalerOrigNet(Net):
             setattr(self, "_%s_dirty" % s, False)
         if "infer" not in sets:
             return
+        self._sat_pending = True
         w = self.weights
         nfold = 2 * self.res_block_num + 1
         fold = self._vec("fold", 2 * 64 * nfold)
@@ -472,48 +500,106 @@ class UpscalerOrigNet(Net):
         return (None if h is None else h * f, None if w is None else w * f, 3)
 
     # ---------------------------------------------------------------- inference
-    def forward_infer(self, x, out=None):
+    def forward_infer(self, x, out=None, check_saturation=None):
         """x: (B,H,W,3) float32 CUDA in [-1,1] -> (B, H*f, W*f, 3) float32.  BatchNorm uses moving statistics folded
-        into the conv epilogues (Keras learning_phase=0, i.e. Model.predict)."""
+        into the conv epilogues (Keras learning_phase=0, i.e. Model.predict).  `check_saturation`: None = only on the
+        first pass after a weight change; see `on_saturation`."""
         self._need_gpu()
         if getattr(self, "_infer_dirty", False):     # fp32 masters changed (training step / set_weights)
             self.refresh(("infer",))
         B, H, W, C = x.shape
         if C != 3 or x.dtype != torch.float32:
             raise ValueError("expected (B,H,W,3) float32 input, got %s %s" % (tuple(x.shape), x.dtype))
+        check = self._sat_pending if check_saturation is None else bool(check_saturation)
+        counters = self._sat_counters(check)
+        y = self._forward_infer(x, out, counters)
+        if check:
+            counts = counters.cpu().numpy()          # the one host read of a checked pass
+            self._sat_pending = False
+            self.saturation_report = {n: int(c) for n, c in zip(self._sat_names(), counts) if c}
+            if self.saturation_report:
+                msg = ("%s: %d stored activations reached the edge of %s in %s (first layer: %s)" % (
+                    type(self).__name__, int(counts.sum()), str(self.infer_dtype).replace("torch.", ""),
+                    "%d layers" % len(self.saturation_report), next(iter(self.saturation_report))))
+                if self.on_saturation == "raise" or self.infer_dtype != torch.float16:
+                    raise FloatingPointError(msg)
+                import warnings
+                warnings.warn(msg + "; switching this network's inference storage to bfloat16 and rerunning", RuntimeWarning)
+                self.set_infer_dtype(torch.bfloat16)
+                return self.forward_infer(x, out, check_saturation=True)
+        return y
+
+    def set_infer_dtype(self, dtype):
+        """Switches the 16-bit storage type of the inference path (activations + packed weights)."""
+        if dtype not in (torch.float16, torch.bfloat16):
+            raise ValueError("inference storage is float16 or bfloat16")
+        self.infer_dtype = dtype
+        ps = self._pack_sets["infer"]
+        ps["dtype"], ps["buf"] = dtype, None
+        if self.on_gpu:
+            self.refresh(("infer",))
+
+    def _sat_names(self):
+        names = ["initial/conv"]
+        for i in range(self.res_block_num):
+            names += ["res_block/%d/conv_pre" % i, "res_block/%d/conv_post" % i]
+        names.append("prefinal/conv2d")
+        names += ["upscaling/%d/block/conv_transp" % i for i in range(self.upscale_times)]
+        return names
+
+    def _sat_counters(self, check):
+        if not check:
+            return None
+        c = self._buffers.get("sat_counters")
+        n = len(self._sat_names())
+        if c is None or c.numel() != n:
+            c = self._buffers["sat_counters"] = torch.zeros(n, dtype=torch.int32, device=self.device)
+        else:
+            c.zero_()
+        return c
+
+    def _forward_infer(self, x, out, counters):
+        B, H, W, C = x.shape
         k, f, dt = self.kernel_size, self.filters, self.infer_dtype
         inf, pk = self._infer, self._packed["infer"]
+        slot = [0]
+
+        def chk(t):          # saturation guard: count this layer's stored activations at the edge of the 16-bit type
+            if counters is not None:
+                ops.count_saturated(t, counters[slot[0]:slot[0] + 1])
+                slot[0] += 1
+            return t
         # head: fold the 9 horizontal taps of the 3-channel input into 27 (of 64) channels, then a 9x1 conv
         T = self._timed
         xp = T("initial/fold", lambda: ops.fold_taps(x, [(0, dx - 4) for dx in range(9)],
                                                      out=self._buf("fold", (B, H, W, 64), dt), dtype=dt))
         s, b, a = inf["initial/conv"]
-        skip = T("initial/conv", lambda: ops.conv2d(xp, pk["initial/conv"], f, 9, 1,
-                                                    out=self._buf("skip", (B, H, W, f), dt), scale=s, shift=b, alpha=a,
-                                                    act=ops.ACT_PRELU))
+        skip = chk(T("initial/conv", lambda: ops.conv2d(xp, pk["initial/conv"], f, 9, 1,
+                                                        out=self._buf("skip", (B, H, W, f), dt), scale=s, shift=b, alpha=a,
+                                                        act=ops.ACT_PRELU)))
         m = skip
         ping = [self._buf("t%d" % i, (B, H, W, f), dt) for i in range(3)]
         for i in range(self.res_block_num):
             n = "res_block/%d" % i
             free = [t for t in ping if t is not m]
             s, b, a = inf[n + "/conv_pre"]
-            h = T("res_block/*/conv_pre", lambda: ops.conv2d(m, pk[n + "/conv_pre"], f, k, k, out=free[0], scale=s, shift=b,
-                                                             alpha=a, act=ops.ACT_PRELU))
+            h = chk(T("res_block/*/conv_pre", lambda: ops.conv2d(m, pk[n + "/conv_pre"], f, k, k, out=free[0], scale=s, shift=b,
+                                                                 alpha=a, act=ops.ACT_PRELU)))
             s, b, _ = inf[n + "/conv_post"]
-            m = T("res_block/*/conv_post", lambda: ops.conv2d(h, pk[n + "/conv_post"], f, k, k, out=free[1], scale=s,
-                                                              shift=b, residual=m))
+            m = chk(T("res_block/*/conv_post", lambda: ops.conv2d(h, pk[n + "/conv_post"], f, k, k, out=free[1], scale=s,
+                                                                  shift=b, residual=m)))
         free = [t for t in ping if t is not m]
         s, b, _ = inf["prefinal/conv2d"]
         kp, ku = self.prefinal_kernel, self.up_kernel
         upc = -(-self.up_filters // 64) * 64           # 224 -> 256: padded channels carry zeros
-        m = T("prefinal/conv2d", lambda: ops.conv2d(m, pk["prefinal/conv2d"], 64, kp, kp, out=free[0], scale=s, shift=b,
-                                                    residual=skip))
+        m = chk(T("prefinal/conv2d", lambda: ops.conv2d(m, pk["prefinal/conv2d"], 64, kp, kp, out=free[0], scale=s, shift=b,
+                                                        residual=skip)))
         h, w_ = H, W
         for i in range(self.upscale_times):
             n = "upscaling/%d/block/conv_transp" % i
             _, b, _ = inf[n]
             ob = self._buf("up%d" % i, (B, 2 * h, 2 * w_, upc), dt)
-            m = T(n, lambda: ops.conv2d_transpose_s2(m, pk[n], upc, ku, ku, out=ob, shift=b, act=ops.ACT_LEAKY, leaky=0.2))
+            m = chk(T(n, lambda: ops.conv2d_transpose_s2(m, pk[n], upc, ku, ku, out=ob, shift=b, act=ops.ACT_LEAKY, leaky=0.2)))
             h, w_ = 2 * h, 2 * w_
         if self.concat_input:      # Concatenate([bilinear-resized input, features]) = three of the padding channels
             T("final/resize_input", lambda: ops.resize_bilinear_into(x, m, self.up_filters, 2 ** self.upscale_times))
@@ -525,12 +611,10 @@ class UpscalerOrigNet(Net):
         return T("final/conv", lambda: ops.conv2d(m, pk["final/conv"], 3, 9, 9, out=out, shift=b, act=ops.ACT_TANH))
 
     # ---------------------------------------------------------------- training
-    def forward_train(self, x, sync=None):
+    def forward_train(self, x, sync=None, update_moving=True):
         """Training-phase forward (BatchNorm on batch statistics, moving statistics updated).  Returns
         (y fp32 (B,4H,4W,3), tape).  Packed 'train' weights must be current (refresh(('train',)))."""
         self._need_gpu()
-        if not self.supports_training:
-            raise NotImplementedError("%s: inference only on the B200 path so far (training covers make_upscaler_orig)" % type(self).__name__)
         if not self._final_rows:
             raise RuntimeError("training needs the row-streaming final conv (Cin <= 256)")
         B, H, W, _ = x.shape
@@ -546,18 +630,24 @@ class UpscalerOrigNet(Net):
         m = skip
         for i in range(self.res_block_num):
             n = "res_block/%d" % i
-            z1 = ops.conv2d(m, pk[n + "/conv_pre"], f, k, k, out=new((B, H, W, f)), shift=w[n + "/conv_pre"][1])
+            # the BatchNorm statistics of each conv output come out of the conv's own epilogue (stats_part): no extra pass
+            st1 = ops.new_stats_part(f, self.device)
+            z1 = ops.conv2d(m, pk[n + "/conv_pre"], f, k, k, out=new((B, H, W, f)), shift=w[n + "/conv_pre"][1], stats_part=st1[0])
             h = self._bn_forward(tape, n + "/pre", n + "/batch_norm_pre", z1, new((B, H, W, f)), ops.ACT_PRELU,
-                                 alpha=w[n + "/prelu"][0].reshape(-1), sync=sync)
-            z2 = ops.conv2d(h, pk[n + "/conv_post"], f, k, k, out=new((B, H, W, f)), shift=w[n + "/conv_post"][1])
+                                 alpha=w[n + "/prelu"][0].reshape(-1), sync=sync, update_moving=update_moving, stats=st1)
+            st2 = ops.new_stats_part(f, self.device)
+            z2 = ops.conv2d(h, pk[n + "/conv_post"], f, k, k, out=new((B, H, W, f)), shift=w[n + "/conv_post"][1], stats_part=st2[0])
             mo = self._bn_forward(tape, n + "/post", n + "/batch_norm_post", z2, new((B, H, W, f)), ops.ACT_NONE, residual=m,
-                                  sync=sync)
+                                  sync=sync, update_moving=update_moving, stats=st2)
             tape[n] = (m, h)
             m = mo
         kp, ku = self.prefinal_kernel, self.up_kernel
         upc = -(-self.up_filters // 64) * 64
-        zp = ops.conv2d(m, pk["prefinal/conv2d"], 64, kp, kp, out=new((B, H, W, 64)), shift=w["prefinal/conv2d"][1])
-        t = self._bn_forward(tape, "prefinal", "prefinal/batch_norm", zp, new((B, H, W, 64)), ops.ACT_NONE, residual=skip, sync=sync)
+        stp = ops.new_stats_part(64, self.device)
+        zp = ops.conv2d(m, pk["prefinal/conv2d"], 64, kp, kp, out=new((B, H, W, 64)), shift=w["prefinal/conv2d"][1],
+                        stats_part=stp[0])
+        t = self._bn_forward(tape, "prefinal", "prefinal/batch_norm", zp, new((B, H, W, 64)), ops.ACT_NONE, residual=skip, sync=sync,
+                             update_moving=update_moving, stats=stp)
         tape["prefinal/in"] = m
         ups, h_, w_ = [t], H, W
         for i in range(self.upscale_times):
@@ -770,8 +860,7 @@ class DiscriminatorSimple512Net(Net):
     def __init__(self, input_shape, activation="none", weights=None, device="cuda", seed=None, dtype=None):
         self.input_shape = tuple(input_shape)
         self.activation = activation
-        if dtype is not None:       # fp16 storage is offered for numerics checks; bf16 (default) has the range a
-            self.train_dtype = dtype  # diverging Wasserstein critic needs (gan_test.ipynb cell 17: |D| up to 2e11)
+        self.train_dtype = dtype or TRAIN_DTYPE
         specs = self._layer_specs()
         super().__init__(specs, weights, seed, device)
         self.extra_layers = [("discriminator/final/Flatten", "flatten")]
@@ -811,27 +900,28 @@ class DiscriminatorSimple512Net(Net):
     def output_shape_for(self, input_shape):
         return (1,)
 
-    def _bn_act(self, tape, bn_name, z, training, sync):
+    def _bn_act(self, tape, bn_name, z, training, sync, update_moving=True):
         """BatchNormalization + LeakyReLU(0.1): batch statistics when training, moving statistics otherwise."""
         out = torch.empty_like(z)
         if training:
-            return self._bn_forward(tape, bn_name, bn_name, z, out, ops.ACT_LEAKY, leaky=0.1, sync=sync)
+            return self._bn_forward(tape, bn_name, bn_name, z, out, ops.ACT_LEAKY, leaky=0.1, sync=sync,
+                                    update_moving=update_moving)
         C = z.shape[-1]
         aff = self._vec("aff/" + bn_name, 4 * C)
         g, b, mm, mv = self.weights[bn_name]
         ops.bn_fold(g, b, mm, mv, None, aff[:C], aff[C:2 * C], BN_EPS)
         return ops.affine_act(z, out, aff[:C], aff[C:2 * C], None, ops.ACT_LEAKY, 0.1)
 
-    def forward(self, x, training, sync=None):
-        """x: (n,H,W,3) fp32 -> ((n,1) fp32 scores, tape).  training=True normalises with batch statistics (and updates
-        the moving ones, as Keras does even for a frozen discriminator inside the GAN model); False = Model.predict."""
+    def forward(self, x, training, sync=None, update_moving=True):
+        """x: (n,H,W,3) fp32 -> ((n,1) fp32 scores, tape).  training=True normalises with batch statistics and, when
+        `update_moving`, moves the moving ones (training.py decides that per compiled model); False = Model.predict."""
         self._need_gpu()
         dt, pk, w = self.train_dtype, self._packed["train"], self.weights
         n = x.shape[0]
         if tuple(x.shape[1:]) != self.input_shape:
             raise ValueError("discriminator expects input %s, got %s" % (self.input_shape, tuple(x.shape[1:])))
         tape = {}
-        a = self._conv_forward(x, tape, training, sync)
+        a = self._conv_forward(x, tape, training, sync, update_moving)
         a = a.reshape(n, -1)                                   # Keras Flatten of an NHWC tensor
         dins = []
         for j, (name, c) in enumerate(self._dense):
@@ -839,14 +929,14 @@ class DiscriminatorSimple512Net(Net):
             last = j == len(self._dense) - 1
             z = ops.dense_fwd(a, w[name][0], w[name][1],
                               torch.empty((n, c["cout"]), dtype=torch.float32 if last else dt, device=self.device))
-            a = z if last else self._bn_act(tape, "discriminator/final/BatchNorm_%d" % (j + 1), z, training, sync)
+            a = z if last else self._bn_act(tape, "discriminator/final/BatchNorm_%d" % (j + 1), z, training, sync, update_moving)
         tape["dins"] = dins
         if self.activation in ops.SCORE_ACTS:                   # model.py:885-892; any other string: no output layer
             tape["score_pre"] = a
             a = ops.score_act(a, self.activation)
         return a, tape
 
-    def _conv_forward(self, x, tape, training, sync):
+    def _conv_forward(self, x, tape, training, sync, update_moving=True):
         """The convolutional blocks: block_1 with all nine taps folded into channels, then 3x3 'same' convs."""
         dt, pk, w = self.train_dtype, self._packed["train"], self.weights
         taps = [(ky - 1, kx - 1) for ky in range(3) for kx in range(3)]
@@ -856,17 +946,25 @@ class DiscriminatorSimple512Net(Net):
             kk = 1 if bi == 0 else 3
             ins.append(a)
             z = ops.conv2d(a, pk[name], c["cout"], kk, kk, stride=c["stride"], shift=w[name][1])
-            a = self._bn_act(tape, name.replace("Conv2d", "BatchNorm"), z, training, sync)
+            a = self._bn_act(tape, name.replace("Conv2d", "BatchNorm"), z, training, sync, update_moving)
         tape["ins"] = ins
         return a
 
     def forward_infer(self, x, out=None):
         return self.forward(x, False)[0]
 
-    def backward(self, tape, dscore, want_wgrad=True, want_input_grad=False, sync=None, on_ready=None):
+    def backward(self, tape, dscore, want_wgrad=True, want_input_grad=False, sync=None, on_ready=None, grad_scale=1.0):
         """dscore: (n,1) fp32 gradient w.r.t. the scores.  Accumulates weight gradients unless the discriminator is
         frozen (gan_train, model.py:1040); returns the gradient w.r.t. the input image (fp32) when asked.
-        `on_ready(offset)`: see UpscalerOrigNet.backward (the dense head, most of the parameters, is ready first)."""
+        `on_ready(offset)`: see UpscalerOrigNet.backward (the dense head, most of the parameters, is ready first).
+        `grad_scale`: dscore carries this factor on top of the step's scale (fp16 range inside a frozen discriminator whose
+        adversarial weight is tiny, train_gan.py -dw 1e-10); it is divided out of the returned image gradient in fp32."""
+        if want_wgrad and grad_scale != 1.0:
+            raise ValueError("an internal gradient scale is only supported for a frozen discriminator")
+        self._inv_gscale = None
+        if grad_scale != 1.0:
+            self._inv_gscale = self._vec("inv_gscale", 64)
+            self._inv_gscale.fill_(1.0 / grad_scale)
         ready = on_ready if (on_ready is not None and want_wgrad) else (lambda off: None)
         dt, pk, w = self.train_dtype, self._packed["train"], self.weights
         if want_wgrad:
@@ -913,7 +1011,7 @@ class DiscriminatorSimple512Net(Net):
                     ops.gather_f32(raw, self._first_wgrad_idx, g[name][0], accumulate=True)
                 ready(0)
                 if want_input_grad:
-                    return ops.conv2d(dz, pk[name + "#dgrad"], c["cin"], 3, 3,
+                    return ops.conv2d(dz, pk[name + "#dgrad"], c["cin"], 3, 3, scale=self._inv_gscale,
                                       out=torch.empty((n, h, w_, c["cin"]), dtype=torch.float32, device=self.device))
         return None
 
@@ -954,7 +1052,7 @@ class DiscriminatorSparse512Net(DiscriminatorSimple512Net):
         c1 = specs[0][2]
         self._first_wgrad_idx = torch.from_numpy(ops.rowfold_wgrad_gather_index(5, 5, c1["cin"], c1["cout"])).to(self.device)
 
-    def _conv_forward(self, x, tape, training, sync):
+    def _conv_forward(self, x, tape, training, sync, update_moving=True):
         dt, pk, w = self.train_dtype, self._packed["train"], self.weights
         H, W = self.input_shape[:2]
         a = ops.fold_taps(x, [(0, kx) for kx in range(5)], out_hw=(H, W - 4), dtype=dt)
@@ -962,7 +1060,7 @@ class DiscriminatorSparse512Net(DiscriminatorSimple512Net):
         for bi, (name, c, _, ohw) in enumerate(self._conv_geom):
             ins.append(a)
             z = ops.conv2d_pad(a, pk[name], c["cout"], 5, 1 if bi == 0 else 5, c["stride"], (0, 0), ohw, shift=w[name][1])
-            a = self._bn_act(tape, name.replace("Conv2d", "BatchNorm"), z, training, sync)
+            a = self._bn_act(tape, name.replace("Conv2d", "BatchNorm"), z, training, sync, update_moving)
         tape["ins"] = ins
         return a
 
@@ -987,6 +1085,6 @@ class DiscriminatorSparse512Net(DiscriminatorSimple512Net):
                     ops.gather_f32(raw, self._first_wgrad_idx, g[name][0], accumulate=True)
                 ready(0)
                 if want_input_grad:
-                    return ops.conv2d_pad(dz, pk[name + "#dgrad"], c["cin"], 5, 5, 1, (4, 4), (h, w_),
+                    return ops.conv2d_pad(dz, pk[name + "#dgrad"], c["cin"], 5, 5, 1, (4, 4), (h, w_), scale=self._inv_gscale,
                                           out=torch.empty((n, h, w_, c["cin"]), dtype=torch.float32, device=self.device))
         return None

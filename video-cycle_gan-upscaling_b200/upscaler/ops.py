@@ -52,8 +52,11 @@ def tf_same_out(size, stride):
 
 
 def conv2d(x, w_packed, cout, kh, kw, stride=1, out=None, out_dtype=None, scale=None, shift=None, alpha=None,
-           act=ACT_NONE, leaky=0.0, residual=None, direct=False, gate=None, gate_slope=0.0):
-    """Conv2D(padding='same') forward (reference: keras Conv2D at model.py:19, 22, 275, 283, 290, 839-871)."""
+           act=ACT_NONE, leaky=0.0, residual=None, direct=False, gate=None, gate_slope=0.0, stats_part=None):
+    """Conv2D(padding='same') forward (reference: keras Conv2D at model.py:19, 22, 275, 283, 290, 839-871).
+    `stats_part` (float32 (bn_part_rows(), 2*cout)): receives the partial per-channel [sum | sum of squares] rows of the
+    output for the train-mode BatchNorm that follows (fused into the epilogue where the kernel supports it); finalize with
+    nparts = bn_part_rows()."""
     B, H, W, Cin = x.shape
     OH, OW = tf_same_out(H, stride), tf_same_out(W, stride)
     f16 = _elem_flag(x, w_packed)
@@ -71,8 +74,10 @@ def conv2d(x, w_packed, cout, kh, kw, stride=1, out=None, out_dtype=None, scale=
         raise ValueError("conv2d: residual must have the activation dtype and the output's shape")
     if gate is not None and (tuple(gate.shape) != tuple(out.shape) or gate.dtype != x.dtype):
         raise ValueError("conv2d: gate must have the activation dtype and the output's shape")
-    _require_cuda(x, w_packed, out, scale, shift, alpha, residual, gate)
-    ep = _lib.make_epilogue(out, scale, shift, alpha, act, leaky, residual, f16, gate, gate_slope)
+    _require_cuda(x, w_packed, out, scale, shift, alpha, residual, gate, stats_part)
+    if stats_part is not None and (stats_part.dtype != torch.float32 or tuple(stats_part.shape) != (bn_part_rows(), 2 * cout)):
+        raise ValueError("conv2d: stats_part must be float32 (%d, %d)" % (bn_part_rows(), 2 * cout))
+    ep = _lib.make_epilogue(out, scale, shift, alpha, act, leaky, residual, f16, gate, gate_slope, stats_part)
     lib = _lib.load()
     if direct:
         rc = lib.b2_conv2d_direct(_lib.ptr(x), B, H, W, Cin, _lib.ptr(w_packed), cout, kh, kw, stride, 0,
@@ -83,6 +88,11 @@ def conv2d(x, w_packed, cout, kh, kw, stride=1, out=None, out_dtype=None, scale=
     _lib.check(rc, "b2_conv2d_fprop")
     _count(1)
     return out
+
+
+def new_stats_part(cout, device):
+    """Scratch for conv2d(..., stats_part=...) -> (tensor, nparts)."""
+    return torch.empty((bn_part_rows(), 2 * cout), dtype=torch.float32, device=device), bn_part_rows()
 
 
 def conv2d_rows(x, w_rows, cout, kh, kw, bias=None, act=ACT_TANH, out=None):
@@ -215,6 +225,18 @@ def f32_to_u8_denorm(x, out=None):
     return out
 
 
+def count_saturated(x, counter):
+    """counter (1-element int32 CUDA tensor) += number of elements of the 16-bit tensor x at the edge of their type
+    (fp16: |x| >= 65504, inf, NaN; bf16: inf, NaN)."""
+    if x.dtype not in (torch.float16, torch.bfloat16) or counter.dtype != torch.int32:
+        raise ValueError("count_saturated expects a 16-bit tensor and an int32 counter")
+    _require_cuda(x, counter)
+    rc = _lib.load().b2_count_saturated(_lib.ptr(x), x.numel(), 1 if x.dtype == torch.float16 else 0, _lib.ptr(counter),
+                                        _lib.stream_ptr())
+    _lib.check(rc, "b2_count_saturated")
+    _count(1)
+
+
 def gather_cast(src, idx, out=None, dtype=torch.bfloat16):
     """out[i] = idx[i] >= 0 ? cast(src.flat[idx[i]]) : 0 — refreshes a packed 16-bit weight copy from fp32 masters."""
     if src.dtype != torch.float32 or idx.dtype != torch.int32:
@@ -258,7 +280,7 @@ def conv2d_s2_dgrad(dz, w_packed_t, cin, kh, kw, in_hw, out=None, gate=None, gat
 
 
 def conv2d_pad(x, w_packed, cout, kh, kw, stride, pad, out_hw, out=None, out_dtype=None, shift=None, gate=None,
-               gate_slope=0.0):
+               gate_slope=0.0, scale=None):
     """Conv2D with explicit zero padding `pad` = (pad_h, pad_w) on an explicit output grid: padding='valid' (pad 0,
     out = (in - k) // stride + 1; make_discriminator_sparse_512, model.py:967-989) or the 'full' correlation (pad k-1)."""
     B, H, W, Cin = x.shape
@@ -268,8 +290,8 @@ def conv2d_pad(x, w_packed, cout, kh, kw, stride, pad, out_hw, out=None, out_dty
         raise ValueError("conv2d_pad: Cin must be a multiple of 64 and the packed weight [Cout][kh*kw*Cin]")
     if out is None:
         out = torch.empty((B, OH, OW, cout), dtype=out_dtype or x.dtype, device=x.device)
-    _require_cuda(x, w_packed, out, shift, gate)
-    ep = _lib.make_epilogue(out, None, shift, None, ACT_NONE, 0.0, None, f16, gate, gate_slope)
+    _require_cuda(x, w_packed, out, shift, gate, scale)
+    ep = _lib.make_epilogue(out, scale, shift, None, ACT_NONE, 0.0, None, f16, gate, gate_slope)
     rc = _lib.load().b2_conv2d_fprop_pad(_lib.ptr(x), B, H, W, Cin, _lib.ptr(w_packed), cout, kh, kw, stride, pad[0], pad[1],
                                          OH, OW, ctypes.byref(ep), _lib.stream_ptr())
     _lib.check(rc, "b2_conv2d_fprop_pad")
@@ -382,6 +404,80 @@ def bn_bwd_apply(z, g, scale, shift, alpha, act, leaky, mean, invstd, s1, s2, co
     _lib.check(rc, "b2_bn_bwd_apply")
     _count(1)
     return dz
+
+
+_bn_rows = None
+
+
+def bn_part_rows():
+    """Rows a stage-1 BatchNorm statistics producer may write (2 per SM)."""
+    global _bn_rows
+    if _bn_rows is None:
+        _bn_rows = int(_lib.load().b2_bn_part_rows())
+    return _bn_rows
+
+
+def sm_count():
+    return int(_lib.load().b2_sm_count())
+
+
+def _peer_args(peer):
+    """(regions, rank, world, epoch) of one exchange on `peer` (upscaler.peer.PeerReducer), or the inactive form."""
+    if peer is None:
+        return None, 0, 1, 0
+    return peer.regions, peer.rank, peer.world, peer.next_epoch()
+
+
+def bn_stats_partial(x, part=None):
+    """Stage 1 of the train-mode BatchNorm statistics: per-CTA partial [sum | sum of squares] rows of x viewed as
+    [rows][C].  Returns (part, nparts)."""
+    rows, C = _rows_c(x)
+    if part is None:
+        part = torch.empty((bn_part_rows(), 2 * C), dtype=torch.float32, device=x.device)
+    _require_cuda(x, part)
+    n = ctypes.c_int(0)
+    rc = _lib.load().b2_bn_stats_partial(_lib.ptr(x), rows, C, _dt(x), _lib.ptr(part), ctypes.byref(n), _lib.stream_ptr())
+    _lib.check(rc, "b2_bn_stats_partial")
+    _count(1)
+    return part, n.value
+
+
+def bn_fwd_finalize(part, nparts, C, count, gamma, beta, aff, moving_mean=None, moving_var=None, peer=None, sums_out=None,
+                    eps=1e-3, momentum=0.99):
+    """Stage 2: partial rows (+ the other replicas' through `peer`) -> aff = [scale | shift | mean | invstd]; updates the
+    moving statistics when given.  aff=None with sums_out: only the summed statistics (NCCL fallback)."""
+    regions, rank, world, epoch = _peer_args(peer)
+    rc = _lib.load().b2_bn_fwd_finalize(_lib.ptr(part), int(nparts), int(C), float(count), regions, rank, world, epoch,
+                                        _lib.ptr(sums_out), _lib.ptr(gamma), _lib.ptr(beta), eps, momentum,
+                                        _lib.ptr(moving_mean), _lib.ptr(moving_var), _lib.ptr(aff), _lib.stream_ptr())
+    _lib.check(rc, "b2_bn_fwd_finalize")
+    _count(1)
+    return aff
+
+
+def bn_bwd_partial(z, g, aff, alpha, act, leaky, part=None):
+    """Stage 1 of the BatchNorm backward sums through act(BN(z)): partial [sum dy | sum dy*xhat | sum g*min(u,0)] rows."""
+    rows, C = _rows_c(z)
+    if part is None:
+        part = torch.empty((bn_part_rows(), 3 * C), dtype=torch.float32, device=z.device)
+    _require_cuda(z, g, aff, part)
+    n = ctypes.c_int(0)
+    rc = _lib.load().b2_bn_bwd_partial(_lib.ptr(z), _lib.ptr(g), rows, C, _dt(z), _lib.ptr(aff), _lib.ptr(alpha), act, leaky,
+                                       _lib.ptr(part), ctypes.byref(n), _lib.stream_ptr())
+    _lib.check(rc, "b2_bn_bwd_partial")
+    _count(1)
+    return part, n.value
+
+
+def bn_bwd_finalize(part, nparts, C, sums, dgamma=None, dbeta=None, dalpha=None, gscale=1.0, peer=None, raw_out=None):
+    """Stage 2: sums = [s1 | s2] over all replicas; dbeta += s1*gscale, dgamma += s2*gscale, dalpha += local third sum."""
+    regions, rank, world, epoch = _peer_args(peer)
+    rc = _lib.load().b2_bn_bwd_finalize(_lib.ptr(part), int(nparts), int(C), regions, rank, world, epoch, _lib.ptr(raw_out),
+                                        _lib.ptr(sums), _lib.ptr(dgamma), _lib.ptr(dbeta), _lib.ptr(dalpha), float(gscale),
+                                        _lib.stream_ptr())
+    _lib.check(rc, "b2_bn_bwd_finalize")
+    _count(1)
+    return sums
 
 
 def maxpool2x2(x, out=None):

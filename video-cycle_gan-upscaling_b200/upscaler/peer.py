@@ -34,16 +34,20 @@ class PeerReducer:
         self.epoch = 0
         self.calls = 0
 
+    def next_epoch(self):
+        """Epoch of the next exchange (identical call sequence on every rank); 1 .. 0x7FFFFFFE, never 0."""
+        self.epoch = (self.epoch % 0x7FFFFFFE) + 1
+        self.calls += 1
+        return self.epoch
+
     def all_reduce(self, buf):
         """In-place sum over the ranks of a contiguous float32 CUDA tensor of at most max_elems elements."""
         import torch
         if buf.dtype != torch.float32 or not buf.is_cuda or not buf.is_contiguous() or buf.numel() > self.max_elems:
             raise ValueError("peer all-reduce takes contiguous float32 CUDA tensors of at most %d elements" % self.max_elems)
-        self.epoch = (self.epoch % 0x7FFFFFFE) + 1
-        rc = _lib.load().b2_peer_allreduce_f32(_lib.ptr(buf), buf.numel(), self.regions, self.rank, self.world, self.epoch,
+        rc = _lib.load().b2_peer_allreduce_f32(_lib.ptr(buf), buf.numel(), self.regions, self.rank, self.world, self.next_epoch(),
                                                _lib.stream_ptr())
         _lib.check(rc, "b2_peer_allreduce_f32")
-        self.calls += 1
         from . import ops
         ops._count(1)
         return buf

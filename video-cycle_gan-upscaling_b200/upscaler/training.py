@@ -9,9 +9,22 @@ Recognised structures (everything else raises at compile time):
   'gan2'   inputs [x, real], outputs [G(x), D(G(x))], loss = [content, GanLosses.generator_loss]   ...  gan_train
 
 Keras semantics kept: losses are returned as computed in the forward pass (before the update); a model's `trainable`
-flag is snapshotted at compile time (model.py:1034, 1040); BatchNormalization of a frozen discriminator still runs on
-batch statistics inside a training step and still updates its moving statistics; one Adam instance shared between
-compiled models shares `iterations` while each compiled model owns its moment slots.
+flag is snapshotted at compile time for the WEIGHTS (model.py:1034, 1040: `_collected_trainable_weights`); BatchNormalization
+of a frozen discriminator still normalises with batch statistics inside a training step (Keras 2.2.x keeps
+learning_phase = 1 for every layer of a train function); one Adam instance shared between compiled models shares
+`iterations` while each compiled model owns its moment slots.
+
+Moving statistics of a frozen model — UNPINNED third-party behaviour, exposed as a switch.  In Keras >= 2.1.3
+`Layer.updates` / `Network.updates` return [] while the layer's or nested model's `trainable` is False
+(keras/engine/base_layer.py `updates`, keras/engine/network.py `updates`: "if not self.trainable and not self.stateful:
+return []"), and a compiled model collects its updates when it builds the train function, which happens lazily at the
+FIRST train_on_batch (keras/engine/training.py `_make_train_function`).  The reference's helpers leave
+`discriminator.trainable = False` behind (model.py:1040, 1101) and its scripts never set it back, so under that reading
+the discriminator's moving mean / variance never move in either compiled model — the saved model_discriminator_*.h5
+and D.predict differ, losses do not.  `FROZEN_MODEL_UPDATES_MOVING_STATS = False` (default) follows that reading: the
+flag is sampled from the leaf model's `trainable` at the first train_on_batch of each compiled model.  Set it to True
+for the pre-2.1.3 behaviour (moving statistics follow every training-phase pass).  No Keras is installed here to pin
+either.
 
 Data parallelism: when torch.distributed is initialised, every rank runs the same step on its shard of the batch;
 BatchNorm statistics (forward sums and backward sums) are all-reduced so that N replicas normalise like one big batch,
@@ -20,7 +33,6 @@ buckets, launched on a side stream as soon as backward has finished the slice (t
 order, so the tail of the network — whose gradients are ready first — is the last slice).
 """
 import math
-import os
 
 import numpy as np
 import torch
@@ -53,13 +65,16 @@ class GanLossFn:
 
 
 def loss_activation(name, x):
-    """(value, derivative) of GanLosses' loss activations at the scalar x (model.py:170-181)."""
-    if name == "sigmoid":
-        s = 1.0 / (1.0 + math.exp(-x))
-        return s, s * (1 - s)
-    if name == "log-sigm":
-        s = 1.0 / (1.0 + math.exp(-x))
-        return math.log(s), 1 - s
+    """(value, derivative) of GanLosses' loss activations at the scalar x (model.py:170-181).  Saturating forms: the
+    un-clipped critic reaches |D| ~ 1e11 (gan_test.ipynb cell 17), where K.sigmoid / K.log saturate instead of
+    overflowing: sigmoid -> 0 / 1, log(sigmoid) -> x (Keras' two-step log(sigmoid(x)) gives -inf there; the value is
+    only reported, the derivative 1 - sigmoid(x) is what drives the update and is identical)."""
+    if name in ("sigmoid", "log-sigm"):
+        e = math.exp(-abs(x))                       # in (0, 1]: never overflows
+        s = 1.0 / (1.0 + e) if x >= 0 else e / (1.0 + e)
+        if name == "sigmoid":
+            return s, s * (1 - s)
+        return min(x, 0.0) - math.log1p(e), 1 - s
     if name == "tanh":
         t = math.tanh(x)
         return t, 1 - t * t
@@ -70,6 +85,16 @@ def loss_activation(name, x):
     return x, 1.0
 
 
+FROZEN_MODEL_UPDATES_MOVING_STATS = False      # see the module docstring
+
+# Gradient scaling of the training step.  Every loss gradient is multiplied by S at its source, the whole backward pass
+# (linear in that gradient) carries S x the true values, and Adam divides S out again (b2_adam's gscale).  With bf16
+# storage S = 1.  With fp16 storage S lifts the gradients out of the subnormal range: "numel" = the number of elements of
+# the generated batch (cancels the 1/n of the mean-type content losses: per-pixel gradients become O(1)); for a
+# discriminator step S = D_SCALE x batch size (the score gradients +-1/n become +-D_SCALE).
+GRAD_SCALE = {"G": "numel", "D": 256.0}
+
+
 # ------------------------------------------------------------------------------------------------ distributed helpers
 def _dist():
     import torch.distributed as dist
@@ -78,28 +103,50 @@ def _dist():
     return None
 
 
+class BnSync:
+    """Cross-replica exchange of the BatchNorm sums.  Where the replicas can map each other's memory the exchange is
+    folded into the BatchNorm finalize kernels (csrc/b2_bn_train.cu over csrc/b2_peer.cuh): `peer_for(device)` returns
+    the PeerReducer whose regions / epoch those launches take.  Otherwise `all_reduce(buf)` runs on the process group
+    (NCCL, or gloo in the CPU tests).  Calling the object keeps the older protocol: sync(buf, rows) all-reduces buf in
+    place and returns the global row count (or the world size when rows is None)."""
+
+    def __init__(self, dist):
+        self.dist, self.world = dist, dist.get_world_size()
+        self._peer, self._asked = None, False
+
+    def peer_for(self, device):
+        if not self._asked:
+            self._asked = True
+            if torch.device(device).type == "cuda":
+                from . import peer
+                self._peer = peer.reducer(self.dist, device)
+        return self._peer
+
+    def all_reduce(self, buf):
+        r = self.peer_for(buf.device) if buf.is_cuda else None
+        if r is not None and buf.dtype == torch.float32 and buf.is_contiguous() and buf.numel() <= r.max_elems:
+            r.all_reduce(buf)
+        else:
+            self.dist.all_reduce(buf)
+        return buf
+
+    def __call__(self, buf, rows):
+        self.all_reduce(buf)
+        return rows * self.world if rows is not None else self.world
+
+
+_sync_state = {}
+
+
 def _make_sync():
-    """Cross-replica sum for BatchNorm statistics: sync(buffer, rows) -> global rows (or the world size)."""
+    """The process-wide BnSync when torch.distributed runs with more than one rank, else None."""
     dist = _dist()
     if dist is None:
+        _sync_state.clear()
         return None
-    world = dist.get_world_size()
-
-    skip = bool(os.environ.get("B2_DP_NO_BN_SYNC"))       # timing experiments only: replicas keep local statistics
-    red = {"r": None, "asked": False}
-
-    def sync(buf, rows):
-        if not skip:
-            if not red["asked"] and buf.is_cuda:           # NVLink peer-memory reduction (csrc/b2_peer.cu) where available
-                from . import peer
-                red["r"], red["asked"] = peer.reducer(dist, buf.device), True
-            r = red["r"]
-            if r is not None and buf.is_cuda and buf.dtype == torch.float32 and buf.is_contiguous() and buf.numel() <= r.max_elems:
-                r.all_reduce(buf)
-            else:
-                dist.all_reduce(buf)
-        return rows * world if rows is not None else world
-    return sync
+    if _sync_state.get("dist") is not dist or _sync_state.get("world") != dist.get_world_size():
+        _sync_state.update(dist=dist, world=dist.get_world_size(), sync=BnSync(dist))
+    return _sync_state["sync"]
 
 
 class GradReducer:
@@ -132,7 +179,7 @@ class GradReducer:
     def reduce_slice(self, flat, lo, hi):
         self.log.append((lo, hi))
         dist = _dist()
-        if dist is None or hi <= lo or os.environ.get("B2_DP_NO_GRAD_SYNC"):
+        if dist is None or hi <= lo:
             return
         if flat.is_cuda:
             if self.stream is None:
@@ -226,6 +273,7 @@ class Compiled:
     def __init__(self, kind, model, optimizer):
         self.kind, self.model, self.opt = kind, model, optimizer
         self.G = self.D = None
+        self.G_model = self.D_model = None     # the leaf Model objects (their `trainable` flags; see _moves)
         self.content = None
         self.g_frozen = self.d_frozen = False
         self.weights = (1.0, 1.0)
@@ -233,8 +281,36 @@ class Compiled:
         self.gan_losses = None
         self.reducer = GradReducer()
 
+    def _moves(self, which):
+        """Whether this compiled model's training-phase passes update the moving statistics of G / D: sampled once, at
+        the first train_on_batch, from the leaf model's `trainable` (module docstring)."""
+        key = "_moves_" + which
+        if key not in self.__dict__:
+            m = self.G_model if which == "G" else self.D_model
+            self.__dict__[key] = bool(FROZEN_MODEL_UPDATES_MOVING_STATS or m is None or m.trainable)
+        return self.__dict__[key]
+
     # -------------------------------------------------------------- Adam
-    def _adam(self, net):
+    @staticmethod
+    def _scale_for(net, numel, n):
+        """S for a step whose backward starts in `net` ('numel' elements generated / `n` scores)."""
+        if net.train_dtype != torch.float16:
+            return 1.0
+        from .networks import UpscalerOrigNet
+        if isinstance(net, UpscalerOrigNet):
+            g = GRAD_SCALE["G"]
+            return float(numel) if g == "numel" else float(g)
+        return float(GRAD_SCALE["D"]) * float(n)
+
+    @staticmethod
+    def _inner_scale(D, max_abs_ds):
+        """Extra factor for the score gradient of a (frozen) fp16 discriminator inside a generator step, so that it enters
+        D's backward at magnitude GRAD_SCALE['D'] whatever the adversarial loss weight is; D.backward divides it out."""
+        if D.train_dtype != torch.float16 or not (max_abs_ds > 0.0) or not math.isfinite(max_abs_ds):
+            return 1.0
+        return float(2.0 ** round(math.log2(float(GRAD_SCALE["D"]) / max_abs_ds)))
+
+    def _adam(self, net, S=1.0):
         opt = self.opt
         opt.iterations += 1
         t = opt.iterations
@@ -245,7 +321,7 @@ class Compiled:
             self.slots[key] = (torch.zeros_like(net.grad_flat), torch.zeros_like(net.grad_flat))
         m, v = self.slots[key]
         self.reducer.wait()
-        ops.adam(net.flat[:net.n_trainable], net.grad_flat, m, v, lr_t, opt.beta_1, opt.beta_2, opt.epsilon)
+        ops.adam(net.flat[:net.n_trainable], net.grad_flat, m, v, lr_t, opt.beta_1, opt.beta_2, opt.epsilon, gscale=1.0 / S)
         net._train_dirty = True
         net._infer_dirty = True
 
@@ -259,8 +335,8 @@ class Compiled:
                 setattr(net, flag, False)
 
     # -------------------------------------------------------------- content loss (+ gradient w.r.t. the generated image)
-    def _content(self, y, y_true, loss_buf, weight):
-        """loss_buf += content loss (unweighted); returns the gradient tensors (fp32 images) scaled by `weight`/world."""
+    def _content(self, y, y_true, loss_buf, weight, S=1.0):
+        """loss_buf += content loss (unweighted); returns the gradient tensors (fp32 images) scaled by S * `weight` / world."""
         cl = self.content
         dist = _dist()
         gs = weight / (dist.get_world_size() if dist else 1)
@@ -269,12 +345,12 @@ class Compiled:
         ft = vgg.forward(y_true)
         fp, acts = vgg.forward(y, save=True)
         dfeat = torch.empty_like(fp)
-        S = float(fp.numel())       # carry the feature gradient without the 1/n of the mean (fp16 range), see Vgg19Net
-        ops.loss_pair(fp, ft, loss_buf, mae=cl.mae, weight=1.0, gscale=gs * S, grad=dfeat)
-        grads = [vgg.backward(acts, dfeat, S)]
+        Sv = float(fp.numel())      # carry the feature gradient without the 1/n of the mean (fp16 range), see Vgg19Net
+        ops.loss_pair(fp, ft, loss_buf, mae=cl.mae, weight=1.0, gscale=gs * Sv, grad=dfeat)
+        grads = [vgg.backward(acts, dfeat, Sv / S)]   # the last data-gradient conv multiplies by S / Sv in fp32
         if cl.kind in ("vgg-mse", "vgg-mae"):
             gpix = torch.empty_like(y)
-            ops.loss_pair(y, y_true, loss_buf, mae=cl.mae, weight=cl.rate, gscale=gs * cl.rate, grad=gpix)
+            ops.loss_pair(y, y_true, loss_buf, mae=cl.mae, weight=cl.rate, gscale=gs * cl.rate * S, grad=gpix)
             grads.append(gpix)
         return grads
 
@@ -286,14 +362,15 @@ class Compiled:
         xd = _to_dev(x, dev, "x")
         pending = _uploader.begin(y_true, "y")        # the 16x larger target batch is staged while the forward pass is launched
         sync = _make_sync()
-        y, tape = G.forward_train(xd, sync)
+        y, tape = G.forward_train(xd, sync, update_moving=self._moves('G'))
         yt = _uploader.finish(pending, dev, side_stream=True)
         loss = torch.zeros(1, device=dev)
-        grads = self._content(y, yt, loss, 1.0)
+        S = self._scale_for(G, y.numel(), y.shape[0])
+        grads = self._content(y, yt, loss, 1.0, S)
         dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1] if len(grads) > 1 else None)
         G.ensure_grads().zero_()
         G.backward(tape, dz, sync, on_ready=self.reducer.hook(G.grad_flat, G.n_trainable))
-        self._adam(G)
+        self._adam(G, S)
         return self._mean_over_ranks(loss)[0]
 
     def step_disc(self, x, y):
@@ -303,14 +380,15 @@ class Compiled:
         xd = _to_dev(x, dev, "x")
         yd = _to_dev(np.asarray(y, np.float32).reshape(-1), dev, "labels")
         sync = _make_sync()
-        scores, tape = D.forward(xd, True, sync)
+        scores, tape = D.forward(xd, True, sync, update_moving=self._moves('D'))
         loss = torch.zeros(1, device=dev)
         ds = torch.empty_like(scores)
         dist = _dist()
-        ops.mean_prod(scores, yd, loss, 1.0, 1.0 / (dist.get_world_size() if dist else 1), ds)
+        S = self._scale_for(D, 0, scores.shape[0])
+        ops.mean_prod(scores, yd, loss, 1.0, S / (dist.get_world_size() if dist else 1), ds)
         D.ensure_grads().zero_()
         D.backward(tape, ds, True, False, sync, on_ready=self.reducer.hook(D.grad_flat, D.n_trainable))
-        self._adam(D)
+        self._adam(D, S)
         return self._mean_over_ranks(loss)[0]
 
     def step_gan(self, x, y_true, adv_y):
@@ -325,18 +403,21 @@ class Compiled:
         sync = _make_sync()
         dist = _dist()
         world = dist.get_world_size() if dist else 1
-        y, gtape = G.forward_train(xd, sync)
+        y, gtape = G.forward_train(xd, sync, update_moving=self._moves('G'))
         yt = _uploader.finish(pending, dev, side_stream=True)
-        scores, dtape = D.forward(y, True, sync)
+        scores, dtape = D.forward(y, True, sync, update_moving=self._moves('D'))
         losses = torch.zeros(2, device=dev)
-        grads = self._content(y, yt, losses[0:1], cw)
+        S = self._scale_for(G, y.numel(), y.shape[0])
+        grads = self._content(y, yt, losses[0:1], cw, S)
         ds = torch.empty_like(scores)
-        ops.mean_prod(scores, ad, losses[1:2], 1.0, dw / world, ds)
-        grads.append(D.backward(dtape, ds, not self.d_frozen, True, sync))
+        amax = float(np.abs(np.asarray(adv_y, np.float32)).max()) if np.size(adv_y) else 0.0
+        kD = self._inner_scale(D, abs(dw * S / world) * amax / max(scores.shape[0], 1)) if self.d_frozen else 1.0
+        ops.mean_prod(scores, ad, losses[1:2], 1.0, dw * S * kD / world, ds)
+        grads.append(D.backward(dtape, ds, not self.d_frozen, True, sync, grad_scale=kD))
         dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1], g3=grads[2] if len(grads) > 2 else None)
         G.ensure_grads().zero_()
         G.backward(gtape, dz, sync, on_ready=self.reducer.hook(G.grad_flat, G.n_trainable))
-        self._adam(G)
+        self._adam(G, S)
         lc, la = self._mean_over_ranks(losses)
         return [cw * lc + dw * la, lc, la]
 
@@ -359,21 +440,22 @@ class Compiled:
         sync = _make_sync()
         dist = _dist()
         world = dist.get_world_size() if dist else 1
-        sr, tr = D.forward(rd, True, sync)
-        sf, tf = D.forward(fd, True, sync)
+        sr, tr = D.forward(rd, True, sync, update_moving=self._moves('D'))
+        sf, tf = D.forward(fd, True, sync, update_moving=self._moves('D'))
         means = torch.zeros(2, device=dev)
         ops.mean_prod(sr, None, means[0:1], 1.0, 0.0, None, 1.0)
         ops.mean_prod(sf, None, means[1:2], 1.0, 0.0, None, 1.0)
         mr, mf = self._mean_over_ranks(means)
         val, d_real, d_fake = self._relativistic(mr, mf, "disc")
         D.ensure_grads().zero_()
+        S = self._scale_for(D, 0, sr.shape[0])
         for scores, tape, coef in ((sr, tr, d_real), (sf, tf, d_fake)):
             ds = torch.empty_like(scores)
-            ops.mean_prod(scores, None, None, 0.0, coef / world, ds, 1.0)
+            ops.mean_prod(scores, None, None, 0.0, coef * S / world, ds, 1.0)
             # the two passes accumulate into the same buffer: only the second one's slices are final
             D.backward(tape, ds, True, False, sync,
                        on_ready=self.reducer.hook(D.grad_flat, D.n_trainable) if scores is sf else None)
-        self._adam(D)
+        self._adam(D, S)
         return val
 
     def step_gan2(self, x, real, y_true):
@@ -387,22 +469,24 @@ class Compiled:
         sync = _make_sync()
         dist = _dist()
         world = dist.get_world_size() if dist else 1
-        sr, _ = D.forward(rd, True, sync)
-        y, gtape = G.forward_train(xd, sync)
-        sf, dtape = D.forward(y, True, sync)
+        sr, _ = D.forward(rd, True, sync, update_moving=self._moves('D'))
+        y, gtape = G.forward_train(xd, sync, update_moving=self._moves('G'))
+        sf, dtape = D.forward(y, True, sync, update_moving=self._moves('D'))
         buf = torch.zeros(3, device=dev)
         ops.mean_prod(sr, None, buf[0:1], 1.0, 0.0, None, 1.0)
         ops.mean_prod(sf, None, buf[1:2], 1.0, 0.0, None, 1.0)
-        grads = self._content(y, yt, buf[2:3], cw)
+        S = self._scale_for(G, y.numel(), y.shape[0])
+        grads = self._content(y, yt, buf[2:3], cw, S)
         mr, mf, lc = self._mean_over_ranks(buf)
         la, _, d_fake = self._relativistic(mr, mf, "gen")
         ds = torch.empty_like(sf)
-        ops.mean_prod(sf, None, None, 0.0, dw * d_fake / world, ds, 1.0)
-        grads.append(D.backward(dtape, ds, not self.d_frozen, True, sync))
+        kD = self._inner_scale(D, abs(dw * d_fake * S / world) / max(sf.shape[0], 1)) if self.d_frozen else 1.0
+        ops.mean_prod(sf, None, None, 0.0, dw * d_fake * S * kD / world, ds, 1.0)
+        grads.append(D.backward(dtape, ds, not self.d_frozen, True, sync, grad_scale=kD))
         dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1], g3=grads[2] if len(grads) > 2 else None)
         G.ensure_grads().zero_()
         G.backward(gtape, dz, sync, on_ready=self.reducer.hook(G.grad_flat, G.n_trainable))
-        self._adam(G)
+        self._adam(G, S)
         return [cw * lc + dw * la, lc, la]
 
     def _mean_over_ranks(self, buf):
@@ -473,6 +557,7 @@ def compile_model(model, loss, optimizer, loss_weights):
     if len(nets_per_out) == 1 and len(nets_per_out[0]) == 1 and isG(nets_per_out[0][0]) and n_in == 1:
         c = Compiled("gen", model, optimizer)
         c.G, c.content = nets_per_out[0][0], content_of(losses[0])
+        c.G_model = models_per_out[0][0]
         c.g_frozen = not models_per_out[0][0].trainable
     elif len(nets_per_out) == 1 and len(nets_per_out[0]) == 1 and isD(nets_per_out[0][0]):
         D = nets_per_out[0][0]
@@ -485,6 +570,7 @@ def compile_model(model, loss, optimizer, loss_weights):
         else:
             raise ValueError("unsupported discriminator loss %r" % (losses[0],))
         c.D = D
+        c.D_model = models_per_out[0][0]
         c.d_frozen = not models_per_out[0][0].trainable
     elif len(nets_per_out) == 2 and len(nets_per_out[0]) == 1 and isG(nets_per_out[0][0]) and \
             len(nets_per_out[1]) == 2 and nets_per_out[1][0] is nets_per_out[0][0] and isD(nets_per_out[1][1]):
@@ -497,6 +583,7 @@ def compile_model(model, loss, optimizer, loss_weights):
         else:
             raise ValueError("unsupported adversarial loss %r" % (losses[1],))
         c.G, c.D = nets_per_out[0][0], nets_per_out[1][1]
+        c.G_model, c.D_model = models_per_out[0][0], models_per_out[1][1]
         c.content = content_of(losses[0])
         c.d_frozen = not models_per_out[1][1].trainable
         lw = list(loss_weights) if loss_weights is not None else [1.0, 1.0]
