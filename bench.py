@@ -41,6 +41,26 @@ def load_peaks():
     return {"bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "hbm_gbs": 6650.0, "source": "fallback"}
 
 
+def profiled_dram_traffic(kernel_tag="conv_phases2"):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, read from the newest committed
+    `ncu --set full` summary under profiles/ (tools/ncu_raw_pick.py output; captured at B = 8, k = 3).  None when absent."""
+    import glob
+    import re
+    best = None
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*ncu_full*%s*summary.txt" % kernel_tag))):
+        vals = {}
+        with open(path) as f:
+            for line in f:
+                m = re.match(r"(dram__bytes_(?:read|write)\.sum)\s+(\w+)\s+\['([0-9.]+)'", line)
+                if m:
+                    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(m.group(2))
+                    if scale:
+                        vals[m.group(1)] = float(m.group(3)) * scale
+        if len(vals) == 2:
+            best = (sum(vals.values()), os.path.basename(path))
+    return best
+
+
 class ClockSampler:
     """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -135,30 +155,80 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
-def bench_train_step(args, rank, world, dev, barrier, B=16, hw=(96, 96)):
-    """Generator-only training step with the VGG19 content loss (train.py; BASELINE.json configs[2]): B = 16 LR patches
-    of 96x96 per GPU through compile_training_model(...).train_on_batch(host x, host y) -- forward with batch-statistics
+def cpu_oracle_train_samples_per_s(ks, B=2, hw=(96, 96)):
+    """the CPU oracle's generator-only training step (fp32 autograd + Adam) on all host cores, at a
+    reduced batch (B = 2 patches; a batch of 16 needs ~15 GB and > 15 minutes of CPU backward); samples/s."""
+    import numpy as np
+    import torch
+    from oracle import srgan_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    h, w_ = hw
+    ref = O.GeneratorTrainer(O.init_upscaler_orig_weights(seed=1234, kernel_size=ks), O.init_vgg19_weights(), "vgg-mse", 1e-3)
+    rng = np.random.default_rng(0)
+    hr = rng.uniform(-1, 1, (B, 4 * h, 4 * w_, 3)).astype(np.float32)
+    x = hr.reshape(B, h, 4, w_, 4, 3).mean(axis=(2, 4)).astype(np.float32)
+    t0 = time.perf_counter()
+    ref.train_on_batch(x, hr)
+    dt = time.perf_counter() - t0
+    return {"value": B / dt, "unit": "samples/s", "cores": cores, "kind": "port",
+            "sample": "one train_on_batch of %d patches of %dx%d -> %dx%d (%.1f s) through the PyTorch-CPU fp32 autograd oracle "
+                      "(the step named by the config has 16: scaled by batch size, BatchNorm over 2 instead of 16 samples)" % (B, h, w_, 4 * h, 4 * w_, dt)}
+
+
+def cpu_oracle_gan_images_per_s(ks, n=1, lr=128):
+    """one train_gan.py loop iteration (predict + discriminator step + GAN step) of the CPU oracle, n LR
+    images of 128x128 -> 512x512."""
+    import numpy as np
+    import torch
+    from oracle import srgan_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    ref = O.GanTrainer(O.init_upscaler_orig_weights(seed=1234, kernel_size=ks),
+                       O.init_discriminator_simple_512_weights(seed=77, input_shape=(4 * lr, 4 * lr, 3)), O.init_vgg19_weights(), "vgg-mse", 1e-3, 1.0, 1e-5)
+    rng = np.random.default_rng(0)
+    hr = rng.uniform(-1, 1, (n, 4 * lr, 4 * lr, 3)).astype(np.float32)
+    x = hr.reshape(n, lr, 4, lr, 4, 3).mean(axis=(2, 4)).astype(np.float32)
+    t0 = time.perf_counter()
+    ref.step(x, hr)
+    dt = time.perf_counter() - t0
+    return {"value": n / dt, "unit": "samples/s", "cores": cores, "kind": "port",
+            "sample": "one loop iteration with n = %d LR image(s) of %dx%d -> %dx%d (%.1f s) through the PyTorch-CPU fp32 oracle "
+                      "(the GPU leg pushes 6 per iteration)" % (n, lr, lr, 4 * lr, 4 * lr, dt)}
+
+
+def bench_train_step(args, rank, world, dev, barrier, B=16, hw=(96, 96), builder="orig", loss_kind="vgg-mse", calls=1,
+                     what="generator-only step"):
+    """Generator-only training step with the VGG19 content loss (train.py; BASELINE.json configs[2]): B LR patches of
+    hw per GPU through compile_training_model(...).train_on_batch(host x, host y) -- forward with batch-statistics
     BatchNorm, VGG19 loss, backward, Adam; data-parallel over NCCL when N > 1 (cross-replica BatchNorm sums, bucketed
-    gradient all-reduce overlapped with backward).  H2D of the batch and the D2H read of the loss are inside."""
+    gradient all-reduce overlapped with backward).  H2D of the batch and the D2H read of the loss are inside.
+    `calls` > 1 = one ITERATION of train_cgc.py:275-277: that many train_on_batch calls on different LR renderings of the
+    same HR frame (gen1, gen2, scaled), each a full step; value then counts HR frames/s."""
     import numpy as np
     import torch
     import torch.distributed as dist
     from upscaler import ops
-    from upscaler.model import VGG_MSE_LOSS, compile_training_model, make_upscaler_orig
+    from upscaler import model as M
     ks = args.kernel_size
     h, w_ = hw
-    up = make_upscaler_orig((4 * h, 4 * w_, 3), kernel_size=ks)
-    tm = compile_training_model(up, VGG_MSE_LOSS((4 * h, 4 * w_, 3), 1e-3).loss)
+    make = {"orig": M.make_upscaler_orig, "skip-con": M.make_upscaler_skip_con}[builder]
+    up = make((4 * h, 4 * w_, 3), kernel_size=ks)
+    lobj = {"vgg-mse": lambda: M.VGG_MSE_LOSS((4 * h, 4 * w_, 3), 1e-3), "vgg": lambda: M.VGG_LOSS((4 * h, 4 * w_, 3))}[loss_kind]()
+    tm = M.compile_training_model(up, lobj.loss)
     rng = np.random.default_rng(100 + rank)
     hr = rng.uniform(-1, 1, (B, 4 * h, 4 * w_, 3)).astype(np.float32)
-    x = hr.reshape(B, h, 4, w_, 4, 3).mean(axis=(2, 4)).astype(np.float32)
+    base = hr.reshape(B, h, 4, w_, 4, 3).mean(axis=(2, 4)).astype(np.float32)
+    xs = [np.clip(base + 0.05 * c * rng.standard_normal(base.shape).astype(np.float32), -1, 1) for c in range(calls)]
     for _ in range(3):
-        loss = tm.train_on_batch(x, hr)
+        for x in xs:
+            loss = tm.train_on_batch(x, hr)
     barrier()
     ops.reset_launch_count()
     t0 = time.perf_counter()
     for _ in range(args.train_steps):
-        loss = tm.train_on_batch(x, hr)       # returns the loss as a host float: the step's D2H read + sync
+        for x in xs:
+            loss = tm.train_on_batch(x, hr)       # returns the loss as a host float: the step's D2H read + sync
     barrier()
     t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
     if world > 1:
@@ -167,15 +237,19 @@ def bench_train_step(args, rank, world, dev, barrier, B=16, hw=(96, 96)):
     peaks = load_peaks()
     # 3 G + 3 V per sample; V scales with the HR pixel count (114.66 GFLOP at 384 x 384)
     flops = B * 3 * (GEN_FLOPS[ks] * (h * w_) / float(H_LR * W_LR) + 114.66e9 * (16 * h * w_) / float(384 * 384))
-    if (B, hw) == (16, (96, 96)):
+    if (B, hw, builder) == (16, (96, 96), "orig"):
         flops = TRAIN_STEP_FLOPS[ks]
+    flops *= calls       # (skip-con: the generator FLOPs are make_upscaler_orig's; its 224-filter 3x3 ConvT layers do less -> a lower bound on the fraction is not claimed)
     tf = flops * world / (ms * 1e-3) / 1e12
-    out = {"metric": "train samples/s", "value": world * B * 1000.0 / ms, "unit": "samples/s", "ms_per_step": ms,
-           "steps": args.train_steps, "config": "generator-only step, vgg-mse content loss, %d x (%dx%d -> %dx%d) per GPU, k=%d, "
-           "bf16 storage / fp32 accumulate / fp32 master weights + Adam%s" % (B, h, w_, 4 * h, 4 * w_, ks, ", NCCL data-parallel (SyncBN sums + bucketed gradient all-reduce)" if world > 1 else ""),
-           "algorithmic_tflops": tf, "frac_of_bf16_sustained_peak": tf / world / peaks["bf16_tflops_sustained"],
+    out = {"metric": "train samples/s", "value": world * B * 1000.0 / ms, "unit": "samples/s" if calls == 1 else "HR frames/s (iterations/s x batch)",
+           "ms_per_step": ms, "steps": args.train_steps,
+           "config": "%s, %s content loss, %d x (%dx%d -> %dx%d) per GPU, make_upscaler_%s k=%d, "
+           "bf16 storage / fp32 accumulate / fp32 master weights + Adam%s" % (what, loss_kind, B, h, w_, 4 * h, 4 * w_, builder.replace("-", "_"), ks, ", NCCL data-parallel (SyncBN sums + bucketed gradient all-reduce)" if world > 1 else ""),
+           "train_on_batch_calls_per_step": calls,
            "gpu_launches_per_step": ops.launch_count() // args.train_steps, "loss": float(loss),
-           "h2d_bytes_per_step": int(x.nbytes + hr.nbytes), "d2h_bytes_per_step": 4}
+           "h2d_bytes_per_step": int(sum(x.nbytes for x in xs) + calls * hr.nbytes), "d2h_bytes_per_step": 4 * calls}
+    if builder == "orig":
+        out.update({"algorithmic_tflops": tf, "frac_of_bf16_sustained_peak": tf / world / peaks["bf16_tflops_sustained"]})
     del tm, up
     torch.cuda.empty_cache()
     return out
@@ -350,27 +424,43 @@ def main():
     e2e_u8 = world * B * e2e_steps / float(t_u8.item())
 
     # ------------------------------------------------------------------ training step (BASELINE.json configs[2])
-    train = train_gan = train_full = None
+    train = train_gan = train_full = train_cgc = train_cgc_mini = train_strong = None
     if not args.no_train:
         train = bench_train_step(args, rank, world, dev, barrier)
+        if world > 1 and 16 % world == 0:
+            # strong scaling of the same step: the config's global batch of 16 split over the ranks
+            train_strong = bench_train_step(args, rank, world, dev, barrier, B=16 // world,
+                                            what="generator-only step, STRONG scaling: global batch 16 = %d per GPU" % (16 // world))
         train_gan = bench_gan_step(args, rank, world, dev, barrier)
-        # train.py's own workload and one of the three steps of a train_cgc.py iteration (configs[4]):
-        # batch 1 of a full 270x480 -> 1080x1920 frame
+        # train.py's own workload: batch 1 of a full 270x480 -> 1080x1920 frame
         train_full = bench_train_step(args, rank, world, dev, barrier, B=1, hw=(H_LR, W_LR))
+        # BASELINE.json configs[4]: one train_cgc.py ITERATION (train_cgc.py:275-277) = three full-frame train_on_batch calls
+        # (gen1 / gen2 / scaled renderings -> the same HR frame), make_upscaler_skip_con, its default loss vgg-only, bs 1
+        train_cgc = bench_train_step(args, rank, world, dev, barrier, B=1, hw=(H_LR, W_LR), builder="skip-con", loss_kind="vgg",
+                                     calls=3, what="train_cgc.py iteration (3 train_on_batch calls)")
+        # train_cgc_mini.py:269-275: the three renderings concatenated into ONE batch of 3 x bs (bs = 3) 128x128 -> 512x512 crops
+        train_cgc_mini = bench_train_step(args, rank, world, dev, barrier, B=9, hw=(128, 128), builder="skip-con", loss_kind="vgg",
+                                          what="train_cgc_mini.py step (3 x bs = 9 crops in one batch)")
+        if rank == 0 and world == 1 and not args.no_cpu_baseline:
+            train["cpu_baseline"] = cpu_oracle_train_samples_per_s(ks)
+            train_gan["cpu_baseline"] = cpu_oracle_gan_images_per_s(ks)
 
     if rank == 0:
         peaks = load_peaks()
         dom = "upscaling/1/block/conv_transp"
         dom_ms = layer_ms.get(dom)
         achieved = CONVT2_FLOPS[ks] * B / (dom_ms * 1e-3) / 1e12 if dom_ms else None
-        # DRAM bytes of that launch from `ncu --set full` (profiles/r01_s40_ncu_full_conv_phases2_convT2_summary.txt,
-        # B = 8, k = 3): 2.17 GB read + 8.44 GB written, tensor pipe 67 % active under ncu; algorithmic = 2.12 GB input + 8.49 GB output -> no wasted re-reads
-        traffic = 10.61e9 * B / 8 if ks == 3 else None
+        # DRAM bytes of that launch from the committed `ncu --set full` summary (captured at B = 8, k = 3; algorithmic =
+        # 2.12 GB input + 8.49 GB output per 8 frames)
+        prof = profiled_dram_traffic() if ks == 3 else None
+        traffic = prof[0] * B / 8 if prof else None
         roof = {"bound": "tensor", "kernel": "conv_phases2_kernel (all 4 sub-pixel phases of " + dom + " in one persistent CTA-pair launch)",
                 "achieved": achieved, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
                 "frac": (achieved / peaks["bf16_tflops_sustained"]) if achieved else None,
                 "peak_kind": "bf16 dense sustained, %s" % peaks["source"], "traffic": traffic,
                 "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)",
+                "traffic_source": ("profiles/" + prof[1]) if prof else None,
+                "algorithmic_bytes": (2.12e9 + 8.49e9) * B / 8 if ks == 3 else None,
                 "share_of_step": (dom_ms / ms_step) if dom_ms else None}
         whole = GEN_FLOPS[ks] * world * B / (ms_step * 1e-3) / 1e12
         cpu = None
@@ -391,7 +481,8 @@ def main():
                               "d2h_bytes_per_step": int(yu.nbytes),
                               "api": "Model.predict_uint8(uint8 frames)->uint8 frames (data.py:253-270 conversions fused on the device)"},
                 "gpu_launches": launches,
-                "roofline": roof, "cpu_baseline": cpu, "train": train, "train_gan": train_gan, "train_full_frame": train_full,
+                "roofline": roof, "cpu_baseline": cpu, "train": train, "train_strong_scaling": train_strong, "train_gan": train_gan, "train_full_frame": train_full,
+                "train_cgc_iteration": train_cgc, "train_cgc_mini": train_cgc_mini,
                 "layers_ms": {k: round(v, 4) for k, v in sorted(layer_ms.items(), key=lambda kv: -kv[1])[:8]}}
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -17,6 +17,8 @@ BatchNorm statistics and Adam).  Tolerances, and why:
     lr = 1e-3 (measured).  The free-running check therefore only asserts the same training behaviour
     (monotone decrease to a comparable level); the 1 % bar is enforced by the teacher-forced test.
 """
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -291,18 +293,19 @@ def test_full_generator_loss_curve_teacher_forced_48px():
     tm = compile_training_model(up, VGG_MSE_LOSS((192, 192, 3), 1e-3, vgg19=vw).loss, optimizer=Adam())
     ref = O.GeneratorTrainer(gw, vw, "vgg-mse", 1e-3)
     got, want = [], []
-    for step in range(40):
+    for step in range(40 if os.environ.get("B2_SLOW", "0") not in ("", "0") else 8):     # 40 with B2_SLOW=1 (log under profiles/)
         x, hr = _data(4, 48, seed=2000 + step % 10)
         _sync_weights(up, ref)
         got.append(tm.train_on_batch(x, hr))
         want.append(ref.train_on_batch(x, hr))
     got, want = np.array(got), np.array(want)
     rel = np.abs(got - want) / want
-    print("full generator, teacher-forced, 40 steps: max per-step rel diff %.4f, mean %.4f; loss %.4f -> %.4f" % (
-        rel.max(), rel.mean(), want[0], want[-1]))
+    print("full generator, teacher-forced, %d steps: max per-step rel diff %.4f, mean %.4f; loss %.4f -> %.4f" % (
+        len(got), rel.max(), rel.mean(), want[0], want[-1]))
     assert rel.max() <= 1e-2
 
 
+@pytest.mark.slow
 def test_free_running_divergence_against_the_oracles_own_spread():
     """the free-running trajectory is judged against the fp32 oracle's OWN spread instead of a hand-picked
     band.  Three oracle runs differ only in the order of the two samples inside each batch (exact in real arithmetic:
