@@ -129,6 +129,22 @@ int b2_resize_bilinear_into(const float* in, int B, int H, int W, int C, int fac
                             void* stream);
 int b2_f32_to_u8_denorm(const float* in, uint8_t* out, int64_t n, void* stream);
 
+/* Layers make_upscaler_attention adds to the generator (reference upscaling/upscaler/model.py:30-48, 78-98, 296-328).
+ * b2_gate_mul: Multiply([Activation('sigmoid')(attention conv), stream]) (model.py:34-36, 88-91):
+ *   out[r, c] = sigmoid(att[r * att_ld + att_c0 + c]) * m[r * C + c], 16-bit in / out, rows pixels, C channels (the
+ *   attention convs of all residual blocks are evaluated as one wide convolution; att_c0 selects a block's slice).
+ * b2_resize_nearest_bilinear_pair: Concatenate([K.resize_images(x, f, f, 'nearest'), K.resize_images(x, f, f, 'bilinear')])
+ *   (model.py:80-82; TensorFlow 1.x kernels, align_corners = False, no half-pixel centres): fp32 [B,H,W,C] -> fp32
+ *   [B, f*H, f*W, 2*C].
+ * b2_atanh_conv2d_transpose_small: Conv2DTranspose(Cout, kernel_size = stride + 1, strides = stride, padding = 'same') of
+ *   atanh(0.99999 * x) on the Cin = 3 network input (model.py:94-95); w fp32 in the Keras layout (k, k, Cout, Cin), bias fp32,
+ *   out 16-bit [B, stride*H, stride*W, Cout] (it then enters the block's Conv2DTranspose as b2_epilogue.residual:
+ *   Add, model.py:97). */
+int b2_gate_mul(const void* att, int att_ld, int att_c0, const void* m, void* out, int64_t rows, int C, int f16, void* stream);
+int b2_resize_nearest_bilinear_pair(const float* in, int B, int H, int W, int C, int factor, float* out, void* stream);
+int b2_atanh_conv2d_transpose_small(const float* in, int B, int H, int W, int Cin, const float* w, const float* bias, int stride,
+                                    int Cout, void* out, int f16, void* stream);
+
 /* Saturation guard of the 16-bit storage: *count += number of elements of x[n] at the edge of their type -- fp16 (f16 != 0):
  * |x| >= 65504 (the value the convolution epilogues' saturating conversion stores for anything larger), inf or NaN; bf16:
  * inf or NaN.  The host runs it over every layer output of the first inference pass after a weight change (and on
@@ -226,10 +242,12 @@ int b2_bn_stats_partial(const void* x, int64_t rows, int C, int f16, float* part
 /* forward stage 2: sums (x world) -> mean, biased variance -> aff = [scale | shift | mean | invstd] (4*C floats, owned by
  * the caller's tape), Keras moving-statistics update when moving_mean / moving_var are given (momentum 0.99, variance
  * n/(n-(1+eps))).  `count` = rows over ALL replicas.  sums_out (2*C, nullable) receives the summed statistics; with
- * aff == NULL nothing else is computed (NCCL fallback: all-reduce sums_out, call again with nparts = 1). */
+ * aff == NULL nothing else is computed (NCCL fallback: all-reduce sums_out, call again with nparts = 1).
+ * range_watch (nullable, one float): set to 1 when a channel's root mean square reaches range_limit or is not finite --
+ * the guard of fp16 training storage (the tensor was stored with a saturating conversion; the host switches to bf16). */
 int b2_bn_fwd_finalize(const float* part, int nparts, int C, float count, void* const* peer_regions, int rank, int world,
                        unsigned epoch, float* sums_out, const float* gamma, const float* beta, float eps, float momentum,
-                       float* moving_mean, float* moving_var, float* aff, void* stream);
+                       float* moving_mean, float* moving_var, float* aff, float* range_watch, float range_limit, void* stream);
 /* backward stage 1 through y = act(u), u = z*scale + shift (aff from the forward tape): with dy = g*act'(u),
  * part[row] = [sum dy | sum dy*xhat | sum g*min(u,0)]. */
 int b2_bn_bwd_partial(const void* z, const void* g, int64_t rows, int C, int f16, const float* aff, const float* alpha, int act,

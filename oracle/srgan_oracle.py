@@ -16,6 +16,7 @@ Reference lines each function follows (all under /root/reference/upscaling/upsca
   make_upscaler_orig        model.py:267-295    VGG_*_LOSS            model.py:101-157
   wasserstein_loss          model.py:159-160    GanLosses family      model.py:166-261
   make_discriminator_simple_512  model.py:836-896
+  make_upscaler_attention   model.py:296-328 (residual_block_attention :30-48, upsampling_block_attention :78-98)
   compile helpers / train steps  model.py:1017-1137, train_mini.py:224-234, train_gan.py:296-321, train_gan3.py:337-354
   tensor I/O contract       data.py:253-270
 
@@ -311,6 +312,91 @@ def upscaler_skip_con_forward(w, x_nhwc, training=False, stats_out=None, upscale
         m = leaky(conv2d_transpose_same_s2(m, *w["upscaling/%d/block/conv_transp" % i]), 0.2)
     m = torch.cat([resize_bilinear_tf1(x, upscale_factor), m], dim=1)      # Concatenate(axis=3) in NHWC
     return torch.tanh(conv2d_same(m, *w["final/conv"])).permute(0, 2, 3, 1)
+
+
+def conv2d_transpose_same(x, kernel, bias=None, stride=2):
+    """Conv2DTranspose(padding='same') for any stride <= kernel: the gradient of the SAME conv that maps stride*in -> in
+    (pad_total = kernel - stride, pad_before = pad_total // 2), out = stride * in.  x NCHW; kernel (kh, kw, Cout, Cin)."""
+    kh, kw = kernel.shape[0], kernel.shape[1]
+    y = F.conv_transpose2d(x, kernel.permute(3, 2, 0, 1), None, stride=stride, padding=0)
+    pbh, pbw = max(kh - stride, 0) // 2, max(kw - stride, 0) // 2
+    y = y[:, :, pbh:pbh + stride * x.shape[2], pbw:pbw + stride * x.shape[3]]
+    if bias is not None:
+        y = y + bias.view(1, -1, 1, 1)
+    return y
+
+
+def resize_nearest_tf1(x_nchw, factor):
+    """K.resize_images(..., 'nearest') = tf.image.resize_nearest_neighbor, align_corners=False: source = out // factor."""
+    return x_nchw.repeat_interleave(factor, dim=2).repeat_interleave(factor, dim=3)
+
+
+ATT_UP_FILTERS = 128      # make_upscaler_attention passes filters=128 to its upsampling blocks (model.py:319)
+
+
+def init_upscaler_attention_weights(seed=1234, kernel_size=5, filters=64, upscale_factor=4, res_block_num=16, randomize=True):
+    """make_upscaler_attention (model.py:296-328) in Keras layout under the reference's layer names."""
+    rng = np.random.default_rng(seed)
+    bs = 0.05 if randomize else 0.0
+    k = kernel_size
+    alpha = lambda: [(rng.uniform(0, 0.3, (1, 1, filters)) if randomize else np.zeros((1, 1, filters))).astype(np.float32)]
+    w = {"initial/conv": _conv_w(rng, 9, 9, 3, filters, bs), "initial/prelu": alpha()}
+    for i in range(res_block_num):
+        n = "res_block/%d" % i
+        w[n + "/attention"] = _conv_w(rng, k, k, 3, filters, bs)
+        w[n + "/conv_pre"] = _conv_w(rng, k, k, filters, filters, bs)
+        w[n + "/batch_norm_pre"] = _bn_w(rng, filters, randomize)
+        w[n + "/prelu"] = alpha()
+        w[n + "/conv_post"] = _conv_w(rng, k, k, filters, filters, bs)
+        w[n + "/batch_norm_post"] = _bn_w(rng, filters, randomize)
+    w["after_res/conv"] = _conv_w(rng, k, k, filters, filters, bs)
+    w["after_res/batch_norm"] = _bn_w(rng, filters, randomize)
+    cin = filters
+    for i in range(int(math.log(upscale_factor, 2))):
+        n, scale = "upscaling/%d/block" % i, 2 ** (i + 1)
+        w[n + "/attention"] = _conv_w(rng, k, k, 6, cin, bs)
+        w[n + "/conv_transp"] = [glorot_uniform(rng, (k, k, ATT_UP_FILTERS, cin), k * k * cin, k * k * ATT_UP_FILTERS),
+                                 (rng.standard_normal(ATT_UP_FILTERS) * bs).astype(np.float32)]
+        ks = scale + 1
+        w[n + "/to_add_input_conv_transp"] = [glorot_uniform(rng, (ks, ks, ATT_UP_FILTERS, 3), ks * ks * 3, ks * ks * ATT_UP_FILTERS),
+                                              (rng.standard_normal(ATT_UP_FILTERS) * bs).astype(np.float32)]
+        cin = ATT_UP_FILTERS
+    w["final/conv"] = _conv_w(rng, 9, 9, cin, 3, bs)
+    return w
+
+
+def upscaler_attention_forward(w, x_nhwc, training=False, stats_out=None, upscale_factor=4, res_block_num=16):
+    """make_upscaler_attention (model.py:296-328) with residual_block_attention (:30-48) and upsampling_block_attention
+    (:78-98): every residual block's input is gated by sigmoid(conv(network input)); each upsampling block gates its
+    input by sigmoid(conv(Concatenate([nearest, bilinear] resize of the network input by scale // 2))), applies
+    Conv2DTranspose(128, k, stride 2) + LeakyReLU(0.2) and adds Conv2DTranspose(128, scale + 1, stride scale) of
+    atanh(0.99999 * network input)."""
+    x = _t(x_nhwc).permute(0, 3, 1, 2)
+    m = prelu(conv2d_same(x, *w["initial/conv"]), w["initial/prelu"][0])
+    skip = m
+    for i in range(res_block_num):
+        n = "res_block/%d" % i
+        h = torch.sigmoid(conv2d_same(x, *w[n + "/attention"])) * m
+        h = conv2d_same(h, *w[n + "/conv_pre"])
+        h = prelu(batch_norm(h, *w[n + "/batch_norm_pre"], training, stats_out), w[n + "/prelu"][0])
+        h = batch_norm(conv2d_same(h, *w[n + "/conv_post"]), *w[n + "/batch_norm_post"], training, stats_out)
+        m = m + h
+    m = skip + batch_norm(conv2d_same(m, *w["after_res/conv"]), *w["after_res/batch_norm"], training, stats_out)
+    for i in range(int(math.log(upscale_factor, 2))):
+        n, scale = "upscaling/%d/block" % i, 2 ** (i + 1)
+        r = scale // 2
+        iu = torch.cat([resize_nearest_tf1(x, r), resize_bilinear_tf1(x, r)], dim=1)
+        m = torch.sigmoid(conv2d_same(iu, *w[n + "/attention"])) * m
+        m = leaky(conv2d_transpose_same(m, *w[n + "/conv_transp"], stride=2), 0.2)
+        m = m + conv2d_transpose_same(torch.atanh(0.99999 * x), *w[n + "/to_add_input_conv_transp"], stride=scale)
+    return torch.tanh(conv2d_same(m, *w["final/conv"])).permute(0, 2, 3, 1)
+
+
+def upscaler_attention_bn_names(res_block_num=16):
+    names = []
+    for i in range(res_block_num):
+        names += ["res_block/%d/batch_norm_pre" % i, "res_block/%d/batch_norm_post" % i]
+    return names + ["after_res/batch_norm"]
 
 
 def upscaler_bn_names(res_block_num=16):

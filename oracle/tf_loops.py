@@ -51,6 +51,33 @@ def conv2d_transpose_same_s2_loops(x, kernel):
     return out
 
 
+def conv2d_transpose_same_loops(x, kernel, stride):
+    """Keras Conv2DTranspose(strides=stride, padding='same') for any stride <= kernel size (make_upscaler_attention uses
+    kernel = stride + 1, reference model.py:95): the gradient w.r.t. the input of the SAME conv that maps stride*in -> in;
+    input pixel i scatters x[i] * W[k] into y = stride*i + k - pad_before.  x (H,W,Cin), kernel (kh,kw,Cout,Cin)."""
+    H, W, _ = x.shape
+    kh, kw, cout, _ = kernel.shape
+    pt, oh = same_pad(stride * H, kh, stride)
+    pl, ow = same_pad(stride * W, kw, stride)
+    assert (oh, ow) == (H, W)
+    out = np.zeros((stride * H, stride * W, cout), np.float64)
+    for iy in range(H):
+        for ix in range(W):
+            for ky in range(kh):
+                for kx in range(kw):
+                    y, xx = stride * iy + ky - pt, stride * ix + kx - pl
+                    if 0 <= y < stride * H and 0 <= xx < stride * W:
+                        out[y, xx] += kernel[ky, kx].astype(np.float64) @ x[iy, ix].astype(np.float64)
+    return out
+
+
+def resize_nearest_tf1_loops(img, factor):
+    """tf.image.resize_nearest_neighbor (TF 1.x, align_corners=False): source index = floor(out * in / out_size)."""
+    H, W = len(img), len(img[0])
+    return [[img[int(oy * (H / float(H * factor)))][int(ox * (W / float(W * factor)))] for ox in range(W * factor)]
+            for oy in range(H * factor)]
+
+
 def resize_bilinear_tf1_loops(img, factor):
     """tf.image.resize_bilinear (TF 1.x, align_corners=False, no half-pixel centres) as plain loops over an (H, W)
     list-of-lists image: the independent restatement oracle.resize_bilinear_tf1 is checked against."""

@@ -175,3 +175,33 @@ def test_skip_con_oracle_shapes_and_param_count():
     with torch.no_grad():
         y = O.upscaler_skip_con_forward(O.to_torch(w), x)
     assert tuple(y.shape) == (1, 24, 20, 3) and float(y.abs().max()) <= 1.0
+
+
+def test_attention_generator_oracle_pieces_and_shapes():
+    """make_upscaler_attention (model.py:296-328): the general-stride Conv2DTranspose and the nearest resize against the loop
+    restatements of TensorFlow's rules; output shape; parameter count against the layer list of model.py:30-48, 78-98."""
+    from oracle import tf_loops
+    rng = np.random.default_rng(3)
+    for k, s in ((3, 2), (5, 4), (5, 2), (4, 4)):
+        x = rng.standard_normal((4, 5, 3)).astype(np.float32)
+        ker = rng.standard_normal((k, k, 6, 3)).astype(np.float32)
+        got = O.conv2d_transpose_same(torch.from_numpy(x).permute(2, 0, 1)[None], torch.from_numpy(ker), None, s)[0].permute(1, 2, 0).numpy()
+        want = tf_loops.conv2d_transpose_same_loops(x, ker, s)
+        assert got.shape == (4 * s, 5 * s, 6)
+        assert np.abs(got - want).max() < 1e-4
+    img = rng.standard_normal((3, 4)).astype(np.float32)
+    near = O.resize_nearest_tf1(torch.from_numpy(img)[None, None], 2)[0, 0].numpy()
+    assert np.array_equal(near, np.array(tf_loops.resize_nearest_tf1_loops(img.tolist(), 2), np.float32))
+    for k in (3, 5):
+        w = O.init_upscaler_attention_weights(seed=2, kernel_size=k)
+        f, up = 64, 128
+        want = (81 * 3 * f + f) + f                                          # initial conv + PReLU
+        want += 16 * ((k * k * 3 * f + f) + 2 * (k * k * f * f + f) + 2 * 4 * f + f)      # attention conv, 2 convs, 2 BN, PReLU
+        want += k * k * f * f + f + 4 * f                                     # after_res conv + BN
+        for cin, scale in ((f, 2), (up, 4)):
+            want += (k * k * 6 * cin + cin) + (k * k * cin * up + up) + ((scale + 1) ** 2 * 3 * up + up)
+        want += 81 * up * 3 + 3
+        assert O.count_params(w) == want
+        with torch.no_grad():
+            y = O.upscaler_attention_forward(O.to_torch(w), rng.uniform(-1, 1, (2, 6, 7, 3)).astype(np.float32))
+        assert tuple(y.shape) == (2, 24, 28, 3) and float(y.abs().max()) <= 1.0

@@ -334,3 +334,34 @@ def test_free_running_divergence_against_the_oracles_own_spread():
     print("oracle windows (3 batch orders):\n%s\nours:\n%s\noracle spread / level per window: %s" % (
         np.round(runs, 5), np.round(win, 5), np.round((hi - lo) / runs.mean(0), 3)))
     assert np.all(win >= lo - 3 * spread) and np.all(win <= hi + 3 * spread), (win, lo, hi)
+
+
+def test_fp16_training_storage_range_guard_falls_back_to_bf16():
+    """The training passes store fp16 with a saturating conversion; a BatchNorm input whose RMS approaches the edge must be
+    REPORTED, not clipped silently: the step warns and the network continues in bf16 storage (networks.RANGE_LIMIT)."""
+    import warnings
+    from upscaler import networks
+    from upscaler.keras_compat import Adam
+    from upscaler.model import VGG_MSE_LOSS, compile_training_model, make_upscaler_orig
+    gw = O.init_upscaler_orig_weights(seed=11, kernel_size=3, res_block_num=1)
+    gw["res_block/0/conv_pre"][0] = gw["res_block/0/conv_pre"][0] * 4000.0        # conv output RMS far above RANGE_LIMIT
+    x, hr = _data(2, 16, seed=3)
+    up = make_upscaler_orig((64, 64, 3), kernel_size=3, res_block_num=1)
+    up.net.set_weights(gw)
+    assert up.net.train_dtype == networks.TRAIN_DTYPE == torch.float16
+    tm = compile_training_model(up, VGG_MSE_LOSS((64, 64, 3), 1e-3, vgg19=O.init_vgg19_weights()).loss, optimizer=Adam())
+    with warnings.catch_warnings(record=True) as rec:
+        warnings.simplefilter("always")
+        tm.train_on_batch(x, hr)
+    assert any("float16" in str(r.message) for r in rec), [str(r.message) for r in rec]
+    assert up.net.train_dtype == torch.bfloat16
+    ref = O.GeneratorTrainer(gw, O.init_vgg19_weights(), "vgg-mse", 1e-3, res_block_num=1)
+    _sync_weights(up, ref)
+    got, want = tm.train_on_batch(x, hr), ref.train_on_batch(x, hr)             # the bf16 step is a correct one
+    assert np.isfinite(got) and abs(got - want) <= 3e-2 * want
+    # a well-scaled network never trips the guard
+    up2, tm2, _ = _gen_setup(3, 1, "vgg-mse", 1e-3)
+    with warnings.catch_warnings(record=True) as rec2:
+        warnings.simplefilter("always")
+        tm2.train_on_batch(x, hr)
+    assert not rec2 and up2.net.train_dtype == torch.float16

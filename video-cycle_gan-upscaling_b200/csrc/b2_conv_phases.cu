@@ -294,6 +294,7 @@ bool conv_phases_applicable(const ConvIgemmArgs* ph, int nph) {
     if (nph != 4) return false;
     const IgemmParams& p0 = ph[0].p;
     if (p0.n_valid != kPhBN || p0.out_ld != kPhBN || ph[0].w_rows != kPhBN) return false;
+    if (p0.residual || p0.gate || p0.out_fp32) return false;       // their TMA-store epilogue carries neither
     if (ph[0].xC % 64 != 0 || p0.cin != ph[0].xC || p0.cin / 64 > 7) return false;
     if (p0.H < kPhTH || p0.W < kPhTW) return false;
     int total = 0;

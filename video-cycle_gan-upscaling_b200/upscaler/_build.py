@@ -10,7 +10,7 @@ import subprocess
 CSRC = os.path.normpath(os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "csrc"))
 LIB_PATH = os.path.join(CSRC, "libb2srgan.so")
 SOURCES = ["b2_api.cu", "b2_host.cu", "b2_conv_igemm.cu", "b2_conv_direct.cu", "b2_conv_tail.cu", "b2_conv_halo.cu",
-           "b2_elementwise.cu", "b2_conv_wgrad.cu", "b2_conv_scatter.cu", "b2_train_elementwise.cu", "b2_conv_stack.cu", "b2_conv_phases.cu", "b2_conv_phases2.cu", "b2_peer.cu", "b2_bn_train.cu"]
+           "b2_elementwise.cu", "b2_conv_wgrad.cu", "b2_conv_scatter.cu", "b2_train_elementwise.cu", "b2_conv_stack.cu", "b2_conv_phases.cu", "b2_conv_phases2.cu", "b2_peer.cu", "b2_bn_train.cu", "b2_attention.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
 if os.environ.get("B2_BUILD_PROFILING"):       # tools/ only: compiles the environment-driven A/B switches in (b2_host.h)
     NVCC_FLAGS.append("-DB2_PROFILING")

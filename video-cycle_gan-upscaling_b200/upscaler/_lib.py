@@ -60,6 +60,9 @@ _SIGNATURES = {
     "b2_u8_to_f32_norm": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
     "b2_count_saturated": (ctypes.c_int, [_P, _L, _I, _P, _P]),
     "b2_f32_to_u8_denorm": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
+    "b2_gate_mul": (ctypes.c_int, [_P, _I, _I, _P, _P, _L, _I, _I, _P]),
+    "b2_resize_nearest_bilinear_pair": (ctypes.c_int, [_P, _I, _I, _I, _I, _I, _P, _P]),
+    "b2_atanh_conv2d_transpose_small": (ctypes.c_int, [_P, _I, _I, _I, _I, _P, _P, _I, _I, _P, _I, _P]),
     # ---- training step
     "b2_conv2d_s2_dgrad": (ctypes.c_int, [_P] + [_I] * 4 + [_P] + [_I] * 5 + [ctypes.POINTER(Epilogue), _P]),
     "b2_conv2d_wgrad": (ctypes.c_int, [_P] + [_I] * 4 + [_P] + [_I] * 4 + [_P, _I, _P]),
@@ -76,7 +79,7 @@ _SIGNATURES = {
     "b2_bn_part_rows": (ctypes.c_int, []),
     "b2_bn_stats_partial": (ctypes.c_int, [_P, _L, _I, _I, _P, ctypes.POINTER(ctypes.c_int), _P]),
     "b2_bn_fwd_finalize": (ctypes.c_int, [_P, _I, _I, _F, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _P, _P, _P, _F, _F,
-                                          _P, _P, _P, _P]),
+                                          _P, _P, _P, _P, _F, _P]),
     "b2_bn_bwd_partial": (ctypes.c_int, [_P, _P, _L, _I, _I, _P, _P, _I, _F, _P, ctypes.POINTER(ctypes.c_int), _P]),
     "b2_bn_bwd_finalize": (ctypes.c_int, [_P, _I, _I, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _P, _P, _P, _P, _P,
                                           _F, _P]),

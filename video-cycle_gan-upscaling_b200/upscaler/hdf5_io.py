@@ -670,7 +670,10 @@ def load_model(filepath, custom_objects=None, compile=False):
         f = 2 ** nup
         if in_shape is None or in_shape[0] is None or in_shape[1] is None:
             in_shape = (96, 96, 3)                       # fully-convolutional: re-bind with model(Input(shape=...))
-        if int(weights["final/conv"][0].shape[2]) == 227:      # Concatenate([resized input, 224 features]): skip-con
+        if "res_block/0/attention" in names:                   # residual_block_attention layers: make_upscaler_attention
+            m = M.make_upscaler_attention((in_shape[0] * f, in_shape[1] * f, 3), kernel_size=k, filters=filters, upscale_factor=f,
+                                          res_block_num=nres)
+        elif int(weights["final/conv"][0].shape[2]) == 227:    # Concatenate([resized input, 224 features]): skip-con
             m = M.make_upscaler_skip_con((in_shape[0] * f, in_shape[1] * f, 3), kernel_size=k, filters=filters, upscale_factor=f)
         else:
             m = M.make_upscaler_orig((in_shape[0] * f, in_shape[1] * f, 3), kernel_size=k, filters=filters, upscale_factor=f,

@@ -37,7 +37,8 @@ def make_upscaler_skip_con(output_image_shape, kernel_size=5, filters=64, upscal
 def _not_built(name, lines):
     raise NotImplementedError(
         "%s (reference upscaling/upscaler/model.py:%s) is not built on the B200 path yet; the generators that run are "
-        "make_upscaler_orig and make_upscaler_skip_con (SURVEY.md 8f-3 lists the rest as next)" % (name, lines))
+        "make_upscaler_orig, make_upscaler_skip_con and (inference) make_upscaler_attention (SURVEY.md 8f-3 lists the rest as "
+        "next)" % (name, lines))
 
 
 def make_upscaler_unetish(output_image_shape, kernel_size=5, upscale_factor=4, step_size=4, downscale_times=5,
@@ -60,9 +61,16 @@ def make_upscaler_unetish_complex(output_image_shape, kernel_size=5, upscale_fac
 
 
 def make_upscaler_attention(output_image_shape, kernel_size=5, filters=64, upscale_factor=4, res_block_num=16):
-    """model.py:296-328 (sigmoid-gated residual blocks, atanh skip, Conv2DTranspose with kernel scale+1 / stride scale);
-    raises when called."""
-    _not_built("make_upscaler_attention", "296-328")
+    """model.py:296-328 — the generator with sigmoid-gated residual blocks (residual_block_attention, :30-48) and gated
+    upsampling blocks that add Conv2DTranspose(128, scale + 1, strides=scale)(atanh(0.99999 x)) of the network input
+    (upsampling_block_attention, :78-98).  Inference (predict / save / load_model) runs on the B200 kernels; compiling it
+    for training raises (its training step is not built)."""
+    h, w, c = output_image_shape
+    if c != 3:
+        raise ValueError("make_upscaler_attention: the final conv emits 3 channels (model.py:322)")
+    net = networks.UpscalerAttentionNet(kernel_size=kernel_size, filters=filters, upscale_factor=upscale_factor,
+                                        res_block_num=res_block_num)
+    return Model(net=net, input_shape=(h // upscale_factor, w // upscale_factor, c), name="model_1")
 
 
 def make_upscaler_incep_resnet(output_image_shape, filters=64, upscale_factor=4, a_block_type='3path', a_block_num=5,

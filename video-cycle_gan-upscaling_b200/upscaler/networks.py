@@ -20,9 +20,22 @@ import torch
 from . import ops
 
 # 16-bit storage type of the TRAINING passes of the generator and the discriminators (activations, packed weights and
-# gradients; every kernel takes the element type per call).  fp16 keeps 11 significand bits against bf16's 8; its narrow
-# range is handled by carrying the gradients multiplied by a power-of-two-free scale chosen per step (training.py).
-TRAIN_DTYPE = torch.bfloat16
+# gradients; every kernel takes the element type per call).  IEEE fp16 keeps 11 significand bits against bf16's 8: measured
+# on B200 against the fp32 oracle (profiles/r02_s4_train_numerics.log, 16 residual blocks) the generator's weight gradients
+# sit at a median relative L2 error of 0.14 (worst cosine 0.978) instead of 0.35 (0.872), the first loss at 6e-5 instead of
+# 9e-4, and the direction of the two-pass critic gradient g(real) - g(fake) survives (cosine 0.99 instead of 0.3-0.6, which
+# is what the fp32 oracle itself gives once its activations are rounded to bf16: profiles/r02_s4_disc2_grad_check.log).
+# fp16's narrow range is handled on both sides: gradients are carried multiplied by a per-step scale (training.GRAD_SCALE),
+# and the forward range is watched (RANGE_LIMIT below): if it is ever approached the network drops to bf16 storage.
+TRAIN_DTYPE = torch.float16
+# fp16 training storage stores with a saturating conversion (+-65504).  Every train-mode BatchNorm finalize raises a device
+# flag when a channel of its input has a root mean square above RANGE_LIMIT (1/32 of the edge), and the step samples the
+# tensors no BatchNorm sees (head conv, Conv2DTranspose outputs, generated image) with count_saturated; the host reads the
+# flag every RANGE_CHECK_EVERY steps and switches that network to bf16 storage with a warning (ON_RANGE = "fallback") or
+# raises FloatingPointError ("raise").
+RANGE_LIMIT = 2048.0
+RANGE_CHECK_EVERY = 32
+ON_RANGE = "fallback"
 
 BN_EPS = 1e-3       # keras BatchNormalization defaults, model.py:20
 BN_MOMENTUM = 0.99
@@ -57,6 +70,35 @@ def upscaler_orig_layer_specs(kernel_size=5, filters=64, upscale_factor=4, res_b
         specs.append(("upscaling/%d/block/conv_transp" % i, "convT", dict(kh=uk, kw=uk, cin=cin, cout=up_filters)))
         cin = up_filters
     specs.append(("final/conv", "conv", dict(kh=9, kw=9, cin=cin + (3 if concat_input else 0), cout=3)))
+    return specs
+
+
+ATT_UP_FILTERS = 128      # make_upscaler_attention passes filters = 128 to its upsampling blocks (model.py:319)
+
+
+def upscaler_attention_layer_specs(kernel_size=5, filters=64, upscale_factor=4, res_block_num=16):
+    """make_upscaler_attention (model.py:296-328, blocks :30-48 and :78-98) in graph order with the reference's layer names."""
+    k = kernel_size
+    specs = [("initial/conv", "conv", dict(kh=9, kw=9, cin=3, cout=filters)),
+             ("initial/prelu", "prelu", dict(c=filters))]
+    for i in range(res_block_num):
+        n = "res_block/%d" % i
+        specs += [(n + "/attention", "conv", dict(kh=k, kw=k, cin=3, cout=filters)),
+                  (n + "/conv_pre", "conv", dict(kh=k, kw=k, cin=filters, cout=filters)),
+                  (n + "/batch_norm_pre", "bn", dict(c=filters)),
+                  (n + "/prelu", "prelu", dict(c=filters)),
+                  (n + "/conv_post", "conv", dict(kh=k, kw=k, cin=filters, cout=filters)),
+                  (n + "/batch_norm_post", "bn", dict(c=filters))]
+    specs += [("after_res/conv", "conv", dict(kh=k, kw=k, cin=filters, cout=filters)),
+              ("after_res/batch_norm", "bn", dict(c=filters))]
+    cin = filters
+    for i in range(int(math.log(upscale_factor, 2))):
+        n, scale = "upscaling/%d/block" % i, 2 ** (i + 1)
+        specs += [(n + "/attention", "conv", dict(kh=k, kw=k, cin=6, cout=cin)),
+                  (n + "/conv_transp", "convT", dict(kh=k, kw=k, cin=cin, cout=ATT_UP_FILTERS)),
+                  (n + "/to_add_input_conv_transp", "convT", dict(kh=scale + 1, kw=scale + 1, cin=3, cout=ATT_UP_FILTERS))]
+        cin = ATT_UP_FILTERS
+    specs.append(("final/conv", "conv", dict(kh=9, kw=9, cin=cin, cout=3)))
     return specs
 
 
@@ -173,7 +215,7 @@ def _shapes(kind, c):
 class Net:
     """Flat parameter store + packed 16-bit weight copies shared by the three networks."""
 
-    train_dtype = torch.bfloat16   # gradients need bf16's range; every kernel takes the element type per call
+    train_dtype = torch.float16    # see TRAIN_DTYPE; every kernel takes the element type per call
 
     def __init__(self, specs, weights, seed, device):
         self.on_gpu = torch.cuda.is_available()
@@ -304,6 +346,53 @@ class Net:
         self.layer_events.setdefault(name, []).append((e0, e1))
         return r
 
+    # ---------------------------------------------------------------- fp16 training-storage range guard
+    def range_flag(self):
+        """One-float device flag the BatchNorm finalize launches of this network raise (None for bf16 storage)."""
+        if self.train_dtype != torch.float16:
+            return None
+        f = self._buffers.get("range_flag")
+        if f is None:
+            f = self._buffers["range_flag"] = torch.zeros(1, dtype=torch.float32, device=self.device)
+        return f
+
+    def set_train_dtype(self, dtype):
+        """Switches the 16-bit storage type of the training passes (activations, packed weights, gradients)."""
+        if dtype not in (torch.float16, torch.bfloat16):
+            raise ValueError("training storage is float16 or bfloat16")
+        self.train_dtype = dtype
+        ps = self._pack_sets.get("train")
+        if ps is not None:
+            ps["dtype"], ps["buf"] = dtype, None
+            if self.on_gpu:
+                self.refresh(("train",))
+
+    def check_range(self, extra=()):
+        """Host side of the guard: reads the flag (one small D2H) plus a saturation count of `extra` tensors; on a hit warns and
+        drops to bf16 storage, or raises (ON_RANGE).  Returns True when the storage type was switched."""
+        flag = self.range_flag()
+        if flag is None:
+            return False
+        cnt = self._buffers.get("range_count")
+        if cnt is None:
+            cnt = self._buffers["range_count"] = torch.zeros(1, dtype=torch.int32, device=self.device)
+        for t in extra:
+            if t is not None and t.dtype == torch.float16:
+                ops.count_saturated(t, cnt)
+        hit = float(flag.item()) != 0.0 or int(cnt.item()) != 0
+        if not hit:
+            return False
+        flag.zero_()
+        cnt.zero_()
+        msg = ("%s: the training passes approached the edge of float16 storage (a BatchNorm input channel with RMS >= %g, or "
+               "saturated stored values)" % (type(self).__name__, RANGE_LIMIT))
+        if ON_RANGE == "raise":
+            raise FloatingPointError(msg)
+        import warnings
+        warnings.warn(msg + "; switching this network's training storage to bfloat16", RuntimeWarning)
+        self.set_train_dtype(torch.bfloat16)
+        return True
+
     def _need_gpu(self):
         if not self.on_gpu:
             raise RuntimeError("this network runs on hand-written sm_100a kernels only; no CUDA device is available")
@@ -324,13 +413,16 @@ class Net:
             mm = mv = None
         world = sync.world if sync is not None else 1
         peer = sync.peer_for(z.device) if sync is not None else None
+        watch = self.range_flag() if z.dtype == torch.float16 else None
         if sync is None or peer is not None:
-            ops.bn_fwd_finalize(part, nparts, C, rows * world, gamma, beta, aff, mm, mv, peer=peer, eps=BN_EPS, momentum=BN_MOMENTUM)
+            ops.bn_fwd_finalize(part, nparts, C, rows * world, gamma, beta, aff, mm, mv, peer=peer, eps=BN_EPS, momentum=BN_MOMENTUM,
+                                range_watch=watch, range_limit=RANGE_LIMIT)
         else:                   # replicas that cannot map each other's memory: sums over NCCL, two stage-2 launches
             sums = torch.empty(2 * C, dtype=torch.float32, device=z.device)
             ops.bn_fwd_finalize(part, nparts, C, rows, None, None, None, sums_out=sums)
             sync.all_reduce(sums)
-            ops.bn_fwd_finalize(sums, 1, C, rows * world, gamma, beta, aff, mm, mv, eps=BN_EPS, momentum=BN_MOMENTUM)
+            ops.bn_fwd_finalize(sums, 1, C, rows * world, gamma, beta, aff, mm, mv, eps=BN_EPS, momentum=BN_MOMENTUM,
+                                range_watch=watch, range_limit=RANGE_LIMIT)
         ops.affine_act(z, out, aff[:C], aff[C:2 * C], alpha, act, leaky, residual)
         tape[key] = (z, aff, rows * world)
         return out
@@ -390,14 +482,17 @@ class UpscalerOrigNet(Net):
         self.train_dtype = train_dtype or TRAIN_DTYPE
         self.up_kernel = self.up_kernel or kernel_size
         self.prefinal_kernel = self.prefinal_kernel or kernel_size
-        super().__init__(upscaler_orig_layer_specs(kernel_size, filters, upscale_factor, res_block_num, self.up_filters,
-                                                   self.up_kernel, self.prefinal_kernel, self.concat_input), weights, seed, device)
+        super().__init__(self._layer_specs(), weights, seed, device)
         self._infer = {}
         self._final_rows = False
         self._sat_pending, self.saturation_report = True, {}
         self._build_index_maps()
         if self.on_gpu:
             self.refresh()
+
+    def _layer_specs(self):
+        return upscaler_orig_layer_specs(self.kernel_size, self.filters, self.upscale_factor, self.res_block_num, self.up_filters,
+                                         self.up_kernel, self.prefinal_kernel, self.concat_input)
 
     # ---------------------------------------------------------------- weights
     def _build_index_maps(self):
@@ -760,6 +855,166 @@ class UpscalerSkipConNet(UpscalerOrigNet):
     layout and gathered back into the Keras one)."""
 
     up_filters, up_kernel, prefinal_kernel, concat_input, supports_training = 224, 3, 3, True, True
+
+
+class UpscalerAttentionNet(UpscalerOrigNet):
+    """make_upscaler_attention (model.py:296-328): the `orig` trunk with every residual block's input gated by
+    sigmoid(conv(network input)) (residual_block_attention, :30-48) and upsampling blocks that gate their input by
+    sigmoid(conv(Concatenate([nearest, bilinear] resize of the network input))), run Conv2DTranspose(128, k, stride 2) +
+    LeakyReLU(0.2) and add Conv2DTranspose(128, scale + 1, stride scale)(atanh(0.99999 * network input))
+    (upsampling_block_attention, :78-98).  Inference path (Model.predict / load_model / save); the training step of this
+    variant is not built.
+    On the B200 path: the 16 residual-block attention convs all read the same 3-channel image, so they run as ONE
+    convolution with 16 x 64 = 1024 output channels over the row-folded input (kw taps x 3 colours in 64 channels, the head
+    conv's trick) -- a full-width tensor-core GEMM instead of sixteen N = 64 ones; a block takes its 64-channel slice in the
+    gate kernel (b2_gate_mul).  The atanh / stride-`scale` Conv2DTranspose of the 3-channel input is write-bound
+    (b2_atanh_conv2d_transpose_small) and enters the block's Conv2DTranspose as the epilogue's residual operand."""
+
+    supports_training = False
+    extra_layers = [("after_res/add", "add"), ("final/tanh", "activation")]
+
+    def _layer_specs(self):
+        return upscaler_attention_layer_specs(self.kernel_size, self.filters, self.upscale_factor, self.res_block_num)
+
+    def _build_index_maps(self):
+        k, f = self.kernel_size, self.filters
+        if k * 6 > 64:
+            raise ValueError("make_upscaler_attention on the B200 path: kernel_size <= 10 (row fold of the 6-channel attention input)")
+        self._final_chan_map, self._convT_wgrad_idx, self._convT_bias_idx = None, {}, {}
+        self._final_rows = True
+        off0 = None
+        att_idx = []
+        for name, kind, c in self.specs:
+            if name.endswith("to_add_input_conv_transp"):
+                continue                                   # read as fp32 masters by b2_atanh_conv2d_transpose_small
+            if kind == "conv":
+                if name == "final/conv":
+                    idx = ops.conv_scatter_pack_index(9, 9, c["cin"], 3)
+                elif name.startswith("res_block/") and name.endswith("/attention"):
+                    o = self.offsets[(name, 0)][0]
+                    off0 = o if off0 is None else off0
+                    ix = ops.conv_rowfold_pack_index(k, k, 3, f).astype(np.int64)
+                    att_idx.append(np.where(ix >= 0, ix + (o - off0), -1))
+                    continue
+                elif c["cin"] < 64:
+                    idx = ops.conv_rowfold_pack_index(c["kh"], c["kw"], c["cin"], c["cout"])
+                else:
+                    idx = ops.conv_pack_index(c["kh"], c["kw"], c["cin"], c["cout"])
+            elif kind == "convT":
+                idx = ops.convT_pack_index(c["kh"], c["kw"], c["cin"], c["cout"])
+            else:
+                continue
+            self.add_pack("infer", name, name, idx)
+        if att_idx:      # [res_block_num * 64][k][64]: all residual-block attention convs as one wide convolution
+            self.add_pack("infer", "res_block/*/attention", "res_block/0/attention", np.concatenate(att_idx, axis=0).astype(np.int32))
+        self.build_packs({"infer": self.infer_dtype})
+
+    def refresh(self, sets=("infer",)):
+        for s in sets:
+            self.refresh_packs(s)
+            setattr(self, "_%s_dirty" % s, False)
+        if "infer" not in sets:
+            return
+        self._sat_pending = True
+        w, f, R = self.weights, self.filters, self.res_block_num
+        fold = self._vec("fold", 2 * 64 * (2 * R + 1))
+        inf, slot = {}, [0]
+
+        def fold_bn(conv, bn):
+            i = slot[0]
+            slot[0] += 1
+            scale, shift = fold[2 * 64 * i:2 * 64 * i + 64], fold[2 * 64 * i + 64:2 * 64 * (i + 1)]
+            gamma, beta, mean, var = w[bn]
+            ops.bn_fold(gamma, beta, mean, var, w[conv][1], scale, shift, BN_EPS)
+            return scale, shift
+
+        inf["initial/conv"] = (None, w["initial/conv"][1], w["initial/prelu"][0].reshape(-1))
+        att_bias = self._vec("att_bias", f * R)
+        for i in range(R):
+            n = "res_block/%d" % i
+            att_bias[f * i:f * (i + 1)].copy_(w[n + "/attention"][1])
+            s, b = fold_bn(n + "/conv_pre", n + "/batch_norm_pre")
+            inf[n + "/conv_pre"] = (s, b, w[n + "/prelu"][0].reshape(-1))
+            s, b = fold_bn(n + "/conv_post", n + "/batch_norm_post")
+            inf[n + "/conv_post"] = (s, b, None)
+        inf["res_block/*/attention"] = (None, att_bias, None)
+        s, b = fold_bn("after_res/conv", "after_res/batch_norm")
+        inf["after_res/conv"] = (s, b, None)
+        self._infer = inf
+
+    def _sat_names(self):
+        names = ["initial/conv", "res_block/*/attention"]
+        for i in range(self.res_block_num):
+            names += ["res_block/%d/conv_pre" % i, "res_block/%d/conv_post" % i]
+        names.append("after_res/conv")
+        for i in range(self.upscale_times):
+            names += ["upscaling/%d/block/attention" % i, "upscaling/%d/block/to_add_input_conv_transp" % i,
+                      "upscaling/%d/block/conv_transp" % i]
+        return names
+
+    def forward_train(self, *a, **k):
+        raise NotImplementedError("make_upscaler_attention: the inference path is built on the B200 kernels; its training step "
+                                  "is not (use make_upscaler_orig or make_upscaler_skip_con for training)")
+
+    backward = forward_train
+
+    def _forward_infer(self, x, out, counters):
+        B, H, W, C = x.shape
+        k, f, dt, R = self.kernel_size, self.filters, self.infer_dtype, self.res_block_num
+        inf, pk, w = self._infer, self._packed["infer"], self.weights
+        slot = [0]
+
+        def chk(t):
+            if counters is not None:
+                ops.count_saturated(t, counters[slot[0]:slot[0] + 1])
+                slot[0] += 1
+            return t
+        T = self._timed
+        row_taps = lambda kk: [(0, dx - (kk - 1) // 2) for dx in range(kk)]
+        xp = T("initial/fold", lambda: ops.fold_taps(x, row_taps(9), out=self._buf("fold", (B, H, W, 64), dt), dtype=dt))
+        s, b, a = inf["initial/conv"]
+        skip = chk(T("initial/conv", lambda: ops.conv2d(xp, pk["initial/conv"], f, 9, 1, out=self._buf("skip", (B, H, W, f), dt),
+                                                        scale=s, shift=b, alpha=a, act=ops.ACT_PRELU)))
+        # every residual block's attention map in one convolution: (B,H,W, R*64) pre-sigmoid
+        xa = T("res_block/*/attention", lambda: ops.fold_taps(x, row_taps(k), out=self._buf("fold_att", (B, H, W, 64), dt), dtype=dt))
+        att = chk(T("res_block/*/attention", lambda: ops.conv2d(xa, pk["res_block/*/attention"], f * R, k, 1,
+                                                                out=self._buf("att", (B, H, W, f * R), dt),
+                                                                shift=inf["res_block/*/attention"][1])))
+        m = skip
+        ping = [self._buf("t%d" % i, (B, H, W, f), dt) for i in range(3)]
+        gated = self._buf("gated", (B, H, W, f), dt)
+        for i in range(R):
+            n = "res_block/%d" % i
+            free = [t for t in ping if t is not m]
+            T("res_block/*/attention_multiply", lambda: ops.gate_mul(att, m, gated, att_c0=f * i))
+            s, b, a = inf[n + "/conv_pre"]
+            h = chk(T("res_block/*/conv_pre", lambda: ops.conv2d(gated, pk[n + "/conv_pre"], f, k, k, out=free[0], scale=s, shift=b,
+                                                                 alpha=a, act=ops.ACT_PRELU)))
+            s, b, _ = inf[n + "/conv_post"]
+            m = chk(T("res_block/*/conv_post", lambda: ops.conv2d(h, pk[n + "/conv_post"], f, k, k, out=free[1], scale=s,
+                                                                  shift=b, residual=m)))
+        free = [t for t in ping if t is not m]
+        s, b, _ = inf["after_res/conv"]
+        m = chk(T("after_res/conv", lambda: ops.conv2d(m, pk["after_res/conv"], f, k, k, out=free[0], scale=s, shift=b, residual=skip)))
+        h_, w_, cin = H, W, f
+        for i in range(self.upscale_times):
+            n, scale = "upscaling/%d/block" % i, 2 ** (i + 1)
+            r = scale // 2
+            iu = T(n + "/upscaled_concat", lambda: ops.resize_nearest_bilinear_pair(x, r))
+            ia = T(n + "/attention", lambda: ops.fold_taps(iu, row_taps(k), out=self._buf("fold_up%d" % i, (B, h_, w_, 64), dt), dtype=dt))
+            au = chk(T(n + "/attention", lambda: ops.conv2d(ia, pk[n + "/attention"], cin, k, 1,
+                                                            out=self._buf("att_up%d" % i, (B, h_, w_, cin), dt), shift=w[n + "/attention"][1])))
+            g = T(n + "/attention_multiply", lambda: ops.gate_mul(au, m, self._buf("gated_up%d" % i, (B, h_, w_, cin), dt)))
+            wt, bt = w[n + "/to_add_input_conv_transp"]
+            ta = chk(T(n + "/to_add_input_conv_transp", lambda: ops.atanh_conv2d_transpose_small(
+                x, wt, bt, scale, out=self._buf("to_add%d" % i, (B, 2 * h_, 2 * w_, ATT_UP_FILTERS), dt))))
+            m = chk(T(n + "/conv_transp", lambda: ops.conv2d_transpose_s2(
+                g, pk[n + "/conv_transp"], ATT_UP_FILTERS, k, k, out=self._buf("up%d" % i, (B, 2 * h_, 2 * w_, ATT_UP_FILTERS), dt),
+                shift=w[n + "/conv_transp"][1], act=ops.ACT_LEAKY, leaky=0.2, residual=ta)))
+            h_, w_, cin = 2 * h_, 2 * w_, ATT_UP_FILTERS
+        if out is None:
+            out = torch.empty((B, h_, w_, 3), dtype=torch.float32, device=self.device)
+        return T("final/conv", lambda: ops.conv2d_scatter(m, pk["final/conv"], 3, 9, 9, bias=w["final/conv"][1], act=ops.ACT_TANH, out=out))
 
 
 class Vgg19Net(Net):

@@ -134,8 +134,9 @@ def conv2d_scatter(x, w_taps, cout, kh, kw, bias=None, act=ACT_TANH, out=None):
 
 
 def conv2d_transpose_s2(x, w_packed, cout, kh, kw, out=None, scale=None, shift=None, alpha=None, act=ACT_NONE,
-                        leaky=0.0, direct=False):
-    """Conv2DTranspose(strides=2, padding='same') forward (reference: model.py:72)."""
+                        leaky=0.0, direct=False, residual=None):
+    """Conv2DTranspose(strides=2, padding='same') forward (reference: model.py:72).  `residual` (same shape / type as the
+    output) is added after the activation (Add of model.py:97)."""
     B, H, W, Cin = x.shape
     f16 = _elem_flag(x, w_packed)
     if Cin % 64 != 0:
@@ -146,8 +147,10 @@ def conv2d_transpose_s2(x, w_packed, cout, kh, kw, out=None, scale=None, shift=N
         out = torch.empty((B, 2 * H, 2 * W, cout), dtype=x.dtype, device=x.device)
     elif tuple(out.shape) != (B, 2 * H, 2 * W, cout) or out.dtype != x.dtype:
         raise ValueError("conv2d_transpose_s2: bad output shape / dtype")
-    _require_cuda(x, w_packed, out, scale, shift, alpha)
-    ep = _lib.make_epilogue(out, scale, shift, alpha, act, leaky, None, f16)
+    if residual is not None and (tuple(residual.shape) != tuple(out.shape) or residual.dtype != out.dtype):
+        raise ValueError("conv2d_transpose_s2: residual must match the output")
+    _require_cuda(x, w_packed, out, scale, shift, alpha, residual)
+    ep = _lib.make_epilogue(out, scale, shift, alpha, act, leaky, residual, f16)
     lib = _lib.load()
     if direct:
         rc = lib.b2_conv2d_direct(_lib.ptr(x), B, H, W, Cin, _lib.ptr(w_packed), cout, kh, kw, 1, 1, ctypes.byref(ep),
@@ -208,6 +211,52 @@ def resize_bilinear_into(x, out, c0, factor):
     rc = _lib.load().b2_resize_bilinear_into(_lib.ptr(x), B, H, W, C, factor, _lib.ptr(out), out.shape[3], c0,
                                              1 if out.dtype == torch.float16 else 0, _lib.stream_ptr())
     _lib.check(rc, "b2_resize_bilinear_into")
+    _count(1)
+    return out
+
+
+def gate_mul(att, m, out=None, att_c0=0):
+    """Multiply([sigmoid(attention), stream]) (model.py:34-36, 88-91): out = sigmoid(att[..., att_c0:att_c0+C]) * m; `att` may
+    be wider than m (the attention convs of all residual blocks evaluated as one convolution)."""
+    C = m.shape[-1]
+    if att.dtype != m.dtype or m.dtype not in (torch.float16, torch.bfloat16) or tuple(att.shape[:-1]) != tuple(m.shape[:-1]):
+        raise ValueError("gate_mul: 16-bit operands over the same pixel grid expected")
+    if out is None:
+        out = torch.empty_like(m)
+    _require_cuda(att, m, out)
+    rc = _lib.load().b2_gate_mul(_lib.ptr(att), att.shape[-1], att_c0, _lib.ptr(m), _lib.ptr(out), m.numel() // C, C,
+                                 1 if m.dtype == torch.float16 else 0, _lib.stream_ptr())
+    _lib.check(rc, "b2_gate_mul")
+    _count(1)
+    return out
+
+
+def resize_nearest_bilinear_pair(x, factor):
+    """Concatenate([nearest, bilinear] x`factor` resize of the fp32 NHWC image) (model.py:80-82) -> fp32 (B, fH, fW, 2C)."""
+    B, H, W, C = x.shape
+    if x.dtype != torch.float32:
+        raise ValueError("resize_nearest_bilinear_pair expects float32")
+    out = torch.empty((B, H * factor, W * factor, 2 * C), dtype=torch.float32, device=x.device)
+    _require_cuda(x, out)
+    rc = _lib.load().b2_resize_nearest_bilinear_pair(_lib.ptr(x), B, H, W, C, factor, _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(rc, "b2_resize_nearest_bilinear_pair")
+    _count(1)
+    return out
+
+
+def atanh_conv2d_transpose_small(x, w, bias, stride, out=None, dtype=torch.float16):
+    """Conv2DTranspose(Cout, stride + 1, strides=stride, 'same')(atanh(0.99999 x)) on the 3-channel fp32 input (model.py:94-95);
+    w fp32 in the Keras layout (k, k, Cout, 3)."""
+    B, H, W, Cin = x.shape
+    k, cout = stride + 1, w.shape[2]
+    if x.dtype != torch.float32 or w.dtype != torch.float32 or tuple(w.shape) != (k, k, cout, Cin):
+        raise ValueError("atanh_conv2d_transpose_small: fp32 input and a (%d,%d,Cout,%d) fp32 kernel expected" % (k, k, Cin))
+    if out is None:
+        out = torch.empty((B, H * stride, W * stride, cout), dtype=dtype, device=x.device)
+    _require_cuda(x, w, bias, out)
+    rc = _lib.load().b2_atanh_conv2d_transpose_small(_lib.ptr(x), B, H, W, Cin, _lib.ptr(w), _lib.ptr(bias), stride, cout,
+                                                     _lib.ptr(out), 1 if out.dtype == torch.float16 else 0, _lib.stream_ptr())
+    _lib.check(rc, "b2_atanh_conv2d_transpose_small")
     _count(1)
     return out
 
@@ -443,13 +492,15 @@ def bn_stats_partial(x, part=None):
 
 
 def bn_fwd_finalize(part, nparts, C, count, gamma, beta, aff, moving_mean=None, moving_var=None, peer=None, sums_out=None,
-                    eps=1e-3, momentum=0.99):
+                    eps=1e-3, momentum=0.99, range_watch=None, range_limit=0.0):
     """Stage 2: partial rows (+ the other replicas' through `peer`) -> aff = [scale | shift | mean | invstd]; updates the
-    moving statistics when given.  aff=None with sums_out: only the summed statistics (NCCL fallback)."""
+    moving statistics when given.  aff=None with sums_out: only the summed statistics (NCCL fallback).  `range_watch`
+    (one float32) is set to 1 when a channel's root mean square reaches `range_limit` (guard of fp16 storage)."""
     regions, rank, world, epoch = _peer_args(peer)
     rc = _lib.load().b2_bn_fwd_finalize(_lib.ptr(part), int(nparts), int(C), float(count), regions, rank, world, epoch,
                                         _lib.ptr(sums_out), _lib.ptr(gamma), _lib.ptr(beta), eps, momentum,
-                                        _lib.ptr(moving_mean), _lib.ptr(moving_var), _lib.ptr(aff), _lib.stream_ptr())
+                                        _lib.ptr(moving_mean), _lib.ptr(moving_var), _lib.ptr(aff), _lib.ptr(range_watch),
+                                        float(range_limit), _lib.stream_ptr())
     _lib.check(rc, "b2_bn_fwd_finalize")
     _count(1)
     return aff

@@ -280,6 +280,7 @@ class Compiled:
         self.slots = {}
         self.gan_losses = None
         self.reducer = GradReducer()
+        self._ticks = {}
 
     def _moves(self, which):
         """Whether this compiled model's training-phase passes update the moving statistics of G / D: sampled once, at
@@ -289,6 +290,20 @@ class Compiled:
             m = self.G_model if which == "G" else self.D_model
             self.__dict__[key] = bool(FROZEN_MODEL_UPDATES_MOVING_STATS or m is None or m.trainable)
         return self.__dict__[key]
+
+    # -------------------------------------------------------------- fp16 storage range guard (networks.RANGE_LIMIT)
+    def _range_tick(self, net, tape=None):
+        """First step and every RANGE_CHECK_EVERY-th: read the network's range flag and sample the stored tensors no BatchNorm
+        watches (head conv, Conv2DTranspose outputs); a hit drops that network to bf16 storage (or raises)."""
+        from . import networks
+        if net.train_dtype != torch.float16:
+            return
+        n = self._ticks[id(net)] = self._ticks.get(id(net), 0) + 1
+        if n == 1 or n % networks.RANGE_CHECK_EVERY == 0:
+            extra = []
+            if tape is not None and "ups" in tape:
+                extra = [tape["head"][1]] + list(tape["ups"][1:])
+            net.check_range(extra)
 
     # -------------------------------------------------------------- Adam
     @staticmethod
@@ -371,6 +386,7 @@ class Compiled:
         G.ensure_grads().zero_()
         G.backward(tape, dz, sync, on_ready=self.reducer.hook(G.grad_flat, G.n_trainable))
         self._adam(G, S)
+        self._range_tick(G, tape)
         return self._mean_over_ranks(loss)[0]
 
     def step_disc(self, x, y):
@@ -389,6 +405,7 @@ class Compiled:
         D.ensure_grads().zero_()
         D.backward(tape, ds, True, False, sync, on_ready=self.reducer.hook(D.grad_flat, D.n_trainable))
         self._adam(D, S)
+        self._range_tick(D)
         return self._mean_over_ranks(loss)[0]
 
     def step_gan(self, x, y_true, adv_y):
@@ -418,6 +435,8 @@ class Compiled:
         G.ensure_grads().zero_()
         G.backward(gtape, dz, sync, on_ready=self.reducer.hook(G.grad_flat, G.n_trainable))
         self._adam(G, S)
+        self._range_tick(G, gtape)
+        self._range_tick(D)
         lc, la = self._mean_over_ranks(losses)
         return [cw * lc + dw * la, lc, la]
 
@@ -456,6 +475,7 @@ class Compiled:
             D.backward(tape, ds, True, False, sync,
                        on_ready=self.reducer.hook(D.grad_flat, D.n_trainable) if scores is sf else None)
         self._adam(D, S)
+        self._range_tick(D)
         return val
 
     def step_gan2(self, x, real, y_true):
@@ -487,6 +507,8 @@ class Compiled:
         G.ensure_grads().zero_()
         G.backward(gtape, dz, sync, on_ready=self.reducer.hook(G.grad_flat, G.n_trainable))
         self._adam(G, S)
+        self._range_tick(G, gtape)
+        self._range_tick(D)
         return [cw * lc + dw * la, lc, la]
 
     def _mean_over_ranks(self, buf):
@@ -550,7 +572,11 @@ def compile_model(model, loss, optimizer, loss_weights):
             return ContentLoss(owner.kind, owner.rate, owner.net)
         raise ValueError("unsupported content loss %r: the B200 path implements VGG_LOSS / VGG_MSE_LOSS / VGG_MAE_LOSS" % (l,))
 
-    isG = lambda n: isinstance(n, UpscalerOrigNet)
+    def isG(n):
+        if isinstance(n, UpscalerOrigNet) and not n.supports_training:
+            raise NotImplementedError("%s: the inference path of this generator is built on the B200 kernels, its training "
+                                      "step is not (train make_upscaler_orig / make_upscaler_skip_con)" % type(n).__name__)
+        return isinstance(n, UpscalerOrigNet)
     isD = lambda n: isinstance(n, DiscriminatorSimple512Net)
     n_in = len(model._inputs)
     c = None
