@@ -244,7 +244,7 @@ def bench_train_step(args, rank, world, dev, barrier, B=16, hw=(96, 96), builder
     out = {"metric": "train samples/s", "value": world * B * 1000.0 / ms, "unit": "samples/s" if calls == 1 else "HR frames/s (iterations/s x batch)",
            "ms_per_step": ms, "steps": args.train_steps,
            "config": "%s, %s content loss, %d x (%dx%d -> %dx%d) per GPU, make_upscaler_%s k=%d, "
-           "bf16 storage / fp32 accumulate / fp32 master weights + Adam%s" % (what, loss_kind, B, h, w_, 4 * h, 4 * w_, builder.replace("-", "_"), ks, ", NCCL data-parallel (SyncBN sums + bucketed gradient all-reduce)" if world > 1 else ""),
+           "%s storage / fp32 accumulate / fp32 master weights + Adam%s" % (what, loss_kind, B, h, w_, 4 * h, 4 * w_, builder.replace("-", "_"), ks, str(up.net.train_dtype).replace("torch.", ""), ", NCCL data-parallel (SyncBN sums + bucketed gradient all-reduce)" if world > 1 else ""),
            "train_on_batch_calls_per_step": calls,
            "gpu_launches_per_step": ops.launch_count() // args.train_steps, "loss": float(loss),
            "h2d_bytes_per_step": int(sum(x.nbytes for x in xs) + calls * hr.nbytes), "d2h_bytes_per_step": 4 * calls}
@@ -304,7 +304,7 @@ def bench_gan_step(args, rank, world, dev, barrier):
     tf = GAN_STEP_FLOPS_PER_IMAGE[ks] * n * world / (ms * 1e-3) / 1e12
     out = {"metric": "GAN train LR images/s", "value": world * n * 1000.0 / ms, "unit": "samples/s", "ms_per_step": ms, "steps": steps,
            "config": "train_gan.py step: predict + discriminator step (2n images) + GAN step, n = %d LR images of 128x128 -> 512x512 per GPU, "
-                     "k=%d, simple_512 discriminator, vgg-mse + Wasserstein, shared Adam%s" % (n, ks, ", NCCL data-parallel" if world > 1 else ""),
+                     "k=%d, simple_512 discriminator, vgg-mse + Wasserstein, shared Adam, %s training storage%s" % (n, ks, str(G.net.train_dtype).replace("torch.", ""), ", NCCL data-parallel" if world > 1 else ""),
            "algorithmic_tflops": tf, "frac_of_bf16_sustained_peak": tf / world / peaks["bf16_tflops_sustained"],
            "gpu_launches_per_step": ops.launch_count() // steps, "loss_disc": float(ld), "loss_gan": [float(v) for v in lg]}
     del gen_train, disc_train, gan_train, G, D

@@ -121,7 +121,11 @@ def test_train_gan3_py_loop_iterations(family, act):
     _check("train_gan3.py %s/%s generator adversarial loss" % (family, act), la, la_ref, sa)
 
 
-def _compare_d_grads(D, ref, S=1.0, tol_n=0.2, tol_c=0.9):
+def _compare_d_grads(D, ref, S=1.0, tol_n=0.2, tol_c=0.9, sens=None):
+    """Per-tensor comparison of the discriminator's weight gradients with the oracle's autograd gradients.  With `sens`
+    (the oracle's own gradients recomputed with every stored activation rounded to the CUDA path's 16-bit type) the bar is
+    DERIVED: a tensor's relative L2 deviation may be at most twice the deviation that storage rounding alone causes in the
+    fp32 oracle (+ 2 %); without it the fixed norm / cosine bars apply."""
     bad, worst = [], (0.0, 1.0)
     for name, kind, cfg in D.net.specs:
         for j, gt in enumerate(D.net.grads[name]):
@@ -136,28 +140,51 @@ def _compare_d_grads(D, ref, S=1.0, tol_n=0.2, tol_c=0.9):
             nr = np.linalg.norm(got) / np.linalg.norm(r)
             cos = float(np.vdot(got, r) / max(np.linalg.norm(got) * np.linalg.norm(r), 1e-30))
             worst = (max(worst[0], abs(nr - 1)), min(worst[1], cos))
-            if abs(nr - 1) > tol_n or cos < tol_c:
+            if sens is not None:
+                d = float(np.linalg.norm(got - r) / np.linalg.norm(r))
+                dq = float(np.linalg.norm(sens[name][j].numpy() - r) / np.linalg.norm(r))
+                if d > 2.0 * dq + 2e-2:
+                    bad.append((name, j, "rel L2 %.3f vs oracle storage-rounding %.3f" % (d, dq), round(cos, 4)))
+            elif abs(nr - 1) > tol_n or cos < tol_c:
                 bad.append((name, j, round(nr, 4), round(cos, 4)))
     print("   discriminator weight gradients: worst |norm ratio - 1| %.4f, worst cos %.4f" % worst)
     assert not bad, bad
+
+
+def _oracle_disc2_grads_with_rounded_storage(ref, real, fake, family, act, q):
+    """The fp32 oracle's gradient of the two-input discriminator loss with every stored activation rounded to the CUDA
+    path's 16-bit type (straight-through rounding): what storage rounding ALONE does to this gradient.  It is large here by
+    construction -- the loss is a difference of two batch means that nearly cancel for an untrained critic."""
+    r = ref.dfwd(ref.d, real, ref.dact, True, [], q=q)
+    f = ref.dfwd(ref.d, fake, ref.dact, True, [], q=q)
+    loss, _ = O.gan_losses(family, act, r, f)
+    loss.backward()
+    out = {k: [None if t.grad is None else t.grad.detach().clone() for t in ts] for k, ts in ref.d.items()}
+    for ts in ref.d.values():
+        for t in ts:
+            t.grad = None
+    return out
 
 
 @pytest.mark.parametrize("family,act", [("wasserstein", "none"), ("relativistic", "log-sigm"), ("relativistic", "bi-log")])
 def test_disc2_weight_gradients_two_pass_backward(family, act):
     """step_disc2 runs D forward twice (real, fake) and backpropagates both tapes into one gradient buffer; every weight
     gradient must equal autograd's through  act(mean(D(real)) - mean(D(fake)))  (train_gan3.py:353, model.py:215-261).
-    Bars as in test_discriminator_forward_backward (this network amplifies storage rounding strongly)."""
+    The bar is derived from the oracle itself (see _compare_d_grads): on this input -- an untrained critic, real and generated
+    batches normalised separately -- the two passes' gradients nearly cancel, and rounding the oracle's OWN activations to
+    fp16 already turns the result by cos 0.95-0.97 (to bf16: 0.57-0.66, profiles/r02_s4_disc2_grad_check.log shows each
+    pass alone at cos 0.993-0.995)."""
     from upscaler import training
     G, D, (gen_train, disc_train, gan_train), ref = _gan_models(True, family, act)
     x, hr = _data(8, 16, seed=16)
     gen = ref.predict(x)
     n = x.shape[0]
+    sens = _oracle_disc2_grads_with_rounded_storage(ref, hr, gen, family, act, _q_of(D))
     ld = disc_train.train_on_batch([hr, gen], -np.ones(n))
     ld_ref = ref.disc_train_on_batch2(hr, gen)
     S = disc_train._compiled._scale_for(D.net, 0, n)
     print("%s/%s: disc loss %.5f vs oracle %.5f" % (family, act, ld, ld_ref))
-    fp16 = D.net.train_dtype == torch.float16
-    _compare_d_grads(D, ref, S, *((0.06, 0.97) if fp16 else (0.2, 0.9)))
+    _compare_d_grads(D, ref, S, sens=sens)
     # the real pass contributes: gradients differ from a fake-only backward (guards against a pass being dropped)
     g_all = D.net.grad_flat.clone()
     assert float(g_all.abs().sum()) > 0

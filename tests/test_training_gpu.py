@@ -344,7 +344,7 @@ def test_fp16_training_storage_range_guard_falls_back_to_bf16():
     from upscaler.keras_compat import Adam
     from upscaler.model import VGG_MSE_LOSS, compile_training_model, make_upscaler_orig
     gw = O.init_upscaler_orig_weights(seed=11, kernel_size=3, res_block_num=1)
-    gw["res_block/0/conv_pre"][0] = gw["res_block/0/conv_pre"][0] * 4000.0        # conv output RMS far above RANGE_LIMIT
+    gw["res_block/0/conv_pre"][0] = gw["res_block/0/conv_pre"][0] * 30000.0       # conv output RMS ~1e4: far above RANGE_LIMIT
     x, hr = _data(2, 16, seed=3)
     up = make_upscaler_orig((64, 64, 3), kernel_size=3, res_block_num=1)
     up.net.set_weights(gw)
