@@ -32,6 +32,12 @@ int b2_version(void);
 /* Switches the CTA-pair (tcgen05 cta_group::2) kernels on or off for subsequent calls; returns the previous setting.
  * Both settings compute the same results; the switch exists for A/B measurements and tests. */
 int b2_set_pair_kernels(int enable);
+/* Programmatic dependent launch.  Every kernel of the library begins with griddepcontrol.wait (a no-op in a plain launch);
+ * b2_set_pdl(1) makes every launch carry programmatic stream serialization, so a kernel's CTAs may become resident while the
+ * preceding grid of its stream drains and the launch latency of the ~360 launches of a training step overlaps the previous
+ * kernel.  Stream order as the host sees it is unchanged.  Off by default (measured neutral on B200); returns the previous
+ * setting. */
+int b2_set_pdl(int enable);
 
 /* Epilogue shared by every convolution entry point:
  *   out = act(acc * scale[c] + shift[c]) + residual
@@ -295,6 +301,11 @@ int b2_peer_max_elems(void);
 int b2_peer_alloc(void** region, unsigned char* handle64);
 int b2_peer_open(const unsigned char* handle64, void** region);
 int b2_peer_close(void* region, int opened);
+/* Measurement aid (tools/peer_probe.py): `iters` back-to-back exchanges of n floats inside ONE launch, epochs epoch0 ..
+ * epoch0 + iters - 1 (the caller advances its epoch counter by iters); cycles[0] receives the SM clock cycles the loop took,
+ * cycles[1] the SM clock in kHz.  Isolates the exchange latency from launch latency and host effects. */
+int b2_peer_exchange_probe(float* data, int n, void* const* peer_regions, int rank, int world, unsigned epoch0, int iters,
+                           long long* cycles, void* stream);
 int b2_peer_allreduce_f32(float* data, int n, void* const* regions, int rank, int world, unsigned epoch, void* stream);
 
 /* Dense layers of the discriminator head (model.py:876-884; batch-sized M, negligible FLOPs) on CUDA cores, reading

@@ -4,6 +4,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "video-cycle_gan-upscaling_b200"))
 import numpy as np, torch
 from upscaler import ops
+if os.environ.get('B2_NO_PDL'):
+    ops.set_pdl(False)      # A/B: plain stream order instead of programmatic dependent launch
 from upscaler import model as M
 from upscaler.model import VGG_MSE_LOSS, make_and_compile_gan, make_upscaler_orig, wasserstein_loss
 ks = int(sys.argv[1]) if len(sys.argv) > 1 else 3

@@ -4,6 +4,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "video-cycle_gan-upscaling_b200"))
 import numpy as np, torch
 from upscaler.networks import UpscalerOrigNet
+from upscaler import ops
+if os.environ.get('B2_NO_PDL'):
+    ops.set_pdl(False)      # A/B: plain stream order instead of programmatic dependent launch
 ks = int(sys.argv[1]) if len(sys.argv) > 1 else 3
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 net = UpscalerOrigNet(kernel_size=ks, seed=1)

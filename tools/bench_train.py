@@ -6,6 +6,8 @@ sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "video-cycle_gan
 import numpy as np, torch
 from upscaler.model import VGG_MSE_LOSS, compile_training_model, make_upscaler_orig
 from upscaler import ops
+if os.environ.get('B2_NO_PDL'):
+    ops.set_pdl(False)      # A/B: plain stream order instead of programmatic dependent launch
 ks = int(sys.argv[1]) if len(sys.argv) > 1 else 3
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 16
 steps = int(sys.argv[3]) if len(sys.argv) > 3 else 5

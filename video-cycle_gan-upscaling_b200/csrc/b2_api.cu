@@ -193,6 +193,8 @@ int b2_epilogue_field_offset(int field) {
     }
 }
 
+int b2_set_pdl(int enable) { return set_pdl_enabled(enable); }
+
 int b2_set_pair_kernels(int enable) {
     const int old = g_pair_kernels;
     g_pair_kernels = enable ? 1 : 0;

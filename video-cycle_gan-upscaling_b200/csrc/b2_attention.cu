@@ -43,6 +43,7 @@ inline int grid_for(long work, int threads) {
 __global__ void __launch_bounds__(256)
 gate_mul_kernel(const uint4* __restrict__ att, int att_ld8, int att_c08, const uint4* __restrict__ m, uint4* __restrict__ out,
                 long rows, int C8, int f16) {
+    b2::pdl_entry();
     const long total = rows * C8;
     for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
         const long r = i / C8;
@@ -63,6 +64,7 @@ gate_mul_kernel(const uint4* __restrict__ att, int att_ld8, int att_c08, const u
 // out[b, oy, ox, C..2C) = TF 1.x resize_bilinear (source = out / f, no half-pixel centres), fp32 throughout.
 __global__ void __launch_bounds__(256)
 resize_pair_kernel(const float* __restrict__ in, int B, int H, int W, int C, int factor, float* __restrict__ out) {
+    b2::pdl_entry();
     const int OH = H * factor, OW = W * factor;
     const float inv = 1.0f / float(factor);
     for (int row = blockIdx.x; row < B * OH; row += gridDim.x) {
@@ -97,6 +99,7 @@ template <int CIN>
 __global__ void __launch_bounds__(256)
 atanh_convT_kernel(const float* __restrict__ in, int B, int H, int W, const float* __restrict__ w, const float* __restrict__ bias,
                    int s, int Cout, void* __restrict__ out, int f16) {
+    b2::pdl_entry();
     extern __shared__ float s_w[];
     const int k = s + 1;
     float* s_b = s_w + k * k * CIN * Cout;
@@ -155,8 +158,7 @@ int b2_gate_mul(const void* att, int att_ld, int att_c0, const void* m, void* ou
         return set_error("b2_gate_mul: channels [%d, %d) of %d must be multiples of 8", att_c0, att_c0 + C, att_ld);
     if ((reinterpret_cast<uintptr_t>(att) | reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(out)) & 15)
         return set_error("b2_gate_mul: buffers must be 16-byte aligned");
-    gate_mul_kernel<<<grid_for(rows * (C / 8), 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-        reinterpret_cast<const uint4*>(att), att_ld / 8, att_c0 / 8, reinterpret_cast<const uint4*>(m), reinterpret_cast<uint4*>(out),
+    b2::launch_k(gate_mul_kernel, grid_for(rows * (C / 8), 256), 256, 0, reinterpret_cast<cudaStream_t>(stream), reinterpret_cast<const uint4*>(att), att_ld / 8, att_c0 / 8, reinterpret_cast<const uint4*>(m), reinterpret_cast<uint4*>(out),
         long(rows), C / 8, f16);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("b2_gate_mul launch: %s", cudaGetErrorString(e));
@@ -166,8 +168,7 @@ int b2_gate_mul(const void* att, int att_ld, int att_c0, const void* m, void* ou
 int b2_resize_nearest_bilinear_pair(const float* in, int B, int H, int W, int C, int factor, float* out, void* stream) {
     if (!in || !out) return set_error("b2_resize_nearest_bilinear_pair: null pointer");
     if (B < 1 || H < 1 || W < 1 || C < 1 || factor < 1) return set_error("b2_resize_nearest_bilinear_pair: bad geometry");
-    resize_pair_kernel<<<grid_for(long(B) * H * factor * 256, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-        in, B, H, W, C, factor, out);
+    b2::launch_k(resize_pair_kernel, grid_for(long(B) * H * factor * 256, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream), in, B, H, W, C, factor, out);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("b2_resize_nearest_bilinear_pair launch: %s", cudaGetErrorString(e));
     return 0;
@@ -191,7 +192,7 @@ int b2_atanh_conv2d_transpose_small(const float* in, int B, int H, int W, int Ci
     long blocks = (work + 255) / 256;
     const long cap = long(device_sm_count()) * 4;         // each block re-lays the weights once: keep the grid persistent
     if (blocks > cap) blocks = cap;
-    atanh_convT_kernel<3><<<int(blocks), 256, smem, reinterpret_cast<cudaStream_t>(stream)>>>(in, B, H, W, w, bias, stride, Cout, out, f16);
+    b2::launch_k(atanh_convT_kernel<3>, int(blocks), 256, smem, reinterpret_cast<cudaStream_t>(stream), in, B, H, W, w, bias, stride, Cout, out, f16);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("b2_atanh_conv2d_transpose_small launch: %s", cudaGetErrorString(e));
     return 0;

@@ -86,6 +86,7 @@ __device__ __forceinline__ void block_combine_store(float (&acc)[NQ][8], int gro
 // ------------------------------------------------------------------------------------------------ stage 1, forward
 __global__ void __launch_bounds__(kEwThreads)
 bn_stats_partial_kernel(const void* __restrict__ x, long rows, int C, int f16, float* __restrict__ part, int zero_rows) {
+    b2::pdl_entry();
     // rows of `part` beyond this launch's grid, up to zero_rows, are cleared (callers that read a fixed number of rows)
     for (int r = int(gridDim.x) + int(blockIdx.x); r < zero_rows; r += int(gridDim.x))
         for (int i = threadIdx.x; i < 2 * C; i += kEwThreads) part[size_t(r) * 2 * C + i] = 0.f;
@@ -127,6 +128,7 @@ __global__ void __launch_bounds__(kEwThreads)
 bn_bwd_partial_kernel(const void* __restrict__ z, const void* __restrict__ gin, long rows, int C, int f16,
                       const float* __restrict__ aff, const float* __restrict__ alpha, int act, float leaky,
                       float* __restrict__ part) {
+    b2::pdl_entry();
     const int groups = C >> 3, g = threadIdx.x % groups, c0 = g * 8;
     const int rpb = kEwThreads / groups;
     float sc[8], sh[8], al[8], mu[8], is[8];
@@ -229,6 +231,7 @@ __global__ void __launch_bounds__(kFinThreads)
 bn_fwd_finalize_kernel(const float* __restrict__ part, int nparts, int C, float count, PeerBases pb, float* sums_out,
                        const float* __restrict__ gamma, const float* __restrict__ beta, float eps, float momentum,
                        float* moving_mean, float* moving_var, float* aff, float* range_watch, float range_limit_sq) {
+    b2::pdl_entry();
     __shared__ float sh[4 * kFinThreads];
     __shared__ float tot[3 * kFinChan];
     const int c0 = blockIdx.x * kFinChan, cb = min(kFinChan, C - c0);
@@ -265,6 +268,7 @@ bn_fwd_finalize_kernel(const float* __restrict__ part, int nparts, int C, float 
 __global__ void __launch_bounds__(kFinThreads)
 bn_bwd_finalize_kernel(const float* __restrict__ part, int nparts, int C, PeerBases pb, float* raw_out, float* sums,
                        float* dgamma, float* dbeta, float* dalpha, float gscale) {
+    b2::pdl_entry();
     __shared__ float sh[4 * kFinThreads];
     __shared__ float tot[3 * kFinChan];
     const int c0 = blockIdx.x * kFinChan, cb = min(kFinChan, C - c0);
@@ -312,7 +316,7 @@ namespace b2 {
 int launch_bn_stats_all_rows(const void* x, long rows, int C, int f16, float* part, cudaStream_t stream) {
     int blocks;
     if (part_grid(rows, C, &blocks)) return set_error("BatchNorm statistics: C=%d unsupported (C/8 must divide %d)", C, kEwThreads);
-    bn_stats_partial_kernel<<<blocks, kEwThreads, 0, stream>>>(x, rows, C, f16, part, 2 * device_sm_count());
+    b2::launch_k(bn_stats_partial_kernel, blocks, kEwThreads, 0, stream, x, rows, C, f16, part, 2 * device_sm_count());
     return launch_ok("bn_stats_partial");
 }
 }  // namespace b2
@@ -328,7 +332,7 @@ int b2_bn_stats_partial(const void* x, int64_t rows, int C, int f16, float* part
     if (!x || !part || !nparts) return set_error("b2_bn_stats_partial: null pointer");
     int blocks;
     if (part_grid(rows, C, &blocks)) return set_error("b2_bn_stats_partial: C=%d unsupported (C/8 must divide %d)", C, kEwThreads);
-    bn_stats_partial_kernel<<<blocks, kEwThreads, 0, B2_STREAM>>>(x, rows, C, f16, part, 0);
+    b2::launch_k(bn_stats_partial_kernel, blocks, kEwThreads, 0, B2_STREAM, x, rows, C, f16, part, 0);
     *nparts = blocks;
     return launch_ok("b2_bn_stats_partial");
 }
@@ -343,7 +347,7 @@ int b2_bn_fwd_finalize(const float* part, int nparts, int C, float count, void* 
     PeerBases pb;
     if (int rc = make_peer_bases(peer_regions, rank, world, epoch, &pb)) return rc;
     if (pb.world > 1 && 2 * C > kPeerMaxElems) return set_error("b2_bn_fwd_finalize: %d sums exceed the peer staging area", 2 * C);
-    bn_fwd_finalize_kernel<<<(C + kFinChan - 1) / kFinChan, kFinThreads, 0, B2_STREAM>>>(part, nparts, C, count, pb, sums_out, gamma, beta, eps, momentum,
+    b2::launch_k(bn_fwd_finalize_kernel, (C + kFinChan - 1) / kFinChan, kFinThreads, 0, B2_STREAM, part, nparts, C, count, pb, sums_out, gamma, beta, eps, momentum,
                                                              moving_mean, moving_var, aff, range_watch, range_limit * range_limit);
     return launch_ok("b2_bn_fwd_finalize");
 }
@@ -353,7 +357,7 @@ int b2_bn_bwd_partial(const void* z, const void* g, int64_t rows, int C, int f16
     if (!z || !g || !aff || !part || !nparts) return set_error("b2_bn_bwd_partial: null pointer");
     int blocks;
     if (part_grid(rows, C, &blocks)) return set_error("b2_bn_bwd_partial: C=%d unsupported", C);
-    bn_bwd_partial_kernel<<<blocks, kEwThreads, 0, B2_STREAM>>>(z, g, rows, C, f16, aff, alpha, act, leaky, part);
+    b2::launch_k(bn_bwd_partial_kernel, blocks, kEwThreads, 0, B2_STREAM, z, g, rows, C, f16, aff, alpha, act, leaky, part);
     *nparts = blocks;
     return launch_ok("b2_bn_bwd_partial");
 }
@@ -366,7 +370,7 @@ int b2_bn_bwd_finalize(const float* part, int nparts, int C, void* const* peer_r
     PeerBases pb;
     if (int rc = make_peer_bases(peer_regions, rank, world, epoch, &pb)) return rc;
     if (pb.world > 1 && 2 * C > kPeerMaxElems) return set_error("b2_bn_bwd_finalize: %d sums exceed the peer staging area", 2 * C);
-    bn_bwd_finalize_kernel<<<(C + kFinChan - 1) / kFinChan, kFinThreads, 0, B2_STREAM>>>(part, nparts, C, pb, raw_out, sums, dgamma, dbeta, dalpha, gscale);
+    b2::launch_k(bn_bwd_finalize_kernel, (C + kFinChan - 1) / kFinChan, kFinThreads, 0, B2_STREAM, part, nparts, C, pb, raw_out, sums, dgamma, dbeta, dalpha, gscale);
     return launch_ok("b2_bn_bwd_finalize");
 }
 

@@ -19,6 +19,7 @@ __device__ __forceinline__ float direct_act(float v, int act, float leaky, float
 
 __global__ void conv_direct_kernel(const __nv_bfloat16* __restrict__ x, int xB, int xH, int xW, int xC,
                                    const __nv_bfloat16* __restrict__ w, int w_rows, int w_k, IgemmParams p) {
+    b2::pdl_entry();
     const long total = long(p.B) * p.H * p.W * p.n_valid;
     for (long idx = blockIdx.x * long(blockDim.x) + threadIdx.x; idx < total; idx += long(gridDim.x) * blockDim.x) {
         const int n = int(idx % p.n_valid);
@@ -64,7 +65,7 @@ int launch_conv_direct(const ConvIgemmArgs& a, cudaStream_t stream) {
     long blocks = (total + 255) / 256;
     if (blocks > 148L * 64) blocks = 148L * 64;
     if (blocks < 1) blocks = 1;
-    conv_direct_kernel<<<int(blocks), 256, 0, stream>>>(a.x, a.xB, a.xH, a.xW, a.xC, a.w, a.w_rows, a.w_k, a.p);
+    b2::launch_k(conv_direct_kernel, int(blocks), 256, 0, stream, a.x, a.xB, a.xH, a.xW, a.xC, a.w, a.w_rows, a.w_k, a.p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("conv_direct launch: %s", cudaGetErrorString(e));
     return 0;

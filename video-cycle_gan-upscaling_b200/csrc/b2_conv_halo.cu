@@ -41,6 +41,7 @@ template <int BN>
 __global__ void __launch_bounds__(kHaloThreads, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                  const __grid_constant__ IgemmParams p, const __grid_constant__ HaloGeom g) {
+    b2::pdl_entry();
     constexpr int kBBlock = BN * 128;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -235,7 +236,7 @@ static int launch_halo_bn(const CUtensorMap& mapA, const CUtensorMap& mapB, cons
     }
     const int sms = device_sm_count();
     const int grid = p.num_tiles < sms ? p.num_tiles : sms;
-    conv_halo_kernel<BN><<<grid, kHaloThreads, smem_bytes, stream>>>(mapA, mapB, p, g);
+    b2::launch_k(conv_halo_kernel<BN>, grid, kHaloThreads, smem_bytes, stream, mapA, mapB, p, g);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("conv_halo launch: %s", cudaGetErrorString(e));
     return 0;

@@ -39,6 +39,7 @@ template <int BN>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                   const __grid_constant__ IgemmParams p) {
+    b2::pdl_entry();
     using Cfg = IgemmCfg<BN>;
     constexpr int STAGES = Cfg::kStages;
 
@@ -234,7 +235,7 @@ static int launch_bn(const CUtensorMap& mapA, const CUtensorMap& mapB, const Ige
         attr_set = true;
     }
     const int grid = p.num_tiles < num_sms ? p.num_tiles : num_sms;
-    conv_igemm_kernel<BN><<<grid, kThreads, Cfg::kSmemBytes, stream>>>(mapA, mapB, p);
+    b2::launch_k(conv_igemm_kernel<BN>, grid, kThreads, Cfg::kSmemBytes, stream, mapA, mapB, p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("conv_igemm launch: %s", cudaGetErrorString(e));
     return 0;

@@ -113,6 +113,7 @@ __global__ void __launch_bounds__(kPhThreads, 1)
 conv_phases_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                    const __grid_constant__ PhaseOutMaps mapO, const __grid_constant__ IgemmParams p,
                    const __grid_constant__ PhaseGeom g) {
+    b2::pdl_entry();
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smemB = smem;
@@ -399,7 +400,7 @@ int launch_conv_phases(const ConvIgemmArgs* ph, int nph, cudaStream_t stream) {
     }
     const int sms = device_sm_count();
     const int grid = p.num_tiles < sms ? p.num_tiles : sms;
-    conv_phases_kernel<<<grid, kPhThreads, smem_bytes, stream>>>(mapA, mapB, mapO, p, g);
+    b2::launch_k(conv_phases_kernel, grid, kPhThreads, smem_bytes, stream, mapA, mapB, mapO, p, g);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("conv_phases launch: %s", cudaGetErrorString(e));
     return 0;

@@ -151,6 +151,7 @@ __global__ void __launch_bounds__(kPhThreads, 1)
 conv_phases2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                    const __grid_constant__ PhaseOutMaps mapO, const __grid_constant__ IgemmParams p,
                    const __grid_constant__ PhaseGeom g) {
+    b2::pdl_entry();
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smemB = smem;
@@ -459,11 +460,13 @@ int launch_conv_phases2(const ConvIgemmArgs* ph, int nph, cudaStream_t stream) {
     cfg.blockDim = dim3(kPhThreads, 1, 1);
     cfg.dynamicSmemBytes = smem_bytes;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;       // see pdl_entry() in b2_host.h
+    attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = 2;
     cudaError_t e = cudaLaunchKernelEx(&cfg, conv_phases2_kernel, mapA, mapB, mapO, p, g);
     if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("conv_phases2 launch: %s", cudaGetErrorString(e));

@@ -77,6 +77,7 @@ template <int COUT>
 __global__ void __launch_bounds__(kScThreads, 1)
 conv_scatter_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                     const __grid_constant__ ScatterParams p) {
+    b2::pdl_entry();
     static_assert(COUT == 3, "column mapping is written for 3 output channels");
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -263,7 +264,7 @@ int launch_conv_scatter(const void* x, int B, int H, int W, int Cin, const void*
     }
     long grid = device_sm_count();
     if (grid > p.total_tiles) grid = p.total_tiles;
-    conv_scatter_kernel<3><<<int(grid), kScThreads, smem_bytes, stream>>>(mapA, mapB, p);
+    b2::launch_k(conv_scatter_kernel<3>, int(grid), kScThreads, smem_bytes, stream, mapA, mapB, p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("conv_scatter launch: %s", cudaGetErrorString(e));
     return 0;

@@ -239,6 +239,7 @@ template <int R, bool STREAM>
 __global__ void __launch_bounds__(STREAM ? kStackThreads + 32 : kStackThreads, 1)
 conv_stack_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                   const __grid_constant__ IgemmParams p, const __grid_constant__ StackGeom g) {
+    b2::pdl_entry();
     constexpr int kBlk = 64 * 128;            // one [64 cout x 64 k] weight block
     constexpr int kThreads = STREAM ? kStackThreads + 32 : kStackThreads;
     constexpr int kAccCols = 64 * R;
@@ -497,7 +498,7 @@ static int launch_stack_r(const CUtensorMap& mapA, const CUtensorMap& mapB, cons
     }
     const int sms = device_sm_count();
     const int grid = p.num_tiles < sms ? p.num_tiles : sms;
-    conv_stack_kernel<R, STREAM><<<grid, STREAM ? kStackThreads + 32 : kStackThreads, smem_bytes, stream>>>(mapA, mapB, p, g);
+    b2::launch_k(conv_stack_kernel<R, STREAM>, grid, STREAM ? kStackThreads + 32 : kStackThreads, smem_bytes, stream, mapA, mapB, p, g);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("conv_stack launch: %s", cudaGetErrorString(e));
     return 0;

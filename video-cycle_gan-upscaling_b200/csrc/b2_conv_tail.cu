@@ -64,6 +64,7 @@ template <int KH, int COUT>
 __global__ void __launch_bounds__(kTailThreads, 1)
 conv_tail_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                  const __grid_constant__ TailParams p) {
+    b2::pdl_entry();
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smemA = smem;
@@ -285,7 +286,7 @@ int launch_conv_tail(const void* x, int B, int H, int W, int Cin, const void* w,
     }
     long grid = device_sm_count();
     if (grid > p.total_tiles) grid = p.total_tiles;
-    conv_tail_kernel<9, 3><<<int(grid), kTailThreads, kTailSmem, stream>>>(mapA, mapB, p);
+    b2::launch_k(conv_tail_kernel<9, 3>, int(grid), kTailThreads, kTailSmem, stream, mapA, mapB, p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("conv_tail launch: %s", cudaGetErrorString(e));
     return 0;

@@ -60,6 +60,7 @@ template <int BN>
 __global__ void __launch_bounds__(kWgThreads, 1)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapZ,
                   const __grid_constant__ WgradParams p) {
+    b2::pdl_entry();
     constexpr int kZStage = (BN / 64) * kWgBox;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -252,7 +253,7 @@ static int launch_wgrad_bn(const CUtensorMap& mapX, const CUtensorMap& mapZ, con
     }
     const int sms = device_sm_count();
     const int grid = p.num_jobs < sms ? p.num_jobs : sms;
-    conv_wgrad_kernel<BN><<<grid, kWgThreads, smem_bytes, stream>>>(mapX, mapZ, p);
+    b2::launch_k(conv_wgrad_kernel<BN>, grid, kWgThreads, smem_bytes, stream, mapX, mapZ, p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("conv_wgrad launch: %s", cudaGetErrorString(e));
     return 0;

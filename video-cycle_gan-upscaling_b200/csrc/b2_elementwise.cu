@@ -20,6 +20,7 @@ struct FoldParams {
 // per CTA into shared memory.  Thread = (pixel, group of 8 channels): one 16-byte store, 8 L1-served scalar loads.
 template <typename TIn>
 __global__ void __launch_bounds__(256) fold_taps_kernel(const TIn* __restrict__ in, void* __restrict__ out, FoldParams p) {
+    b2::pdl_entry();
     // per output channel: x = element offset (dy * W + dx) * Cin + c from the stride-scaled output pixel,
     //                     y = dy, z = dx (dy = -2^20 marks an unused channel: always out of range -> zero)
     __shared__ int4 s_tab[64];     // index = (ch % 8) * 8 + ch / 8
@@ -71,6 +72,7 @@ __global__ void __launch_bounds__(256) fold_taps_kernel(const TIn* __restrict__ 
 
 __global__ void gather_cast_kernel(const float* __restrict__ src, const int32_t* __restrict__ idx, long n,
                                    void* __restrict__ out, int f16) {
+    b2::pdl_entry();
     for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < n; i += long(gridDim.x) * blockDim.x) {
         const int32_t j = idx[i];
         const float v = j >= 0 ? src[j] : 0.f;
@@ -87,6 +89,7 @@ __global__ void gather_cast_kernel(const float* __restrict__ src, const int32_t*
 __global__ void __launch_bounds__(256)
 resize_bilinear_into_kernel(const float* __restrict__ in, int B, int H, int W, int C, int factor, void* __restrict__ out,
                             int ld, int c0, int f16) {
+    b2::pdl_entry();
     const int OH = H * factor, OW = W * factor;
     const float inv = 1.0f / float(factor);
     for (int row = blockIdx.x; row < B * OH; row += gridDim.x) {
@@ -130,6 +133,7 @@ inline int grid_for(long work, int threads) {
 //   f32 -> u8:  uint8(around((a + 1) * 127.5)) in float32 with separate add and multiply (no FMA contraction) and
 //               round-half-to-even, bit-exact with convert_array_to_image on a float32 prediction.
 __global__ void u8_to_f32_norm_kernel(const uint8_t* __restrict__ in, float* __restrict__ out, long n) {
+    b2::pdl_entry();
     const long nv = n >> 4;
     for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < nv; i += long(gridDim.x) * blockDim.x) {
         const uint4 u = __ldg(reinterpret_cast<const uint4*>(in) + i);
@@ -150,6 +154,7 @@ __device__ __forceinline__ uint8_t denorm_u8(float a) {
     return uint8_t(int(fminf(fmaxf(v, 0.f), 255.f)));
 }
 __global__ void f32_to_u8_denorm_kernel(const float* __restrict__ in, uint8_t* __restrict__ out, long n) {
+    b2::pdl_entry();
     const long nv = n >> 4;
     for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < nv; i += long(gridDim.x) * blockDim.x) {
         float4 v[4];
@@ -170,6 +175,7 @@ __global__ void f32_to_u8_denorm_kernel(const float* __restrict__ in, uint8_t* _
 // cvt.rn.satfinite stores for anything larger), inf or NaN; bf16 inf or NaN.  One atomic per CTA, and only when non-zero.
 __global__ void count_saturated_kernel(const uint4* __restrict__ x, long n8, const uint16_t* __restrict__ tail, int ntail,
                                        uint32_t limit, unsigned int* __restrict__ count) {
+    b2::pdl_entry();
     unsigned int c = 0;
     for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < n8; i += long(gridDim.x) * blockDim.x) {
         const uint4 v = __ldg(x + i);
@@ -199,8 +205,7 @@ int b2_count_saturated(const void* x, int64_t n, int f16, unsigned int* count, v
     if (reinterpret_cast<uintptr_t>(x) & 15) return set_error("b2_count_saturated: tensor must be 16-byte aligned");
     if (n <= 0) return 0;
     const long n8 = n >> 3;
-    count_saturated_kernel<<<grid_for(n8 > 0 ? n8 : 1, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-        reinterpret_cast<const uint4*>(x), n8, reinterpret_cast<const uint16_t*>(x) + (n8 << 3), int(n & 7),
+    b2::launch_k(count_saturated_kernel, grid_for(n8 > 0 ? n8 : 1, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream), reinterpret_cast<const uint4*>(x), n8, reinterpret_cast<const uint16_t*>(x) + (n8 << 3), int(n & 7),
         f16 ? 0x7BFFu : 0x7F80u, count);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("b2_count_saturated launch: %s", cudaGetErrorString(e));
@@ -219,12 +224,11 @@ int b2_fold_taps(const void* in, int in_fp32, int B, int H, int W, int Cin, int 
     const int grid = grid_for(long(B) * OH * 256, 256);     // one CTA per output row, capped at 16 CTAs per SM
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     if (in_fp32)
-        fold_taps_kernel<float><<<grid, 256, 0, s>>>(reinterpret_cast<const float*>(in), out, p);
+        b2::launch_k(fold_taps_kernel<float>, grid, 256, 0, s, reinterpret_cast<const float*>(in), out, p);
     else if (f16)
-        fold_taps_kernel<__half><<<grid, 256, 0, s>>>(reinterpret_cast<const __half*>(in), out, p);
+        b2::launch_k(fold_taps_kernel<__half>, grid, 256, 0, s, reinterpret_cast<const __half*>(in), out, p);
     else
-        fold_taps_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(
-            reinterpret_cast<const __nv_bfloat16*>(in), out, p);
+        b2::launch_k(fold_taps_kernel<__nv_bfloat16>, grid, 256, 0, s, reinterpret_cast<const __nv_bfloat16*>(in), out, p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("b2_fold_taps launch: %s", cudaGetErrorString(e));
     return 0;
@@ -232,8 +236,7 @@ int b2_fold_taps(const void* in, int in_fp32, int B, int H, int W, int Cin, int 
 
 int b2_gather_cast(const float* src, const int32_t* idx, int64_t n, void* out, int f16, void* stream) {
     if (!src || !idx || !out) return set_error("b2_gather_cast: null pointer");
-    gather_cast_kernel<<<grid_for(n, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-        src, idx, long(n), out, f16);
+    b2::launch_k(gather_cast_kernel, grid_for(n, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream), src, idx, long(n), out, f16);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("b2_gather_cast launch: %s", cudaGetErrorString(e));
     return 0;
@@ -243,7 +246,7 @@ int b2_u8_to_f32_norm(const uint8_t* in, float* out, int64_t n, void* stream) {
     if (!in || !out) return set_error("b2_u8_to_f32_norm: null pointer");
     if ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) return set_error("b2_u8_to_f32_norm: buffers must be 16-byte aligned");
     if (n <= 0) return 0;
-    u8_to_f32_norm_kernel<<<grid_for((n + 15) / 16, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(in, out, long(n));
+    b2::launch_k(u8_to_f32_norm_kernel, grid_for((n + 15) / 16, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream), in, out, long(n));
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("b2_u8_to_f32_norm launch: %s", cudaGetErrorString(e));
     return 0;
@@ -254,8 +257,7 @@ int b2_resize_bilinear_into(const float* in, int B, int H, int W, int C, int fac
     if (!in || !out) return set_error("b2_resize_bilinear_into: null pointer");
     if (B < 1 || H < 1 || W < 1 || C < 1 || factor < 1 || c0 < 0 || c0 + C > ld)
         return set_error("b2_resize_bilinear_into: bad geometry (%d,%d,%d,%d) x%d into channels [%d,%d) of %d", B, H, W, C, factor, c0, c0 + C, ld);
-    resize_bilinear_into_kernel<<<grid_for(long(B) * H * factor * 256, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-        in, B, H, W, C, factor, out, ld, c0, f16);
+    b2::launch_k(resize_bilinear_into_kernel, grid_for(long(B) * H * factor * 256, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream), in, B, H, W, C, factor, out, ld, c0, f16);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("b2_resize_bilinear_into launch: %s", cudaGetErrorString(e));
     return 0;
@@ -265,7 +267,7 @@ int b2_f32_to_u8_denorm(const float* in, uint8_t* out, int64_t n, void* stream) 
     if (!in || !out) return set_error("b2_f32_to_u8_denorm: null pointer");
     if ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) return set_error("b2_f32_to_u8_denorm: buffers must be 16-byte aligned");
     if (n <= 0) return 0;
-    f32_to_u8_denorm_kernel<<<grid_for((n + 15) / 16, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(in, out, long(n));
+    b2::launch_k(f32_to_u8_denorm_kernel, grid_for((n + 15) / 16, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream), in, out, long(n));
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("b2_f32_to_u8_denorm launch: %s", cudaGetErrorString(e));
     return 0;

@@ -17,6 +17,14 @@ int set_error(const char* fmt, ...) {
 }
 const char* last_error() { return g_err; }
 
+static int g_pdl = 0;     // off by default: measured neutral (profiles/r02_s8_pdl_ab.log); b2_set_pdl(1) enables it
+int pdl_enabled() { return g_pdl; }
+int set_pdl_enabled(int enable) {
+    const int old = g_pdl;
+    g_pdl = enable ? 1 : 0;
+    return old;
+}
+
 int device_sm_count() {
     static int sms[64] = {0};
     int dev = 0;

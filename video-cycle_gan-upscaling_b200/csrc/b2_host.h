@@ -5,6 +5,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <string.h>
 
 #include "b2_conv_igemm.cuh"
 
@@ -24,6 +25,43 @@ int set_error(const char* fmt, ...);
 const char* last_error();
 
 int device_sm_count();
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Programmatic dependent launch.  A training step is ~360 launches (an adversarial iteration ~800), many of them a few
+// microseconds long, so the grid-to-grid hand-off is a visible share of the step.  Every kernel of this library starts
+// with pdl_entry() -- wait until the preceding grid of the stream has completed and flushed, THEN allow the next grid of the
+// stream to be scheduled -- and every launch goes through launch_k(), which sets programmatic stream serialization: the
+// next kernel's CTAs become resident (where registers / shared memory allow) while this one still runs and block in
+// griddepcontrol.wait, so the launch latency and CTA scheduling of kernel N+1 overlap kernel N.  Because the trigger follows
+// the wait, a kernel can never run ahead of anything it may read, whatever came before it in the stream; nothing precedes
+// pdl_entry() in any kernel.  Measured on B200 (profiles/r02_s8_pdl_ab.log) the wait-first form is neutral -- inference
+// 11.32 vs 11.19 ms, training step 17.73 vs 18.06 ms, adversarial iteration 32.67 vs 32.77 ms with / without -- so the
+// attribute is OFF by default and b2_set_pdl(1) turns it on; griddepcontrol.wait is a no-op in a plain launch.
+int pdl_enabled();
+int set_pdl_enabled(int enable);
+
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_entry() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+template <typename K, typename... Args>
+inline cudaError_t launch_k(K kernel, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<Args&&>(args)...);
+}
+#endif
 
 // rank-`rank` bf16 tensor, 128-byte swizzle, zero fill for out-of-bounds elements.
 int encode_tensor_map(CUtensorMap* map, const void* base, int rank, const cuuint64_t* dims,

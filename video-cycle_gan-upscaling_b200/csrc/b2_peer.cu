@@ -26,8 +26,24 @@ using b2::kPeerMaxWorld;
 using b2::kPeerRegionBytes;
 
 __global__ void __launch_bounds__(512) peer_allreduce_kernel(float* data, int n, b2::PeerBases pb) {
+    b2::pdl_entry();
     for (int i = threadIdx.x; i < n; i += blockDim.x) b2::peer_put(pb, i, data[i]);
     for (int i = threadIdx.x; i < n; i += blockDim.x) data[i] = b2::peer_get_sum(pb, i);
+}
+
+// `iters` dependent exchanges in one launch (tools/peer_probe.py): what one exchange costs once launch latency, the host
+// and the skew between the ranks' streams are out of the picture.
+__global__ void __launch_bounds__(512) peer_probe_kernel(float* data, int n, b2::PeerBases pb, int iters, float inv_world,
+                                                         long long* cycles) {
+    b2::pdl_entry();
+    const long long t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+        for (int i = threadIdx.x; i < n; i += blockDim.x) b2::peer_put(pb, i, data[i]);
+        for (int i = threadIdx.x; i < n; i += blockDim.x) data[i] = b2::peer_get_sum(pb, i) * inv_world;
+        pb.epoch = pb.epoch % 0x7FFFFFFEu + 1u;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) cycles[0] = clock64() - t0;
 }
 
 }  // namespace
@@ -92,6 +108,19 @@ int b2_peer_close(void* region, int opened) {
     return 0;
 }
 
+int b2_peer_exchange_probe(float* data, int n, void* const* regions, int rank, int world, unsigned epoch0, int iters,
+                           long long* cycles, void* stream) {
+    if (!data || !regions || !cycles) return set_error("b2_peer_exchange_probe: null pointer");
+    if (n < 1 || n > kPeerMaxElems || iters < 1) return set_error("b2_peer_exchange_probe: bad sizes");
+    b2::PeerBases pb;
+    if (int rc = b2::make_peer_bases(regions, rank, world, epoch0, &pb)) return rc;
+    const int threads = n >= 512 ? 512 : ((n + 31) / 32) * 32;
+    b2::launch_k(peer_probe_kernel, 1, threads, 0, reinterpret_cast<cudaStream_t>(stream), data, n, pb, iters, 1.0f / float(pb.world), cycles);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error("b2_peer_exchange_probe launch: %s", cudaGetErrorString(e));
+    return 0;
+}
+
 int b2_peer_allreduce_f32(float* data, int n, void* const* regions, int rank, int world, unsigned epoch, void* stream) {
     if (!data || !regions) return set_error("b2_peer_allreduce_f32: null pointer");
     if (n < 0 || n > kPeerMaxElems) return set_error("b2_peer_allreduce_f32: %d elements exceed %d", n, kPeerMaxElems);
@@ -101,7 +130,7 @@ int b2_peer_allreduce_f32(float* data, int n, void* const* regions, int rank, in
     pb.world = world;      // world == 1 still runs the exchange through the own region (identity; exercised by the tests)
     if (n == 0) return 0;
     const int threads = n >= 512 ? 512 : ((n + 31) / 32) * 32;
-    peer_allreduce_kernel<<<1, threads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(data, n, pb);
+    b2::launch_k(peer_allreduce_kernel, 1, threads, 0, reinterpret_cast<cudaStream_t>(stream), data, n, pb);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error("b2_peer_allreduce_f32 launch: %s", cudaGetErrorString(e));
     return 0;

@@ -118,6 +118,7 @@ __device__ __forceinline__ void block_combine(float (&acc)[NQ][8], int groups, i
 // ------------------------------------------------------------------------------------------------ batch statistics
 __global__ void __launch_bounds__(kEwThreads)
 colstats_kernel(const void* __restrict__ x, long rows, int C, int f16, float* __restrict__ sum, float* __restrict__ sumsq) {
+    b2::pdl_entry();
     const int groups = C >> 3, g = threadIdx.x % groups, c0 = g * 8;
     const int rpb = kEwThreads / groups;
     float acc[2][8] = {};
@@ -146,6 +147,7 @@ colstats_kernel(const void* __restrict__ x, long rows, int C, int f16, float* __
 __global__ void bn_finalize_kernel(const float* sum, const float* sumsq, float count, const float* gamma, const float* beta,
                                    float eps, float momentum, float* moving_mean, float* moving_var, float* scale,
                                    float* shift, float* mean_out, float* invstd_out, int C) {
+    b2::pdl_entry();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     const float m = sum[c] / count;
@@ -168,6 +170,7 @@ __global__ void bn_finalize_kernel(const float* sum, const float* sumsq, float c
 // inference-mode fold: scale = gamma / sqrt(var + eps); shift = beta + (bias - mean) * scale
 __global__ void bn_fold_kernel(const float* gamma, const float* beta, const float* mean, const float* var, const float* bias,
                                float eps, float* scale, float* shift, int C) {
+    b2::pdl_entry();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     const float sc = gamma[c] * rsqrtf(var[c] + eps);
@@ -198,6 +201,7 @@ __global__ void __launch_bounds__(kEwThreads)
 affine_act_kernel(const void* __restrict__ z, long rows, int C, int f16, const float* __restrict__ scale,
                   const float* __restrict__ shift, const float* __restrict__ alpha, int act, float leaky,
                   const void* __restrict__ residual, void* __restrict__ out) {
+    b2::pdl_entry();
     const int groups = C >> 3, g = threadIdx.x % groups, c0 = g * 8;
     const int rpb = kEwThreads / groups;
     float sc[8], sh[8], al[8];
@@ -226,6 +230,7 @@ bn_bwd_reduce_kernel(const void* __restrict__ z, const void* __restrict__ gin, l
                      const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ alpha,
                      int act, float leaky, const float* __restrict__ mean, const float* __restrict__ invstd,
                      float* __restrict__ s1, float* __restrict__ s2, float* __restrict__ dalpha) {
+    b2::pdl_entry();
     const int groups = C >> 3, g = threadIdx.x % groups, c0 = g * 8;
     const int rpb = kEwThreads / groups;
     float sc[8], sh[8], al[8], mu[8], is[8];
@@ -272,6 +277,7 @@ bn_bwd_apply_kernel(const void* __restrict__ z, const void* __restrict__ gin, lo
                     const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ alpha,
                     int act, float leaky, const float* __restrict__ mean, const float* __restrict__ invstd,
                     const float* __restrict__ s1, const float* __restrict__ s2, float inv_count, void* __restrict__ dz) {
+    b2::pdl_entry();
     const int groups = C >> 3, g = threadIdx.x % groups, c0 = g * 8;
     const int rpb = kEwThreads / groups;
     float sc[8], sh[8], al[8], mu[8], is[8], m1[8], m2[8];
@@ -320,6 +326,7 @@ bn_bwd_apply_kernel(const void* __restrict__ z, const void* __restrict__ gin, lo
 // channel groups of consecutive pixels, four independent loads per thread.
 __global__ void __launch_bounds__(kEwThreads)
 maxpool_fwd_kernel(const void* __restrict__ x, int B, int H, int W, int C, int f16, void* __restrict__ y) {
+    b2::pdl_entry();
     const int OH = H >> 1, OW = W >> 1, groups = C >> 3;
     const int per_row = OW * groups;
     for (int row = blockIdx.x; row < B * OH; row += gridDim.x) {
@@ -348,6 +355,7 @@ maxpool_fwd_kernel(const void* __restrict__ x, int B, int H, int W, int C, int f
 __global__ void __launch_bounds__(kEwThreads)
 maxpool_bwd_kernel(const void* __restrict__ x, const void* __restrict__ y, const void* __restrict__ dy, int B, int H, int W,
                    int C, int f16, int relu_gate, void* __restrict__ dx) {
+    b2::pdl_entry();
     const int OH = H >> 1, OW = W >> 1, groups = C >> 3;
     const int WH = (H + 1) >> 1, WW = (W + 1) >> 1;       // windows including the zero-filled odd edge
     const int per_row = WW * groups;
@@ -405,6 +413,7 @@ template <typename T>
 __global__ void __launch_bounds__(kEwThreads)
 loss_pair_kernel(const T* __restrict__ a, const T* __restrict__ b, long n, int mae, float weight, float gscale,
                  float* __restrict__ loss, T* __restrict__ grad) {
+    b2::pdl_entry();
     const float inv_n = 1.f / float(n);
     float acc = 0.f;
     for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < n; i += long(gridDim.x) * blockDim.x) {
@@ -430,6 +439,7 @@ loss_pair_kernel(const T* __restrict__ a, const T* __restrict__ b, long n, int m
 // grad[i] = gscale * y[i] / n.  x, y, grad fp32; tiny.
 __global__ void mean_prod_kernel(const float* x, const float* y, float yconst, long n, float weight, float gscale, float* loss,
                                  float* grad) {
+    b2::pdl_entry();
     float acc = 0.f;
     for (long i = threadIdx.x; i < n; i += blockDim.x) {
         const float yv = y ? y[i] : yconst;
@@ -451,6 +461,7 @@ __global__ void mean_prod_kernel(const float* x, const float* y, float yconst, l
 // kind: 1 sigmoid, 2 log(sigmoid), 3 tanh, 4 bi-log = x/(1+|x|) * log(|x|+2).  dy == nullptr: out = f(z); else
 // out = dy * f'(z).  fp32; n = batch size.
 __global__ void score_act_kernel(const float* z, const float* dy, float* out, long n, int kind) {
+    b2::pdl_entry();
     for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < n; i += long(gridDim.x) * blockDim.x) {
         const float x = z[i];
         float f, d;
@@ -476,6 +487,7 @@ __global__ void score_act_kernel(const float* z, const float* dy, float* out, lo
 // gradients (pixel loss, VGG image gradient, discriminator image gradient); all fp32.
 __global__ void tanh_bwd_kernel(const float* __restrict__ y, const float* __restrict__ g1, const float* __restrict__ g2,
                                 const float* __restrict__ g3, long n, float* __restrict__ dz) {
+    b2::pdl_entry();
     for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < n; i += long(gridDim.x) * blockDim.x) {
         float g = g1[i];
         if (g2) g += g2[i];
@@ -487,6 +499,7 @@ __global__ void tanh_bwd_kernel(const float* __restrict__ y, const float* __rest
 
 __global__ void __launch_bounds__(kEwThreads)
 colsum_f32_kernel(const float* __restrict__ x, long rows, int C, float* __restrict__ sum) {
+    b2::pdl_entry();
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (long r = blockIdx.x * long(blockDim.x) + threadIdx.x; r < rows; r += long(gridDim.x) * blockDim.x)
         for (int c = 0; c < C; ++c) acc[c] += x[r * C + c];
@@ -521,6 +534,7 @@ __device__ __forceinline__ void st_any(void* p, size_t i, int dtype, float v) {
 // thread-per-output form needed K = 2048 dependent L2 round trips: 380 us for 12 x 2048 x 1024.)
 __global__ void __launch_bounds__(256)
 dense_fwd_kernel(const void* x, int xd, int n, int K, int N, const float* __restrict__ W, const float* b, void* out, int od) {
+    b2::pdl_entry();
     __shared__ float red[8][8][33];
     const int col = threadIdx.x & 31, ks = threadIdx.x >> 5;
     const int o = blockIdx.x * 32 + col;
@@ -550,6 +564,7 @@ dense_fwd_kernel(const void* x, int xd, int n, int K, int N, const float* __rest
     }
 }
 __global__ void dense_bwd_data_kernel(const void* dy, int yd, int n, int K, int N, const float* __restrict__ W, void* dx, int xd) {
+    b2::pdl_entry();
     const long total = long(n) * K;
     for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
         const int k = int(i % K), r = int(i / K);
@@ -559,6 +574,7 @@ __global__ void dense_bwd_data_kernel(const void* dy, int yd, int n, int K, int 
     }
 }
 __global__ void dense_bwd_weight_kernel(const void* x, int xd, const void* dy, int yd, int n, int K, int N, float* dW, float* db) {
+    b2::pdl_entry();
     const long total = long(K) * N;
     for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
         const int o = int(i % N), k = int(i / N);
@@ -576,6 +592,7 @@ __global__ void dense_bwd_weight_kernel(const void* x, int xd, const void* dy, i
 // out[i] (+)= idx[i] >= 0 ? src[idx[i]] : 0   (fp32; folded-layer weight gradients back to the Keras layout)
 __global__ void gather_f32_kernel(const float* __restrict__ src, const int32_t* __restrict__ idx, long n, float* __restrict__ out,
                                   int accumulate) {
+    b2::pdl_entry();
     for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < n; i += long(gridDim.x) * blockDim.x) {
         const int32_t j = idx[i];
         const float v = j >= 0 ? src[j] : 0.f;
@@ -586,6 +603,7 @@ __global__ void gather_f32_kernel(const float* __restrict__ src, const int32_t* 
 // 16-bit <-> fp32 casts with a scale (gradient hand-off between fp32 image tensors and 16-bit feature tensors)
 template <typename TI, typename TO>
 __global__ void cast_scale_kernel(const TI* __restrict__ in, long n, float scale, TO* __restrict__ out) {
+    b2::pdl_entry();
     for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < n; i += long(gridDim.x) * blockDim.x)
         st_from_float(out, i, ld_as_float(in, i) * scale);
 }
@@ -595,6 +613,7 @@ __global__ void cast_scale_kernel(const TI* __restrict__ in, long n, float scale
 __global__ void __launch_bounds__(kEwThreads)
 adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long n, float lr_t,
             float b1, float b2, float eps, float gscale) {
+    b2::pdl_entry();
     const long n4 = n >> 2;
     for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < n4; i += long(gridDim.x) * blockDim.x) {
         float4 pp = reinterpret_cast<float4*>(p)[i], gg = reinterpret_cast<const float4*>(g)[i];
@@ -643,7 +662,7 @@ int b2_colstats(const void* x, int64_t rows, int C, int f16, float* sum, float* 
     if (!x || !sum) return set_error("b2_colstats: null pointer");
     RowGrid g;
     if (!row_grid(rows, C, g, 2)) return set_error("b2_colstats: C=%d unsupported (C/8 must divide %d)", C, kEwThreads);
-    colstats_kernel<<<g.blocks, kEwThreads, 0, B2_STREAM>>>(x, rows, C, f16, sum, sumsq);
+    b2::launch_k(colstats_kernel, g.blocks, kEwThreads, 0, B2_STREAM, x, rows, C, f16, sum, sumsq);
     return launch_ok("b2_colstats");
 }
 
@@ -651,7 +670,7 @@ int b2_bn_finalize(const float* sum, const float* sumsq, float count, const floa
                    float momentum, float* moving_mean, float* moving_var, float* scale, float* shift, float* mean_out,
                    float* invstd_out, int C, void* stream) {
     if (!sum || !sumsq || !gamma || !beta || !scale || !shift) return set_error("b2_bn_finalize: null pointer");
-    bn_finalize_kernel<<<(C + 127) / 128, 128, 0, B2_STREAM>>>(sum, sumsq, count, gamma, beta, eps, momentum, moving_mean,
+    b2::launch_k(bn_finalize_kernel, (C + 127) / 128, 128, 0, B2_STREAM, sum, sumsq, count, gamma, beta, eps, momentum, moving_mean,
                                                                 moving_var, scale, shift, mean_out, invstd_out, C);
     return launch_ok("b2_bn_finalize");
 }
@@ -659,7 +678,7 @@ int b2_bn_finalize(const float* sum, const float* sumsq, float count, const floa
 int b2_bn_fold(const float* gamma, const float* beta, const float* mean, const float* var, const float* bias, float eps,
                float* scale, float* shift, int C, void* stream) {
     if (!gamma || !beta || !mean || !var || !scale || !shift) return set_error("b2_bn_fold: null pointer");
-    bn_fold_kernel<<<(C + 127) / 128, 128, 0, B2_STREAM>>>(gamma, beta, mean, var, bias, eps, scale, shift, C);
+    b2::launch_k(bn_fold_kernel, (C + 127) / 128, 128, 0, B2_STREAM, gamma, beta, mean, var, bias, eps, scale, shift, C);
     return launch_ok("b2_bn_fold");
 }
 
@@ -668,7 +687,7 @@ int b2_affine_act(const void* z, int64_t rows, int C, int f16, const float* scal
     if (!z || !out) return set_error("b2_affine_act: null pointer");
     RowGrid g;
     if (!row_grid(rows, C, g)) return set_error("b2_affine_act: C=%d unsupported", C);
-    affine_act_kernel<<<g.blocks, kEwThreads, 0, B2_STREAM>>>(z, rows, C, f16, scale, shift, alpha, act, leaky, residual, out);
+    b2::launch_k(affine_act_kernel, g.blocks, kEwThreads, 0, B2_STREAM, z, rows, C, f16, scale, shift, alpha, act, leaky, residual, out);
     return launch_ok("b2_affine_act");
 }
 
@@ -678,7 +697,7 @@ int b2_bn_bwd_reduce(const void* z, const void* g, int64_t rows, int C, int f16,
     if (!z || !g || !s1) return set_error("b2_bn_bwd_reduce: null pointer");
     RowGrid rg;
     if (!row_grid(rows, C, rg, 2)) return set_error("b2_bn_bwd_reduce: C=%d unsupported", C);
-    bn_bwd_reduce_kernel<<<rg.blocks, kEwThreads, 0, B2_STREAM>>>(z, g, rows, C, f16, scale, shift, alpha, act, leaky, mean,
+    b2::launch_k(bn_bwd_reduce_kernel, rg.blocks, kEwThreads, 0, B2_STREAM, z, g, rows, C, f16, scale, shift, alpha, act, leaky, mean,
                                                                    invstd, s1, s2, dalpha);
     return launch_ok("b2_bn_bwd_reduce");
 }
@@ -689,7 +708,7 @@ int b2_bn_bwd_apply(const void* z, const void* g, int64_t rows, int C, int f16, 
     if (!z || !g || !dz) return set_error("b2_bn_bwd_apply: null pointer");
     RowGrid rg;
     if (!row_grid(rows, C, rg)) return set_error("b2_bn_bwd_apply: C=%d unsupported", C);
-    bn_bwd_apply_kernel<<<rg.blocks, kEwThreads, 0, B2_STREAM>>>(z, g, rows, C, f16, scale, shift, alpha, act, leaky, mean,
+    b2::launch_k(bn_bwd_apply_kernel, rg.blocks, kEwThreads, 0, B2_STREAM, z, g, rows, C, f16, scale, shift, alpha, act, leaky, mean,
                                                                   invstd, s1, s2, count > 0.f ? 1.f / count : 0.f, dz);
     return launch_ok("b2_bn_bwd_apply");
 }
@@ -697,7 +716,7 @@ int b2_bn_bwd_apply(const void* z, const void* g, int64_t rows, int C, int f16, 
 int b2_maxpool2x2(const void* x, int B, int H, int W, int C, int f16, void* y, void* stream) {
     if (!x || !y) return set_error("b2_maxpool2x2: null pointer");
     if (C % 8 != 0 || H < 2 || W < 2) return set_error("b2_maxpool2x2: bad geometry %dx%dx%d", H, W, C);
-    maxpool_fwd_kernel<<<flat_grid(long(B) * (H / 2) * kEwThreads), kEwThreads, 0, B2_STREAM>>>(x, B, H, W, C, f16, y);
+    b2::launch_k(maxpool_fwd_kernel, flat_grid(long(B) * (H / 2) * kEwThreads), kEwThreads, 0, B2_STREAM, x, B, H, W, C, f16, y);
     return launch_ok("b2_maxpool2x2");
 }
 
@@ -705,7 +724,7 @@ int b2_maxpool2x2_bwd(const void* x, const void* y, const void* dy, int B, int H
                       void* dx, void* stream) {
     if (!x || !y || !dy || !dx) return set_error("b2_maxpool2x2_bwd: null pointer");
     if (C % 8 != 0 || H < 2 || W < 2) return set_error("b2_maxpool2x2_bwd: bad geometry %dx%dx%d", H, W, C);
-    maxpool_bwd_kernel<<<flat_grid(long(B) * ((H + 1) / 2) * kEwThreads), kEwThreads, 0, B2_STREAM>>>(x, y, dy, B, H, W, C, f16, relu_gate, dx);
+    b2::launch_k(maxpool_bwd_kernel, flat_grid(long(B) * ((H + 1) / 2) * kEwThreads), kEwThreads, 0, B2_STREAM, x, y, dy, B, H, W, C, f16, relu_gate, dx);
     return launch_ok("b2_maxpool2x2_bwd");
 }
 
@@ -714,11 +733,11 @@ int b2_loss_pair(const void* a, const void* b, int64_t n, int dtype, int mae, fl
     if (!a || !b) return set_error("b2_loss_pair: null pointer");
     const int grid = flat_grid(n, 4);
     if (dtype == 2)
-        loss_pair_kernel<float><<<grid, kEwThreads, 0, B2_STREAM>>>(reinterpret_cast<const float*>(a), reinterpret_cast<const float*>(b), n, mae, weight, gscale, loss, reinterpret_cast<float*>(grad));
+        b2::launch_k(loss_pair_kernel<float>, grid, kEwThreads, 0, B2_STREAM, reinterpret_cast<const float*>(a), reinterpret_cast<const float*>(b), n, mae, weight, gscale, loss, reinterpret_cast<float*>(grad));
     else if (dtype == 1)
-        loss_pair_kernel<__half><<<grid, kEwThreads, 0, B2_STREAM>>>(reinterpret_cast<const __half*>(a), reinterpret_cast<const __half*>(b), n, mae, weight, gscale, loss, reinterpret_cast<__half*>(grad));
+        b2::launch_k(loss_pair_kernel<__half>, grid, kEwThreads, 0, B2_STREAM, reinterpret_cast<const __half*>(a), reinterpret_cast<const __half*>(b), n, mae, weight, gscale, loss, reinterpret_cast<__half*>(grad));
     else
-        loss_pair_kernel<__nv_bfloat16><<<grid, kEwThreads, 0, B2_STREAM>>>(reinterpret_cast<const __nv_bfloat16*>(a), reinterpret_cast<const __nv_bfloat16*>(b), n, mae, weight, gscale, loss, reinterpret_cast<__nv_bfloat16*>(grad));
+        b2::launch_k(loss_pair_kernel<__nv_bfloat16>, grid, kEwThreads, 0, B2_STREAM, reinterpret_cast<const __nv_bfloat16*>(a), reinterpret_cast<const __nv_bfloat16*>(b), n, mae, weight, gscale, loss, reinterpret_cast<__nv_bfloat16*>(grad));
     return launch_ok("b2_loss_pair");
 }
 
@@ -726,51 +745,51 @@ int b2_score_act(const float* z, const float* dy, float* out, int64_t n, int kin
     if (!z || !out) return set_error("b2_score_act: null pointer");
     if (kind < 1 || kind > 4) return set_error("b2_score_act: kind must be 1 (sigmoid), 2 (log-sigm), 3 (tanh) or 4 (bi-log)");
     if (n == 0) return 0;
-    score_act_kernel<<<int((n + 255) / 256 < 148 ? (n + 255) / 256 : 148), 256, 0, B2_STREAM>>>(z, dy, out, n, kind);
+    b2::launch_k(score_act_kernel, int((n + 255) / 256 < 148 ? (n + 255) / 256 : 148), 256, 0, B2_STREAM, z, dy, out, n, kind);
     return launch_ok("b2_score_act");
 }
 
 int b2_mean_prod(const float* x, const float* y, float yconst, int64_t n, float weight, float gscale, float* loss, float* grad,
                  void* stream) {
     if (!x) return set_error("b2_mean_prod: null pointer");
-    mean_prod_kernel<<<1, 256, 0, B2_STREAM>>>(x, y, yconst, n, weight, gscale, loss, grad);
+    b2::launch_k(mean_prod_kernel, 1, 256, 0, B2_STREAM, x, y, yconst, n, weight, gscale, loss, grad);
     return launch_ok("b2_mean_prod");
 }
 
 int b2_tanh_bwd(const float* y, const float* g1, const float* g2, const float* g3, int64_t n, float* dz, void* stream) {
     if (!y || !g1 || !dz) return set_error("b2_tanh_bwd: null pointer");
-    tanh_bwd_kernel<<<flat_grid(n), kEwThreads, 0, B2_STREAM>>>(y, g1, g2, g3, n, dz);
+    b2::launch_k(tanh_bwd_kernel, flat_grid(n), kEwThreads, 0, B2_STREAM, y, g1, g2, g3, n, dz);
     return launch_ok("b2_tanh_bwd");
 }
 
 int b2_colsum_f32(const float* x, int64_t rows, int C, float* sum, void* stream) {
     if (!x || !sum) return set_error("b2_colsum_f32: null pointer");
     if (C < 1 || C > 8) return set_error("b2_colsum_f32: C=%d unsupported", C);
-    colsum_f32_kernel<<<flat_grid(rows, 2), kEwThreads, 0, B2_STREAM>>>(x, rows, C, sum);
+    b2::launch_k(colsum_f32_kernel, flat_grid(rows, 2), kEwThreads, 0, B2_STREAM, x, rows, C, sum);
     return launch_ok("b2_colsum_f32");
 }
 
 int b2_dense_fwd(const void* x, int x_dtype, int n, int K, int N, const float* W, const float* b, void* out, int out_dtype,
                  void* stream) {
     if (!x || !W || !out) return set_error("b2_dense_fwd: null pointer");
-    dense_fwd_kernel<<<(N + 31) / 32, 256, 0, B2_STREAM>>>(x, x_dtype, n, K, N, W, b, out, out_dtype);
+    b2::launch_k(dense_fwd_kernel, (N + 31) / 32, 256, 0, B2_STREAM, x, x_dtype, n, K, N, W, b, out, out_dtype);
     return launch_ok("b2_dense_fwd");
 }
 int b2_dense_bwd_data(const void* dy, int dy_dtype, int n, int K, int N, const float* W, void* dx, int dx_dtype, void* stream) {
     if (!dy || !W || !dx) return set_error("b2_dense_bwd_data: null pointer");
-    dense_bwd_data_kernel<<<flat_grid(long(n) * K), kEwThreads, 0, B2_STREAM>>>(dy, dy_dtype, n, K, N, W, dx, dx_dtype);
+    b2::launch_k(dense_bwd_data_kernel, flat_grid(long(n) * K), kEwThreads, 0, B2_STREAM, dy, dy_dtype, n, K, N, W, dx, dx_dtype);
     return launch_ok("b2_dense_bwd_data");
 }
 int b2_dense_bwd_weight(const void* x, int x_dtype, const void* dy, int dy_dtype, int n, int K, int N, float* dW, float* db,
                         void* stream) {
     if (!x || !dy || !dW) return set_error("b2_dense_bwd_weight: null pointer");
-    dense_bwd_weight_kernel<<<flat_grid(long(K) * N), kEwThreads, 0, B2_STREAM>>>(x, x_dtype, dy, dy_dtype, n, K, N, dW, db);
+    b2::launch_k(dense_bwd_weight_kernel, flat_grid(long(K) * N), kEwThreads, 0, B2_STREAM, x, x_dtype, dy, dy_dtype, n, K, N, dW, db);
     return launch_ok("b2_dense_bwd_weight");
 }
 
 int b2_gather_f32(const float* src, const int32_t* idx, int64_t n, float* out, int accumulate, void* stream) {
     if (!src || !idx || !out) return set_error("b2_gather_f32: null pointer");
-    gather_f32_kernel<<<flat_grid(n), kEwThreads, 0, B2_STREAM>>>(src, idx, n, out, accumulate);
+    b2::launch_k(gather_f32_kernel, flat_grid(n), kEwThreads, 0, B2_STREAM, src, idx, n, out, accumulate);
     return launch_ok("b2_gather_f32");
 }
 
@@ -778,7 +797,7 @@ int b2_cast_scale(const void* in, int in_dtype, int64_t n, float scale, void* ou
     if (!in || !out) return set_error("b2_cast_scale: null pointer");
     const int grid = flat_grid(n);
     cudaStream_t s = B2_STREAM;
-#define B2_CAST(TI, TO) cast_scale_kernel<TI, TO><<<grid, kEwThreads, 0, s>>>(reinterpret_cast<const TI*>(in), n, scale, reinterpret_cast<TO*>(out))
+#define B2_CAST(TI, TO) b2::launch_k(cast_scale_kernel<TI, TO>, grid, kEwThreads, 0, s, reinterpret_cast<const TI*>(in), n, scale, reinterpret_cast<TO*>(out))
     if (in_dtype == 2 && out_dtype == 0) B2_CAST(float, __nv_bfloat16);
     else if (in_dtype == 2 && out_dtype == 1) B2_CAST(float, __half);
     else if (in_dtype == 0 && out_dtype == 2) B2_CAST(__nv_bfloat16, float);
@@ -792,7 +811,7 @@ int b2_cast_scale(const void* in, int in_dtype, int64_t n, float scale, void* ou
 int b2_adam(float* params, const float* grads, float* m, float* v, int64_t n, float lr_t, float beta1, float beta2, float eps,
             float gscale, void* stream) {
     if (!params || !grads || !m || !v) return set_error("b2_adam: null pointer");
-    adam_kernel<<<flat_grid((n + 3) / 4), kEwThreads, 0, B2_STREAM>>>(params, grads, m, v, n, lr_t, beta1, beta2, eps, gscale);
+    b2::launch_k(adam_kernel, flat_grid((n + 3) / 4), kEwThreads, 0, B2_STREAM, params, grads, m, v, n, lr_t, beta1, beta2, eps, gscale);
     return launch_ok("b2_adam");
 }
 

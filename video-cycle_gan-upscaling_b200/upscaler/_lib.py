@@ -42,6 +42,7 @@ _SIGNATURES = {
     "b2_epilogue_field_count": (ctypes.c_int, []),
     "b2_epilogue_field_offset": (ctypes.c_int, [ctypes.c_int]),
     "b2_set_pair_kernels": (ctypes.c_int, [ctypes.c_int]),
+    "b2_set_pdl": (ctypes.c_int, [ctypes.c_int]),
     "b2_conv2d_fprop": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p] + [ctypes.c_int] * 4 +
                         [ctypes.POINTER(Epilogue), ctypes.c_void_p]),
     "b2_conv2d_transpose_s2_fprop": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p] +
@@ -92,6 +93,7 @@ _SIGNATURES = {
     "b2_peer_alloc": (ctypes.c_int, [ctypes.POINTER(ctypes.c_void_p), ctypes.c_char_p]),
     "b2_peer_open": (ctypes.c_int, [ctypes.c_char_p, ctypes.POINTER(ctypes.c_void_p)]),
     "b2_peer_close": (ctypes.c_int, [_P, _I]),
+    "b2_peer_exchange_probe": (ctypes.c_int, [_P, _I, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _I, _P, _P]),
     "b2_peer_allreduce_f32": (ctypes.c_int, [_P, _I, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _P]),
     "b2_tanh_bwd": (ctypes.c_int, [_P, _P, _P, _P, _L, _P, _P]),
     "b2_gather_f32": (ctypes.c_int, [_P, _P, _L, _P, _I, _P]),

@@ -29,6 +29,11 @@ def set_pair_kernels(enable):
     return bool(_lib.load().b2_set_pair_kernels(1 if enable else 0))
 
 
+def set_pdl(enable):
+    """Programmatic dependent launch of every kernel on / off (include/b2srgan.h b2_set_pdl); returns the old setting."""
+    return bool(_lib.load().b2_set_pdl(1 if enable else 0))
+
+
 def _count(n):
     global _launches
     _launches += n

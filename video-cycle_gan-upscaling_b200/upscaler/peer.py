@@ -53,6 +53,21 @@ class PeerReducer:
         return buf
 
 
+    def exchange_probe(self, n, iters):
+        """Measurement aid: `iters` dependent exchanges of n floats inside one launch; returns SM clock cycles per exchange."""
+        import torch
+        buf = torch.ones(n, dtype=torch.float32, device="cuda")
+        cyc = torch.zeros(2, dtype=torch.int64, device="cuda")
+        e0 = self.next_epoch()
+        for _ in range(iters - 1):
+            self.next_epoch()
+        rc = _lib.load().b2_peer_exchange_probe(_lib.ptr(buf), n, self.regions, self.rank, self.world, e0, iters, _lib.ptr(cyc),
+                                                _lib.stream_ptr())
+        _lib.check(rc, "b2_peer_exchange_probe")
+        torch.cuda.synchronize()
+        return float(cyc[0].item()) / iters
+
+
 def reducer(dist, device):
     """The process-wide PeerReducer, or None when the ranks cannot reach each other's memory (then NCCL is used).  The
     decision is collective: every rank reports whether it could open all regions, and all follow the minimum."""

@@ -87,6 +87,10 @@ def loss_activation(name, x):
 
 FROZEN_MODEL_UPDATES_MOVING_STATS = False      # see the module docstring
 
+# Host-side accounting of the steps (bench.py, tools/): seconds the host spent blocked in the step's one device -> host
+# read (the loss).  A step whose wait is ~0 is bound by the host's launch rate, not by the GPU.
+HOST_STATS = {"wait_s": 0.0, "reads": 0}
+
 # Gradient scaling of the training step.  Every loss gradient is multiplied by S at its source, the whole backward pass
 # (linear in that gradient) carries S x the true values, and Adam divides S out again (b2_adam's gscale).  With bf16
 # storage S = 1.  With fp16 storage S lifts the gradients out of the subnormal range: "numel" = the number of elements of
@@ -514,11 +518,16 @@ class Compiled:
     def _mean_over_ranks(self, buf):
         """Device scalars -> host floats (the step's single D2H read); averaged over replicas so every rank reports
         the global-batch loss."""
+        import time
         dist = _dist()
         if dist is not None:
             dist.all_reduce(buf)
             buf = buf / dist.get_world_size()
-        return [float(v) for v in buf.cpu().numpy()]
+        t0 = time.perf_counter()
+        host = buf.cpu().numpy()
+        HOST_STATS["wait_s"] += time.perf_counter() - t0
+        HOST_STATS["reads"] += 1
+        return [float(v) for v in host]
 
 
 def evaluate_content_loss(loss_obj, y_true, y_pred):
