@@ -220,7 +220,7 @@ def bench_train_step(args, rank, world, dev, barrier, B=16, hw=(96, 96), builder
     hr = rng.uniform(-1, 1, (B, 4 * h, 4 * w_, 3)).astype(np.float32)
     base = hr.reshape(B, h, 4, w_, 4, 3).mean(axis=(2, 4)).astype(np.float32)
     xs = [np.clip(base + 0.05 * c * rng.standard_normal(base.shape).astype(np.float32), -1, 1) for c in range(calls)]
-    for _ in range(3):
+    for _ in range(6):      # warm-up past training.GRAPH_WARMUP: the one-off CUDA-graph capture of the step is not timed
         for x in xs:
             loss = tm.train_on_batch(x, hr)
     barrier()

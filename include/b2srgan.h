@@ -252,8 +252,9 @@ int b2_bn_stats_partial(const void* x, int64_t rows, int C, int f16, float* part
  * range_watch (nullable, one float): set to 1 when a channel's root mean square reaches range_limit or is not finite --
  * the guard of fp16 training storage (the tensor was stored with a saturating conversion; the host switches to bf16). */
 int b2_bn_fwd_finalize(const float* part, int nparts, int C, float count, void* const* peer_regions, int rank, int world,
-                       unsigned epoch, float* sums_out, const float* gamma, const float* beta, float eps, float momentum,
-                       float* moving_mean, float* moving_var, float* aff, float* range_watch, float range_limit, void* stream);
+                       unsigned epoch, const unsigned* epoch_base, float* sums_out, const float* gamma, const float* beta, float eps,
+                       float momentum, float* moving_mean, float* moving_var, float* aff, float* range_watch, float range_limit,
+                       void* stream);
 /* backward stage 1 through y = act(u), u = z*scale + shift (aff from the forward tape): with dy = g*act'(u),
  * part[row] = [sum dy | sum dy*xhat | sum g*min(u,0)]. */
 int b2_bn_bwd_partial(const void* z, const void* g, int64_t rows, int C, int f16, const float* aff, const float* alpha, int act,
@@ -262,7 +263,7 @@ int b2_bn_bwd_partial(const void* z, const void* g, int64_t rows, int C, int f16
  * dalpha += this replica's third sum (each nullable).  raw_out != NULL: only write the 3*C local sums there and return
  * (NCCL fallback; call again on the all-reduced buffer with nparts = 1). */
 int b2_bn_bwd_finalize(const float* part, int nparts, int C, void* const* peer_regions, int rank, int world, unsigned epoch,
-                       float* raw_out, float* sums, float* dgamma, float* dbeta, float* dalpha, float gscale, void* stream);
+                       const unsigned* epoch_base, float* raw_out, float* sums, float* dgamma, float* dbeta, float* dalpha, float gscale, void* stream);
 
 /* MaxPooling2D(2,2) 'valid' of VGG19 (keras.applications behind model.py:108) and its gradient (first maximum of each
  * window takes the gradient; relu_gate != 0 additionally zeroes it where x <= 0, i.e. the ReLU of the conv below). */
@@ -306,7 +307,12 @@ int b2_peer_close(void* region, int opened);
  * cycles[1] the SM clock in kHz.  Isolates the exchange latency from launch latency and host effects. */
 int b2_peer_exchange_probe(float* data, int n, void* const* peer_regions, int rank, int world, unsigned epoch0, int iters,
                            long long* cycles, void* stream);
-int b2_peer_allreduce_f32(float* data, int n, void* const* regions, int rank, int world, unsigned epoch, void* stream);
+/* epoch_base (device pointer, nullable; also on b2_bn_fwd_finalize / b2_bn_bwd_finalize): when the launch is captured into a
+ * CUDA graph its arguments are baked, so the exchange uses epoch + *epoch_base -- `epoch` = the launch's position inside the
+ * captured step (1, 2, ...), *epoch_base = the number of exchanges completed before the replay, set by the host on the same
+ * stream before every replay.  NULL in a plain launch. */
+int b2_peer_allreduce_f32(float* data, int n, void* const* regions, int rank, int world, unsigned epoch, const unsigned* epoch_base,
+                          void* stream);
 
 /* Dense layers of the discriminator head (model.py:876-884; batch-sized M, negligible FLOPs) on CUDA cores, reading
  * the fp32 master weights in Keras layout W[K][N] directly.  x / dy / dx / out are 16-bit unless the dtype code

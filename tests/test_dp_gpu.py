@@ -47,12 +47,16 @@ def test_peer_allreduce_single_rank_and_errors():
     for epoch, n in enumerate([1, 31, 128, 1000, nmax, 64, 64, 64], start=1):
         x = torch.randn(n, device="cuda")
         ref = x.clone()
-        rc = lib.b2_peer_allreduce_f32(_lib.ptr(x), n, regions, 0, 1, epoch, _lib.stream_ptr())
+        if epoch % 2:       # plain launch: the epoch travels as an argument
+            rc = lib.b2_peer_allreduce_f32(_lib.ptr(x), n, regions, 0, 1, epoch, None, _lib.stream_ptr())
+        else:               # graph-replay form: position 1 inside the step + the device-side base (include/b2srgan.h)
+            base = torch.full((1,), epoch - 1, dtype=torch.int32, device="cuda")
+            rc = lib.b2_peer_allreduce_f32(_lib.ptr(x), n, regions, 0, 1, 1, _lib.ptr(base), _lib.stream_ptr())
         _lib.check(rc, "b2_peer_allreduce_f32")
         torch.cuda.synchronize()
         assert torch.equal(x, ref)
     x = torch.zeros(8, device="cuda")
-    assert lib.b2_peer_allreduce_f32(_lib.ptr(x), nmax + 1, regions, 0, 1, 99, _lib.stream_ptr()) != 0
+    assert lib.b2_peer_allreduce_f32(_lib.ptr(x), nmax + 1, regions, 0, 1, 99, None, _lib.stream_ptr()) != 0
     assert b"exceed" in lib.b2_last_error()
-    assert lib.b2_peer_allreduce_f32(_lib.ptr(x), 8, regions, 3, 2, 99, _lib.stream_ptr()) != 0
+    assert lib.b2_peer_allreduce_f32(_lib.ptr(x), 8, regions, 3, 2, 99, None, _lib.stream_ptr()) != 0
     _lib.check(lib.b2_peer_close(own, 0), "b2_peer_close")

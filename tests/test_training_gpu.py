@@ -365,3 +365,45 @@ def test_fp16_training_storage_range_guard_falls_back_to_bf16():
         warnings.simplefilter("always")
         tm2.train_on_batch(x, hr)
     assert not rec2 and up2.net.train_dtype == torch.float16
+
+
+def test_cuda_graph_replay_of_the_training_step_equals_the_eager_step():
+    """training.GRAPH_STEPS: after GRAPH_WARMUP eager calls the step is replayed from two captured CUDA graphs.  Two models run
+    in lockstep -- one replaying, one eager -- and before every step the eager one is given the replaying one's weights and
+    moving statistics (two free-running runs drift apart chaotically even eager against eager: the split-K weight-gradient
+    flushes are unordered atomics and Adam's first updates are sign-like).  From identical weights the two steps must return
+    the same loss and produce the same update."""
+    from upscaler import training
+    old = training.GRAPH_STEPS
+    try:
+        training.GRAPH_STEPS = True
+        up_g, tm_g, _ = _gen_setup(3, 2, "vgg-mse", 1e-3)
+        training.GRAPH_STEPS = False
+        up_e, tm_e, _ = _gen_setup(3, 2, "vgg-mse", 1e-3)
+        worst_l, worst_u = 0.0, 0.0
+        for step in range(training.GRAPH_WARMUP + 6):
+            x, hr = _data(2, 16, seed=700 + step)
+            up_e.net.flat.copy_(up_g.net.flat)
+            up_e.net._train_dirty = up_e.net._infer_dirty = True
+            before = up_g.net.flat.detach().clone()
+            training.GRAPH_STEPS = True
+            lg = tm_g.train_on_batch(x, hr)
+            training.GRAPH_STEPS = False
+            le = tm_e.train_on_batch(x, hr)
+            torch.cuda.synchronize()
+            ug = (up_g.net.flat - before)[:up_g.net.n_trainable]
+            ue = (up_e.net.flat - before)[:up_e.net.n_trainable]
+            worst_l = max(worst_l, abs(lg - le) / abs(le))
+            if step >= 2:       # Adam moments differ only through the (identical) history; compare the updates' direction
+                cos = float(torch.dot(ug, ue) / (ug.norm() * ue.norm()))
+                worst_u = max(worst_u, 1 - cos)
+            mm_g = up_g.net.weights["res_block/0/batch_norm_pre"][2]
+            mm_e = up_e.net.weights["res_block/0/batch_norm_pre"][2]
+            assert torch.allclose(mm_g, mm_e, rtol=1e-4, atol=1e-6)
+        print("graph replay vs eager from identical weights: worst rel loss diff %.2e, worst 1 - cos(update) %.2e; graphs held: %d / %d"
+              % (worst_l, worst_u, len(tm_g._compiled._graphs), len(tm_e._compiled._graphs)))
+        assert len(tm_g._compiled._graphs) == 1 and len(tm_e._compiled._graphs) == 0
+        assert worst_l <= 1e-5
+        assert worst_u <= 2e-2
+    finally:
+        training.GRAPH_STEPS = old

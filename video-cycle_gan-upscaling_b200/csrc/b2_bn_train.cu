@@ -234,6 +234,7 @@ bn_fwd_finalize_kernel(const float* __restrict__ part, int nparts, int C, float 
     b2::pdl_entry();
     __shared__ float sh[4 * kFinThreads];
     __shared__ float tot[3 * kFinChan];
+    peer_resolve_epoch(pb);
     const int c0 = blockIdx.x * kFinChan, cb = min(kFinChan, C - c0);
     sum_partial_rows<2>(part, nparts, C, c0, cb, sh, tot);
     exchange(pb, tot, 2, C, c0, cb);
@@ -271,6 +272,7 @@ bn_bwd_finalize_kernel(const float* __restrict__ part, int nparts, int C, PeerBa
     b2::pdl_entry();
     __shared__ float sh[4 * kFinThreads];
     __shared__ float tot[3 * kFinChan];
+    peer_resolve_epoch(pb);
     const int c0 = blockIdx.x * kFinChan, cb = min(kFinChan, C - c0);
     sum_partial_rows<3>(part, nparts, C, c0, cb, sh, tot);
     const int cl = threadIdx.x;
@@ -338,14 +340,14 @@ int b2_bn_stats_partial(const void* x, int64_t rows, int C, int f16, float* part
 }
 
 int b2_bn_fwd_finalize(const float* part, int nparts, int C, float count, void* const* peer_regions, int rank, int world,
-                       unsigned epoch, float* sums_out, const float* gamma, const float* beta, float eps, float momentum,
+                       unsigned epoch, const unsigned* epoch_base, float* sums_out, const float* gamma, const float* beta, float eps, float momentum,
                        float* moving_mean, float* moving_var, float* aff, float* range_watch, float range_limit, void* stream) {
     if (!part || nparts < 1) return set_error("b2_bn_fwd_finalize: no partial sums");
     if (aff && (!gamma || !beta)) return set_error("b2_bn_fwd_finalize: gamma / beta missing");
     if (C < 1 || 3 * C > kFinMaxElems) return set_error("b2_bn_fwd_finalize: C=%d exceeds %d", C, kFinMaxElems / 3);
     if ((C & 3) || (reinterpret_cast<uintptr_t>(part) & 15)) return set_error("b2_bn_fwd_finalize: C must be a multiple of 4 and part 16-byte aligned");
     PeerBases pb;
-    if (int rc = make_peer_bases(peer_regions, rank, world, epoch, &pb)) return rc;
+    if (int rc = make_peer_bases(peer_regions, rank, world, epoch, &pb, epoch_base)) return rc;
     if (pb.world > 1 && 2 * C > kPeerMaxElems) return set_error("b2_bn_fwd_finalize: %d sums exceed the peer staging area", 2 * C);
     b2::launch_k(bn_fwd_finalize_kernel, (C + kFinChan - 1) / kFinChan, kFinThreads, 0, B2_STREAM, part, nparts, C, count, pb, sums_out, gamma, beta, eps, momentum,
                                                              moving_mean, moving_var, aff, range_watch, range_limit * range_limit);
@@ -363,12 +365,12 @@ int b2_bn_bwd_partial(const void* z, const void* g, int64_t rows, int C, int f16
 }
 
 int b2_bn_bwd_finalize(const float* part, int nparts, int C, void* const* peer_regions, int rank, int world, unsigned epoch,
-                       float* raw_out, float* sums, float* dgamma, float* dbeta, float* dalpha, float gscale, void* stream) {
+                       const unsigned* epoch_base, float* raw_out, float* sums, float* dgamma, float* dbeta, float* dalpha, float gscale, void* stream) {
     if (!part || nparts < 1) return set_error("b2_bn_bwd_finalize: no partial sums");
     if (C < 1 || 3 * C > kFinMaxElems) return set_error("b2_bn_bwd_finalize: C=%d exceeds %d", C, kFinMaxElems / 3);
     if ((C & 3) || (reinterpret_cast<uintptr_t>(part) & 15)) return set_error("b2_bn_bwd_finalize: C must be a multiple of 4 and part 16-byte aligned");
     PeerBases pb;
-    if (int rc = make_peer_bases(peer_regions, rank, world, epoch, &pb)) return rc;
+    if (int rc = make_peer_bases(peer_regions, rank, world, epoch, &pb, epoch_base)) return rc;
     if (pb.world > 1 && 2 * C > kPeerMaxElems) return set_error("b2_bn_bwd_finalize: %d sums exceed the peer staging area", 2 * C);
     b2::launch_k(bn_bwd_finalize_kernel, (C + kFinChan - 1) / kFinChan, kFinThreads, 0, B2_STREAM, part, nparts, C, pb, raw_out, sums, dgamma, dbeta, dalpha, gscale);
     return launch_ok("b2_bn_bwd_finalize");

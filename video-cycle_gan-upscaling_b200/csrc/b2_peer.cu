@@ -27,6 +27,7 @@ using b2::kPeerRegionBytes;
 
 __global__ void __launch_bounds__(512) peer_allreduce_kernel(float* data, int n, b2::PeerBases pb) {
     b2::pdl_entry();
+    b2::peer_resolve_epoch(pb);
     for (int i = threadIdx.x; i < n; i += blockDim.x) b2::peer_put(pb, i, data[i]);
     for (int i = threadIdx.x; i < n; i += blockDim.x) data[i] = b2::peer_get_sum(pb, i);
 }
@@ -49,9 +50,9 @@ __global__ void __launch_bounds__(512) peer_probe_kernel(float* data, int n, b2:
 }  // namespace
 
 namespace b2 {
-int make_peer_bases(void* const* regions, int rank, int world, unsigned epoch, PeerBases* out) {
+int make_peer_bases(void* const* regions, int rank, int world, unsigned epoch, PeerBases* out, const unsigned* epoch_base) {
     memset(out, 0, sizeof(*out));
-    out->rank = 0; out->world = 1; out->epoch = epoch;
+    out->rank = 0; out->world = 1; out->epoch = epoch; out->epoch_base = epoch_base;
     if (!regions || world <= 1) {
         if (regions && world == 1 && regions[0]) out->base[0] = reinterpret_cast<unsigned char*>(regions[0]);
         return 0;
@@ -121,12 +122,13 @@ int b2_peer_exchange_probe(float* data, int n, void* const* regions, int rank, i
     return 0;
 }
 
-int b2_peer_allreduce_f32(float* data, int n, void* const* regions, int rank, int world, unsigned epoch, void* stream) {
+int b2_peer_allreduce_f32(float* data, int n, void* const* regions, int rank, int world, unsigned epoch, const unsigned* epoch_base,
+                          void* stream) {
     if (!data || !regions) return set_error("b2_peer_allreduce_f32: null pointer");
     if (n < 0 || n > kPeerMaxElems) return set_error("b2_peer_allreduce_f32: %d elements exceed %d", n, kPeerMaxElems);
     b2::PeerBases pb;
     if (world < 1) return set_error("b2_peer_allreduce_f32: rank %d of %d (at most %d peers)", rank, world, kPeerMaxWorld);
-    if (int rc = b2::make_peer_bases(regions, rank, world, epoch, &pb)) return rc;
+    if (int rc = b2::make_peer_bases(regions, rank, world, epoch, &pb, epoch_base)) return rc;
     pb.world = world;      // world == 1 still runs the exchange through the own region (identity; exercised by the tests)
     if (n == 0) return 0;
     const int threads = n >= 512 ? 512 : ((n + 31) / 32) * 32;

@@ -15,12 +15,20 @@ struct PeerBases {
     unsigned char* base[kPeerMaxWorld];
     int rank, world;      // world <= 1: no exchange
     unsigned epoch;
+    // CUDA-graph replay: a captured launch bakes its arguments, so the epoch of a replayed exchange is epoch (the launch's
+    // position inside the captured step, baked) + *epoch_base (a device word the host sets before every replay).  Null in
+    // a plain launch.
+    const unsigned* epoch_base;
 };
 
 // Host: validates and packs the caller's region table; world <= 1 or regions == null gives an inactive descriptor.
-int make_peer_bases(void* const* regions, int rank, int world, unsigned epoch, PeerBases* out);
+int make_peer_bases(void* const* regions, int rank, int world, unsigned epoch, PeerBases* out, const unsigned* epoch_base = nullptr);
 
 #ifdef __CUDACC__
+// First statement of every kernel that exchanges: resolve the epoch of a graph-replayed launch.
+__device__ __forceinline__ void peer_resolve_epoch(PeerBases& pb) {
+    if (pb.epoch_base) pb.epoch += *pb.epoch_base;
+}
 __device__ __forceinline__ void peer_st_pair(uint2* p, unsigned v, unsigned flag) {
     asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(v), "r"(flag) : "memory");
 }

@@ -79,10 +79,10 @@ _SIGNATURES = {
     "b2_sm_count": (ctypes.c_int, []),
     "b2_bn_part_rows": (ctypes.c_int, []),
     "b2_bn_stats_partial": (ctypes.c_int, [_P, _L, _I, _I, _P, ctypes.POINTER(ctypes.c_int), _P]),
-    "b2_bn_fwd_finalize": (ctypes.c_int, [_P, _I, _I, _F, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _P, _P, _P, _F, _F,
+    "b2_bn_fwd_finalize": (ctypes.c_int, [_P, _I, _I, _F, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _P, _P, _P, _P, _F, _F,
                                           _P, _P, _P, _P, _F, _P]),
     "b2_bn_bwd_partial": (ctypes.c_int, [_P, _P, _L, _I, _I, _P, _P, _I, _F, _P, ctypes.POINTER(ctypes.c_int), _P]),
-    "b2_bn_bwd_finalize": (ctypes.c_int, [_P, _I, _I, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _P, _P, _P, _P, _P,
+    "b2_bn_bwd_finalize": (ctypes.c_int, [_P, _I, _I, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _P, _P, _P, _P, _P, _P,
                                           _F, _P]),
     "b2_maxpool2x2": (ctypes.c_int, [_P, _I, _I, _I, _I, _I, _P, _P]),
     "b2_maxpool2x2_bwd": (ctypes.c_int, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
@@ -94,7 +94,7 @@ _SIGNATURES = {
     "b2_peer_open": (ctypes.c_int, [ctypes.c_char_p, ctypes.POINTER(ctypes.c_void_p)]),
     "b2_peer_close": (ctypes.c_int, [_P, _I]),
     "b2_peer_exchange_probe": (ctypes.c_int, [_P, _I, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _I, _P, _P]),
-    "b2_peer_allreduce_f32": (ctypes.c_int, [_P, _I, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _P]),
+    "b2_peer_allreduce_f32": (ctypes.c_int, [_P, _I, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _P, _P]),
     "b2_tanh_bwd": (ctypes.c_int, [_P, _P, _P, _P, _L, _P, _P]),
     "b2_gather_f32": (ctypes.c_int, [_P, _P, _L, _P, _I, _P]),
     "b2_colsum_f32": (ctypes.c_int, [_P, _L, _I, _P, _P]),

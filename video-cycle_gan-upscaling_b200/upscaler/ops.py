@@ -478,8 +478,9 @@ def sm_count():
 def _peer_args(peer):
     """(regions, rank, world, epoch) of one exchange on `peer` (upscaler.peer.PeerReducer), or the inactive form."""
     if peer is None:
-        return None, 0, 1, 0
-    return peer.regions, peer.rank, peer.world, peer.next_epoch()
+        return None, 0, 1, 0, None
+    epoch = peer.next_epoch()
+    return peer.regions, peer.rank, peer.world, epoch, peer.epoch_base_ptr()
 
 
 def bn_stats_partial(x, part=None):
@@ -501,8 +502,8 @@ def bn_fwd_finalize(part, nparts, C, count, gamma, beta, aff, moving_mean=None, 
     """Stage 2: partial rows (+ the other replicas' through `peer`) -> aff = [scale | shift | mean | invstd]; updates the
     moving statistics when given.  aff=None with sums_out: only the summed statistics (NCCL fallback).  `range_watch`
     (one float32) is set to 1 when a channel's root mean square reaches `range_limit` (guard of fp16 storage)."""
-    regions, rank, world, epoch = _peer_args(peer)
-    rc = _lib.load().b2_bn_fwd_finalize(_lib.ptr(part), int(nparts), int(C), float(count), regions, rank, world, epoch,
+    regions, rank, world, epoch, ebase = _peer_args(peer)
+    rc = _lib.load().b2_bn_fwd_finalize(_lib.ptr(part), int(nparts), int(C), float(count), regions, rank, world, epoch, ebase,
                                         _lib.ptr(sums_out), _lib.ptr(gamma), _lib.ptr(beta), eps, momentum,
                                         _lib.ptr(moving_mean), _lib.ptr(moving_var), _lib.ptr(aff), _lib.ptr(range_watch),
                                         float(range_limit), _lib.stream_ptr())
@@ -527,8 +528,8 @@ def bn_bwd_partial(z, g, aff, alpha, act, leaky, part=None):
 
 def bn_bwd_finalize(part, nparts, C, sums, dgamma=None, dbeta=None, dalpha=None, gscale=1.0, peer=None, raw_out=None):
     """Stage 2: sums = [s1 | s2] over all replicas; dbeta += s1*gscale, dgamma += s2*gscale, dalpha += local third sum."""
-    regions, rank, world, epoch = _peer_args(peer)
-    rc = _lib.load().b2_bn_bwd_finalize(_lib.ptr(part), int(nparts), int(C), regions, rank, world, epoch, _lib.ptr(raw_out),
+    regions, rank, world, epoch, ebase = _peer_args(peer)
+    rc = _lib.load().b2_bn_bwd_finalize(_lib.ptr(part), int(nparts), int(C), regions, rank, world, epoch, ebase, _lib.ptr(raw_out),
                                         _lib.ptr(sums), _lib.ptr(dgamma), _lib.ptr(dbeta), _lib.ptr(dalpha), float(gscale),
                                         _lib.stream_ptr())
     _lib.check(rc, "b2_bn_bwd_finalize")

@@ -33,20 +33,50 @@ class PeerReducer:
         dist.barrier()
         self.epoch = 0
         self.calls = 0
+        # CUDA-graph replay of a training step (training.py): a captured launch bakes its arguments, so while a step is being
+        # captured next_epoch() hands out the exchange's POSITION in the step (1, 2, ...) and the kernels add the device word
+        # `base_dev`, which the host sets to `epoch` (exchanges completed so far) before every replay.
+        self.base_dev = torch.zeros(1, dtype=torch.int32, device=device)
+        self._cap = None
 
     def next_epoch(self):
         """Epoch of the next exchange (identical call sequence on every rank); 1 .. 0x7FFFFFFE, never 0."""
+        if self._cap is not None:
+            self._cap += 1
+            return self._cap
         self.epoch = (self.epoch % 0x7FFFFFFE) + 1
         self.calls += 1
         return self.epoch
+
+    def epoch_base_ptr(self):
+        return _lib.ptr(self.base_dev) if self._cap is not None else None
+
+    def begin_capture(self):
+        self._cap = 0
+
+    def end_capture(self):
+        n, self._cap = self._cap or 0, None
+        return n
+
+    def can_replay(self, n):
+        return self.epoch + n < 0x7FFFFFF0
+
+    def before_replay(self):
+        """Enqueue (current stream) the epoch base of the captured exchanges that follow."""
+        self.base_dev.fill_(self.epoch)
+
+    def after_replay(self, n):
+        self.epoch += n
+        self.calls += n
 
     def all_reduce(self, buf):
         """In-place sum over the ranks of a contiguous float32 CUDA tensor of at most max_elems elements."""
         import torch
         if buf.dtype != torch.float32 or not buf.is_cuda or not buf.is_contiguous() or buf.numel() > self.max_elems:
             raise ValueError("peer all-reduce takes contiguous float32 CUDA tensors of at most %d elements" % self.max_elems)
-        rc = _lib.load().b2_peer_allreduce_f32(_lib.ptr(buf), buf.numel(), self.regions, self.rank, self.world, self.next_epoch(),
-                                               _lib.stream_ptr())
+        epoch = self.next_epoch()
+        rc = _lib.load().b2_peer_allreduce_f32(_lib.ptr(buf), buf.numel(), self.regions, self.rank, self.world, epoch,
+                                               self.epoch_base_ptr(), _lib.stream_ptr())
         _lib.check(rc, "b2_peer_allreduce_f32")
         from . import ops
         ops._count(1)

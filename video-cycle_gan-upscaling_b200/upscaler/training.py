@@ -87,6 +87,17 @@ def loss_activation(name, x):
 
 FROZEN_MODEL_UPDATES_MOVING_STATS = False      # see the module docstring
 
+# CUDA-graph replay of the generator-only training step.  A step is ~360 launches of which two thirds last a few microseconds;
+# issued from Python the stream runs dry whenever the host falls behind (measured on 8 GPUs sharing 32 host cores: the ranks
+# wait for each other's hosts at every one of the 66 cross-replica BatchNorm exchanges, 17.5 -> 22.3 ms per step,
+# profiles/r02_s9_peer_probe_8gpu.log).  After GRAPH_WARMUP eager calls with the same shapes the step is captured as two
+# graphs -- [weight repack + forward] and [VGG19 loss + backward] -- split where the target batch is needed, so its host
+# staging and DMA still overlap the forward pass; the gradient all-reduce (one NCCL call), Adam and the loss read stay
+# eager.  Captured launches bake their arguments: the cross-replica exchanges take their epoch from a device word
+# (peer.PeerReducer.before_replay).  Any failure to capture falls back to the eager path for good.
+GRAPH_STEPS = True
+GRAPH_WARMUP = 3
+
 # Host-side accounting of the steps (bench.py, tools/): seconds the host spent blocked in the step's one device -> host
 # read (the loss).  A step whose wait is ~0 is bound by the host's launch rate, not by the GPU.
 HOST_STATS = {"wait_s": 0.0, "reads": 0}
@@ -263,6 +274,31 @@ class _Uploader:
         return t
 
 
+def _finish_into(self, handle, dst, side_stream=False, after=None):
+    """Like finish(), but the DMA lands in the caller's persistent device tensor `dst` (CUDA-graph replay reads fixed
+    addresses).  side_stream: the copy runs on the copy stream once event `after` (recorded on the compute stream) has
+    passed, and the compute stream waits for it."""
+    key, buf, futs = handle
+    for f in futs:
+        f.result()
+    if side_stream:
+        if self.stream is None:
+            self.stream = torch.cuda.Stream(device=dst.device)
+        if after is not None:
+            self.stream.wait_event(after)
+        with torch.cuda.stream(self.stream):
+            dst.copy_(buf, non_blocking=True)
+            ev = self.events[key] = torch.cuda.Event()
+            ev.record()
+        torch.cuda.current_stream().wait_event(ev)
+        return dst
+    dst.copy_(buf, non_blocking=True)
+    ev = self.events[key] = torch.cuda.Event()
+    ev.record()
+    return dst
+
+
+_Uploader.finish_into = _finish_into
 _uploader = _Uploader()
 
 
@@ -285,6 +321,7 @@ class Compiled:
         self.gan_losses = None
         self.reducer = GradReducer()
         self._ticks = {}
+        self._warm, self._graphs, self._graph_off = {}, {}, False
 
     def _moves(self, which):
         """Whether this compiled model's training-phase passes update the moving statistics of G / D: sampled once, at
@@ -374,9 +411,120 @@ class Compiled:
         return grads
 
     # -------------------------------------------------------------- steps
+    # -------------------------------------------------------------- CUDA-graph replay of step_gen (see GRAPH_STEPS)
+    def _graph_key(self, x, y_true):
+        G = self.G
+        dist = _dist()
+        return (tuple(np.shape(x)), tuple(np.shape(y_true)), G.train_dtype, self.content.vgg.train_dtype,
+                dist.get_world_size() if dist else 1)
+
+    def _graph_state(self, x, y_true):
+        """The captured step for these shapes, capturing it when the shapes have been seen GRAPH_WARMUP times; None = run
+        the eager path."""
+        G = self.G
+        if not GRAPH_STEPS or self._graph_off or not G.on_gpu or G.device.type != "cuda":
+            return None
+        key = self._graph_key(x, y_true)
+        st = self._graphs.get(key)
+        if st is not None:
+            return st
+        n = self._warm[key] = self._warm.get(key, 0) + 1
+        if n <= GRAPH_WARMUP:
+            return None
+        sync = _make_sync()
+        peer = sync.peer_for(G.device) if sync is not None else None
+        if sync is not None and peer is None:
+            self._graph_off = True          # BatchNorm sums over NCCL: collectives stay out of captured graphs
+            return None
+        try:
+            st = self._capture_gen(key, x, y_true, sync, peer)
+        except Exception as e:  # noqa: BLE001
+            if peer is not None:
+                peer.end_capture()
+            self._graph_off = True
+            import warnings
+            warnings.warn("CUDA-graph capture of the training step failed (%s: %s); staying on the eager path" % (type(e).__name__, e),
+                          RuntimeWarning)
+            return None
+        for k in [k for k in self._graphs if k[2] != G.train_dtype]:
+            del self._graphs[k]             # graphs of a storage type the network has left (range guard)
+        self._graphs[key] = st
+        return st
+
+    def _capture_gen(self, key, x, y_true, sync, peer):
+        from types import SimpleNamespace
+        G = self.G
+        dev = G.device
+        st = SimpleNamespace(peer=peer, n1=0, n2=0)
+        st.x = torch.empty(tuple(np.shape(x)), dtype=torch.float32, device=dev)
+        st.y = torch.empty(tuple(np.shape(y_true)), dtype=torch.float32, device=dev)
+        G.ensure_grads()
+        G._train_dirty = True               # the captured forward always starts with the repack of the fp32 masters
+        pool = torch.cuda.graph_pool_handle()
+        torch.cuda.synchronize()
+        n0 = ops.launch_count()
+        st.g1, st.g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        if peer is not None:
+            peer.begin_capture()
+        with torch.cuda.graph(st.g1, pool=pool, capture_error_mode="thread_local"):
+            self._fresh(G)
+            y, tape = G.forward_train(st.x, sync, update_moving=self._moves('G'))
+        if peer is not None:
+            st.n1 = peer.end_capture()
+            peer.begin_capture()
+        with torch.cuda.graph(st.g2, pool=pool, capture_error_mode="thread_local"):
+            loss = torch.zeros(1, device=dev)
+            S = self._scale_for(G, y.numel(), y.shape[0])
+            grads = self._content(y, st.y, loss, 1.0, S)
+            dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1] if len(grads) > 1 else None)
+            G.grad_flat.zero_()
+            G.backward(tape, dz, sync, on_ready=None)
+        if peer is not None:
+            st.n2 = peer.end_capture()
+        st.launches = ops.launch_count() - n0
+        ops._count(-st.launches)            # nothing ran yet: replays are what counts
+        st.loss, st.S = loss, S
+        st.tape = {"head": tape["head"], "ups": tape["ups"]}       # tensors the range guard samples (graph-owned memory)
+        return st
+
+    def _step_gen_graph(self, st, x, y_true):
+        G = self.G
+        peer = st.peer
+        if peer is not None and not peer.can_replay(st.n1 + st.n2):
+            return None
+        hx = _uploader.begin(x, "x")
+        pending = _uploader.begin(y_true, "y")          # staged by the pool threads while the forward graph runs
+        _uploader.finish_into(hx, st.x)
+        started = torch.cuda.Event()
+        started.record()
+        if peer is not None:
+            peer.before_replay()
+        st.g1.replay()
+        if peer is not None:
+            peer.after_replay(st.n1)
+        G._train_dirty = False
+        _uploader.finish_into(pending, st.y, side_stream=True, after=started)
+        if peer is not None:
+            peer.before_replay()
+        st.g2.replay()
+        if peer is not None:
+            peer.after_replay(st.n2)
+        ops._count(st.launches)
+        dist = _dist()
+        if dist is not None:
+            dist.all_reduce(G.grad_flat)                # loss gradients carry 1/world: the sum is the global-batch gradient
+        self._adam(G, st.S)
+        self._range_tick(G, st.tape)
+        return self._mean_over_ranks(st.loss)[0]
+
     def step_gen(self, x, y_true):
         G = self.G
         dev = G.device
+        st = self._graph_state(x, y_true)
+        if st is not None:
+            r = self._step_gen_graph(st, x, y_true)
+            if r is not None:
+                return r
         self._fresh(G)
         xd = _to_dev(x, dev, "x")
         pending = _uploader.begin(y_true, "y")        # the 16x larger target batch is staged while the forward pass is launched
