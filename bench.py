@@ -291,7 +291,7 @@ def bench_gan_step(args, rank, world, dev, barrier):
         lg = gan_train.train_on_batch(x, [hr, ones])
         return ld, lg
 
-    for _ in range(3):
+    for _ in range(6):      # past training.GRAPH_WARMUP: the one-off CUDA-graph captures are not timed
         step()
     barrier()
     ops.reset_launch_count()

@@ -4,6 +4,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "video-cycle_gan-upscaling_b200"))
 import numpy as np, torch
 from upscaler import ops
+if os.environ.get('B2_NO_GRAPH'):
+    training_mod = __import__('upscaler.training', fromlist=['x'])
+    training_mod.GRAPH_STEPS = False      # A/B: eager launches instead of CUDA-graph replay
 if os.environ.get('B2_NO_PDL'):
     ops.set_pdl(False)      # A/B: plain stream order instead of programmatic dependent launch
 from upscaler import model as M
@@ -37,7 +40,7 @@ def _begin(*a, **k):
 def _finish(*a, **k):
     t0 = time.perf_counter(); r = _orig_finish(*a, **k); _up[0] += time.perf_counter() - t0; return r
 training._uploader.begin, training._uploader.finish = _begin, _finish
-for _ in range(2):
+for _ in range(6):      # past training.GRAPH_WARMUP
     step()
 _up[0] = 0.0
 rec = []

@@ -412,19 +412,11 @@ class Compiled:
 
     # -------------------------------------------------------------- steps
     # -------------------------------------------------------------- CUDA-graph replay of step_gen (see GRAPH_STEPS)
-    def _graph_key(self, x, y_true):
-        G = self.G
-        dist = _dist()
-        return (tuple(np.shape(x)), tuple(np.shape(y_true)), G.train_dtype, self.content.vgg.train_dtype,
-                dist.get_world_size() if dist else 1)
-
-    def _graph_state(self, x, y_true):
-        """The captured step for these shapes, capturing it when the shapes have been seen GRAPH_WARMUP times; None = run
-        the eager path."""
-        G = self.G
-        if not GRAPH_STEPS or self._graph_off or not G.on_gpu or G.device.type != "cuda":
+    def _graph_lookup(self, key, device, capture):
+        """The captured step stored under `key`, capturing it (capture(sync, peer) -> state) when the key has been seen
+        GRAPH_WARMUP times; None = run the eager path."""
+        if not GRAPH_STEPS or self._graph_off or device.type != "cuda":
             return None
-        key = self._graph_key(x, y_true)
         st = self._graphs.get(key)
         if st is not None:
             return st
@@ -432,12 +424,12 @@ class Compiled:
         if n <= GRAPH_WARMUP:
             return None
         sync = _make_sync()
-        peer = sync.peer_for(G.device) if sync is not None else None
+        peer = sync.peer_for(device) if sync is not None else None
         if sync is not None and peer is None:
             self._graph_off = True          # BatchNorm sums over NCCL: collectives stay out of captured graphs
             return None
         try:
-            st = self._capture_gen(key, x, y_true, sync, peer)
+            st = capture(sync, peer)
         except Exception as e:  # noqa: BLE001
             if peer is not None:
                 peer.end_capture()
@@ -446,10 +438,34 @@ class Compiled:
             warnings.warn("CUDA-graph capture of the training step failed (%s: %s); staying on the eager path" % (type(e).__name__, e),
                           RuntimeWarning)
             return None
-        for k in [k for k in self._graphs if k[2] != G.train_dtype]:
-            del self._graphs[k]             # graphs of a storage type the network has left (range guard)
+        dts = tuple(n_.train_dtype for n_ in (self.G, self.D) if n_ is not None)
+        for k in [k for k in self._graphs if k[-1] != dts]:
+            del self._graphs[k]             # graphs of a storage type a network has left (range guard)
         self._graphs[key] = st
         return st
+
+    def _dtypes(self):
+        return tuple(n_.train_dtype for n_ in (self.G, self.D) if n_ is not None)
+
+    @staticmethod
+    def _world():
+        dist = _dist()
+        return dist.get_world_size() if dist else 1
+
+    def _graph_state(self, x, y_true):
+        G = self.G
+        if not G.on_gpu:
+            return None
+        key = ("gen", tuple(np.shape(x)), tuple(np.shape(y_true)), self.content.vgg.train_dtype, self._world(), self._dtypes())
+        return self._graph_lookup(key, G.device, lambda sync, peer: self._capture_gen(key, x, y_true, sync, peer))
+
+    @staticmethod
+    def _replay(st, graph, n_exchanges):
+        if st.peer is not None:
+            st.peer.before_replay()
+        graph.replay()
+        if st.peer is not None:
+            st.peer.after_replay(n_exchanges)
 
     def _capture_gen(self, key, x, y_true, sync, peer):
         from types import SimpleNamespace
@@ -541,9 +557,62 @@ class Compiled:
         self._range_tick(G, tape)
         return self._mean_over_ranks(loss)[0]
 
+    def _capture_disc(self, x, nlab, sync, peer):
+        from types import SimpleNamespace
+        D = self.D
+        dev = D.device
+        st = SimpleNamespace(peer=peer, n1=0)
+        st.x = torch.empty(tuple(np.shape(x)), dtype=torch.float32, device=dev)
+        st.lab = torch.empty((nlab,), dtype=torch.float32, device=dev)
+        D.ensure_grads()
+        D._train_dirty = True
+        torch.cuda.synchronize()
+        n0 = ops.launch_count()
+        st.g1 = torch.cuda.CUDAGraph()
+        if peer is not None:
+            peer.begin_capture()
+        with torch.cuda.graph(st.g1, capture_error_mode="thread_local"):
+            self._fresh(D)
+            scores, tape = D.forward(st.x, True, sync, update_moving=self._moves('D'))
+            loss = torch.zeros(1, device=dev)
+            ds = torch.empty_like(scores)
+            S = self._scale_for(D, 0, scores.shape[0])
+            ops.mean_prod(scores, st.lab, loss, 1.0, S / self._world(), ds)
+            D.grad_flat.zero_()
+            D.backward(tape, ds, True, False, sync, on_ready=None)
+        if peer is not None:
+            st.n1 = peer.end_capture()
+        st.launches = ops.launch_count() - n0
+        ops._count(-st.launches)
+        st.loss, st.S = loss, S
+        return st
+
+    def _step_disc_graph(self, st, x, y):
+        D = self.D
+        if st.peer is not None and not st.peer.can_replay(st.n1):
+            return None
+        _uploader.finish_into(_uploader.begin(x, "x"), st.x)
+        _uploader.finish_into(_uploader.begin(np.asarray(y, np.float32).reshape(-1), "labels"), st.lab)
+        self._replay(st, st.g1, st.n1)
+        D._train_dirty = False
+        ops._count(st.launches)
+        dist = _dist()
+        if dist is not None:
+            dist.all_reduce(D.grad_flat)
+        self._adam(D, st.S)
+        self._range_tick(D)
+        return self._mean_over_ranks(st.loss)[0]
+
     def step_disc(self, x, y):
         D = self.D
         dev = D.device
+        if D.on_gpu:
+            key = ("disc", tuple(np.shape(x)), int(np.size(y)), self._world(), self._dtypes())
+            st = self._graph_lookup(key, dev, lambda sync, peer: self._capture_disc(x, int(np.size(y)), sync, peer))
+            if st is not None:
+                r = self._step_disc_graph(st, x, y)
+                if r is not None:
+                    return r
         self._fresh(D)
         xd = _to_dev(x, dev, "x")
         yd = _to_dev(np.asarray(y, np.float32).reshape(-1), dev, "labels")
@@ -560,9 +629,90 @@ class Compiled:
         self._range_tick(D)
         return self._mean_over_ranks(loss)[0]
 
+    def _capture_gan(self, x, y_true, nadv, amax, sync, peer):
+        from types import SimpleNamespace
+        G, D = self.G, self.D
+        dev = G.device
+        cw, dw = self.weights
+        world = self._world()
+        st = SimpleNamespace(peer=peer, n1=0, n2=0)
+        st.x = torch.empty(tuple(np.shape(x)), dtype=torch.float32, device=dev)
+        st.y = torch.empty(tuple(np.shape(y_true)), dtype=torch.float32, device=dev)
+        st.adv = torch.empty((nadv,), dtype=torch.float32, device=dev)
+        G.ensure_grads()
+        if not self.d_frozen:
+            D.ensure_grads()
+        G._train_dirty = D._train_dirty = True      # both repacks are part of the captured forward
+        pool = torch.cuda.graph_pool_handle()
+        torch.cuda.synchronize()
+        n0 = ops.launch_count()
+        st.g1, st.g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        if peer is not None:
+            peer.begin_capture()
+        with torch.cuda.graph(st.g1, pool=pool, capture_error_mode="thread_local"):
+            self._fresh(G)
+            self._fresh(D)
+            y, gtape = G.forward_train(st.x, sync, update_moving=self._moves('G'))
+            scores, dtape = D.forward(y, True, sync, update_moving=self._moves('D'))
+        if peer is not None:
+            st.n1 = peer.end_capture()
+            peer.begin_capture()
+        with torch.cuda.graph(st.g2, pool=pool, capture_error_mode="thread_local"):
+            losses = torch.zeros(2, device=dev)
+            S = self._scale_for(G, y.numel(), y.shape[0])
+            grads = self._content(y, st.y, losses[0:1], cw, S)
+            ds = torch.empty_like(scores)
+            kD = self._inner_scale(D, abs(dw * S / world) * amax / max(scores.shape[0], 1)) if self.d_frozen else 1.0
+            ops.mean_prod(scores, st.adv, losses[1:2], 1.0, dw * S * kD / world, ds)
+            grads.append(D.backward(dtape, ds, not self.d_frozen, True, sync, grad_scale=kD))
+            dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1], g3=grads[2] if len(grads) > 2 else None)
+            G.grad_flat.zero_()
+            G.backward(gtape, dz, sync, on_ready=None)
+        if peer is not None:
+            st.n2 = peer.end_capture()
+        st.launches = ops.launch_count() - n0
+        ops._count(-st.launches)
+        st.losses, st.S = losses, S
+        st.tape = {"head": gtape["head"], "ups": gtape["ups"]}
+        return st
+
+    def _step_gan_graph(self, st, x, y_true, adv_y):
+        G, D = self.G, self.D
+        cw, dw = self.weights
+        if st.peer is not None and not st.peer.can_replay(st.n1 + st.n2):
+            return None
+        hx = _uploader.begin(x, "x")
+        pending = _uploader.begin(y_true, "y")
+        _uploader.finish_into(hx, st.x)
+        _uploader.finish_into(_uploader.begin(np.asarray(adv_y, np.float32).reshape(-1), "adv"), st.adv)
+        started = torch.cuda.Event()
+        started.record()
+        self._replay(st, st.g1, st.n1)
+        G._train_dirty = D._train_dirty = False
+        _uploader.finish_into(pending, st.y, side_stream=True, after=started)
+        self._replay(st, st.g2, st.n2)
+        ops._count(st.launches)
+        dist = _dist()
+        if dist is not None:
+            dist.all_reduce(G.grad_flat)
+        self._adam(G, st.S)
+        self._range_tick(G, st.tape)
+        self._range_tick(D)
+        lc, la = self._mean_over_ranks(st.losses)
+        return [cw * lc + dw * la, lc, la]
+
     def step_gan(self, x, y_true, adv_y):
         G, D = self.G, self.D
         dev = G.device
+        if G.on_gpu:
+            amax_k = float(np.abs(np.asarray(adv_y, np.float32)).max()) if np.size(adv_y) else 0.0
+            key = ("gan", tuple(np.shape(x)), tuple(np.shape(y_true)), int(np.size(adv_y)), amax_k, self.content.vgg.train_dtype,
+                   self._world(), self._dtypes())
+            st = self._graph_lookup(key, dev, lambda sync, peer: self._capture_gan(x, y_true, int(np.size(adv_y)), amax_k, sync, peer))
+            if st is not None:
+                r = self._step_gan_graph(st, x, y_true, adv_y)
+                if r is not None:
+                    return r
         self._fresh(G)
         self._fresh(D)
         cw, dw = self.weights
