@@ -579,8 +579,13 @@ class GeneratorTrainer:
     """compile_training_model + train_on_batch (model.py:1130-1137; train_mini.py:232)."""
 
     def __init__(self, gen_weights, vgg_weights, loss_kind="vgg-mse", rate=1e-3, optimizer=None, res_block_num=16,
-                 upscale_factor=4, forward=None):
+                 upscale_factor=4, forward=None, grad_noise=None):
         self.forward = forward or upscaler_orig_forward        # or upscaler_skip_con_forward (same signature)
+        # grad_noise = (relative L2 size, seed): every gradient tensor gets white noise of that relative norm before the
+        # update.  Tests use it to measure how far the oracle's OWN trajectory moves under a perturbation of the size 16-bit
+        # storage causes in the CUDA path (the spread a free-running comparison has to be judged against).
+        self.grad_noise = grad_noise
+        self._noise_gen = torch.Generator().manual_seed(int(grad_noise[1])) if grad_noise else None
         self.w = to_torch(gen_weights, requires_grad=True)
         self.vw = to_torch(vgg_weights) if vgg_weights is not None else None
         self.kind, self.rate = loss_kind, rate
@@ -592,6 +597,12 @@ class GeneratorTrainer:
         y = self.forward(self.w, x_lr, True, stats, self.uf, self.rbn)
         loss = content_loss(self.kind, self.vw, _t(y_hr), y, self.rate)
         loss.backward()
+        if self.grad_noise:
+            with torch.no_grad():
+                for _, p in _trainable(self.w, "g"):
+                    if p.grad is not None and p.grad.numel() > 0:
+                        n = torch.randn(p.grad.shape, generator=self._noise_gen)
+                        p.grad += n * (self.grad_noise[0] * p.grad.norm() / max(float(n.norm()), 1e-30))
         self.opt.apply(_trainable(self.w, "g"))
         _apply_moving(self.w, upscaler_bn_names(self.rbn), stats)
         return float(loss.detach())

@@ -97,6 +97,7 @@ FROZEN_MODEL_UPDATES_MOVING_STATS = False      # see the module docstring
 # (peer.PeerReducer.before_replay).  Any failure to capture falls back to the eager path for good.
 GRAPH_STEPS = True
 GRAPH_WARMUP = 3
+GRAPH_MAX_SHAPES = 4          # captured steps kept per compiled model (each owns its activations: GBs at full-frame sizes)
 
 # Host-side accounting of the steps (bench.py, tools/): seconds the host spent blocked in the step's one device -> host
 # read (the loss).  A step whose wait is ~0 is bound by the host's launch rate, not by the GPU.
@@ -421,7 +422,7 @@ class Compiled:
         if st is not None:
             return st
         n = self._warm[key] = self._warm.get(key, 0) + 1
-        if n <= GRAPH_WARMUP:
+        if n <= GRAPH_WARMUP or len(self._graphs) >= GRAPH_MAX_SHAPES:
             return None
         sync = _make_sync()
         peer = sync.peer_for(device) if sync is not None else None
