@@ -153,11 +153,17 @@ class BnSync:
 
 _sync_state = {}
 
+# Data-parallel BatchNorm semantics.  True (default): the replicas exchange their BatchNorm sums, so N replicas of B/N samples
+# normalise exactly like the reference's single process does over the batch of B (parity; 66 exchanges per generator step).
+# False: every replica normalises over its own shard (what torch's DistributedDataParallel does without SyncBatchNorm) --
+# no exchange on the critical path, results differ from the single-process step.
+SYNC_BATCHNORM = True
+
 
 def _make_sync():
     """The process-wide BnSync when torch.distributed runs with more than one rank, else None."""
     dist = _dist()
-    if dist is None:
+    if dist is None or not SYNC_BATCHNORM:
         _sync_state.clear()
         return None
     if _sync_state.get("dist") is not dist or _sync_state.get("world") != dist.get_world_size():
