@@ -226,12 +226,13 @@ def bench_train_step(args, rank, world, dev, barrier, B=16, hw=(96, 96), builder
     barrier()
     ops.reset_launch_count()
     from upscaler import training as _tr
-    _tr.HOST_STATS.update(wait_s=0.0, reads=0)
+    _tr.HOST_STATS.update(wait_s=0.0, reads=0, stage_wait_s=0.0)
     t0 = time.perf_counter()
     for _ in range(args.train_steps):
         for x in xs:
             loss = tm.train_on_batch(x, hr)       # returns the loss as a host float: the step's D2H read + sync
     host_wait_ms = 1000.0 * _tr.HOST_STATS["wait_s"] / args.train_steps
+    stage_wait_ms = 1000.0 * _tr.HOST_STATS.get("stage_wait_s", 0.0) / args.train_steps
     barrier()
     t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
     if world > 1:
@@ -249,7 +250,8 @@ def bench_train_step(args, rank, world, dev, barrier, B=16, hw=(96, 96), builder
            "config": "%s, %s content loss, %d x (%dx%d -> %dx%d) per GPU, make_upscaler_%s k=%d, "
            "%s storage / fp32 accumulate / fp32 master weights + Adam%s" % (what, loss_kind, B, h, w_, 4 * h, 4 * w_, builder.replace("-", "_"), ks, str(up.net.train_dtype).replace("torch.", ""), ", NCCL data-parallel (SyncBN sums + bucketed gradient all-reduce)" if world > 1 else ""),
            "train_on_batch_calls_per_step": calls,
-           "host_wait_ms_per_step": host_wait_ms,      # time rank 0's host sat in the loss read: ~0 = bound by the host's launch rate
+           "host_wait_ms_per_step": host_wait_ms,
+           "host_stage_wait_ms_per_step": stage_wait_ms,      # time the host waited for its staging threads (pageable -> pinned copy of the batch)      # time rank 0's host sat in the loss read: ~0 = bound by the host's launch rate
            "gpu_launches_per_step": ops.launch_count() // args.train_steps, "loss": float(loss),
            "h2d_bytes_per_step": int(sum(x.nbytes for x in xs) + calls * hr.nbytes), "d2h_bytes_per_step": 4 * calls}
     if builder == "orig":

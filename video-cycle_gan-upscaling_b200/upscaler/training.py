@@ -238,9 +238,9 @@ class _Uploader:
         self.pinned, self.events, self.stream, self.pool = {}, {}, None, None
 
     def begin(self, a, slot=0):
-        a = np.asarray(a)
-        if a.dtype != np.float32:
-            a = a.astype(np.float32)
+        a = np.asarray(a)       # any numeric dtype: the reference's convert_image_series_to_array hands over float64
+        if not a.flags.c_contiguous:
+            a = np.ascontiguousarray(a)
         key = (slot, tuple(a.shape))
         buf = self.pinned.get(key)
         if buf is None:
@@ -252,13 +252,14 @@ class _Uploader:
         src = a.reshape(-1)
         n = src.size
         if n < (1 << 20):
-            dst[:] = src
+            np.copyto(dst, src, casting="unsafe")
             return key, buf, []
         if self.pool is None:
             from concurrent.futures import ThreadPoolExecutor
             self.pool = ThreadPoolExecutor(self.THREADS)
         step = -(-n // self.THREADS)
-        futs = [self.pool.submit(np.copyto, dst[i:i + step], src[i:i + step]) for i in range(0, n, step)]
+        # the cast to float32 (float64 batches are twice the bytes) happens inside the chunked, GIL-free copies
+        futs = [self.pool.submit(np.copyto, dst[i:i + step], src[i:i + step], "unsafe") for i in range(0, n, step)]
         return key, buf, futs
 
     def finish(self, handle, dev, side_stream=False):
@@ -286,8 +287,11 @@ def _finish_into(self, handle, dst, side_stream=False, after=None):
     addresses).  side_stream: the copy runs on the copy stream once event `after` (recorded on the compute stream) has
     passed, and the compute stream waits for it."""
     key, buf, futs = handle
+    import time
+    t0 = time.perf_counter()
     for f in futs:
         f.result()
+    HOST_STATS["stage_wait_s"] = HOST_STATS.get("stage_wait_s", 0.0) + time.perf_counter() - t0
     if side_stream:
         if self.stream is None:
             self.stream = torch.cuda.Stream(device=dst.device)
@@ -398,15 +402,17 @@ class Compiled:
                 setattr(net, flag, False)
 
     # -------------------------------------------------------------- content loss (+ gradient w.r.t. the generated image)
-    def _content(self, y, y_true, loss_buf, weight, S=1.0):
-        """loss_buf += content loss (unweighted); returns the gradient tensors (fp32 images) scaled by S * `weight` / world."""
+    def _content(self, y, y_true, loss_buf, weight, S=1.0, pre=None):
+        """loss_buf += content loss (unweighted); returns the gradient tensors (fp32 images) scaled by S * `weight` / world.
+        `pre` = (features, activations) of vgg.forward(y, save=True) when the caller already ran it (the graph-replayed steps
+        run the VGG19 pass over the GENERATED batch before the target batch has arrived on the device)."""
         cl = self.content
         dist = _dist()
         gs = weight / (dist.get_world_size() if dist else 1)
         vgg = cl.vgg
         self._fresh(vgg)
         ft = vgg.forward(y_true)
-        fp, acts = vgg.forward(y, save=True)
+        fp, acts = pre if pre is not None else vgg.forward(y, save=True)
         dfeat = torch.empty_like(fp)
         Sv = float(fp.numel())      # carry the feature gradient without the 1/n of the mean (fp16 range), see Vgg19Net
         ops.loss_pair(fp, ft, loss_buf, mae=cl.mae, weight=1.0, gscale=gs * Sv, grad=dfeat)
@@ -492,13 +498,15 @@ class Compiled:
         with torch.cuda.graph(st.g1, pool=pool, capture_error_mode="thread_local"):
             self._fresh(G)
             y, tape = G.forward_train(st.x, sync, update_moving=self._moves('G'))
+            self._fresh(self.content.vgg)
+            pre = self.content.vgg.forward(y, save=True)     # needs no target: more cover for the target batch's staging + DMA
         if peer is not None:
             st.n1 = peer.end_capture()
             peer.begin_capture()
         with torch.cuda.graph(st.g2, pool=pool, capture_error_mode="thread_local"):
             loss = torch.zeros(1, device=dev)
             S = self._scale_for(G, y.numel(), y.shape[0])
-            grads = self._content(y, st.y, loss, 1.0, S)
+            grads = self._content(y, st.y, loss, 1.0, S, pre=pre)
             dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1] if len(grads) > 1 else None)
             G.grad_flat.zero_()
             G.backward(tape, dz, sync, on_ready=None)
@@ -515,8 +523,8 @@ class Compiled:
         peer = st.peer
         if peer is not None and not peer.can_replay(st.n1 + st.n2):
             return None
+        pending = _uploader.begin(y_true, "y")          # the long pole first: staged by the pool threads while graph 1 runs
         hx = _uploader.begin(x, "x")
-        pending = _uploader.begin(y_true, "y")          # staged by the pool threads while the forward graph runs
         _uploader.finish_into(hx, st.x)
         started = torch.cuda.Event()
         started.record()
@@ -661,13 +669,15 @@ class Compiled:
             self._fresh(D)
             y, gtape = G.forward_train(st.x, sync, update_moving=self._moves('G'))
             scores, dtape = D.forward(y, True, sync, update_moving=self._moves('D'))
+            self._fresh(self.content.vgg)
+            pre = self.content.vgg.forward(y, save=True)
         if peer is not None:
             st.n1 = peer.end_capture()
             peer.begin_capture()
         with torch.cuda.graph(st.g2, pool=pool, capture_error_mode="thread_local"):
             losses = torch.zeros(2, device=dev)
             S = self._scale_for(G, y.numel(), y.shape[0])
-            grads = self._content(y, st.y, losses[0:1], cw, S)
+            grads = self._content(y, st.y, losses[0:1], cw, S, pre=pre)
             ds = torch.empty_like(scores)
             kD = self._inner_scale(D, abs(dw * S / world) * amax / max(scores.shape[0], 1)) if self.d_frozen else 1.0
             ops.mean_prod(scores, st.adv, losses[1:2], 1.0, dw * S * kD / world, ds)
@@ -688,8 +698,8 @@ class Compiled:
         cw, dw = self.weights
         if st.peer is not None and not st.peer.can_replay(st.n1 + st.n2):
             return None
-        hx = _uploader.begin(x, "x")
         pending = _uploader.begin(y_true, "y")
+        hx = _uploader.begin(x, "x")
         _uploader.finish_into(hx, st.x)
         _uploader.finish_into(_uploader.begin(np.asarray(adv_y, np.float32).reshape(-1), "adv"), st.adv)
         started = torch.cuda.Event()
@@ -934,21 +944,31 @@ def compile_model(model, loss, optimizer, loss_weights):
     return c
 
 
+def _as4d(x):
+    """Shape check of a batch argument WITHOUT a dtype conversion: float64 batches (what the reference's
+    convert_image_series_to_array produces) are cast to float32 inside the multi-threaded staging copy (_Uploader.begin)."""
+    a = np.asarray(x)
+    if a.ndim != 4:
+        raise ValueError("Error when checking input: expected 4 dimensions (batch, height, width, channels), got array "
+                         "with shape %s" % (a.shape,))
+    return a
+
+
 def train_on_batch(model, x, y):
     c = model._compiled
     xs = list(x) if isinstance(x, (list, tuple)) else [x]
     ys = list(y) if isinstance(y, (list, tuple)) else [y]
-    xs = [as_batch(a) for a in xs]
+    xs = [_as4d(a) for a in xs]
     if c.kind == "gen":
-        return c.step_gen(xs[0], as_batch(ys[0]))
+        return c.step_gen(xs[0], _as4d(ys[0]))
     if c.kind == "disc":
         return c.step_disc(xs[0], ys[0])
     if c.kind == "gan":
-        return c.step_gan(xs[0], as_batch(ys[0]), ys[1])
+        return c.step_gan(xs[0], _as4d(ys[0]), ys[1])
     if c.kind == "disc2":
         fi = c.fake_input_index
         return c.step_disc2(xs[1 - fi], xs[fi])
     if c.kind == "gan2":
         li = c.lr_input_index
-        return c.step_gan2(xs[li], xs[1 - li], as_batch(ys[0]))
+        return c.step_gan2(xs[li], xs[1 - li], _as4d(ys[0]))
     raise RuntimeError(c.kind)
