@@ -85,3 +85,29 @@ def test_train_on_batch_with_one_sample_and_odd_patch():
     got = tm.train_on_batch(x, hr)
     want = O.GeneratorTrainer(gw, vw, "vgg-mse", 1e-3, res_block_num=2).train_on_batch(x, hr)
     assert abs(got - want) <= 1e-2 * want
+
+
+def test_train_on_batch_takes_float64_and_strided_batches():
+    """The reference's loaders hand train_on_batch float64 arrays (data.py:266-270: array / 127.5 - 1) and slices of larger
+    arrays; the staging copy casts them to float32 on its way into pinned memory.  Same weights: same loss as the float32,
+    contiguous batch (large enough for the multi-threaded staging path)."""
+    from upscaler.keras_compat import Adam
+    from upscaler.model import VGG_MSE_LOSS, compile_training_model, make_upscaler_orig
+    gw, vw = O.init_upscaler_orig_weights(seed=4, kernel_size=3, res_block_num=1), O.init_vgg19_weights()
+    rng = np.random.default_rng(12)
+    hr = rng.uniform(-1, 1, (4, 192, 192, 3)).astype(np.float32)
+    x = hr.reshape(4, 48, 4, 48, 4, 3).mean(axis=(2, 4)).astype(np.float32)
+    losses = []
+    for variant in range(3):
+        up = make_upscaler_orig((192, 192, 3), kernel_size=3, res_block_num=1)
+        up.net.set_weights(gw)
+        tm = compile_training_model(up, VGG_MSE_LOSS((192, 192, 3), 1e-3, vgg19=vw).loss, optimizer=Adam())
+        if variant == 0:
+            xa, ya = x, hr
+        elif variant == 1:
+            xa, ya = x.astype(np.float64), hr.astype(np.float64)
+        else:                                                        # every other sample of a twice larger array
+            xa, ya = np.repeat(x, 2, axis=0)[::2], np.repeat(hr, 2, axis=0)[::2]
+            assert not ya.flags.c_contiguous
+        losses.append(tm.train_on_batch(xa, ya))
+    assert losses[0] == losses[1] == losses[2], losses

@@ -257,9 +257,14 @@ class _Uploader:
         if self.pool is None:
             from concurrent.futures import ThreadPoolExecutor
             self.pool = ThreadPoolExecutor(self.THREADS)
-        step = -(-n // self.THREADS)
-        # the cast to float32 (float64 batches are twice the bytes) happens inside the chunked, GIL-free copies
+        # Twice as many chunks as threads: finish_into() sends a chunk's DMA off as soon as it is staged, so the first half of
+        # the batch crosses PCIe while the second half is still being copied.  The cast to float32 (float64 batches are
+        # twice the bytes) happens inside the chunked, GIL-free copies.
+        step = -(-n // (2 * self.THREADS))
+        step += (-step) % 1024
+        self.ranges = getattr(self, "ranges", {})
         futs = [self.pool.submit(np.copyto, dst[i:i + step], src[i:i + step], "unsafe") for i in range(0, n, step)]
+        self.ranges[key] = [(i, min(i + step, n)) for i in range(0, n, step)]
         return key, buf, futs
 
     def finish(self, handle, dev, side_stream=False):
@@ -288,17 +293,27 @@ def _finish_into(self, handle, dst, side_stream=False, after=None):
     passed, and the compute stream waits for it."""
     key, buf, futs = handle
     import time
-    t0 = time.perf_counter()
-    for f in futs:
-        f.result()
-    HOST_STATS["stage_wait_s"] = HOST_STATS.get("stage_wait_s", 0.0) + time.perf_counter() - t0
+    HOST_STATS.setdefault("stage_wait_s", 0.0)
+    if not side_stream:
+        t0 = time.perf_counter()
+        for f in futs:
+            f.result()
+        HOST_STATS["stage_wait_s"] += time.perf_counter() - t0
     if side_stream:
         if self.stream is None:
             self.stream = torch.cuda.Stream(device=dst.device)
         if after is not None:
             self.stream.wait_event(after)
         with torch.cuda.stream(self.stream):
-            dst.copy_(buf, non_blocking=True)
+            if futs:                 # chunk by chunk, in staging order
+                flat_d, flat_s = dst.view(-1), buf.view(-1)
+                for f, (lo, hi) in zip(futs, self.ranges[key]):
+                    t1 = time.perf_counter()
+                    f.result()
+                    HOST_STATS["stage_wait_s"] += time.perf_counter() - t1
+                    flat_d[lo:hi].copy_(flat_s[lo:hi], non_blocking=True)
+            else:
+                dst.copy_(buf, non_blocking=True)
             ev = self.events[key] = torch.cuda.Event()
             ev.record()
         torch.cuda.current_stream().wait_event(ev)
