@@ -110,4 +110,5 @@ def test_train_on_batch_takes_float64_and_strided_batches():
             xa, ya = np.repeat(x, 2, axis=0)[::2], np.repeat(hr, 2, axis=0)[::2]
             assert not ya.flags.c_contiguous
         losses.append(tm.train_on_batch(xa, ya))
-    assert losses[0] == losses[1] == losses[2], losses
+    # equal up to the summation order of the loss reduction's atomics (run-to-run: ~5e-7 relative)
+    assert max(losses) - min(losses) <= 1e-5 * abs(losses[0]), losses
