@@ -10,6 +10,8 @@ if os.environ.get('B2_NO_PDL'):
 ks = int(sys.argv[1]) if len(sys.argv) > 1 else 3
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 net = UpscalerOrigNet(kernel_size=ks, seed=1)
+if os.environ.get('B2_TRUNK_CHUNK'):
+    net.TRUNK_CHUNK = int(os.environ['B2_TRUNK_CHUNK'])      # A/B: frames per trunk chunk of the inference pass
 x = torch.rand(B, 270, 480, 3, device="cuda") * 2 - 1
 out = torch.empty(B, 1080, 1920, 3, device="cuda")
 for _ in range(3): net.forward_infer(x, out)

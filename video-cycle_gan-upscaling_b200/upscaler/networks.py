@@ -466,6 +466,8 @@ class UpscalerOrigNet(Net):
     # FloatingPointError.  `saturation_report` keeps the last per-layer counts.
     on_saturation = "fallback"
     SAT_CLEAN_STREAK, SAT_CHECK_EVERY = 4, 16
+    # Frames per trunk chunk of the inference pass: None = the whole batch in one launch per layer (see _forward_infer).
+    TRUNK_CHUNK = None
     extra_layers = [("prefinal/tanh", "add"), ("final/tanh", "activation")]
 
     # graph variant (overridden by UpscalerSkipConNet)
@@ -644,6 +646,10 @@ class UpscalerOrigNet(Net):
         if self.on_gpu:
             self.refresh(("infer",))
 
+    def trunk_chunk_for(self, B, H, W):
+        c = self.TRUNK_CHUNK
+        return max(1, B) if not c or c >= B else max(1, int(c))
+
     def _sat_names(self):
         names = ["initial/conv"]
         for i in range(self.res_block_num):
@@ -682,23 +688,34 @@ class UpscalerOrigNet(Net):
         skip = chk(T("initial/conv", lambda: ops.conv2d(xp, pk["initial/conv"], f, 9, 1,
                                                         out=self._buf("skip", (B, H, W, f), dt), scale=s, shift=b, alpha=a,
                                                         act=ops.ACT_PRELU)))
-        m = skip
+        # The residual trunk walks the batch in chunks of `trunk_chunk` frames (None = whole batch): a 64-channel trunk tensor
+        # of 8 frames is 133 MB -- each layer then streams its input, residual and output through HBM -- while chunks whose three
+        # live tensors fit the 126 MB L2 keep the layer chain on-chip at the price of more launches (see TRUNK_CHUNK).
         ping = [self._buf("t%d" % i, (B, H, W, f), dt) for i in range(3)]
-        for i in range(self.res_block_num):
-            n = "res_block/%d" % i
-            free = [t for t in ping if t is not m]
-            s, b, a = inf[n + "/conv_pre"]
-            h = chk(T("res_block/*/conv_pre", lambda: ops.conv2d(m, pk[n + "/conv_pre"], f, k, k, out=free[0], scale=s, shift=b,
-                                                                 alpha=a, act=ops.ACT_PRELU)))
-            s, b, _ = inf[n + "/conv_post"]
-            m = chk(T("res_block/*/conv_post", lambda: ops.conv2d(h, pk[n + "/conv_post"], f, k, k, out=free[1], scale=s,
-                                                                  shift=b, residual=m)))
-        free = [t for t in ping if t is not m]
-        s, b, _ = inf["prefinal/conv2d"]
         kp, ku = self.prefinal_kernel, self.up_kernel
         upc = -(-self.up_filters // 64) * 64           # 224 -> 256: padded channels carry zeros
-        m = chk(T("prefinal/conv2d", lambda: ops.conv2d(m, pk["prefinal/conv2d"], 64, kp, kp, out=free[0], scale=s, shift=b,
-                                                        residual=skip)))
+        chunk = self.trunk_chunk_for(B, H, W)
+        slot0, pi_out = slot[0], 0
+        for b0 in range(0, B, chunk):
+            b1 = min(B, b0 + chunk)
+            slot[0] = slot0                            # the saturation counters of a layer add up over the chunks
+            skip_c, ping_c = skip[b0:b1], [t[b0:b1] for t in ping]
+            m = skip_c
+            for i in range(self.res_block_num):
+                n = "res_block/%d" % i
+                free = [t for t in ping_c if t is not m]
+                s, b, a = inf[n + "/conv_pre"]
+                h = chk(T("res_block/*/conv_pre", lambda: ops.conv2d(m, pk[n + "/conv_pre"], f, k, k, out=free[0], scale=s, shift=b,
+                                                                     alpha=a, act=ops.ACT_PRELU)))
+                s, b, _ = inf[n + "/conv_post"]
+                m = chk(T("res_block/*/conv_post", lambda: ops.conv2d(h, pk[n + "/conv_post"], f, k, k, out=free[1], scale=s,
+                                                                      shift=b, residual=m)))
+            free = [t for t in ping_c if t is not m]
+            s, b, _ = inf["prefinal/conv2d"]
+            m = chk(T("prefinal/conv2d", lambda: ops.conv2d(m, pk["prefinal/conv2d"], 64, kp, kp, out=free[0], scale=s, shift=b,
+                                                            residual=skip_c)))
+            pi_out = [j for j, t in enumerate(ping_c) if t is m][0]
+        m = ping[pi_out]
         h, w_ = H, W
         for i in range(self.upscale_times):
             n = "upscaling/%d/block/conv_transp" % i
