@@ -784,10 +784,79 @@ class Compiled:
         val, der = loss_activation(gl.loss_activation_name, delta)
         return (val, der, -der) if role == "disc" else (val, -der, der)
 
+    def _capture_disc2(self, real, fake, sync, peer):
+        """Two graphs around the step's host read of the two critic means (the loss activation is evaluated on the host):
+        [repack, both forward passes, means] -> host -> the two score gradients are FILLED into fixed tensors -> [both
+        backward passes]."""
+        from types import SimpleNamespace
+        D = self.D
+        dev = D.device
+        st = SimpleNamespace(peer=peer, n1=0, n2=0)
+        st.real = torch.empty(tuple(np.shape(real)), dtype=torch.float32, device=dev)
+        st.fake = torch.empty(tuple(np.shape(fake)), dtype=torch.float32, device=dev)
+        D.ensure_grads()
+        D._train_dirty = True
+        pool = torch.cuda.graph_pool_handle()
+        torch.cuda.synchronize()
+        n0 = ops.launch_count()
+        st.g1, st.g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        if peer is not None:
+            peer.begin_capture()
+        with torch.cuda.graph(st.g1, pool=pool, capture_error_mode="thread_local"):
+            self._fresh(D)
+            sr, tr = D.forward(st.real, True, sync, update_moving=self._moves('D'))
+            sf, tf = D.forward(st.fake, True, sync, update_moving=self._moves('D'))
+            st.means = torch.zeros(2, device=dev)
+            ops.mean_prod(sr, None, st.means[0:1], 1.0, 0.0, None, 1.0)
+            ops.mean_prod(sf, None, st.means[1:2], 1.0, 0.0, None, 1.0)
+            st.ds_r, st.ds_f = torch.empty_like(sr), torch.empty_like(sf)
+        if peer is not None:
+            st.n1 = peer.end_capture()
+            peer.begin_capture()
+        with torch.cuda.graph(st.g2, pool=pool, capture_error_mode="thread_local"):
+            D.grad_flat.zero_()
+            D.backward(tr, st.ds_r, True, False, sync, on_ready=None)
+            D.backward(tf, st.ds_f, True, False, sync, on_ready=None)
+        if peer is not None:
+            st.n2 = peer.end_capture()
+        st.launches = ops.launch_count() - n0
+        ops._count(-st.launches)
+        st.S, st.n = self._scale_for(D, 0, sr.shape[0]), int(sr.shape[0])
+        return st
+
+    def _step_disc2_graph(self, st, real, fake):
+        D = self.D
+        if st.peer is not None and not st.peer.can_replay(st.n1 + st.n2):
+            return None
+        world = self._world()
+        _uploader.finish_into(_uploader.begin(real, "real"), st.real)
+        _uploader.finish_into(_uploader.begin(fake, "fake"), st.fake)
+        self._replay(st, st.g1, st.n1)
+        D._train_dirty = False
+        mr, mf = self._mean_over_ranks(st.means)
+        val, d_real, d_fake = self._relativistic(mr, mf, "disc")
+        st.ds_r.fill_(d_real * st.S / world / st.n)          # = mean_prod's gradient of coef * mean(scores)
+        st.ds_f.fill_(d_fake * st.S / world / st.n)
+        self._replay(st, st.g2, st.n2)
+        ops._count(st.launches)
+        dist = _dist()
+        if dist is not None:
+            dist.all_reduce(D.grad_flat)
+        self._adam(D, st.S)
+        self._range_tick(D)
+        return val
+
     def step_disc2(self, real, fake):
         """train_gan3.py:353 — loss = act(mean(D(real)) - mean(D(fake))); real and fake are separate BatchNorm batches."""
         D = self.D
         dev = D.device
+        if D.on_gpu:
+            key = ("disc2", tuple(np.shape(real)), tuple(np.shape(fake)), self._world(), self._dtypes())
+            st = self._graph_lookup(key, dev, lambda sync, peer: self._capture_disc2(real, fake, sync, peer))
+            if st is not None:
+                r = self._step_disc2_graph(st, real, fake)
+                if r is not None:
+                    return r
         self._fresh(D)
         rd, fd = _to_dev(real, dev, "real"), _to_dev(fake, dev, "fake")
         sync = _make_sync()
@@ -812,10 +881,105 @@ class Compiled:
         self._range_tick(D)
         return val
 
+    def _capture_gan2(self, x, real, y_true, sync, peer):
+        """Three graphs: [repacks, D(real), G(x), D(G(x)), the two means, VGG19(G(x))] -> (target batch arrives) -> [content
+        loss and its gradient] -> host read of the means and the content loss -> the score gradient is FILLED into a fixed
+        tensor -> [critic backward, generator backward].  The internal critic scale kD is the one of the capturing step."""
+        from types import SimpleNamespace
+        G, D = self.G, self.D
+        dev = G.device
+        cw, dw = self.weights
+        world = self._world()
+        st = SimpleNamespace(peer=peer, n1=0, n2=0, n3=0)
+        st.x = torch.empty(tuple(np.shape(x)), dtype=torch.float32, device=dev)
+        st.real = torch.empty(tuple(np.shape(real)), dtype=torch.float32, device=dev)
+        st.y = torch.empty(tuple(np.shape(y_true)), dtype=torch.float32, device=dev)
+        G.ensure_grads()
+        if not self.d_frozen:
+            D.ensure_grads()
+        G._train_dirty = D._train_dirty = True
+        pool = torch.cuda.graph_pool_handle()
+        torch.cuda.synchronize()
+        n0 = ops.launch_count()
+        st.g1, st.g2, st.g3 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        if peer is not None:
+            peer.begin_capture()
+        with torch.cuda.graph(st.g1, pool=pool, capture_error_mode="thread_local"):
+            self._fresh(G)
+            self._fresh(D)
+            sr, _ = D.forward(st.real, True, sync, update_moving=self._moves('D'))
+            y, gtape = G.forward_train(st.x, sync, update_moving=self._moves('G'))
+            sf, dtape = D.forward(y, True, sync, update_moving=self._moves('D'))
+            st.buf = torch.zeros(3, device=dev)
+            ops.mean_prod(sr, None, st.buf[0:1], 1.0, 0.0, None, 1.0)
+            ops.mean_prod(sf, None, st.buf[1:2], 1.0, 0.0, None, 1.0)
+            self._fresh(self.content.vgg)
+            pre = self.content.vgg.forward(y, save=True)
+            st.ds = torch.empty_like(sf)
+        if peer is not None:
+            st.n1 = peer.end_capture()
+            peer.begin_capture()
+        S = self._scale_for(G, y.numel(), y.shape[0])
+        with torch.cuda.graph(st.g2, pool=pool, capture_error_mode="thread_local"):
+            grads = self._content(y, st.y, st.buf[2:3], cw, S, pre=pre)
+        if peer is not None:
+            st.n2 = peer.end_capture()
+            peer.begin_capture()
+        st.n = int(sf.shape[0])
+        st.kD = self._inner_scale(D, abs(dw * S / world) / max(st.n, 1)) if self.d_frozen else 1.0
+        with torch.cuda.graph(st.g3, pool=pool, capture_error_mode="thread_local"):
+            grads.append(D.backward(dtape, st.ds, not self.d_frozen, True, sync, grad_scale=st.kD))
+            dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1], g3=grads[2] if len(grads) > 2 else None)
+            G.grad_flat.zero_()
+            G.backward(gtape, dz, sync, on_ready=None)
+        if peer is not None:
+            st.n3 = peer.end_capture()
+        st.launches = ops.launch_count() - n0
+        ops._count(-st.launches)
+        st.S = S
+        st.tape = {"head": gtape["head"], "ups": gtape["ups"]}
+        return st
+
+    def _step_gan2_graph(self, st, x, real, y_true):
+        G, D = self.G, self.D
+        cw, dw = self.weights
+        world = self._world()
+        if st.peer is not None and not st.peer.can_replay(st.n1 + st.n2 + st.n3):
+            return None
+        pending = _uploader.begin(y_true, "y")
+        _uploader.finish_into(_uploader.begin(x, "x"), st.x)
+        _uploader.finish_into(_uploader.begin(real, "real"), st.real)
+        started = torch.cuda.Event()
+        started.record()
+        self._replay(st, st.g1, st.n1)
+        G._train_dirty = D._train_dirty = False
+        _uploader.finish_into(pending, st.y, side_stream=True, after=started)
+        self._replay(st, st.g2, st.n2)
+        mr, mf, lc = self._mean_over_ranks(st.buf)
+        la, _, d_fake = self._relativistic(mr, mf, "gen")
+        st.ds.fill_(dw * d_fake * st.S * st.kD / world / st.n)
+        self._replay(st, st.g3, st.n3)
+        ops._count(st.launches)
+        dist = _dist()
+        if dist is not None:
+            dist.all_reduce(G.grad_flat)
+        self._adam(G, st.S)
+        self._range_tick(G, st.tape)
+        self._range_tick(D)
+        return [cw * lc + dw * la, lc, la]
+
     def step_gan2(self, x, real, y_true):
         """train_gan3.py:354 — outputs [G(x), D(G(x))]; generator loss from D(fake) and D(real), D frozen."""
         G, D = self.G, self.D
         dev = G.device
+        if G.on_gpu:
+            key = ("gan2", tuple(np.shape(x)), tuple(np.shape(real)), tuple(np.shape(y_true)), self.content.vgg.train_dtype,
+                   self._world(), self._dtypes())
+            st = self._graph_lookup(key, dev, lambda sync, peer: self._capture_gan2(x, real, y_true, sync, peer))
+            if st is not None:
+                r = self._step_gan2_graph(st, x, real, y_true)
+                if r is not None:
+                    return r
         self._fresh(G)
         self._fresh(D)
         cw, dw = self.weights
