@@ -17,6 +17,7 @@ Reference lines each function follows (all under /root/reference/upscaling/upsca
   wasserstein_loss          model.py:159-160    GanLosses family      model.py:166-261
   make_discriminator_simple_512  model.py:836-896
   make_upscaler_attention   model.py:296-328 (residual_block_attention :30-48, upsampling_block_attention :78-98)
+  make_upscaler_incep_resnet model.py:445-497 (inception_mini_resblock :372-382, _3path :389-413, _2path :420-443)
   compile helpers / train steps  model.py:1017-1137, train_mini.py:224-234, train_gan.py:296-321, train_gan3.py:337-354
   tensor I/O contract       data.py:253-270
 
@@ -397,6 +398,81 @@ def upscaler_attention_bn_names(res_block_num=16):
     for i in range(res_block_num):
         names += ["res_block/%d/batch_norm_pre" % i, "res_block/%d/batch_norm_post" % i]
     return names + ["after_res/batch_norm"]
+
+
+def incep_resnet_blocks(filters=64, a=("3path", 5, 3), b=("2path", 10, 7), c=("2path", 5, 3)):
+    """[(block name, [(path, [(mini-block name, (kh, kw), cin, cout), ...]), ...], concat width)] in graph order for
+    make_upscaler_incep_resnet (model.py:389-443, 445-497): the three groups are named inc_res_block/A, /B and /c."""
+    f = filters
+    out = []
+    for tag, (btype, num, k) in (("A", a), ("B", b), ("c", c)):
+        for i in range(num):
+            if btype == "3path":
+                base = "inc_res_block/%s/3p/%d" % (tag, i)
+                f1, f2, f3 = int(f * 0.5), int(f * 0.75), f
+                paths = [("a", [(base + "/a/1", (1, 1), f, f1)]),
+                         ("b", [(base + "/b/1", (1, 1), f, f1), (base + "/b/2", (k, k), f1, f1)]),
+                         ("c", [(base + "/c/1", (1, 1), f, f1), (base + "/c/2", (k, k), f1, f2), (base + "/c/3", (k, k), f2, f3)])]
+            else:
+                base = "inc_res_block/%s/2p/%d" % (tag, i)
+                fa, f1, f2, f3 = int(f * 0.5), int(f * 0.3), int(f * 0.4), int(f * 0.5)
+                paths = [("a", [(base + "/a/1", (1, 1), f, fa)]),
+                         ("b", [(base + "/b/1", (1, 1), f, f1), (base + "/b/2", (1, k), f1, f2), (base + "/b/3", (k, 1), f2, f3)])]
+            out.append((base, paths, sum(p[1][-1][3] for p in paths)))
+    return out
+
+
+def init_upscaler_incep_resnet_weights(seed=1234, filters=64, upscale_factor=4, a=("3path", 5, 3), b=("2path", 10, 7),
+                                       c=("2path", 5, 3), randomize=True, block_gain=0.5):
+    """make_upscaler_incep_resnet (model.py:445-497) in Keras layout under the reference's layer names: every mini block is
+    BatchNormalization -> PReLU -> Conv2D named <name>/batch_norm, <name>/prelu, <name>/<kh>x<kw> (model.py:372-382)."""
+    rng = np.random.default_rng(seed)
+    bs = 0.05 if randomize else 0.0
+    f = filters
+    w = {"initial/conv/9x9": _conv_w(rng, 9, 9, 3, f, bs)}
+    for base, paths, cat in incep_resnet_blocks(f, a, b, c):
+        for _, minis in paths:
+            for name, (kh, kw), cin, cout in minis:
+                w[name + "/batch_norm"] = _bn_w(rng, cin, randomize)
+                w[name + "/prelu"] = [(rng.uniform(0, 0.3, (1, 1, cin)) if randomize else np.zeros((1, 1, cin))).astype(np.float32)]
+                w[name + "/%dx%d" % (kh, kw)] = _conv_w(rng, kh, kw, cin, cout, bs)
+        # block_gain scales the 1x1 conv that closes a block: with glorot kernels at gain 1 the 20 pre-activation blocks
+        # push the residual stream to std ~20 and 13 % of the outputs into tanh saturation, where nothing can be compared
+        w[base + "/final/1x1"] = _conv_w(rng, 1, 1, cat, f, bs)
+        w[base + "/final/1x1"][0] = (w[base + "/final/1x1"][0] * block_gain).astype(np.float32)
+    ck = c[2]
+    w["prefinal/conv2d"] = _conv_w(rng, ck, ck, f, f, bs)
+    w["prefinal/batch_norm"] = _bn_w(rng, f, randomize)
+    cin = f
+    for i in range(int(math.log(upscale_factor, 2))):
+        w["upscaling/%d/block/conv_transp" % i] = [glorot_uniform(rng, (ck, ck, 256, cin), ck * ck * cin, ck * ck * 256),
+                                                   (rng.standard_normal(256) * bs).astype(np.float32)]
+        cin = 256
+    w["final/conv"] = _conv_w(rng, 9, 9, cin, 3, bs)
+    return w
+
+
+def upscaler_incep_resnet_forward(w, x_nhwc, training=False, stats_out=None, filters=64, upscale_factor=4, a=("3path", 5, 3),
+                                  b=("2path", 10, 7), c=("2path", 5, 3)):
+    """make_upscaler_incep_resnet (model.py:445-497): 9x9 conv (no activation) -> inception residual blocks (each path a chain
+    of BN -> PReLU -> conv mini blocks, the paths concatenated, a 1x1 conv back to `filters`, added to the block input) ->
+    conv + BN + skip -> two Conv2DTranspose(256, k, stride 2) + LeakyReLU(0.2) -> 9x9 conv -> tanh."""
+    x = _t(x_nhwc).permute(0, 3, 1, 2)
+    m = conv2d_same(x, *w["initial/conv/9x9"])
+    skip = m
+    for base, paths, _ in incep_resnet_blocks(filters, a, b, c):
+        outs = []
+        for _, minis in paths:
+            t = m
+            for name, (kh, kw), _, _ in minis:
+                t = prelu(batch_norm(t, *w[name + "/batch_norm"], training, stats_out), w[name + "/prelu"][0])
+                t = conv2d_same(t, *w[name + "/%dx%d" % (kh, kw)])
+            outs.append(t)
+        m = m + conv2d_same(torch.cat(outs, dim=1), *w[base + "/final/1x1"])
+    m = skip + batch_norm(conv2d_same(m, *w["prefinal/conv2d"]), *w["prefinal/batch_norm"], training, stats_out)
+    for i in range(int(math.log(upscale_factor, 2))):
+        m = leaky(conv2d_transpose_same_s2(m, *w["upscaling/%d/block/conv_transp" % i]), 0.2)
+    return torch.tanh(conv2d_same(m, *w["final/conv"])).permute(0, 2, 3, 1)
 
 
 def upscaler_bn_names(res_block_num=16):

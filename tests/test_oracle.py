@@ -205,3 +205,26 @@ def test_attention_generator_oracle_pieces_and_shapes():
         with torch.no_grad():
             y = O.upscaler_attention_forward(O.to_torch(w), rng.uniform(-1, 1, (2, 6, 7, 3)).astype(np.float32))
         assert tuple(y.shape) == (2, 24, 28, 3) and float(y.abs().max()) <= 1.0
+
+
+def test_incep_resnet_oracle_structure_matches_the_package_and_the_reference_layer_list():
+    """make_upscaler_incep_resnet (model.py:445-497): filter counts int(64 * .3 / .4 / .5 / .75) = 19 / 25 / 32 / 48, layer names
+    <block>/<path>/<i>/{batch_norm, prelu, KHxKW}; the oracle's weight keys equal the package's layer list (two independent
+    restatements of the same graph), parameter counts agree, shapes propagate."""
+    import sys, os
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "video-cycle_gan-upscaling_b200"))
+    from upscaler import networks
+    w = O.init_upscaler_incep_resnet_weights(seed=5)
+    specs = networks.upscaler_incep_resnet_layer_specs()
+    assert [n for n, _, _ in specs] == list(w.keys())
+    for name, kind, cfg in specs:
+        for a, shp in zip(w[name], networks._shapes(kind, cfg)):
+            assert tuple(a.shape) == tuple(shp), name
+    assert tuple(w["inc_res_block/B/2p/3/b/2/1x7"][0].shape) == (1, 7, 19, 25)
+    assert tuple(w["inc_res_block/B/2p/3/b/3/7x1"][0].shape) == (7, 1, 25, 32)
+    assert tuple(w["inc_res_block/A/3p/0/c/2/3x3"][0].shape) == (3, 3, 32, 48)
+    assert tuple(w["inc_res_block/A/3p/0/final/1x1"][0].shape) == (1, 1, 128, 64)
+    assert tuple(w["inc_res_block/c/2p/4/final/1x1"][0].shape) == (1, 1, 64, 64)
+    with torch.no_grad():
+        y = O.upscaler_incep_resnet_forward(O.to_torch(w), np.random.default_rng(1).uniform(-1, 1, (2, 6, 7, 3)).astype(np.float32))
+    assert tuple(y.shape) == (2, 24, 28, 3)

@@ -662,7 +662,25 @@ def load_model(filepath, custom_objects=None, compile=False):
     attrs, weights = read_keras_weights(filepath)
     in_shape, arch = _input_shape_from_config(attrs)
     names = set(weights)
-    if "initial/conv" in names and "final/conv" in names:
+    if "initial/conv/9x9" in names and "final/conv" in names:       # make_upscaler_incep_resnet (model.py:445-497)
+        def group(tag):
+            for typ, sub, axis in (("3path", "3p", 0), ("2path", "2p", 1)):
+                pre = "inc_res_block/%s/%s/" % (tag, sub)
+                idxs = {n[len(pre):].split("/")[0] for n in names if n.startswith(pre)}
+                if idxs:
+                    conv = [n for n in names if n.startswith(pre + "0/b/2/") and not n.endswith(("batch_norm", "prelu"))][0]
+                    return (typ, len(idxs), int(weights[conv][0].shape[axis]))
+            return ("2path", 0, int(weights["prefinal/conv2d"][0].shape[0]))
+        nup = len([n for n in names if n.startswith("upscaling/") and n.endswith("/conv_transp")])
+        f = 2 ** nup
+        if in_shape is None or in_shape[0] is None or in_shape[1] is None:
+            in_shape = (96, 96, 3)
+        a, b, c = group("A"), group("B"), group("c")
+        m = M.make_upscaler_incep_resnet((in_shape[0] * f, in_shape[1] * f, 3), filters=int(weights["initial/conv/9x9"][0].shape[3]),
+                                         upscale_factor=f, a_block_type=a[0], a_block_num=a[1], a_block_kernel=a[2],
+                                         b_block_type=b[0], b_block_num=b[1], b_block_kernel=b[2],
+                                         c_block_type=c[0], c_block_num=c[1], c_block_kernel=c[2])
+    elif "initial/conv" in names and "final/conv" in names:
         k = int(weights["res_block/0/conv_pre"][0].shape[0]) if "res_block/0/conv_pre" in names else int(arch.get("kernel_size", 5))
         nres = len([n for n in names if n.startswith("res_block/") and n.endswith("/conv_pre")])
         nup = len([n for n in names if n.startswith("upscaling/") and n.endswith("/conv_transp")])

@@ -37,8 +37,8 @@ def make_upscaler_skip_con(output_image_shape, kernel_size=5, filters=64, upscal
 def _not_built(name, lines):
     raise NotImplementedError(
         "%s (reference upscaling/upscaler/model.py:%s) is not built on the B200 path yet; the generators that run are "
-        "make_upscaler_orig, make_upscaler_skip_con and (inference) make_upscaler_attention (SURVEY.md 8f-3 lists the rest as "
-        "next)" % (name, lines))
+        "make_upscaler_orig, make_upscaler_skip_con and (inference) make_upscaler_attention / make_upscaler_incep_resnet "
+        "(SURVEY.md 8f-3 lists the rest as next)" % (name, lines))
 
 
 def make_upscaler_unetish(output_image_shape, kernel_size=5, upscale_factor=4, step_size=4, downscale_times=5,
@@ -76,8 +76,18 @@ def make_upscaler_attention(output_image_shape, kernel_size=5, filters=64, upsca
 def make_upscaler_incep_resnet(output_image_shape, filters=64, upscale_factor=4, a_block_type='3path', a_block_num=5,
                                a_block_kernel=3, b_block_type='2path', b_block_num=10, b_block_kernel=7,
                                c_block_type='2path', c_block_num=5, c_block_kernel=3):
-    """model.py:445-497 (inception-style residual blocks with 1x1, 1xk, kx1 convs); raises when called."""
-    _not_built("make_upscaler_incep_resnet", "445-497")
+    """model.py:445-497 — generator of inception-style residual blocks (inception_resblock_3path / _2path, model.py:389-443:
+    pre-activation BatchNorm -> PReLU -> Conv2D mini blocks with 1x1, kxk, 1xk, kx1 kernels).  Inference (predict / save /
+    load_model) runs on the B200 kernels; compiling it for training raises (its training step is not built)."""
+    h, w, c = output_image_shape
+    if c != 3:
+        raise ValueError("make_upscaler_incep_resnet: the final conv emits 3 channels (model.py:490)")
+    if filters != 64:
+        raise ValueError("the B200 path is built for filters=64 (reference default, model.py:446)")
+    net = networks.UpscalerIncepResnetNet(filters=filters, upscale_factor=upscale_factor,
+                                          a=(a_block_type, a_block_num, a_block_kernel), b=(b_block_type, b_block_num, b_block_kernel),
+                                          c=(c_block_type, c_block_num, c_block_kernel))
+    return Model(net=net, input_shape=(h // upscale_factor, w // upscale_factor, c), name="model_1")
 
 
 def make_discriminator_simple_512(input_shape, activation='none'):

@@ -102,6 +102,50 @@ def upscaler_attention_layer_specs(kernel_size=5, filters=64, upscale_factor=4, 
     return specs
 
 
+def incep_resnet_blocks(filters=64, a=("3path", 5, 3), b=("2path", 10, 7), c=("2path", 5, 3)):
+    """[(block name, [(path, [(mini-block name, (kh, kw), cin, cout), ...]), ...], concat width)] in graph order for
+    make_upscaler_incep_resnet (model.py:389-443, 445-497); the three groups are named inc_res_block/A, /B and /c."""
+    f = filters
+    out = []
+    for tag, (btype, num, k) in (("A", a), ("B", b), ("c", c)):
+        for i in range(num):
+            if btype == "3path":
+                base = "inc_res_block/%s/3p/%d" % (tag, i)
+                f1, f2, f3 = int(f * 0.5), int(f * 0.75), f
+                paths = [("a", [(base + "/a/1", (1, 1), f, f1)]),
+                         ("b", [(base + "/b/1", (1, 1), f, f1), (base + "/b/2", (k, k), f1, f1)]),
+                         ("c", [(base + "/c/1", (1, 1), f, f1), (base + "/c/2", (k, k), f1, f2), (base + "/c/3", (k, k), f2, f3)])]
+            elif btype == "2path":
+                base = "inc_res_block/%s/2p/%d" % (tag, i)
+                fa, f1, f2, f3 = int(f * 0.5), int(f * 0.3), int(f * 0.4), int(f * 0.5)
+                paths = [("a", [(base + "/a/1", (1, 1), f, fa)]),
+                         ("b", [(base + "/b/1", (1, 1), f, f1), (base + "/b/2", (1, k), f1, f2), (base + "/b/3", (k, 1), f2, f3)])]
+            else:
+                raise ValueError("inception block type %r (the reference knows '3path' and '2path')" % (btype,))
+            out.append((base, paths, sum(p[1][-1][3] for p in paths)))
+    return out
+
+
+def upscaler_incep_resnet_layer_specs(filters=64, upscale_factor=4, a=("3path", 5, 3), b=("2path", 10, 7), c=("2path", 5, 3)):
+    """make_upscaler_incep_resnet (model.py:445-497) in graph order with the reference's layer names."""
+    f = filters
+    specs = [("initial/conv/9x9", "conv", dict(kh=9, kw=9, cin=3, cout=f))]
+    for base, paths, cat in incep_resnet_blocks(f, a, b, c):
+        for _, minis in paths:
+            for name, (kh, kw), cin, cout in minis:
+                specs += [(name + "/batch_norm", "bn", dict(c=cin)), (name + "/prelu", "prelu", dict(c=cin)),
+                          (name + "/%dx%d" % (kh, kw), "conv", dict(kh=kh, kw=kw, cin=cin, cout=cout))]
+        specs.append((base + "/final/1x1", "conv", dict(kh=1, kw=1, cin=cat, cout=f)))
+    ck = c[2]
+    specs += [("prefinal/conv2d", "conv", dict(kh=ck, kw=ck, cin=f, cout=f)), ("prefinal/batch_norm", "bn", dict(c=f))]
+    cin = f
+    for i in range(int(math.log(upscale_factor, 2))):
+        specs.append(("upscaling/%d/block/conv_transp" % i, "convT", dict(kh=ck, kw=ck, cin=cin, cout=256)))
+        cin = 256
+    specs.append(("final/conv", "conv", dict(kh=9, kw=9, cin=cin, cout=3)))
+    return specs
+
+
 VGG19_CFG = [64, 64, "M", 128, 128, "M", 256, 256, 256, 256, "M", 512, 512, 512, 512, "M", 512, 512, 512, 512]
 VGG19_NAMES = ["block1_conv1", "block1_conv2", "block2_conv1", "block2_conv2", "block3_conv1", "block3_conv2",
                "block3_conv3", "block3_conv4", "block4_conv1", "block4_conv2", "block4_conv3", "block4_conv4",
@@ -1041,6 +1085,170 @@ class UpscalerAttentionNet(UpscalerOrigNet):
             h_, w_, cin = 2 * h_, 2 * w_, ATT_UP_FILTERS
         if out is None:
             out = torch.empty((B, h_, w_, 3), dtype=torch.float32, device=self.device)
+        return T("final/conv", lambda: ops.conv2d_scatter(m, pk["final/conv"], 3, 9, 9, bias=w["final/conv"][1], act=ops.ACT_TANH, out=out))
+
+
+class UpscalerIncepResnetNet(UpscalerOrigNet):
+    """make_upscaler_incep_resnet (model.py:445-497): a 9x9 head conv WITHOUT activation, 20 inception residual blocks -- every
+    path a chain of pre-activation mini blocks BatchNorm -> PReLU -> Conv2D with 1x1, kxk, 1xk and kx1 kernels and 19-64
+    filters (model.py:372-443), the paths concatenated and closed by a 1x1 conv -- then the `orig` tail.  Inference path.
+    On the B200 kernels every tensor keeps 64 channels (narrower paths are zero-padded: zero weight rows, zero folded scale /
+    shift, so padding channels stay exactly 0).  Inside a path the NEXT mini block's BatchNorm + PReLU is the epilogue of the
+    conv that feeds it; only the first mini block of a path needs a stand-alone affine + PReLU pass over the block input.
+    Concatenate + 1x1 conv is linear in the paths, so it runs as one 1x1 conv per path chained through the epilogue's
+    residual operand, the first link carrying the block input (the residual Add): no concatenated tensor exists."""
+
+    supports_training = False
+    extra_layers = [("prefinal/tanh", "add"), ("final/tanh", "activation")]
+
+    def __init__(self, filters=64, upscale_factor=4, a=("3path", 5, 3), b=("2path", 10, 7), c=("2path", 5, 3), weights=None,
+                 device="cuda", seed=None, infer_dtype=torch.float16):
+        self.block_cfg = (tuple(a), tuple(b), tuple(c))
+        self.blocks = incep_resnet_blocks(filters, *self.block_cfg)
+        super().__init__(kernel_size=c[2], filters=filters, upscale_factor=upscale_factor, res_block_num=len(self.blocks),
+                         weights=weights, device=device, seed=seed, infer_dtype=infer_dtype)
+
+    def _layer_specs(self):
+        return upscaler_incep_resnet_layer_specs(self.filters, self.upscale_factor, *self.block_cfg)
+
+    def _build_index_maps(self):
+        self._final_chan_map, self._convT_wgrad_idx, self._convT_bias_idx = None, {}, {}
+        self._final_rows = True
+
+        def padded(kh, kw, cin, cout, c0=0, cin_total=None):
+            """[64][kh*kw][64] index map of a Keras kernel (kh, kw, cin_total, cout) restricted to input channels [c0, c0+cin)."""
+            ct = cin_total or cin
+            idx = -np.ones((64, kh * kw, 64), np.int64)
+            t = np.arange(kh * kw)[None, :, None]
+            ci = np.arange(cin)[None, None, :]
+            co = np.arange(cout)[:, None, None]
+            idx[:cout, :, :cin] = (t * ct + c0 + ci) * cout + co
+            return idx.astype(np.int32)
+
+        self.add_pack("infer", "initial/conv/9x9", "initial/conv/9x9", ops.conv_rowfold_pack_index(9, 9, 3, self.filters))
+        for base, paths, cat in self.blocks:
+            c0 = 0
+            for pname, minis in paths:
+                for name, (kh, kw), cin, cout in minis:
+                    lname = name + "/%dx%d" % (kh, kw)
+                    self.add_pack("infer", lname, lname, padded(kh, kw, cin, cout))
+                width = minis[-1][3]
+                self.add_pack("infer", base + "/final/1x1#" + pname, base + "/final/1x1", padded(1, 1, width, self.filters, c0, cat))
+                c0 += width
+        k = self.kernel_size
+        self.add_pack("infer", "prefinal/conv2d", "prefinal/conv2d", ops.conv_pack_index(k, k, 64, 64))
+        cin = 64
+        for i in range(self.upscale_times):
+            n = "upscaling/%d/block/conv_transp" % i
+            self.add_pack("infer", n, n, ops.convT_pack_index(k, k, cin, 256))
+            cin = 256
+        self.add_pack("infer", "final/conv", "final/conv", ops.conv_scatter_pack_index(9, 9, cin, 3))
+        self.build_packs({"infer": self.infer_dtype})
+
+    def refresh(self, sets=("infer",)):
+        for s in sets:
+            self.refresh_packs(s)
+            setattr(self, "_%s_dirty" % s, False)
+        if "infer" not in sets:
+            return
+        self._sat_pending = True
+        w = self.weights
+        nslots = sum(1 + len(m) for _, paths, _ in self.blocks for _, m in paths) + 1     # per path: its pre-activation + its convs
+        vec = self._vec("fold", 4 * 64 * nslots, zero=True)                               # [scale | shift | alpha | bias] x 64 per slot
+        slot = [0]
+
+        def take():
+            i = slot[0]
+            slot[0] += 1
+            return [vec[4 * 64 * i + 64 * j:4 * 64 * i + 64 * (j + 1)] for j in range(4)]
+
+        def fold(bn_name, conv_bias, scale, shift):
+            gamma, beta, mean, var = w[bn_name]
+            C = gamma.numel()
+            ops.bn_fold(gamma, beta, mean, var, conv_bias, scale[:C], shift[:C], BN_EPS)
+
+        inf = {}
+        for base, paths, cat in self.blocks:
+            for pname, minis in paths:
+                # stand-alone BatchNorm + PReLU of the path's first mini block (applied to the block input)
+                sc, sh, al, _ = take()
+                fold(minis[0][0] + "/batch_norm", None, sc, sh)
+                a0 = w[minis[0][0] + "/prelu"][0].reshape(-1)
+                al[:a0.numel()].copy_(a0)
+                inf[minis[0][0] + "#pre"] = (sc, sh, al)
+                for j, (name, (kh, kw), cin, cout) in enumerate(minis):
+                    lname = name + "/%dx%d" % (kh, kw)
+                    sc, sh, al, bi = take()
+                    if j + 1 < len(minis):          # the conv's epilogue = the next mini block's BatchNorm + PReLU
+                        nxt = minis[j + 1][0]
+                        fold(nxt + "/batch_norm", w[lname][1], sc, sh)
+                        an = w[nxt + "/prelu"][0].reshape(-1)
+                        al[:an.numel()].copy_(an)
+                        inf[lname] = (sc, sh, al, ops.ACT_PRELU)
+                    else:                           # last conv of the path: bias only
+                        bi[:cout].copy_(w[lname][1])
+                        inf[lname] = (None, bi, None, ops.ACT_NONE)
+            inf[base + "/final/1x1"] = w[base + "/final/1x1"][1]
+        sc, sh, _, _ = take()
+        fold("prefinal/batch_norm", w["prefinal/conv2d"][1], sc, sh)
+        inf["prefinal/conv2d"] = (sc, sh)
+        for i in range(self.upscale_times):
+            n = "upscaling/%d/block/conv_transp" % i
+            inf[n] = w[n][1]
+        self._infer = inf
+
+    def _sat_names(self):
+        return (["initial/conv/9x9"] + [b[0] for b in self.blocks] + ["prefinal/conv2d"] +
+                ["upscaling/%d/block/conv_transp" % i for i in range(self.upscale_times)])
+
+    def forward_train(self, *a, **k):
+        raise NotImplementedError("make_upscaler_incep_resnet: the inference path is built on the B200 kernels; its training "
+                                  "step is not (use make_upscaler_orig or make_upscaler_skip_con for training)")
+
+    backward = forward_train
+
+    def _forward_infer(self, x, out, counters):
+        B, H, W, C = x.shape
+        f, dt, k = self.filters, self.infer_dtype, self.kernel_size
+        inf, pk, w = self._infer, self._packed["infer"], self.weights
+        slot = [0]
+
+        def chk(t):
+            if counters is not None:
+                ops.count_saturated(t, counters[slot[0]:slot[0] + 1])
+                slot[0] += 1
+            return t
+        T = self._timed
+        buf = lambda name: self._buf(name, (B, H, W, f), dt)
+        xp = T("initial/fold", lambda: ops.fold_taps(x, [(0, dx - 4) for dx in range(9)], out=self._buf("fold", (B, H, W, 64), dt), dtype=dt))
+        skip = chk(T("initial/conv", lambda: ops.conv2d(xp, pk["initial/conv/9x9"], f, 9, 1, out=buf("skip"), shift=w["initial/conv/9x9"][1])))
+        m, streams = skip, [buf("s0"), buf("s1")]
+        for bi, (base, paths, cat) in enumerate(self.blocks):
+            acc = m                                     # the chain of 1x1 convs starts from the block input (the residual Add)
+            for pi, (pname, minis) in enumerate(paths):
+                sc, sh, al = inf[minis[0][0] + "#pre"]
+                t = T("inc_res_block/*/pre", lambda: ops.affine_act(m, buf("p0"), sc, sh, al, ops.ACT_PRELU))
+                for j, (name, (kh, kw), cin, cout) in enumerate(minis):
+                    lname = name + "/%dx%d" % (kh, kw)
+                    sc, sh, al, act = inf[lname]
+                    t = T("inc_res_block/*/conv", lambda: ops.conv2d(t, pk[lname], f, kh, kw, out=buf("p%d" % (1 + j % 2)), scale=sc, shift=sh,
+                                                                     alpha=al, act=act))
+                last = pi == len(paths) - 1
+                dst = [s_ for s_ in streams if s_ is not m][0] if last else buf("c%d" % (pi % 2))
+                acc = T("inc_res_block/*/final_1x1", lambda: ops.conv2d(t, pk[base + "/final/1x1#" + pname], f, 1, 1, out=dst,
+                                                                        shift=inf[base + "/final/1x1"] if pi == 0 else None, residual=acc))
+            m = chk(acc)
+        sc, sh = inf["prefinal/conv2d"]
+        nxt = [s_ for s_ in streams if s_ is not m][0]
+        m = chk(T("prefinal/conv2d", lambda: ops.conv2d(m, pk["prefinal/conv2d"], 64, k, k, out=nxt, scale=sc, shift=sh, residual=skip)))
+        h, w_ = H, W
+        for i in range(self.upscale_times):
+            n = "upscaling/%d/block/conv_transp" % i
+            ob = self._buf("up%d" % i, (B, 2 * h, 2 * w_, 256), dt)
+            m = chk(T(n, lambda: ops.conv2d_transpose_s2(m, pk[n], 256, k, k, out=ob, shift=inf[n], act=ops.ACT_LEAKY, leaky=0.2)))
+            h, w_ = 2 * h, 2 * w_
+        if out is None:
+            out = torch.empty((B, h, w_, 3), dtype=torch.float32, device=self.device)
         return T("final/conv", lambda: ops.conv2d_scatter(m, pk["final/conv"], 3, 9, 9, bias=w["final/conv"][1], act=ops.ACT_TANH, out=out))
 
 
