@@ -55,6 +55,12 @@ def _worker(rank, world, port, q):
         # ---- replica mean of the reported losses
         c = T.Compiled("gen", None, None)
         res["loss"] = c._mean_over_ranks(torch.tensor([1.0 + rank, 10.0 * (rank + 1)]))
+        # ---- switches: per-replica BatchNorm statistics hand the layers no sync object; CPU tensors never reach a CUDA graph
+        T.SYNC_BATCHNORM = False
+        res["nosync"] = T._make_sync() is None
+        T.SYNC_BATCHNORM = True
+        res["sync_again"] = T._make_sync() is not None
+        res["graph_cpu"] = c._graph_lookup(("gen", (1,), (1,), None, world, ()), torch.device("cpu"), lambda s_, p_: 1 / 0) is None
         q.put((rank, res))
     finally:
         dist.destroy_process_group()
@@ -83,6 +89,7 @@ def test_dp_host_logic_world2_gloo():
         assert got[r]["rows"] == 20
         np.testing.assert_allclose(got[r]["st"], 3.0)
         assert got[r]["loss"] == [1.5, 15.0]
+        assert got[r]["nosync"] and got[r]["sync_again"] and got[r]["graph_cpu"]
     assert got[0]["buckets"] == got[1]["buckets"]
 
 
