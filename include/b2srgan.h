@@ -265,6 +265,25 @@ int b2_bn_bwd_partial(const void* z, const void* g, int64_t rows, int C, int f16
 int b2_bn_bwd_finalize(const float* part, int nparts, int C, void* const* peer_regions, int rank, int world, unsigned epoch,
                        const unsigned* epoch_base, float* raw_out, float* sums, float* dgamma, float* dbeta, float* dalpha, float gscale, void* stream);
 
+/* Forward BatchNormalization statistics for callers that cannot allocate device memory.  (No counterpart in the
+ * reference: Keras / TensorFlow allocate freely; this serves hosts that embed the library.)
+ * Same arithmetic and same bits as b2_bn_stats_partial followed by a single-replica b2_bn_fwd_finalize (no moving-statistics
+ * update, no range watch), but the per-CTA partial rows live in a 1 212 416-byte array compiled into the library
+ * (296 rows x 2 x 512 floats, resident on every GPU that loads it until the process exits) instead of a tensor the caller
+ * has to provide.  Meant for a plugin inside another framework's memory arena, a real-time frame loop that must not stall
+ * in the allocator, or a process whose device-memory quota is already committed: those callers own x and the outputs but
+ * have nowhere to get the scratch rows from.  The call performs no cudaMalloc / cudaFree and uses no allocating library.
+ *   x: [rows][C] 16-bit (f16 = 1 fp16, 0 bf16), C a multiple of 8 with 256 % (C/8) == 0 and 8 <= C <= 512; wider layers are
+ *      refused with an error (b2_last_error) -- use the two-call form with your own buffer for those.
+ *   sums_out (2*C floats, nullable): [sum x | sum x^2].  aff (4*C floats, nullable; needs gamma, beta): [scale | shift |
+ *      mean | invstd] for `count` elements per channel.  At least one of the two must be given.
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress, with that device current) and
+ * keeps it; make that first call outside any stream capture.  All calls share the one array: nothing has to be cleared
+ * between calls (every row stage 2 reads is rewritten by stage 1 of the same call), but calls that run concurrently on one
+ * GPU -- two streams, two threads -- overwrite each other's rows.  Issue them in order on a device. */
+int b2_bn_fwd_stats_static(const void* x, int64_t rows, int C, int f16, float count, const float* gamma, const float* beta,
+                           float eps, float* sums_out, float* aff, void* stream);
+
 /* MaxPooling2D(2,2) 'valid' of VGG19 (keras.applications behind model.py:108) and its gradient (first maximum of each
  * window takes the gradient; relu_gate != 0 additionally zeroes it where x <= 0, i.e. the ReLU of the conv below). */
 int b2_maxpool2x2(const void* x, int B, int H, int W, int C, int f16, void* y, void* stream);

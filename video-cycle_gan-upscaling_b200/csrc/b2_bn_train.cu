@@ -15,6 +15,8 @@
 // same layers — real and fake batches of the two-input discriminator model, train_gan3.py:353 — cannot disturb them).
 #include <cuda_fp16.h>
 
+#include <mutex>
+
 #include "../../include/b2srgan.h"
 #include "b2_conv_epilogue.cuh"
 #include "b2_host.h"
@@ -377,3 +379,71 @@ int b2_bn_bwd_finalize(const float* part, int nparts, int C, void* const* peer_r
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------ allocation-free variant
+// b2_bn_fwd_stats_static: both stages of the forward statistics in one call, with the partial rows kept in a buffer that
+// is part of the library image instead of one the caller provides.  It exists for hosts that may not allocate device
+// memory when they reach this code: a plugin running inside another framework's memory arena (every cudaMalloc there
+// fragments or bypasses the arena's accounting), a real-time capture / playback loop where an allocation is an unbounded
+// stall, or a process whose device-memory quota was handed out at start-up and is fully spoken for.  Such callers own
+// their input and output tensors already; the only thing they lack is the [b2_bn_part_rows()][2*C] scratch tensor that
+// b2_bn_stats_partial / b2_bn_fwd_finalize need between the two launches.
+//
+// The buffer costs kStaticPartRows * 2 * kStaticMaxC floats (1 212 416 bytes) on every GPU that loads the library, for the
+// life of the process.  It is shared by all calls: nothing in it needs clearing (stage 1 rewrites every row stage 2 reads,
+// each call), but two calls that overlap on one GPU -- different streams, or different host threads -- write the same rows
+// and corrupt each other.  Keep calls on a device ordered.
+constexpr int kStaticPartRows = 296;            // rows stage 1 may write: 2 CTAs per SM of a 148-SM B200
+constexpr int kStaticMaxC = 512;                // widest BatchNormalization on the path (discriminator blocks, model.py:840-884)
+static __device__ __align__(256) float g_static_part[size_t(kStaticPartRows) * 2 * kStaticMaxC];
+
+namespace {
+// Device address of g_static_part on the current device.  In host code the symbol's own name is only a handle the runtime
+// looks the array up by -- it is not a pointer a kernel may dereference -- so the address is asked for once per device,
+// with that device current, and remembered.  Returns null (error text set) when the lookup fails.
+float* static_part_ptr() {
+    static std::mutex mu;
+    static float* ptrs[64] = {nullptr};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) {
+        set_error("b2_bn_fwd_stats_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_part);
+        if (e != cudaSuccess || !p) {
+            set_error("b2_bn_fwd_stats_static: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+            return nullptr;
+        }
+        ptrs[dev] = static_cast<float*>(p);
+    }
+    return ptrs[dev];
+}
+}  // namespace
+
+extern "C" int b2_bn_fwd_stats_static(const void* x, int64_t rows, int C, int f16, float count, const float* gamma, const float* beta,
+                                      float eps, float* sums_out, float* aff, void* stream) {
+    if (!x) return set_error("b2_bn_fwd_stats_static: x is null");
+    if (!sums_out && !aff) return set_error("b2_bn_fwd_stats_static: neither sums_out nor aff given");
+    if (aff && (!gamma || !beta)) return set_error("b2_bn_fwd_stats_static: gamma / beta missing");
+    if (rows < 1) return set_error("b2_bn_fwd_stats_static: rows=%lld", static_cast<long long>(rows));
+    if (C < 8 || C > kStaticMaxC)
+        return set_error("b2_bn_fwd_stats_static: C=%d is outside the built-in scratch buffer's range (8..%d channels); "
+                         "use b2_bn_stats_partial + b2_bn_fwd_finalize with a buffer of your own", C, kStaticMaxC);
+    int blocks;
+    if (part_grid(rows, C, &blocks)) return set_error("b2_bn_fwd_stats_static: C=%d unsupported (C/8 must divide %d)", C, kEwThreads);
+    if (blocks > kStaticPartRows) blocks = kStaticPartRows;      // a GPU with more SMs than a B200 still fits the buffer
+    float* part = static_part_ptr();                             // first call on a device: symbol lookup (not capturable)
+    if (!part) return -1;
+    b2::launch_k(bn_stats_partial_kernel, blocks, kEwThreads, 0, B2_STREAM, x, long(rows), C, f16, part, 0);
+    if (int rc = launch_ok("b2_bn_fwd_stats_static (stage 1)")) return rc;
+    PeerBases pb;
+    make_peer_bases(nullptr, 0, 1, 0u, &pb, nullptr);            // single replica: no exchange, nothing to fail
+    b2::launch_k(bn_fwd_finalize_kernel, (C + kFinChan - 1) / kFinChan, kFinThreads, 0, B2_STREAM, static_cast<const float*>(part), blocks, C,
+                 count, pb, sums_out, gamma, beta, eps, 0.f, static_cast<float*>(nullptr), static_cast<float*>(nullptr), aff,
+                 static_cast<float*>(nullptr), 0.f);
+    return launch_ok("b2_bn_fwd_stats_static (stage 2)");
+}

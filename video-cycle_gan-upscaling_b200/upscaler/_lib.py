@@ -81,6 +81,7 @@ _SIGNATURES = {
     "b2_bn_stats_partial": (ctypes.c_int, [_P, _L, _I, _I, _P, ctypes.POINTER(ctypes.c_int), _P]),
     "b2_bn_fwd_finalize": (ctypes.c_int, [_P, _I, _I, _F, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _P, _P, _P, _P, _F, _F,
                                           _P, _P, _P, _P, _F, _P]),
+    "b2_bn_fwd_stats_static": (ctypes.c_int, [_P, _L, _I, _I, _F, _P, _P, _F, _P, _P, _P]),
     "b2_bn_bwd_partial": (ctypes.c_int, [_P, _P, _L, _I, _I, _P, _P, _I, _F, _P, ctypes.POINTER(ctypes.c_int), _P]),
     "b2_bn_bwd_finalize": (ctypes.c_int, [_P, _I, _I, ctypes.POINTER(ctypes.c_void_p), _I, _I, ctypes.c_uint, _P, _P, _P, _P, _P, _P,
                                           _F, _P]),

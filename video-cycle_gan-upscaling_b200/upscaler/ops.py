@@ -512,6 +512,19 @@ def bn_fwd_finalize(part, nparts, C, count, gamma, beta, aff, moving_mean=None, 
     return aff
 
 
+def bn_fwd_stats_static(x, count, gamma=None, beta=None, sums_out=None, aff=None, eps=1e-3):
+    """Forward BatchNorm statistics without a scratch tensor: b2_bn_fwd_stats_static keeps the partial rows in an array
+    built into the library (C <= 512), for embedding hosts that may not allocate device memory.  This wrapper allocates
+    nothing either: the caller passes the outputs (sums_out [2*C] and / or aff [4*C]).  Calls on one device must not overlap."""
+    rows, C = _rows_c(x)
+    _require_cuda(x)
+    rc = _lib.load().b2_bn_fwd_stats_static(_lib.ptr(x), rows, C, _dt(x), float(count), _lib.ptr(gamma), _lib.ptr(beta), float(eps),
+                                            _lib.ptr(sums_out), _lib.ptr(aff), _lib.stream_ptr())
+    _lib.check(rc, "b2_bn_fwd_stats_static")
+    _count(2)
+    return sums_out, aff
+
+
 def bn_bwd_partial(z, g, aff, alpha, act, leaky, part=None):
     """Stage 1 of the BatchNorm backward sums through act(BN(z)): partial [sum dy | sum dy*xhat | sum g*min(u,0)] rows."""
     rows, C = _rows_c(z)
