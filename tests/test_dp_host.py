@@ -61,6 +61,25 @@ def _worker(rank, world, port, q):
         T.SYNC_BATCHNORM = True
         res["sync_again"] = T._make_sync() is not None
         res["graph_cpu"] = c._graph_lookup(("gen", (1,), (1,), None, world, ()), torch.device("cpu"), lambda s_, p_: 1 / 0) is None
+        # ---- decisions that change the collectives of a step are taken together: a range hit on rank 0 ALONE moves both
+        # replicas to bf16 storage (one rank switching by itself would change its graph key and all-reduce pattern), and a
+        # capture that fails on one rank keeps every rank on the eager path
+        import warnings
+        from upscaler.networks import UpscalerOrigNet
+        net = UpscalerOrigNet(kernel_size=3, device="cpu")
+        res["dtype_before"] = net.train_dtype
+        if rank == 0:
+            net.range_flag().fill_(1.0)
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            c._range_tick(net)                                  # first tick always reads the flag
+        res["dtype_after"] = net.train_dtype
+        c._range_tick(net)                                      # bf16 now: no collective, no read
+        net2 = UpscalerOrigNet(kernel_size=3, device="cpu")
+        c._range_tick(net2)                                     # nobody hit: nobody switches
+        res["dtype_quiet"] = net2.train_dtype
+        res["any"] = [T.agree(rank == 1, None, "any"), T.agree(False, None, "any")]
+        res["all"] = [T.agree(rank == 1, None, "all"), T.agree(True, None, "all")]
         q.put((rank, res))
     finally:
         dist.destroy_process_group()
@@ -90,6 +109,9 @@ def test_dp_host_logic_world2_gloo():
         np.testing.assert_allclose(got[r]["st"], 3.0)
         assert got[r]["loss"] == [1.5, 15.0]
         assert got[r]["nosync"] and got[r]["sync_again"] and got[r]["graph_cpu"]
+        assert got[r]["dtype_before"] == torch.float16 and got[r]["dtype_after"] == torch.bfloat16
+        assert got[r]["dtype_quiet"] == torch.float16
+        assert got[r]["any"] == [True, False] and got[r]["all"] == [False, True]
     assert got[0]["buckets"] == got[1]["buckets"]
 
 

@@ -412,9 +412,11 @@ class Net:
             if self.on_gpu:
                 self.refresh(("train",))
 
-    def check_range(self, extra=()):
+    def check_range(self, extra=(), agree=None):
         """Host side of the guard: reads the flag (one small D2H) plus a saturation count of `extra` tensors; on a hit warns and
-        drops to bf16 storage, or raises (ON_RANGE).  Returns True when the storage type was switched."""
+        drops to bf16 storage, or raises (ON_RANGE).  Returns True when the storage type was switched.  `agree` (data-parallel
+        training: local hit -> hit on any replica, a collective) makes all replicas switch together; the flag and the sampled
+        count are per replica, and replicas on different storage types would issue different collectives."""
         flag = self.range_flag()
         if flag is None:
             return False
@@ -425,6 +427,8 @@ class Net:
             if t is not None and t.dtype == torch.float16:
                 ops.count_saturated(t, cnt)
         hit = float(flag.item()) != 0.0 or int(cnt.item()) != 0
+        if agree is not None:
+            hit = agree(hit)
         if not hit:
             return False
         flag.zero_()

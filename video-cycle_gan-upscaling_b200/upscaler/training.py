@@ -119,6 +119,21 @@ def _dist():
     return None
 
 
+def agree(flag, device=None, mode="any"):
+    """One decision for all data-parallel replicas: True when `flag` holds on ANY rank (mode "any") or on ALL ranks ("all").
+    Decisions that change which collectives a step issues -- leaving fp16 storage after a range hit (a new graph key, eager
+    warm-up steps with bucketed all-reduces), giving up on CUDA-graph capture -- must fall the same way everywhere, or one
+    rank waits in a collective its peers never post.  Every rank has to call this at the same point of the step sequence;
+    a single process returns `flag` unchanged."""
+    dist = _dist()
+    if dist is None:
+        return bool(flag)
+    on_dev = device is not None and torch.device(device).type == "cuda" and dist.get_backend() == "nccl"
+    t = torch.tensor([1.0 if flag else 0.0], dtype=torch.float32, device=device if on_dev else "cpu")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX if mode == "any" else dist.ReduceOp.MIN)
+    return bool(t.item() != 0.0)
+
+
 class BnSync:
     """Cross-replica exchange of the BatchNorm sums.  Where the replicas can map each other's memory the exchange is
     folded into the BatchNorm finalize kernels (csrc/b2_bn_train.cu over csrc/b2_peer.cuh): `peer_for(device)` returns
@@ -370,7 +385,7 @@ class Compiled:
             extra = []
             if tape is not None and "ups" in tape:
                 extra = [tape["head"][1]] + list(tape["ups"][1:])
-            net.check_range(extra)
+            net.check_range(extra, agree=lambda hit: agree(hit, net.device, "any"))
 
     # -------------------------------------------------------------- Adam
     @staticmethod
@@ -456,15 +471,20 @@ class Compiled:
         if sync is not None and peer is None:
             self._graph_off = True          # BatchNorm sums over NCCL: collectives stay out of captured graphs
             return None
+        st = err = None
         try:
             st = capture(sync, peer)
         except Exception as e:  # noqa: BLE001
+            err = e
             if peer is not None:
                 peer.end_capture()
+        # replayed and eager steps issue different collectives: all replicas replay, or none does (every rank reaches this
+        # point on the same step: the key and its warm-up count are functions of shapes and storage types only)
+        if not agree(st is not None, device, "all"):
             self._graph_off = True
             import warnings
-            warnings.warn("CUDA-graph capture of the training step failed (%s: %s); staying on the eager path" % (type(e).__name__, e),
-                          RuntimeWarning)
+            why = "%s: %s" % (type(err).__name__, err) if err is not None else "another replica could not capture it"
+            warnings.warn("CUDA-graph capture of the training step failed (%s); staying on the eager path" % why, RuntimeWarning)
             return None
         dts = tuple(n_.train_dtype for n_ in (self.G, self.D) if n_ is not None)
         for k in [k for k in self._graphs if k[-1] != dts]:
