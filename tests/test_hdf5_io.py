@@ -181,3 +181,70 @@ def test_save_and_load_model_pick_the_variant_from_the_weight_shapes(tmp_path):
     assert all(np.array_equal(x, y) for k in a for x, y in zip(a[k], b[k]))
     with pytest.raises(ValueError):
         make_discriminator_sparse_512((256, 256, 3))
+
+
+def test_load_model_resolves_keras_auto_named_generator_files(tmp_path):
+    """example_movie_frames/model_upscaler_orig_vgg-mse_best.h5 (example_frame_test.ipynb cell 9) was written by
+    old/train_orig_vgg-mse.py, which names no layer: the file carries Keras' per-class counters (conv2d_N,
+    batch_normalization_N, p_re_lu_N, conv2d_transpose_N, plus weightless add_N / leaky_re_lu_N / activation_N) and a
+    width-first (480, 270, 3) input.  A synthetic file in exactly that layout -- counters NOT starting at 1, as after an
+    earlier model in the same process, layer_names in graph order -- must load into make_upscaler_orig with every weight in
+    the right layer."""
+    import json
+    from upscaler.model import load_model, make_upscaler_orig
+    rng = np.random.default_rng(5)
+    up = make_upscaler_orig((64, 96, 3), kernel_size=3, res_block_num=2)
+    host = {k: [rng.standard_normal(a.shape).astype(np.float32) for a in v] for k, v in up.net.host_weights().items()}
+    up.net.set_weights(host)
+    counters = {"conv2d": 6, "batch_normalization": 3, "p_re_lu": 11, "conv2d_transpose": 0, "add": 1, "leaky_re_lu": 4, "activation": 0}
+    suffixes = {"conv": ("conv2d", ["kernel:0", "bias:0"]), "convT": ("conv2d_transpose", ["kernel:0", "bias:0"]),
+                "bn": ("batch_normalization", ["gamma:0", "beta:0", "moving_mean:0", "moving_variance:0"]), "prelu": ("p_re_lu", ["alpha:0"])}
+
+    def auto(cls):
+        counters[cls] += 1
+        return "%s_%d" % (cls, counters[cls])
+
+    root = H.H5Group()
+    cfg = {"class_name": "Model", "config": {"name": "model_1", "layers": [
+        {"class_name": "InputLayer", "name": "input_1", "config": {"batch_input_shape": [None, 480, 270, 3], "dtype": "float32", "name": "input_1"}}]}}
+    root.attrs += [("keras_version", b"2.2.4"), ("backend", b"tensorflow"), ("model_config", json.dumps(cfg).encode("utf8"))]
+    mw = root.require_group("model_weights")
+    layer_names, mapping = ["input_1"], {}
+    mw.require_group("input_1").attrs.append(("weight_names", np.zeros((0,), dtype="S1")))
+
+    def weightless(cls):
+        n = auto(cls)
+        layer_names.append(n)
+        mw.require_group(n).attrs.append(("weight_names", np.zeros((0,), dtype="S1")))
+
+    for name, kind, _ in up.net.specs:
+        cls, sfx = suffixes[kind]
+        n = auto(cls)
+        mapping[name] = n
+        layer_names.append(n)
+        g = mw.require_group(n)
+        wn = [("%s/%s" % (n, s_)).encode("utf8") for s_ in sfx]
+        g.attrs.append(("weight_names", np.array(wn)))
+        for w, a in zip(wn, host[name]):
+            g.create_dataset(w.decode("utf8"), a)
+        if name.endswith("batch_norm_post") or name == "prefinal/batch_norm":
+            weightless("add")
+        if kind == "convT":
+            weightless("leaky_re_lu")
+    weightless("activation")
+    mw.attrs.append(("layer_names", np.array([n.encode("utf8") for n in layer_names])))
+    p = str(tmp_path / "model_upscaler_orig_vgg-mse_best.h5")
+    H.write_h5(p, root)
+    assert mapping["initial/conv"] == "conv2d_7" and mapping["final/conv"] == "conv2d_13" and mapping["res_block/1/prelu"] == "p_re_lu_14"
+    m = load_model(p, custom_objects={"loss": None})
+    assert m.net.kernel_size == 3 and m.net.res_block_num == 2
+    assert m.input_shape == (None, 480, 270, 3) and m.output_shape == (None, 1920, 1080, 3)      # width-first, as the file says
+    got = m.net.host_weights()
+    for k in host:
+        assert all(np.array_equal(x, y) for x, y in zip(host[k], got[k])), k
+    # a file whose layer counts do not form the generator's graph is refused, not mis-assigned
+    del mw.children[mapping["res_block/1/batch_norm_post"]]
+    mw.attrs[-1] = ("layer_names", np.array([n.encode("utf8") for n in layer_names if n != mapping["res_block/1/batch_norm_post"]]))
+    H.write_h5(p, root)
+    with pytest.raises(ValueError, match="auto-named"):
+        load_model(p)

@@ -18,6 +18,7 @@ parameter stores of networks.py by layer name.  Chunked / compressed datasets an
 reported as unsupported rather than guessed at.
 """
 import json
+import re
 import struct
 
 import numpy as np
@@ -650,6 +651,49 @@ def _input_shape_from_config(attrs):
     return None, arch
 
 
+_AUTO_NAME = re.compile(r"^(conv2d_transpose|conv2d|batch_normalization|p_re_lu)_(\d+)$")
+
+
+def _resolve_auto_names(weights):
+    """Generator files written by a script that names no layer (old/train_orig_vgg-mse.py:25-90, the source of
+    example_movie_frames/model_upscaler_orig_vgg-mse_best.h5) carry Keras' automatic names: `conv2d_7`,
+    `batch_normalization_3`, `p_re_lu_1`, `conv2d_transpose_2`, ... -- one counter per layer class, advancing in construction
+    order (and not necessarily from 1: every earlier model of the process advanced them too).  The graph of that script is
+    make_upscaler_orig's (model.py:267-295), so the i-th layer of each class, by counter, is the i-th layer of that class in
+    graph order; this returns the weights under model.py's names.  Files that already use them pass through."""
+    if "initial/conv" in weights or "initial/conv/9x9" in weights:
+        return weights
+    by_class = {}
+    for n, ws in weights.items():
+        m = _AUTO_NAME.match(n)
+        if m and ws:
+            by_class.setdefault(m.group(1), []).append((int(m.group(2)), n))
+    conv, bn, prelu, convt = ([n for _, n in sorted(by_class.get(c, []))]
+                              for c in ("conv2d", "batch_normalization", "p_re_lu", "conv2d_transpose"))
+    if len(conv) < 3 or not convt:
+        return weights
+    nres = (len(conv) - 3) // 2
+    if len(conv) != 2 * nres + 3 or len(bn) != 2 * nres + 1 or len(prelu) != nres + 1:
+        raise ValueError("auto-named Keras file: %d Conv2D / %d BatchNormalization / %d PReLU layers do not form "
+                         "make_upscaler_orig's graph (2n+3 / 2n+1 / n+1)" % (len(conv), len(bn), len(prelu)))
+    want = {"conv2d": ["initial/conv"], "batch_normalization": [], "p_re_lu": ["initial/prelu"],
+            "conv2d_transpose": ["upscaling/%d/block/conv_transp" % j for j in range(len(convt))]}
+    for i in range(nres):
+        want["conv2d"] += ["res_block/%d/conv_pre" % i, "res_block/%d/conv_post" % i]
+        want["batch_normalization"] += ["res_block/%d/batch_norm_pre" % i, "res_block/%d/batch_norm_post" % i]
+        want["p_re_lu"].append("res_block/%d/prelu" % i)
+    want["conv2d"] += ["prefinal/conv2d", "final/conv"]
+    want["batch_normalization"].append("prefinal/batch_norm")
+    out = {}
+    for have, cls in ((conv, "conv2d"), (bn, "batch_normalization"), (prelu, "p_re_lu"), (convt, "conv2d_transpose")):
+        for old, new in zip(have, want[cls]):
+            out[new] = weights[old]
+    # sanity of the mapping: the head is the 9x9 conv on 3 channels, the tail the 9x9 conv to 3 channels
+    if out["initial/conv"][0].shape[:3] != (9, 9, 3) or out["final/conv"][0].shape[:2] != (9, 9) or out["final/conv"][0].shape[3] != 3:
+        raise ValueError("auto-named Keras file: first / last Conv2D are not the generator's 9x9 head / tail convs")
+    return out
+
+
 def load_model(filepath, custom_objects=None, compile=False):
     """keras.models.load_model for the model families of the hot path (upscaler_mini_testing.ipynb cell 5,
     example_frame_test.ipynb): the architecture is recognised from the layer names and weight shapes in the file
@@ -660,6 +704,7 @@ def load_model(filepath, custom_objects=None, compile=False):
     from .keras_compat import Model
     from . import networks
     attrs, weights = read_keras_weights(filepath)
+    weights = _resolve_auto_names(weights)
     in_shape, arch = _input_shape_from_config(attrs)
     names = set(weights)
     if "initial/conv/9x9" in names and "final/conv" in names:       # make_upscaler_incep_resnet (model.py:445-497)
