@@ -171,7 +171,7 @@ def cpu_oracle_train_samples_per_s(ks, B=2, hw=(96, 96)):
     t0 = time.perf_counter()
     ref.train_on_batch(x, hr)
     dt = time.perf_counter() - t0
-    return {"value": B / dt, "unit": "samples/s", "cores": cores, "kind": "port",
+    return {"value": B / dt, "unit": "samples/s", "cores": cores, "kind": "port", "like_for_like_batch": False,
             "sample": "one train_on_batch of %d patches of %dx%d -> %dx%d (%.1f s) through the PyTorch-CPU fp32 autograd oracle "
                       "(the step named by the config has 16: scaled by batch size, BatchNorm over 2 instead of 16 samples)" % (B, h, w_, 4 * h, 4 * w_, dt)}
 
@@ -192,9 +192,27 @@ def cpu_oracle_gan_images_per_s(ks, n=1, lr=128):
     t0 = time.perf_counter()
     ref.step(x, hr)
     dt = time.perf_counter() - t0
-    return {"value": n / dt, "unit": "samples/s", "cores": cores, "kind": "port",
+    return {"value": n / dt, "unit": "samples/s", "cores": cores, "kind": "port", "like_for_like_batch": False,
             "sample": "one loop iteration with n = %d LR image(s) of %dx%d -> %dx%d (%.1f s) through the PyTorch-CPU fp32 oracle "
                       "(the GPU leg pushes 6 per iteration)" % (n, lr, lr, 4 * lr, 4 * lr, dt)}
+
+
+def training_path_text(compiled_list, dev, world):
+    """Words for a training leg's `config`, derived from the path the timed steps actually took: CUDA-graph replay or eager
+    launches, and for N > 1 how the BatchNorm sums and the gradients crossed the replicas."""
+    from upscaler import training as T
+    replay = all(bool(c._graphs) and not c._graph_off for c in compiled_list)
+    txt = ", steps replayed from captured CUDA graphs" if replay else ", eager launches (no CUDA-graph replay)"
+    if world > 1:
+        sync = T._make_sync()
+        peer = sync.peer_for(dev) if sync is not None else None
+        bn = ("per-replica BatchNorm statistics" if sync is None else
+              "BatchNorm sums exchanged over NVLink peer memory inside the finalize kernels" if peer is not None else
+              "BatchNorm sums all-reduced over NCCL")
+        gr = ("one NCCL all-reduce of the flat gradient after backward (not overlapped)" if replay else
+              "bucketed NCCL gradient all-reduce overlapped with backward")
+        txt += ", data-parallel: %s; %s" % (bn, gr)
+    return txt
 
 
 def bench_train_step(args, rank, world, dev, barrier, B=16, hw=(96, 96), builder="orig", loss_kind="vgg-mse", calls=1,
@@ -248,7 +266,7 @@ def bench_train_step(args, rank, world, dev, barrier, B=16, hw=(96, 96), builder
     out = {"metric": "train samples/s", "value": world * B * 1000.0 / ms, "unit": "samples/s" if calls == 1 else "HR frames/s (iterations/s x batch)",
            "ms_per_step": ms, "steps": args.train_steps,
            "config": "%s, %s content loss, %d x (%dx%d -> %dx%d) per GPU, make_upscaler_%s k=%d, "
-           "%s storage / fp32 accumulate / fp32 master weights + Adam%s" % (what, loss_kind, B, h, w_, 4 * h, 4 * w_, builder.replace("-", "_"), ks, str(up.net.train_dtype).replace("torch.", ""), ", NCCL data-parallel (SyncBN sums + bucketed gradient all-reduce)" if world > 1 else ""),
+           "%s storage / fp32 accumulate / fp32 master weights + Adam%s" % (what, loss_kind, B, h, w_, 4 * h, 4 * w_, builder.replace("-", "_"), ks, str(up.net.train_dtype).replace("torch.", ""), training_path_text([tm._compiled], dev, world)),
            "train_on_batch_calls_per_step": calls,
            "host_wait_ms_per_step": host_wait_ms,
            "host_stage_wait_ms_per_step": stage_wait_ms,      # time the host waited for its staging threads (pageable -> pinned copy of the batch)      # time rank 0's host sat in the loss read: ~0 = bound by the host's launch rate
@@ -310,7 +328,7 @@ def bench_gan_step(args, rank, world, dev, barrier):
     tf = GAN_STEP_FLOPS_PER_IMAGE[ks] * n * world / (ms * 1e-3) / 1e12
     out = {"metric": "GAN train LR images/s", "value": world * n * 1000.0 / ms, "unit": "samples/s", "ms_per_step": ms, "steps": steps,
            "config": "train_gan.py step: predict + discriminator step (2n images) + GAN step, n = %d LR images of 128x128 -> 512x512 per GPU, "
-                     "k=%d, simple_512 discriminator, vgg-mse + Wasserstein, shared Adam, %s training storage%s" % (n, ks, str(G.net.train_dtype).replace("torch.", ""), ", NCCL data-parallel" if world > 1 else ""),
+                     "k=%d, simple_512 discriminator, vgg-mse + Wasserstein, shared Adam, %s training storage%s" % (n, ks, str(G.net.train_dtype).replace("torch.", ""), training_path_text([disc_train._compiled, gan_train._compiled], dev, world)),
            "algorithmic_tflops": tf, "frac_of_bf16_sustained_peak": tf / world / peaks["bf16_tflops_sustained"],
            "gpu_launches_per_step": ops.launch_count() // steps, "loss_disc": float(ld), "loss_gan": [float(v) for v in lg]}
     del gen_train, disc_train, gan_train, G, D
@@ -466,6 +484,7 @@ def main():
                 "peak_kind": "bf16 dense sustained, %s" % peaks["source"], "traffic": traffic,
                 "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)",
                 "traffic_source": ("profiles/" + prof[1]) if prof else None,
+                "traffic_profiled_offline": True,    # read from the committed ncu capture (B = 8) and rescaled by batch; NOT measured in this run
                 "algorithmic_bytes": (2.12e9 + 8.49e9) * B / 8 if ks == 3 else None,
                 "share_of_step": (dom_ms / ms_step) if dom_ms else None}
         whole = GEN_FLOPS[ks] * world * B / (ms_step * 1e-3) / 1e12

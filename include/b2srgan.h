@@ -356,6 +356,14 @@ int b2_cast_scale(const void* in, int in_dtype, int64_t n, float scale, void* ou
  * lr_t = lr*sqrt(1-b2^t)/(1-b1^t) computed by the caller. */
 int b2_adam(float* params, const float* grads, float* m, float* v, int64_t n, float lr_t, float beta1, float beta2, float eps,
             float gscale, void* stream);
+/* The same update behind a device-side guard: guard0 / guard1 (each nullable) point at `guard_words` 32-bit words; if any
+ * word is non-zero when the kernel runs, nothing is written (parameters, m, v keep their bits).  The training step points
+ * them at the words its fp16 passes raise -- the BatchNormalization range flag (b2_bn_fwd_finalize range_watch) and the
+ * saturation count of sampled activation gradients (b2_count_saturated) -- so an update computed from clipped 16-bit
+ * values is dropped without a host round trip; the host reads the words with the step's loss and switches storage type.
+ * (Keras has no counterpart: the reference trains in fp32, model.py:1026-1137.) */
+int b2_adam_guarded(float* params, const float* grads, float* m, float* v, int64_t n, float lr_t, float beta1, float beta2, float eps,
+                    float gscale, const void* guard0, const void* guard1, int guard_words, void* stream);
 
 #ifdef __cplusplus
 }

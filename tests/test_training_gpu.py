@@ -372,6 +372,42 @@ def test_fp16_training_storage_range_guard_falls_back_to_bf16():
     assert not rec2 and up2.net.train_dtype == torch.float16
 
 
+def test_fp16_backward_guard_drops_the_update_and_falls_back_to_bf16():
+    """The forward range guard cannot see the backward pass: activation gradients are stored in fp16 with a saturating
+    conversion too, multiplied by the step's gradient scale.  With a scale far too large they clip at +-65504; the update
+    computed from them must not reach the weights.  The backward pass counts saturated values in the gradient tensors it
+    samples, the (guarded) Adam launch reads that count on the device and does nothing, and the host -- reading the count with
+    the loss -- takes Adam's step counter back, warns and continues in bf16 storage, where the next step is a normal one."""
+    import warnings
+    from upscaler import training
+    up, tm, _ = _gen_setup(3, 1, "vgg-mse", 1e-3)
+    x, hr = _data(2, 16, seed=3)
+    net, opt = up.net, tm._compiled.opt
+    tm.train_on_batch(x, hr)                                   # an ordinary fp16 step: update applied, nothing raised
+    assert net.train_dtype == torch.float16 and opt.iterations == 1
+    assert int(net.guard_words().abs().sum()) == 0
+    nt = net.n_trainable                                       # (the BatchNorm moving statistics behind it move in every forward pass)
+    w1 = net.flat[:nt].clone()
+    slots = [t.clone() for t in tm._compiled.slots[id(net)]]
+    old = training.GRAD_SCALE["G"]
+    training.GRAD_SCALE["G"] = 1e13                            # instead of numel (~1e5): every 16-bit gradient tensor clips
+    try:
+        with warnings.catch_warnings(record=True) as rec:
+            warnings.simplefilter("always")
+            loss = tm.train_on_batch(x, hr)
+    finally:
+        training.GRAD_SCALE["G"] = old
+    assert np.isfinite(loss)                                   # the forward pass and the loss are untouched by the scale
+    msgs = [str(r.message) for r in rec]
+    assert any("gradients" in m and "dropped" in m for m in msgs), msgs
+    assert torch.equal(net.flat[:nt], w1), "a clipped update reached the weights"
+    assert all(torch.equal(a, b) for a, b in zip(slots, tm._compiled.slots[id(net)])), "Adam moments moved"
+    assert opt.iterations == 1
+    assert net.train_dtype == torch.bfloat16
+    loss2 = tm.train_on_batch(x, hr)                           # bf16 storage, scale 1: a normal step again
+    assert np.isfinite(loss2) and opt.iterations == 2 and not torch.equal(net.flat[:nt], w1)
+
+
 def test_cuda_graph_replay_of_the_training_step_equals_the_eager_step():
     """training.GRAPH_STEPS: after GRAPH_WARMUP eager calls the step is replayed from two captured CUDA graphs.  Two models run
     in lockstep -- one replaying, one eager -- and before every step the eager one is given the replaying one's weights and

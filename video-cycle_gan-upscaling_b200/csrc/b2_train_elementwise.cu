@@ -612,8 +612,13 @@ __global__ void cast_scale_kernel(const TI* __restrict__ in, long n, float scale
 // grads are multiplied by gscale first (1 / world_size after a sum all-reduce).
 __global__ void __launch_bounds__(kEwThreads)
 adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long n, float lr_t,
-            float b1, float b2, float eps, float gscale) {
+            float b1, float b2, float eps, float gscale, const unsigned* __restrict__ guard0, const unsigned* __restrict__ guard1,
+            int guard_words) {
     b2::pdl_entry();
+    // guarded form: any non-zero guard word (range flags / saturation counts raised by the passes that produced g) turns the
+    // whole launch into a no-op -- parameters and both moments keep their bits, the host sees the words with the step's loss
+    for (int i = 0; i < guard_words; ++i)
+        if ((guard0 && guard0[i] != 0u) || (guard1 && guard1[i] != 0u)) return;
     const long n4 = n >> 2;
     for (long i = blockIdx.x * long(blockDim.x) + threadIdx.x; i < n4; i += long(gridDim.x) * blockDim.x) {
         float4 pp = reinterpret_cast<float4*>(p)[i], gg = reinterpret_cast<const float4*>(g)[i];
@@ -811,8 +816,18 @@ int b2_cast_scale(const void* in, int in_dtype, int64_t n, float scale, void* ou
 int b2_adam(float* params, const float* grads, float* m, float* v, int64_t n, float lr_t, float beta1, float beta2, float eps,
             float gscale, void* stream) {
     if (!params || !grads || !m || !v) return set_error("b2_adam: null pointer");
-    b2::launch_k(adam_kernel, flat_grid((n + 3) / 4), kEwThreads, 0, B2_STREAM, params, grads, m, v, n, lr_t, beta1, beta2, eps, gscale);
+    b2::launch_k(adam_kernel, flat_grid((n + 3) / 4), kEwThreads, 0, B2_STREAM, params, grads, m, v, n, lr_t, beta1, beta2, eps, gscale,
+                 static_cast<const unsigned*>(nullptr), static_cast<const unsigned*>(nullptr), 0);
     return launch_ok("b2_adam");
+}
+
+int b2_adam_guarded(float* params, const float* grads, float* m, float* v, int64_t n, float lr_t, float beta1, float beta2, float eps,
+                    float gscale, const void* guard0, const void* guard1, int guard_words, void* stream) {
+    if (!params || !grads || !m || !v) return set_error("b2_adam_guarded: null pointer");
+    if (guard_words < 0 || guard_words > 16) return set_error("b2_adam_guarded: guard_words=%d (0..16)", guard_words);
+    b2::launch_k(adam_kernel, flat_grid((n + 3) / 4), kEwThreads, 0, B2_STREAM, params, grads, m, v, n, lr_t, beta1, beta2, eps, gscale,
+                 static_cast<const unsigned*>(guard0), static_cast<const unsigned*>(guard1), guard_words);
+    return launch_ok("b2_adam_guarded");
 }
 
 }  // extern "C"

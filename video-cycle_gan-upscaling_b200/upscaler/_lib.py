@@ -104,6 +104,7 @@ _SIGNATURES = {
     "b2_dense_bwd_weight": (ctypes.c_int, [_P, _I, _P, _I, _I, _I, _I, _P, _P, _P]),
     "b2_cast_scale": (ctypes.c_int, [_P, _I, _L, _F, _P, _I, _P]),
     "b2_adam": (ctypes.c_int, [_P, _P, _P, _P, _L, _F, _F, _F, _F, _F, _P]),
+    "b2_adam_guarded": (ctypes.c_int, [_P, _P, _P, _P, _L, _F, _F, _F, _F, _F, _P, _P, _I, _P]),
 }
 
 

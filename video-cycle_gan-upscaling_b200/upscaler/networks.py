@@ -30,11 +30,14 @@ from . import ops
 TRAIN_DTYPE = torch.float16
 # fp16 training storage stores with a saturating conversion (+-65504).  Every train-mode BatchNorm finalize raises a device
 # flag when a channel of its input has a root mean square above RANGE_LIMIT (1/32 of the edge), and the step samples the
-# tensors no BatchNorm sees (head conv, Conv2DTranspose outputs, generated image) with count_saturated; the host reads the
-# flag every RANGE_CHECK_EVERY steps and switches that network to bf16 storage with a warning (ON_RANGE = "fallback") or
-# raises FloatingPointError ("raise").
+# tensors no BatchNorm sees (head conv, Conv2DTranspose outputs, generated image) with count_saturated every
+# RANGE_CHECK_EVERY steps; the backward passes count saturated values in the (small) activation-gradient tensors every step.
+# Flag and gradient count are the network's two "guard words": the step's Adam launch reads them on the device and drops an
+# update computed from clipped values, and the host reads them with every step's loss and switches that network to bf16
+# storage with a warning (ON_RANGE = "fallback") or raises FloatingPointError ("raise").
 RANGE_LIMIT = 2048.0
 RANGE_CHECK_EVERY = 32
+GRAD_PROBE_MAX_ELEMS = 1 << 25     # activation gradients up to this size are sampled for saturation every step (<= 64 MB read)
 ON_RANGE = "fallback"
 
 BN_EPS = 1e-3       # keras BatchNormalization defaults, model.py:20
@@ -396,10 +399,29 @@ class Net:
         """One-float device flag the BatchNorm finalize launches of this network raise (None for bf16 storage)."""
         if self.train_dtype != torch.float16:
             return None
-        f = self._buffers.get("range_flag")
-        if f is None:
-            f = self._buffers["range_flag"] = torch.zeros(1, dtype=torch.float32, device=self.device)
-        return f
+        return self.guard_words()[0:1].view(torch.float32)
+
+    def guard_words(self):
+        """Two 32-bit device words that stay zero while fp16 storage is safe: [0] the BatchNorm range flag (float bits, raised
+        by the finalize launches), [1] the count of saturated values among the activation gradients the backward pass samples.
+        The guarded Adam update reads them on the device and drops an update computed from clipped values
+        (ops.adam guards=); the host reads them with the step's loss (check_range).  None for bf16 storage."""
+        if self.train_dtype != torch.float16:
+            return None
+        g = self._buffers.get("guard_words")
+        if g is None:
+            g = self._buffers["guard_words"] = torch.zeros(2, dtype=torch.int32, device=self.device)
+        return g
+
+    def probe_grad(self, *tensors):
+        """Backward passes call this on a few (small) fp16 activation-gradient tensors: saturated values are counted into
+        guard word 1.  No-op for bf16 storage, whose exponent range is fp32's."""
+        if self.train_dtype != torch.float16 or not self.on_gpu:
+            return
+        cnt = self.guard_words()[1:2]
+        for t in tensors:
+            if t is not None and t.dtype == torch.float16 and t.numel() <= GRAD_PROBE_MAX_ELEMS:
+                ops.count_saturated(t, cnt)
 
     def set_train_dtype(self, dtype):
         """Switches the 16-bit storage type of the training passes (activations, packed weights, gradients)."""
@@ -413,28 +435,47 @@ class Net:
                 self.refresh(("train",))
 
     def check_range(self, extra=(), agree=None):
-        """Host side of the guard: reads the flag (one small D2H) plus a saturation count of `extra` tensors; on a hit warns and
-        drops to bf16 storage, or raises (ON_RANGE).  Returns True when the storage type was switched.  `agree` (data-parallel
-        training: local hit -> hit on any replica, a collective) makes all replicas switch together; the flag and the sampled
-        count are per replica, and replicas on different storage types would issue different collectives."""
-        flag = self.range_flag()
-        if flag is None:
+        """Host side of the guard, once per training step with the step's loss read: reads the two guard words (one small D2H;
+        with `extra`, also a saturation count of those stored forward tensors); on a hit warns and drops to bf16 storage, or
+        raises (ON_RANGE).  Returns True when the storage type was switched; `self.guard_hit` says whether the guard words
+        themselves were raised, i.e. whether the guarded Adam update of this step was dropped on the device.
+        `agree` (data-parallel training: local hit -> hit on any replica, a collective) makes all replicas switch together:
+        the sampled `extra` count is per replica, and replicas on different storage types would issue different collectives.
+        (Guard words the step has already max-reduced over the replicas before its update read them -- `_guard_reduced`,
+        set by training.Compiled._adam -- need no second agreement.)"""
+        self.guard_hit = False
+        guard = self.guard_words()
+        if guard is None:
             return False
-        cnt = self._buffers.get("range_count")
-        if cnt is None:
-            cnt = self._buffers["range_count"] = torch.zeros(1, dtype=torch.int32, device=self.device)
+        cnt = None
         for t in extra:
             if t is not None and t.dtype == torch.float16:
+                if cnt is None:
+                    cnt = self._buffers.get("range_count")
+                    if cnt is None:
+                        cnt = self._buffers["range_count"] = torch.zeros(1, dtype=torch.int32, device=self.device)
                 ops.count_saturated(t, cnt)
-        hit = float(flag.item()) != 0.0 or int(cnt.item()) != 0
-        if agree is not None:
+        words = guard.cpu()
+        fwd, bwd = int(words[0]) != 0, int(words[1]) != 0
+        self.guard_hit = fwd or bwd
+        hit = self.guard_hit or (cnt is not None and int(cnt.item()) != 0)
+        reduced, self._guard_reduced = getattr(self, "_guard_reduced", False), False
+        if agree is not None and (cnt is not None or not reduced):
             hit = agree(hit)
         if not hit:
             return False
-        flag.zero_()
-        cnt.zero_()
-        msg = ("%s: the training passes approached the edge of float16 storage (a BatchNorm input channel with RMS >= %g, or "
-               "saturated stored values)" % (type(self).__name__, RANGE_LIMIT))
+        guard.zero_()
+        if cnt is not None:
+            cnt.zero_()
+        what = []
+        if fwd:
+            what.append("a BatchNorm input channel with RMS >= %g" % RANGE_LIMIT)
+        if bwd:
+            what.append("saturated activation gradients")
+        if not what or (cnt is not None and not self.guard_hit):
+            what.append("saturated stored values")
+        msg = ("%s: the training passes approached the edge of float16 storage (%s)%s"
+               % (type(self).__name__, ", ".join(what), "; this step's weight update was dropped" if self.guard_hit else ""))
         if ON_RANGE == "raise":
             raise FloatingPointError(msg)
         import warnings
@@ -887,6 +928,7 @@ class UpscalerOrigNet(Net):
             else:
                 d = ops.conv2d(d, pk[n + "#dgrad"], cin, ku, ku, stride=2, out=new(tuple(xin.shape)))
         dt_ = d      # gradient w.r.t. t = skip + BN(prefinal conv): flows into both the trunk and the head skip
+        self.probe_grad(dt_)
         ready(self.offsets[("upscaling/0/block/conv_transp", 0)][0])
         # ---- prefinal conv + BN
         dzp = self._bn_backward(tape, "prefinal", "prefinal/batch_norm", dt_, new(tuple(dt_.shape)), ops.ACT_NONE, sync=sync)
@@ -910,6 +952,7 @@ class UpscalerOrigNet(Net):
         xp, u0 = tape["head"]
         a0 = w["initial/prelu"][0].reshape(-1)
         gm = ops.affine_act(gm, new(tuple(gm.shape)), residual=dt_)     # the skip connection joins here: trunk + upsampling path
+        self.probe_grad(gm)
         ops.bn_bwd_reduce(u0, gm, None, None, a0, ops.ACT_PRELU, 0.0, None, None, g["initial/conv"][1], None,
                           g["initial/prelu"][0].reshape(-1))
         dz0 = ops.bn_bwd_apply(u0, gm, None, None, a0, ops.ACT_PRELU, 0.0, None, None, None, None, 0, new(tuple(u0.shape)))
@@ -1453,10 +1496,13 @@ class DiscriminatorSimple512Net(Net):
         `on_ready(offset)`: see UpscalerOrigNet.backward (the dense head, most of the parameters, is ready first).
         `grad_scale`: dscore carries this factor on top of the step's scale (fp16 range inside a frozen discriminator whose
         adversarial weight is tiny, train_gan.py -dw 1e-10); it is divided out of the returned image gradient in fp32."""
-        if want_wgrad and grad_scale != 1.0:
+        by_tensor = torch.is_tensor(grad_scale)      # a 64-float device vector holding 1 / scale: the caller fills it before
+        if want_wgrad and (by_tensor or grad_scale != 1.0):     # each replay of a captured graph (training._step_gan2_graph)
             raise ValueError("an internal gradient scale is only supported for a frozen discriminator")
         self._inv_gscale = None
-        if grad_scale != 1.0:
+        if by_tensor:
+            self._inv_gscale = grad_scale
+        elif grad_scale != 1.0:
             self._inv_gscale = self._vec("inv_gscale", 64)
             self._inv_gscale.fill_(1.0 / grad_scale)
         ready = on_ready if (on_ready is not None and want_wgrad) else (lambda off: None)
@@ -1479,6 +1525,7 @@ class DiscriminatorSimple512Net(Net):
                 ops.dense_bwd_weight(dins[j], d, g[name][0], g[name][1])
             d = ops.dense_bwd_data(d, w[name][0], torch.empty((n, c["cin"]), dtype=dt, device=self.device))
         ready(self.offsets[(self._dense[0][0], 0)][0])
+        self.probe_grad(d)
         last = self._conv_geom[-1]
         d = d.view(n, last[3][0], last[3][1], last[1]["cout"])
         return self._conv_backward(tape, d, want_wgrad, want_input_grad, sync, ready)
@@ -1493,6 +1540,8 @@ class DiscriminatorSimple512Net(Net):
             bn = name.replace("Conv2d", "BatchNorm")
             dz = self._bn_backward(tape, bn, bn, d, torch.empty_like(d), ops.ACT_LEAKY, leaky=0.1, sync=sync,
                                    want_param_grads=want_wgrad)
+            if bi % 2 == 1:
+                self.probe_grad(dz)
             if bi > 0:
                 if want_wgrad:
                     ops.conv2d_wgrad(ins[bi], dz, 3, 3, c["stride"], g[name][0])
@@ -1567,6 +1616,8 @@ class DiscriminatorSparse512Net(DiscriminatorSimple512Net):
             bn = name.replace("Conv2d", "BatchNorm")
             dz = self._bn_backward(tape, bn, bn, d, torch.empty_like(d), ops.ACT_LEAKY, leaky=0.1, sync=sync,
                                    want_param_grads=want_wgrad)
+            if bi % 2 == 1:
+                self.probe_grad(dz)
             if bi > 0:
                 if want_wgrad:
                     ops.conv2d_wgrad_pad(ins[bi], dz, 5, 5, c["stride"], (0, 0), g[name][0])

@@ -661,10 +661,22 @@ def cast_scale(x, out, scale=1.0):
     return out
 
 
-def adam(params, grads, m, v, lr_t, beta1, beta2, eps, gscale=1.0):
-    rc = _lib.load().b2_adam(_lib.ptr(params), _lib.ptr(grads), _lib.ptr(m), _lib.ptr(v), params.numel(), lr_t, beta1, beta2, eps,
-                             gscale, _lib.stream_ptr())
-    _lib.check(rc, "b2_adam")
+def adam(params, grads, m, v, lr_t, beta1, beta2, eps, gscale=1.0, guards=()):
+    """Keras Adam over a flat fp32 buffer.  `guards`: up to two int32 CUDA tensors of equal length; the update is dropped on
+    the device when any of their words is non-zero (b2_adam_guarded)."""
+    guards = [g for g in guards if g is not None]
+    if not guards:
+        rc = _lib.load().b2_adam(_lib.ptr(params), _lib.ptr(grads), _lib.ptr(m), _lib.ptr(v), params.numel(), lr_t, beta1, beta2, eps,
+                                 gscale, _lib.stream_ptr())
+        _lib.check(rc, "b2_adam")
+    else:
+        if len(guards) > 2 or any(g.dtype != torch.int32 or g.numel() != guards[0].numel() for g in guards):
+            raise ValueError("adam: at most two int32 guard tensors of equal length")
+        _require_cuda(*guards)
+        g1 = guards[1] if len(guards) > 1 else None
+        rc = _lib.load().b2_adam_guarded(_lib.ptr(params), _lib.ptr(grads), _lib.ptr(m), _lib.ptr(v), params.numel(), lr_t, beta1, beta2,
+                                         eps, gscale, _lib.ptr(guards[0]), _lib.ptr(g1), guards[0].numel(), _lib.stream_ptr())
+        _lib.check(rc, "b2_adam_guarded")
     _count(1)
 
 

@@ -363,6 +363,7 @@ class Compiled:
         self.reducer = GradReducer()
         self._ticks = {}
         self._warm, self._graphs, self._graph_off = {}, {}, False
+        self._guarded, self._undone = set(), False
 
     def _moves(self, which):
         """Whether this compiled model's training-phase passes update the moving statistics of G / D: sampled once, at
@@ -375,17 +376,27 @@ class Compiled:
 
     # -------------------------------------------------------------- fp16 storage range guard (networks.RANGE_LIMIT)
     def _range_tick(self, net, tape=None):
-        """First step and every RANGE_CHECK_EVERY-th: read the network's range flag and sample the stored tensors no BatchNorm
-        watches (head conv, Conv2DTranspose outputs); a hit drops that network to bf16 storage (or raises)."""
+        """Every step, after the update was launched: read the network's guard words (the BatchNorm range flag and the count
+        of saturated activation gradients; the stream is about to be drained for the loss anyway).  If they were raised the
+        guarded Adam launch of this step did nothing: the optimizer's step count is taken back and the network continues
+        in bf16 storage (or the step raises, networks.ON_RANGE).  First step and every RANGE_CHECK_EVERY-th additionally
+        sample the stored forward tensors no BatchNorm watches (head conv, Conv2DTranspose outputs)."""
+        import time
         from . import networks
         if net.train_dtype != torch.float16:
             return
         n = self._ticks[id(net)] = self._ticks.get(id(net), 0) + 1
-        if n == 1 or n % networks.RANGE_CHECK_EVERY == 0:
-            extra = []
-            if tape is not None and "ups" in tape:
-                extra = [tape["head"][1]] + list(tape["ups"][1:])
+        extra = []
+        if (n == 1 or n % networks.RANGE_CHECK_EVERY == 0) and tape is not None and "ups" in tape:
+            extra = [tape["head"][1]] + list(tape["ups"][1:])
+        t0 = time.perf_counter()
+        try:
             net.check_range(extra, agree=lambda hit: agree(hit, net.device, "any"))
+        finally:
+            HOST_STATS["wait_s"] += time.perf_counter() - t0
+            if net.guard_hit and id(net) in self._guarded and not self._undone:
+                self.opt.iterations -= 1        # the update was dropped on the device: Adam's t does not advance
+                self._undone = True
 
     # -------------------------------------------------------------- Adam
     @staticmethod
@@ -407,7 +418,10 @@ class Compiled:
             return 1.0
         return float(2.0 ** round(math.log2(float(GRAD_SCALE["D"]) / max_abs_ds)))
 
-    def _adam(self, net, S=1.0):
+    def _adam(self, net, S=1.0, also=None):
+        """Adam update of `net` from its flat gradient.  The launch is guarded by the guard words of `net` and of `also` (the
+        frozen discriminator a generator step differentiates through): if the fp16 passes that produced the gradient raised
+        one, the update is dropped on the device (see _range_tick).  Replicas max-reduce the words first, so all drop or none."""
         opt = self.opt
         opt.iterations += 1
         t = opt.iterations
@@ -418,7 +432,17 @@ class Compiled:
             self.slots[key] = (torch.zeros_like(net.grad_flat), torch.zeros_like(net.grad_flat))
         m, v = self.slots[key]
         self.reducer.wait()
-        ops.adam(net.flat[:net.n_trainable], net.grad_flat, m, v, lr_t, opt.beta_1, opt.beta_2, opt.epsilon, gscale=1.0 / S)
+        guards = [g for g in (n_.guard_words() for n_ in (net, also) if n_ is not None and n_.on_gpu) if g is not None]
+        self._guarded = {id(n_) for n_ in (net, also) if n_ is not None}
+        self._undone = False
+        dist = _dist()
+        if dist is not None:
+            for g in guards:
+                dist.all_reduce(g, op=dist.ReduceOp.MAX)
+            for n_ in (net, also):
+                if n_ is not None:
+                    n_._guard_reduced = True
+        ops.adam(net.flat[:net.n_trainable], net.grad_flat, m, v, lr_t, opt.beta_1, opt.beta_2, opt.epsilon, gscale=1.0 / S, guards=guards)
         net._train_dirty = True
         net._infer_dirty = True
 
@@ -747,7 +771,7 @@ class Compiled:
         dist = _dist()
         if dist is not None:
             dist.all_reduce(G.grad_flat)
-        self._adam(G, st.S)
+        self._adam(G, st.S, also=D)
         self._range_tick(G, st.tape)
         self._range_tick(D)
         lc, la = self._mean_over_ranks(st.losses)
@@ -788,7 +812,7 @@ class Compiled:
         dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1], g3=grads[2] if len(grads) > 2 else None)
         G.ensure_grads().zero_()
         G.backward(gtape, dz, sync, on_ready=self.reducer.hook(G.grad_flat, G.n_trainable))
-        self._adam(G, S)
+        self._adam(G, S, also=D)
         self._range_tick(G, gtape)
         self._range_tick(D)
         lc, la = self._mean_over_ranks(losses)
@@ -946,9 +970,11 @@ class Compiled:
             st.n2 = peer.end_capture()
             peer.begin_capture()
         st.n = int(sf.shape[0])
-        st.kD = self._inner_scale(D, abs(dw * S / world) / max(st.n, 1)) if self.d_frozen else 1.0
+        # the inner scale of the frozen critic depends on |d_fake|, a host value of each step (it shrinks as D wins): the
+        # captured backward reads 1 / kD from a device vector that every replay fills, like the eager step computes it
+        st.inv_kD = torch.ones(64, dtype=torch.float32, device=dev) if self.d_frozen else None
         with torch.cuda.graph(st.g3, pool=pool, capture_error_mode="thread_local"):
-            grads.append(D.backward(dtape, st.ds, not self.d_frozen, True, sync, grad_scale=st.kD))
+            grads.append(D.backward(dtape, st.ds, not self.d_frozen, True, sync, grad_scale=st.inv_kD if self.d_frozen else 1.0))
             dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1], g3=grads[2] if len(grads) > 2 else None)
             G.grad_flat.zero_()
             G.backward(gtape, dz, sync, on_ready=None)
@@ -977,13 +1003,16 @@ class Compiled:
         self._replay(st, st.g2, st.n2)
         mr, mf, lc = self._mean_over_ranks(st.buf)
         la, _, d_fake = self._relativistic(mr, mf, "gen")
-        st.ds.fill_(dw * d_fake * st.S * st.kD / world / st.n)
+        kD = self._inner_scale(D, abs(dw * d_fake * st.S / world) / max(st.n, 1)) if self.d_frozen else 1.0
+        if st.inv_kD is not None:
+            st.inv_kD.fill_(1.0 / kD)
+        st.ds.fill_(dw * d_fake * st.S * kD / world / st.n)
         self._replay(st, st.g3, st.n3)
         ops._count(st.launches)
         dist = _dist()
         if dist is not None:
             dist.all_reduce(G.grad_flat)
-        self._adam(G, st.S)
+        self._adam(G, st.S, also=D)
         self._range_tick(G, st.tape)
         self._range_tick(D)
         return [cw * lc + dw * la, lc, la]
@@ -1024,7 +1053,7 @@ class Compiled:
         dz = ops.tanh_bwd(y, grads[0], torch.empty_like(y), g2=grads[1], g3=grads[2] if len(grads) > 2 else None)
         G.ensure_grads().zero_()
         G.backward(gtape, dz, sync, on_ready=self.reducer.hook(G.grad_flat, G.n_trainable))
-        self._adam(G, S)
+        self._adam(G, S, also=D)
         self._range_tick(G, gtape)
         self._range_tick(D)
         return [cw * lc + dw * la, lc, la]
