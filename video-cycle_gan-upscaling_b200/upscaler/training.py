@@ -496,12 +496,22 @@ class Compiled:
             self._graph_off = True          # BatchNorm sums over NCCL: collectives stay out of captured graphs
             return None
         st = err = None
+        # Python's cyclic collector must not run inside a capture: if it finalises an older CUDAGraph (a compiled model of
+        # an earlier leg that was dropped), the cudaGraphExecDestroy lands in the capturing stream's window and invalidates
+        # the capture (seen on one rank of two, profiles/r03_s4_bench_n2.json.log).  Collect first, then hold it off.
+        import gc
+        gc.collect()
+        gc_was_on = gc.isenabled()
+        gc.disable()
         try:
             st = capture(sync, peer)
         except Exception as e:  # noqa: BLE001
             err = e
             if peer is not None:
                 peer.end_capture()
+        finally:
+            if gc_was_on:
+                gc.enable()
         # replayed and eager steps issue different collectives: all replicas replay, or none does (every rank reaches this
         # point on the same step: the key and its warm-up count are functions of shapes and storage types only)
         if not agree(st is not None, device, "all"):
